@@ -1,0 +1,741 @@
+// Batched MCTS over thousands of concurrent games: SoA/AoS node pools in HBM, one warp per game.  sm_100a only.
+//
+// What the reference does with a pointer tree of Python objects, one simulation at a time
+// (alphazero/mcts.py:8-269), happens here for G games per launch:
+//   * a game's nodes live in its own pool slice; the children of a node are one contiguous block of 32-byte
+//     records, so selecting among them is two coalesced 128-bit loads per lane (lane j <-> child j), a PUCT/UCT
+//     evaluation in float64 (bit-identical to the reference's NumPy arithmetic) and a warp shuffle arg-max;
+//   * the board is replayed in registers along the path (16 B of state, ~400 integer instructions per ply);
+//   * the leaf is handed to the evaluator through flat [G] buffers (board, network encoding) and the result
+//     (probs, value) is consumed by the next launch, which also backs up along the recorded path.
+// There is exactly one warp per game and at most one leaf in flight per game, which is the reference's sequential
+// order (visit counts are identical under a deterministic evaluator); no atomics are needed because a pool is
+// only ever touched by its own warp.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/az_b200.h"
+#include "common.cuh"
+#include "othello_bits.cuh"
+#include "philox.cuh"
+#include "playout.cuh"
+
+static_assert(sizeof(az_node) == 32, "az_node must be 32 bytes");
+
+#define AZ_FULL 0xffffffffu
+#define AZ_WARPS_PER_CTA 4
+
+struct NodeRec {
+    double Q;
+    float P;
+    uint32_t N;
+    uint32_t first_child;
+    uint32_t meta;  // n_children | move << 8 | flags << 16
+    __device__ __forceinline__ int n_children() const { return (int)(meta & 0xffu); }
+    __device__ __forceinline__ int move() const { return (int)((meta >> 8) & 0xffu); }
+    __device__ __forceinline__ uint32_t flags() const { return (meta >> 16) & 0xffu; }
+};
+
+__device__ __forceinline__ NodeRec az_load_node(const az_node* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = q[0], b = q[1];
+    NodeRec r;
+    r.Q = __hiloint2double((int)a.y, (int)a.x);
+    r.P = __uint_as_float(a.z);
+    r.N = a.w;
+    r.first_child = b.x;
+    r.meta = b.y;
+    return r;
+}
+
+__device__ __forceinline__ void az_store_node(az_node* p, double Q, float P, uint32_t N, uint32_t first_child,
+                                              uint32_t meta) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    uint4 a, b;
+    a.x = (uint32_t)__double2loint(Q);
+    a.y = (uint32_t)__double2hiint(Q);
+    a.z = __float_as_uint(P);
+    a.w = N;
+    b.x = first_child;
+    b.y = meta;
+    b.z = 0u;
+    b.w = 0u;
+    q[0] = a;
+    q[1] = b;
+}
+
+__device__ __forceinline__ uint32_t az_make_meta(int n_children, int move, uint32_t flags) {
+    return (uint32_t)n_children | ((uint32_t)move << 8) | (flags << 16);
+}
+
+__device__ __forceinline__ NodeRec az_bcast_node(const NodeRec& r, int src) {
+    NodeRec o;
+    o.Q = __shfl_sync(AZ_FULL, r.Q, src);
+    o.P = __shfl_sync(AZ_FULL, r.P, src);
+    o.N = __shfl_sync(AZ_FULL, r.N, src);
+    o.first_child = __shfl_sync(AZ_FULL, r.first_child, src);
+    o.meta = __shfl_sync(AZ_FULL, r.meta, src);
+    return o;
+}
+
+// Network action index (r*n+c, pass = n*n) of a canvas action (r*8+c, pass = 64).
+__device__ __forceinline__ int az_net_index(int a, int n) { return a == AZ_PASS ? n * n : (a >> 3) * n + (a & 7); }
+
+__device__ __forceinline__ double az_warp_sum(double v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(AZ_FULL, v, off);
+    return v;
+}
+__device__ __forceinline__ float az_warp_sum(float v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(AZ_FULL, v, off);
+    return v;
+}
+
+// Random 32-bit draw for (game, event, lane/sub-event).
+__device__ __forceinline__ az_u32x4 az_draw4(uint64_t seed, uint32_t g, uint32_t event, uint32_t sub, uint32_t tag) {
+    return az_philox4x32_10(g, event, sub, tag, (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
+// Writes the network encoding of a side-relative position: +1 own, -1 opp, 0 empty, row-major n x n.
+__device__ __forceinline__ void az_encode_leaf(const az_tree& t, int g, int lane, uint64_t own, uint64_t opp) {
+    const int n = t.n, cells = n * n;
+    for (int k = lane; k < cells; k += 32) {
+        int bit = (k / n) * 8 + (k % n);
+        float v = (float)((int)((own >> bit) & 1ULL) - (int)((opp >> bit) & 1ULL));
+        if (t.enc_dtype == 0) reinterpret_cast<float*>(t.enc)[(size_t)g * cells + k] = v;
+        else reinterpret_cast<__nv_bfloat16*>(t.enc)[(size_t)g * cells + k] = __float2bfloat16(v);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ finish
+
+// Allocates the children block of `leaf` for all legal moves of (own, opp) and fills the priors.
+// neural: P = probs[idx]/sum over the legal moves in float32, uniform when sum < 1e-6
+//         (OthelloNet.get_normalized_probs, othello.py:384-402);  rollout: P = 0 (mcts.py:152-154).
+// Returns the first child index (0 on pool overflow).
+__device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, az_node* nodes, int g, int lane,
+                                                      uint32_t leaf, uint64_t own, uint64_t opp, bool with_priors,
+                                                      uint32_t extra_flags, int* k_out) {
+    const uint64_t bmask = az_board_mask(t.n);
+    const uint64_t legal = az_legal_mask(own, opp, bmask);
+    const int k = legal ? __popcll(legal) : 1;
+    *k_out = k;
+    const uint32_t base = t.n_alloc[g];
+    if (base + (uint32_t)k > (uint32_t)t.capacity) {
+        if (lane == 0) t.status[g] |= AZ_STATUS_OVERFLOW;
+        return 0u;
+    }
+    // up to 33 children: lane j owns child j and (rarely) child j + 32
+    int a0 = AZ_PASS, a1 = AZ_PASS;
+    float p0 = 0.f, p1 = 0.f;
+    const bool has0 = lane < k, has1 = lane + 32 < k;
+    if (has0) a0 = legal ? az_nth_set_bit(legal, lane) : AZ_PASS;
+    if (has1) a1 = az_nth_set_bit(legal, lane + 32);
+    if (with_priors) {
+        const float* pr = t.probs + (size_t)g * (t.n * t.n + 1);
+        if (has0) p0 = pr[az_net_index(a0, t.n)];
+        if (has1) p1 = pr[az_net_index(a1, t.n)];
+        float sum = az_warp_sum(p0 + p1);
+        if (sum < 1e-6f) {
+            p0 = p1 = (float)(1.0 / (double)k);
+        } else {
+            p0 = __fdiv_rn(p0, sum);
+            p1 = __fdiv_rn(p1, sum);
+        }
+    }
+    if (has0) az_store_node(&nodes[base + lane], 0.0, p0, 0u, 0u, az_make_meta(0, a0, 0u));
+    if (has1) az_store_node(&nodes[base + lane + 32], 0.0, p1, 0u, 0u, az_make_meta(0, a1, 0u));
+    __syncwarp();  // every lane has read n_alloc[g] before lane 0 bumps it
+    if (lane == 0) {
+        // leaf record: keep Q/P/N, set the child block and flags (second 16 bytes only)
+        uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[leaf]);
+        uint32_t meta = w[5];
+        uint32_t flags = ((meta >> 16) & 0xffu) | AZ_NODE_EVAL | extra_flags;
+        w[4] = base;
+        w[5] = az_make_meta(k, (int)((meta >> 8) & 0xffu), flags);
+        t.n_alloc[g] = base + (uint32_t)k;
+    }
+    __syncwarp();
+    return base;
+}
+
+// MCT.back_propagate (mcts.py:197-223): reward for the leaf, sign alternating towards the root; every node on the
+// path gets Q = (N*Q + r)/(N+1) in float64 and N += 1.  Lane j updates path node j (nodes are distinct).
+__device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int g, int lane, int player_to_play,
+                                          double outcome) {
+    double reward;
+    if (fabs(outcome) < 1e-4) reward = 0.0;
+    else reward = ((double)player_to_play * outcome > 0.0) ? -fabs(outcome) : fabs(outcome);
+    const int len = (int)t.path_len[g];
+    const uint32_t* path = t.path + (size_t)g * t.max_depth;
+    for (int j = lane; j < len; j += 32) {
+        az_node* nd = &nodes[path[j]];
+        uint4* q = reinterpret_cast<uint4*>(nd);
+        uint4 a = q[0];
+        double Q = __hiloint2double((int)a.y, (int)a.x);
+        uint32_t N = a.w;
+        double r = ((len - 1 - j) & 1) ? -reward : reward;
+        double Qn = __ddiv_rn(__dadd_rn(__dmul_rn((double)N, Q), r), (double)(N + 1u));
+        a.x = (uint32_t)__double2loint(Qn);
+        a.y = (uint32_t)__double2hiint(Qn);
+        a.w = N + 1u;
+        q[0] = a;
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ void az_finish(const az_tree& t, az_node* nodes, int g, int lane) {
+    const int kind = t.leaf_kind[g];
+    if (kind == AZ_LEAF_IDLE) return;
+    const uint32_t leaf = t.leaf_node[g];
+    const int leaf_player = t.leaf_player[g];
+    if (kind == AZ_LEAF_NN || kind == AZ_LEAF_PRIME) {
+        int k;
+        az_alloc_children(t, nodes, g, lane, leaf, t.leaf_own[g], t.leaf_opp[g], true, 0u, &k);
+    }
+    if (kind != AZ_LEAF_PRIME) {
+        double outcome;
+        if (kind == AZ_LEAF_NN) outcome = (double)((float)leaf_player * t.value[g]);   // base.py:366
+        else if (kind == AZ_LEAF_ROLLOUT) outcome = (double)t.value[g];                 // absolute winner id
+        else outcome = kind == AZ_LEAF_DRAW ? 0.0 : (kind == AZ_LEAF_BLACK ? 1.0 : -1.0);
+        az_backup(t, nodes, g, lane, leaf_player, outcome);
+        if (lane == 0) t.sims_done[g] += 1u;
+    }
+    if (lane == 0) t.leaf_kind[g] = AZ_LEAF_IDLE;
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------ select
+
+// Warp arg-max of `score` over the lanes with valid == true.  Ties: lowest child index (parity mode) or uniform
+// among the tied children (fair_max, utils.py:28-34).  `idx` is the child index held by the lane.
+// Returns the winning child index (same value in every lane) and, through src_lane, the lane that holds it.
+__device__ __forceinline__ int az_warp_argmax(double score, int idx, bool valid, bool tie_random, uint64_t seed,
+                                              uint32_t g, uint32_t event, int* src_lane) {
+    const int lane = threadIdx.x & 31;
+    double best = valid ? score : -INFINITY;
+    // NaN never occurs: Q, P finite; +inf only for unvisited children in UCT mode.
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        double o = __shfl_xor_sync(AZ_FULL, best, off);
+        best = o > best ? o : best;
+    }
+    const bool tied = valid && (score == best);
+    const uint32_t ties = __ballot_sync(AZ_FULL, tied);
+    int win_lane;
+    if (!tie_random || __popc(ties) == 1) {
+        // lowest child index among the tied lanes; lane order == child order within one 32-chunk
+        uint32_t key = tied ? (uint32_t)idx : 0xffffffffu;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) key = min(key, __shfl_xor_sync(AZ_FULL, key, off));
+        const uint32_t who = __ballot_sync(AZ_FULL, tied && (uint32_t)idx == key);
+        win_lane = __ffs(who) - 1;
+    } else {
+        az_u32x4 r = az_draw4(seed, g, event, 0u, 0x54494555u);
+        int pick = (int)az_bounded(r.x, (uint32_t)__popc(ties));
+        uint32_t m = ties;
+        for (int i = 0; i < pick; ++i) m &= m - 1;
+        win_lane = __ffs(m) - 1;
+    }
+    (void)lane;
+    *src_lane = win_lane;
+    return __shfl_sync(AZ_FULL, idx, win_lane);
+}
+
+// Dirichlet noise on the priors of the root's children (mcts.py:234-240): P = (1-eps) P + eps * Dir(alpha)_j with
+// Gamma(alpha) draws by Marsaglia-Tsang (alpha < 1 boosted by U^(1/alpha)), lane j <-> child j.
+__device__ __forceinline__ double az_gamma_draw(double alpha, uint64_t seed, uint32_t g, uint32_t event, uint32_t j) {
+    uint32_t attempt = 0;
+    az_u32x4 r = az_draw4(seed, g, event, j, 0x47414D30u);
+    double boost = 1.0;
+    if (alpha < 1.0) {
+        boost = pow(az_uniform53(r.x, r.y), 1.0 / alpha);
+        alpha += 1.0;
+    }
+    const double d = alpha - 1.0 / 3.0, c = 1.0 / sqrt(9.0 * d);
+    while (true) {
+        ++attempt;
+        az_u32x4 a = az_draw4(seed, g, event, j, 0x47414D30u + attempt);
+        az_u32x4 b = az_draw4(seed, g, event, j, 0x47424D30u + attempt);
+        double u1 = az_uniform53(a.x, a.y), u2 = az_uniform53(a.z, a.w), u = az_uniform53(b.x, b.y);
+        double x = sqrt(-2.0 * log(u1)) * cospi(2.0 * u2);
+        double v = 1.0 + c * x;
+        if (v <= 0.0) continue;
+        v = v * v * v;
+        if (log(u) < 0.5 * x * x + d - d * v + d * log(v)) return boost * d * v;
+    }
+}
+
+__device__ __forceinline__ void az_root_noise(const az_tree& t, az_node* nodes, int g, int lane, const NodeRec& root,
+                                              uint32_t event) {
+    const int k = root.n_children();
+    double g0 = 0.0, g1 = 0.0;
+    if (lane < k) g0 = az_gamma_draw((double)t.dirichlet_alpha, t.seed, (uint32_t)g, event, (uint32_t)lane);
+    if (lane + 32 < k) g1 = az_gamma_draw((double)t.dirichlet_alpha, t.seed, (uint32_t)g, event, (uint32_t)lane + 32u);
+    const double sum = az_warp_sum(g0 + g1);
+    const double eps = (double)t.dirichlet_eps;
+    if (sum > 0.0) {
+        for (int j = lane; j < k; j += 32) {
+            float* P = &nodes[root.first_child + j].P;
+            double noise = (j < 32 ? g0 : g1) / sum;
+            *P = (float)((1.0 - eps) * (double)(*P) + eps * noise);
+        }
+    }
+    if (lane == 0) {
+        uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[0]);
+        w[5] |= (AZ_NODE_NOISED << 16);
+    }
+    __syncwarp();
+}
+
+// Picks the child of `cur` that maximises PUCT (neural, mcts.py:44-46) or UCT (rollout, mcts.py:38-42).
+// Returns the child's pool index and its record (broadcast to all lanes).
+__device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_node* nodes, int g, int lane,
+                                                  const NodeRec& cur, uint32_t event, NodeRec* child_out) {
+    const int k = cur.n_children();
+    const double parentN = (double)cur.N;
+    // sqrt / log of the parent's visit count are shared by all children
+    const double sqrtN = __dsqrt_rn(parentN);
+    const double logN = (t.mode == AZ_MODE_ROLLOUT && cur.N > 0u) ? log(parentN) : 0.0;
+    NodeRec mine;
+    mine.Q = 0.0; mine.P = 0.f; mine.N = 0u; mine.first_child = 0u; mine.meta = 0u;
+    double best_score = -INFINITY;
+    int best_j = -1;
+    for (int j = lane; j < k; j += 32) {
+        NodeRec c = az_load_node(&nodes[cur.first_child + j]);
+        double s;
+        if (t.mode == AZ_MODE_NEURAL) {
+            // Q + c_puct * P * sqrt(N_parent) / (1 + N), c_puct = 1.0, evaluated left to right in float64
+            s = __dadd_rn(c.Q, __ddiv_rn(__dmul_rn((double)c.P, sqrtN), (double)(1u + c.N)));
+        } else {
+            s = c.N == 0u ? INFINITY
+                          : __dadd_rn(c.Q, __dmul_rn(1.4142135623730951, __dsqrt_rn(__ddiv_rn(logN, (double)c.N))));
+        }
+        if (best_j < 0 || s > best_score) { best_score = s; best_j = j; mine = c; }
+    }
+    int src;
+    const int win = az_warp_argmax(best_score, best_j, best_j >= 0, t.tie_random != 0, t.seed, (uint32_t)g, event, &src);
+    *child_out = az_bcast_node(mine, src);
+    return cur.first_child + (uint32_t)win;
+}
+
+__device__ __forceinline__ int az_terminal_kind(uint64_t own, uint64_t opp, int player) {
+    int w = az_winner(own, opp, player);
+    return w == 0 ? AZ_LEAF_DRAW : (w > 0 ? AZ_LEAF_BLACK : AZ_LEAF_WHITE);
+}
+
+// MCT.__search_iter up to the evaluation (mcts.py:226-248): priming, noise, select_node; writes the leaf buffers.
+__device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int g, int lane) {
+    const uint64_t bmask = az_board_mask(t.n);
+    uint64_t own = t.root_own[g], opp = t.root_opp[g];
+    int player = t.root_player[g];
+    uint32_t event = t.rng_ctr[g];
+    uint32_t* path = t.path + (size_t)g * t.max_depth;
+    NodeRec cur = az_load_node(&nodes[0]);
+    uint32_t cur_idx = 0u;
+    int kind = AZ_LEAF_IDLE;
+    int len = 1;
+    if (lane == 0) path[0] = 0u;
+
+    if (t.mode == AZ_MODE_NEURAL && !(cur.flags() & AZ_NODE_EVAL)) {
+        kind = AZ_LEAF_PRIME;                                   // mcts.py:231-233
+        len = 0;
+    } else {
+        if (t.mode == AZ_MODE_NEURAL && t.dirichlet_alpha > 0.f && t.dirichlet_eps > 0.f &&
+            (cur.flags() & AZ_NODE_EXPANDED) && !(cur.flags() & AZ_NODE_NOISED)) {
+            az_root_noise(t, nodes, g, lane, cur, event);       // mcts.py:235-240
+            event += 1u;
+        }
+        while (true) {
+            // invariant: cur is the root or a node with N > 0
+            if (!(cur.flags() & AZ_NODE_EXPANDED)) {
+                if (az_is_terminal(own, opp, bmask)) {          // mcts.py:146-147
+                    kind = t.mode == AZ_MODE_NEURAL ? az_terminal_kind(own, opp, player) : AZ_LEAF_ROLLOUT;
+                    break;
+                }
+                if (t.mode == AZ_MODE_NEURAL) {
+                    if (!(cur.flags() & AZ_NODE_EVAL)) { kind = AZ_LEAF_NN; break; }   // pool-overflow fallback
+                    if (lane == 0) {
+                        uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[cur_idx]);
+                        w[5] |= (AZ_NODE_EXPANDED << 16);       // children become part of the tree (mcts.py:155-160)
+                    }
+                } else {
+                    int k;
+                    uint32_t base = az_alloc_children(t, nodes, g, lane, cur_idx, own, opp, false, AZ_NODE_EXPANDED, &k);
+                    if (base == 0u) { kind = AZ_LEAF_ROLLOUT; break; }                   // overflow: evaluate here
+                    // mcts.py:163-165: uniform pick among the fresh children
+                    az_u32x4 r = az_draw4(t.seed, (uint32_t)g, event, 0u, 0x45585044u);
+                    event += 1u;
+                    int j = (int)az_bounded(r.x, (uint32_t)k);
+                    NodeRec c = az_load_node(&nodes[base + j]);
+                    az_apply(own, opp, c.move());
+                    player = -player;
+                    cur_idx = base + (uint32_t)j;
+                    if (len < t.max_depth) { if (lane == 0) path[len] = cur_idx; ++len; }
+                    kind = AZ_LEAF_ROLLOUT;
+                    break;
+                }
+            }
+            NodeRec child;
+            uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child);
+            event += 1u;
+            az_apply(own, opp, child.move());
+            player = -player;
+            if (len >= t.max_depth) {
+                if (lane == 0) t.status[g] |= AZ_STATUS_DEPTH;
+                kind = t.mode == AZ_MODE_NEURAL ? AZ_LEAF_NN : AZ_LEAF_ROLLOUT;
+                break;
+            }
+            if (lane == 0) path[len] = child_idx;
+            ++len;
+            cur = child;
+            cur_idx = child_idx;
+            if (cur.N == 0u) {                                  // mcts.py:143-144: first visit = the leaf
+                if (t.mode == AZ_MODE_NEURAL)
+                    kind = az_is_terminal(own, opp, bmask) ? az_terminal_kind(own, opp, player) : AZ_LEAF_NN;
+                else
+                    kind = AZ_LEAF_ROLLOUT;
+                break;
+            }
+        }
+    }
+    if (lane == 0) {
+        t.leaf_node[g] = cur_idx;
+        t.leaf_kind[g] = (uint8_t)kind;
+        t.leaf_own[g] = own;
+        t.leaf_opp[g] = opp;
+        t.leaf_player[g] = (int8_t)player;
+        t.path_len[g] = (uint32_t)len;
+        t.rng_ctr[g] = event;
+    }
+    if (t.mode == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t, g, lane, own, opp);
+}
+
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    if (do_finish) az_finish(t, nodes, g, lane);
+    if (do_select && t.sims_done[g] < (uint32_t)n_sim) az_select(t, nodes, g, lane);
+}
+
+// ------------------------------------------------------------------------------------------------ misc kernels
+
+__global__ void __launch_bounds__(256) k_tree_reset(az_tree t, const uint8_t* __restrict__ mask) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= t.G || (mask && !mask[g])) return;
+    az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    az_store_node(&nodes[0], 0.0, 0.f, 0u, 0u, az_make_meta(0, 0xff, 0u));
+    t.n_alloc[g] = 1u;
+    t.leaf_kind[g] = AZ_LEAF_IDLE;
+    t.sims_done[g] = 0u;
+    t.status[g] = 0u;
+    t.path_len[g] = 0u;
+}
+
+// One thread per game: a uniform random playout from the leaf board (MCT.rollout, mcts.py:173-180).
+__global__ void __launch_bounds__(128) k_tree_rollout(az_tree t) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= t.G || !t.active[g] || t.leaf_kind[g] != AZ_LEAF_ROLLOUT) return;
+    uint64_t own = t.leaf_own[g], opp = t.leaf_opp[g];
+    int player = t.leaf_player[g];
+    const uint32_t ev = t.rng_ctr[g];
+    az_random_playout(own, opp, player, az_board_mask(t.n), ((uint64_t)(uint32_t)g << 32) | (uint64_t)ev,
+                      t.seed ^ 0x524F4C4C4F555421ULL);
+    t.rng_ctr[g] = ev + 1u;
+    t.value[g] = (float)az_winner(own, opp, player);
+}
+
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_root_stats(az_tree t, int32_t* __restrict__ N,
+                                                                         double* __restrict__ Q,
+                                                                         float* __restrict__ P,
+                                                                         uint32_t* __restrict__ root_N) {
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G) return;
+    const az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    for (int a = lane; a < AZ_CANVAS_ACTIONS; a += 32) {
+        if (N) N[(size_t)g * AZ_CANVAS_ACTIONS + a] = -1;
+        if (Q) Q[(size_t)g * AZ_CANVAS_ACTIONS + a] = 0.0;
+        if (P) P[(size_t)g * AZ_CANVAS_ACTIONS + a] = 0.f;
+    }
+    __syncwarp();
+    NodeRec root = az_load_node(&nodes[0]);
+    if (lane == 0 && root_N) root_N[g] = root.N;
+    if (!(root.flags() & AZ_NODE_EXPANDED)) return;
+    for (int j = lane; j < root.n_children(); j += 32) {
+        NodeRec c = az_load_node(&nodes[root.first_child + j]);
+        size_t o = (size_t)g * AZ_CANVAS_ACTIONS + c.move();
+        if (N) N[o] = (int32_t)c.N;
+        if (Q) Q[o] = c.Q;
+        if (P) P[o] = c.P;
+    }
+}
+
+// get_action_probs (mcts.py:95-116) + the categorical draw of MCTSPlayer.get_move (players.py:184-189).
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t, const float* __restrict__ temp,
+                                                                     uint8_t* __restrict__ action,
+                                                                     float* __restrict__ pi) {
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    const int A = t.n * t.n + 1;
+    const az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    if (pi) for (int a = lane; a < A; a += 32) pi[(size_t)g * A + a] = 0.f;
+    __syncwarp();
+    NodeRec root = az_load_node(&nodes[0]);
+    const uint32_t event = t.rng_ctr[g];
+    if (!(root.flags() & AZ_NODE_EXPANDED)) {                   // mcts.py:101-102: {pass_move: 1.}
+        if (lane == 0) {
+            action[g] = AZ_PASS;
+            if (pi) pi[(size_t)g * A + A - 1] = 1.f;
+        }
+        return;
+    }
+    const int k = root.n_children();
+    const float T = temp ? temp[g] : 0.f;
+    // lane j holds child j (and j+32 in the 33-children corner case)
+    uint32_t n0 = 0, n1 = 0;
+    int m0 = AZ_PASS, m1 = AZ_PASS;
+    if (lane < k) { NodeRec c = az_load_node(&nodes[root.first_child + lane]); n0 = c.N; m0 = c.move(); }
+    if (lane + 32 < k) { NodeRec c = az_load_node(&nodes[root.first_child + lane + 32]); n1 = c.N; m1 = c.move(); }
+    int chosen_move;
+    if (T == 0.f) {
+        // fair_max over visit counts
+        bool second = (lane + 32 < k) && n1 > n0;
+        int src;
+        az_warp_argmax((double)(second ? n1 : n0), second ? lane + 32 : lane, lane < k, t.tie_random != 0, t.seed,
+                       (uint32_t)g, event, &src);
+        chosen_move = __shfl_sync(AZ_FULL, second ? m1 : m0, src);
+        if (lane == 0 && pi) pi[(size_t)g * A + az_net_index(chosen_move, t.n)] = 1.f;
+    } else {
+        const double inv = 1.0 / (double)T;
+        double w0 = lane < k ? pow((double)n0, inv) : 0.0;
+        double w1 = lane + 32 < k ? pow((double)n1, inv) : 0.0;
+        if (T == 1.f) { w0 = lane < k ? (double)n0 : 0.0; w1 = lane + 32 < k ? (double)n1 : 0.0; }
+        const double sum = az_warp_sum(w0 + w1);
+        const double p0 = w0 / sum, p1 = w1 / sum;
+        if (pi) {
+            if (lane < k) pi[(size_t)g * A + az_net_index(m0, t.n)] = (float)p0;
+            if (lane + 32 < k) pi[(size_t)g * A + az_net_index(m1, t.n)] = (float)p1;
+        }
+        // inverse-CDF draw in child order: inclusive prefix sum of p0 over lanes, then the 33rd child
+        double c = p0;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            double o = __shfl_up_sync(AZ_FULL, c, off);
+            if (lane >= off) c += o;
+        }
+        az_u32x4 r = az_draw4(t.seed, (uint32_t)g, event, 0u, 0x43484F4Fu);
+        const double u = az_uniform53(r.x, r.y);
+        const uint32_t hit = __ballot_sync(AZ_FULL, lane < k && p0 > 0.0 && u < c);
+        if (hit) {
+            chosen_move = __shfl_sync(AZ_FULL, m0, __ffs(hit) - 1);
+        } else {
+            // u beyond the first 32 children: the 33rd if it exists, else the last child with p > 0
+            const uint32_t pos = __ballot_sync(AZ_FULL, lane < k && p0 > 0.0);
+            int last = 31 - __clz(pos);
+            chosen_move = (k > 32 && __shfl_sync(AZ_FULL, p1, 0) > 0.0) ? __shfl_sync(AZ_FULL, m1, 0)
+                                                                       : __shfl_sync(AZ_FULL, m0, last);
+        }
+    }
+    if (lane == 0) {
+        action[g] = (uint8_t)chosen_move;
+        t.rng_ctr[g] = event + 1u;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ advance
+
+// MCT.change_root (mcts.py:118-125) for every active game + the move on the root board.  The kept subtree is
+// copied breadth-first into the other half of the game's pool (32 nodes per round: each lane looks at one copied
+// node, an exclusive warp scan of their child counts assigns the destination blocks, then the child blocks are
+// copied with coalesced 32-byte-per-lane loads/stores), so the root is always node 0 and a game's tree stays
+// dense no matter how long the game lasts.
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree t, const uint8_t* __restrict__ action) {
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    const int a = action[g];
+    if (a == 255) return;
+    const uint64_t bmask = az_board_mask(t.n);
+    uint64_t own = t.root_own[g], opp = t.root_opp[g];
+    const uint64_t legal = az_legal_mask(own, opp, bmask);
+    const bool ok = (a == AZ_PASS) ? (legal == 0ULL) : (a < 64 && ((legal >> a) & 1ULL));
+    if (!ok) {
+        if (lane == 0) t.status[g] |= AZ_STATUS_ILLEGAL;
+        return;
+    }
+    const int h = t.half[g];
+    const az_node* src = t.nodes + ((size_t)g * 2 + h) * (size_t)t.capacity;
+    az_node* dst = t.nodes + ((size_t)g * 2 + (1 - h)) * (size_t)t.capacity;
+    NodeRec root = az_load_node(&src[0]);
+    int found = -1;
+    if (root.flags() & AZ_NODE_EXPANDED) {
+        for (int j = lane; j < root.n_children(); j += 32) {
+            NodeRec c = az_load_node(&src[root.first_child + j]);
+            if (c.move() == a) found = j;
+        }
+        const uint32_t who = __ballot_sync(AZ_FULL, found >= 0);
+        found = who ? __shfl_sync(AZ_FULL, found, __ffs(who) - 1) : -1;
+    }
+    uint32_t n_dst = 1u;
+    if (found < 0) {
+        if (lane == 0) az_store_node(&dst[0], 0.0, 0.f, 0u, 0u, az_make_meta(0, a, 0u));
+    } else {
+        NodeRec nr = az_load_node(&src[root.first_child + found]);
+        if (lane == 0) az_store_node(&dst[0], nr.Q, nr.P, nr.N, nr.first_child, nr.meta);
+        __syncwarp();
+        uint32_t i = 0u;
+        while (i < n_dst) {
+            const uint32_t cnt = min(32u, n_dst - i);
+            NodeRec r;
+            r.first_child = 0u; r.meta = 0u;
+            if ((uint32_t)lane < cnt) r = az_load_node(&dst[i + lane]);
+            const bool has = (uint32_t)lane < cnt && r.first_child != 0u;
+            const uint32_t kk = has ? (uint32_t)r.n_children() : 0u;
+            uint32_t incl = kk;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                uint32_t o = __shfl_up_sync(AZ_FULL, incl, off);
+                if (lane >= off) incl += o;
+            }
+            const uint32_t total = __shfl_sync(AZ_FULL, incl, 31);
+            const uint32_t my_base = n_dst + incl - kk;
+            if (has) reinterpret_cast<uint32_t*>(&dst[i + lane])[4] = my_base;
+            uint32_t mask = __ballot_sync(AZ_FULL, has);
+            while (mask) {
+                const int l = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const uint32_t sfc = __shfl_sync(AZ_FULL, r.first_child, l);
+                const uint32_t kc = __shfl_sync(AZ_FULL, kk, l);
+                const uint32_t db = __shfl_sync(AZ_FULL, my_base, l);
+                for (uint32_t j = lane; j < kc; j += 32) {
+                    const uint4* s = reinterpret_cast<const uint4*>(&src[sfc + j]);
+                    uint4* d = reinterpret_cast<uint4*>(&dst[db + j]);
+                    uint4 x = s[0], y = s[1];
+                    d[0] = x;
+                    d[1] = y;
+                }
+            }
+            n_dst += total;
+            i += cnt;
+            __syncwarp();
+        }
+    }
+    az_apply(own, opp, a);
+    if (lane == 0) {
+        t.root_own[g] = own;
+        t.root_opp[g] = opp;
+        t.root_player[g] = (int8_t)(-t.root_player[g]);
+        t.half[g] = (uint8_t)(1 - h);
+        t.n_alloc[g] = n_dst;
+        t.leaf_kind[g] = AZ_LEAF_IDLE;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ hash evaluator
+
+__device__ __forceinline__ uint64_t az_mix64(uint64_t z) {
+    z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ULL;
+    z ^= z >> 27; z *= 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return z;
+}
+
+// One warp per position: lane a computes probs[a], a + 32, ...; see tests/hash_eval.py for the definition.
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_eval_hash(const uint64_t* __restrict__ own,
+                                                                   const uint64_t* __restrict__ opp, int n, int64_t G,
+                                                                   uint64_t salt, float* __restrict__ probs,
+                                                                   float* __restrict__ value) {
+    const int64_t g = (int64_t)blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= G) return;
+    const int A = n * n + 1;
+    const uint64_t h = az_mix64(own[g] * 0x9E3779B97F4A7C15ULL + az_mix64(opp[g] + 0xD1B54A32D192ED03ULL) + salt);
+    for (int a = lane; a < A; a += 32) {
+        uint64_t q = ((az_mix64(h + (uint64_t)a * 0x632BE59BD9B4E019ULL) >> 40) & 31ULL) + 1ULL;
+        probs[g * A + a] = (float)q / 4096.0f;
+    }
+    if (lane == 0) value[g] = (float)((int)((h >> 20) & 0x1FFULL) - 256) / 256.0f;
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+
+static int az_check_tree(const az_tree* t) {
+    if (!t || !az_valid_n(t->n) || t->G <= 0 || t->capacity < 64 || t->max_depth < 2) return AZ_ERR_ARG;
+    if (!t->nodes || !t->half || !t->n_alloc || !t->root_own || !t->root_opp || !t->root_player || !t->active ||
+        !t->sims_done || !t->rng_ctr || !t->status || !t->leaf_node || !t->leaf_kind || !t->leaf_own ||
+        !t->leaf_opp || !t->leaf_player || !t->path || !t->path_len)
+        return AZ_ERR_ARG;
+    if (t->mode != AZ_MODE_ROLLOUT && t->mode != AZ_MODE_NEURAL) return AZ_ERR_ARG;
+    if (t->mode == AZ_MODE_NEURAL && (!t->probs || !t->value)) return AZ_ERR_ARG;
+    if (t->mode == AZ_MODE_ROLLOUT && !t->value) return AZ_ERR_ARG;
+    return AZ_OK;
+}
+
+static inline int az_warp_grid(int64_t G) { return (int)((G + AZ_WARPS_PER_CTA - 1) / AZ_WARPS_PER_CTA); }
+
+extern "C" int az_tree_reset(const az_tree* t, const uint8_t* mask, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    k_tree_reset<<<(t->G + 255) / 256, 256, 0, (cudaStream_t)stream>>>(*t, mask);
+    AZ_CHECK_LAUNCH("k_tree_reset");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_select, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    if (n_sim < 0) return AZ_ERR_ARG;
+    k_tree_step<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, n_sim, do_finish, do_select);
+    AZ_CHECK_LAUNCH("k_tree_step");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_rollout(const az_tree* t, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    k_tree_rollout<<<(t->G + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*t);
+    AZ_CHECK_LAUNCH("k_tree_rollout");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_root_stats(const az_tree* t, int32_t* N, double* Q, float* P, uint32_t* root_N, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    k_tree_root_stats<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, N, Q, P, root_N);
+    AZ_CHECK_LAUNCH("k_tree_root_stats");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_choose(const az_tree* t, const float* temp, uint8_t* action, float* pi, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    if (!action) return AZ_ERR_ARG;
+    k_tree_choose<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, temp, action, pi);
+    AZ_CHECK_LAUNCH("k_tree_choose");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    if (!action) return AZ_ERR_ARG;
+    k_tree_advance<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, action);
+    AZ_CHECK_LAUNCH("k_tree_advance");
+    return AZ_OK;
+}
+
+extern "C" int az_eval_hash(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t salt, float* probs,
+                            float* value, void* stream) {
+    if (!az_valid_n(n) || G < 0 || (G > 0 && (!own || !opp || !probs || !value))) return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    k_eval_hash<<<az_warp_grid(G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(own, opp, n, G, salt, probs, value);
+    AZ_CHECK_LAUNCH("k_eval_hash");
+    return AZ_OK;
+}

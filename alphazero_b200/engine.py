@@ -1,0 +1,184 @@
+"""TreeBatch: G concurrent MCTS trees on one GPU (host side of the tree kernels, include/az_b200.h).
+
+This is the batched counterpart of alphazero.mcts.MCT (mcts.py:49-269): one object owns the node pools, root
+boards and per-step leaf buffers of G games; `search` runs MCT.search for all of them at once, one simulation per
+game per step (the reference's sequential order per game), with the leaf evaluation delegated to an evaluator:
+
+    evaluator(tree)  must fill  tree.probs [G, n*n+1] float32 (network probabilities, pass last)
+                                tree.value [G] float32      (network value, side to move's view)
+                     from       tree.enc   [G, n, n]         (player*grid, written by the select kernel)
+                     or         tree.leaf_own / tree.leaf_opp (side-relative bitboards of the leaves).
+
+Evaluators: alphazero_b200.evaluators.{NetEvaluator, HashEvaluator}; rollout mode needs none (az_tree_rollout).
+"""
+import ctypes
+import time
+
+import numpy as np
+import torch
+
+from . import _lib
+from .boardops import PASS, _ptr, _stream, start_position, to_i64
+
+NODE_BYTES = 32
+
+
+class TreeBatch:
+    def __init__(self, G: int, n: int = 8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
+                 device="cuda", seed: int = 0, tie_random: bool = True, dirichlet_alpha: float = None,
+                 dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128):
+        if not torch.cuda.is_available():
+            raise RuntimeError("TreeBatch needs a CUDA device (alphazero_b200 has no CPU path)")
+        if mode not in ("neural", "rollout"):
+            raise ValueError(f"unknown mode {mode}")
+        self.G, self.n, self.mode = int(G), int(n), mode
+        self.A = n * n + 1
+        self.device = torch.device(device)
+        if capacity is None:
+            # per search at most (n_sim + 1) child blocks are added; 4x head-room over an average branching of ~12
+            # plus the retained subtree.  Overflow is detected (status bit) and reported, never silent.
+            capacity = max(1024, 48 * (n_sim_hint + 1))
+        self.capacity = int(capacity)
+        self.max_depth = int(max_depth)
+        dev = self.device
+        G = self.G
+        z = lambda *shape, dtype: torch.zeros(*shape, dtype=dtype, device=dev)
+        self.nodes = z(G * 2 * self.capacity * NODE_BYTES, dtype=torch.uint8)
+        self.half = z(G, dtype=torch.uint8)
+        self.n_alloc = z(G, dtype=torch.int32)
+        self.root_own = z(G, dtype=torch.int64)
+        self.root_opp = z(G, dtype=torch.int64)
+        self.root_player = torch.ones(G, dtype=torch.int8, device=dev)
+        self.active = torch.ones(G, dtype=torch.uint8, device=dev)
+        self.sims_done = z(G, dtype=torch.int32)
+        self.rng_ctr = z(G, dtype=torch.int32)
+        self.status = z(G, dtype=torch.int32)
+        self.leaf_node = z(G, dtype=torch.int32)
+        self.leaf_kind = z(G, dtype=torch.uint8)
+        self.leaf_own = z(G, dtype=torch.int64)
+        self.leaf_opp = z(G, dtype=torch.int64)
+        self.leaf_player = z(G, dtype=torch.int8)
+        self.path = z(G * self.max_depth, dtype=torch.int32)
+        self.path_len = z(G, dtype=torch.int32)
+        self.enc_dtype = enc_dtype
+        self.enc = z(G, n, n, dtype=enc_dtype)
+        self.probs = z(G, self.A, dtype=torch.float32)
+        self.value = z(G, dtype=torch.float32)
+        self.n_rollouts = 0
+        self.simulation_time = 0.0
+        self._desc = _lib.AzTree()
+        d = self._desc
+        for name in ("nodes", "half", "n_alloc", "root_own", "root_opp", "root_player", "active", "sims_done",
+                     "rng_ctr", "status", "leaf_node", "leaf_kind", "leaf_own", "leaf_opp", "leaf_player", "path",
+                     "path_len", "enc", "probs", "value"):
+            setattr(d, name, getattr(self, name).data_ptr())
+        d.seed = int(seed) & ((1 << 64) - 1)
+        d.G, d.n, d.capacity, d.max_depth = self.G, self.n, self.capacity, self.max_depth
+        d.mode = _lib.MODE_NEURAL if mode == "neural" else _lib.MODE_ROLLOUT
+        d.tie_random = 1 if tie_random else 0
+        d.enc_dtype = {torch.float32: 0, torch.bfloat16: 1}[enc_dtype]
+        self.set_dirichlet(dirichlet_alpha, dirichlet_epsilon)
+        self.reset_roots()
+
+    # ------------------------------------------------------------------ configuration
+    def set_dirichlet(self, alpha, epsilon) -> None:
+        """Both None (or <= 0) switches the root noise off (mcts.py:235)."""
+        self.dirichlet_alpha, self.dirichlet_epsilon = alpha, epsilon
+        on = alpha is not None and epsilon is not None
+        self._desc.dirichlet_alpha = float(alpha) if on else 0.0
+        self._desc.dirichlet_eps = float(epsilon) if on else 0.0
+
+    @property
+    def desc(self):
+        return ctypes.byref(self._desc)
+
+    # ------------------------------------------------------------------ roots
+    def reset_roots(self, mask: torch.Tensor = None) -> None:
+        """Start position + fresh trees for the masked games (board.reset() + player.reset())."""
+        black, white = start_position(self.n)
+        if mask is None:
+            self.root_own.fill_(to_i64(black)); self.root_opp.fill_(to_i64(white)); self.root_player.fill_(1)
+            self.active.fill_(1)
+        else:
+            m = mask.bool()
+            self.root_own[m] = to_i64(black); self.root_opp[m] = to_i64(white); self.root_player[m] = 1
+            self.active[m] = 1
+        self.reset_trees(mask)
+
+    def set_roots(self, own: torch.Tensor, opp: torch.Tensor, player: torch.Tensor, fresh_trees: bool = True) -> None:
+        self.root_own.copy_(own); self.root_opp.copy_(opp); self.root_player.copy_(player)
+        if fresh_trees:
+            self.reset_trees()
+
+    def reset_trees(self, mask: torch.Tensor = None) -> None:
+        m = None if mask is None else mask.to(torch.uint8).contiguous()
+        _lib.check(_lib.lib().az_tree_reset(self.desc, _ptr(m), _stream()), "az_tree_reset")
+
+    # ------------------------------------------------------------------ search
+    def step(self, n_sim: int, finish: bool, select: bool) -> None:
+        _lib.check(_lib.lib().az_tree_step(self.desc, int(n_sim), int(finish), int(select), _stream()), "az_tree_step")
+
+    def rollout_leaves(self) -> None:
+        _lib.check(_lib.lib().az_tree_rollout(self.desc, _stream()), "az_tree_rollout")
+
+    def search(self, n_sim: int, evaluator=None, extra_steps: int = 1, check: bool = True) -> None:
+        """MCT.search(board, n_sim) for every active game (mcts.py:254-269).
+
+        `extra_steps` = 1 covers the root-priming evaluation of fresh roots (mcts.py:231-233), which costs a step but
+        no simulation; pass 0 when every root is known to be evaluated already (tree reuse in self-play)."""
+        if self.mode == "neural" and evaluator is None:
+            raise ValueError("neural mode needs an evaluator")
+        start = time.time()
+        self.sims_done.zero_()
+        self.step(n_sim, finish=False, select=True)
+        steps = n_sim + (extra_steps if self.mode == "neural" else 0)
+        for _ in range(steps):
+            if self.mode == "neural":
+                evaluator(self)
+            else:
+                self.rollout_leaves()
+            self.step(n_sim, finish=True, select=True)
+        self.n_rollouts = int(n_sim)
+        if check:
+            self.check_status()
+            self.simulation_time = time.time() - start
+
+    def check_status(self) -> None:
+        """Raises if any game hit a pool overflow / depth overflow / illegal move (synchronises)."""
+        st = int(self.status.max().item())
+        if st & _lib.STATUS_OVERFLOW:
+            raise RuntimeError("TreeBatch: node pool overflow -- raise `capacity`")
+        if st & _lib.STATUS_DEPTH:
+            raise RuntimeError("TreeBatch: search path longer than max_depth")
+        if st & _lib.STATUS_ILLEGAL:
+            raise ValueError("TreeBatch: illegal move passed to advance()")
+
+    # ------------------------------------------------------------------ results
+    def root_stats(self):
+        """(N int32 [G,65] with -1 = no child, Q float64 [G,65], P float32 [G,65], root_N int32 [G]) on the canvas
+        action space (a = r*8+c, 64 = pass) -- what root.children exposes in the reference (mcts.py:88-116)."""
+        G = self.G
+        N = torch.empty(G, 65, dtype=torch.int32, device=self.device)
+        Q = torch.empty(G, 65, dtype=torch.float64, device=self.device)
+        P = torch.empty(G, 65, dtype=torch.float32, device=self.device)
+        rn = torch.empty(G, dtype=torch.int32, device=self.device)
+        _lib.check(_lib.lib().az_tree_root_stats(self.desc, _ptr(N), _ptr(Q), _ptr(P), _ptr(rn), _stream()),
+                   "az_tree_root_stats")
+        return N, Q, P, rn
+
+    def choose(self, temp: torch.Tensor = None):
+        """(action uint8 [G], pi float32 [G, n*n+1]): get_action_probs + sampling (mcts.py:95-116,
+        players.py:184-189); temp None = 0 for all games.  Entries of inactive games are left untouched (255 / 0)."""
+        action = torch.full((self.G,), 255, dtype=torch.uint8, device=self.device)
+        pi = torch.zeros(self.G, self.A, dtype=torch.float32, device=self.device)
+        t = None if temp is None else temp.to(device=self.device, dtype=torch.float32).contiguous()
+        _lib.check(_lib.lib().az_tree_choose(self.desc, _ptr(t), _ptr(action), _ptr(pi), _stream()), "az_tree_choose")
+        return action, pi
+
+    def advance(self, action: torch.Tensor) -> None:
+        """board.play_move(action) + MCT.change_root(action) for every active game (255 = leave untouched)."""
+        a = action.to(device=self.device, dtype=torch.uint8).contiguous()
+        _lib.check(_lib.lib().az_tree_advance(self.desc, _ptr(a), _stream()), "az_tree_advance")
+
+    def nodes_used(self) -> torch.Tensor:
+        return self.n_alloc.clone()

@@ -82,7 +82,116 @@ int az_othello_playouts(const uint64_t* own, const uint64_t* opp, const int8_t* 
 int az_othello_encode(const uint64_t* own, const uint64_t* opp, int n, int64_t G, void* out, int dtype,
                       void* stream);
 
-/* AZ_TREE_SECTION */
+/* ---------------------------------------------------------------- MCTS tree kernels -------------------- */
+
+/* One tree node, 32 bytes, 32-byte aligned: a child block is a contiguous run of these, so a warp reads a whole
+ * block with two coalesced 128-bit loads per lane.  Replaces alphazero.mcts.Node (mcts.py:8-46).
+ *   Q  running mean reward of the edge into the node, from the viewpoint of the player who moved into it,
+ *      float64 updated as (N*Q + r)/(N+1) exactly as mcts.py:220;
+ *   P  prior (float32, as the reference's np.float32 until Dirichlet noise);  N visit count. */
+typedef struct az_node {
+    double Q;
+    float P;
+    uint32_t N;
+    uint32_t first_child; /* index of the first child inside the game's pool half; 0 = no child block */
+    uint8_t n_children;
+    uint8_t move;         /* action that led here (0..63, 64 = pass) */
+    uint8_t flags;        /* AZ_NODE_* */
+    uint8_t reserved0;
+    uint32_t reserved1[2];
+} az_node;
+
+#define AZ_NODE_EVAL 1u     /* children allocated with priors (reference: node._children_probs is not None) */
+#define AZ_NODE_EXPANDED 2u /* children are part of the tree (reference: len(node.children) > 0) */
+#define AZ_NODE_NOISED 4u   /* Dirichlet noise applied to the children's priors (node.has_dirichlet_noise) */
+
+/* leaf_kind values (per game, per step) */
+#define AZ_LEAF_IDLE 0
+#define AZ_LEAF_NN 1        /* evaluate with the network, expand, back up */
+#define AZ_LEAF_PRIME 2     /* fresh root: evaluate + expand only, no visit (mcts.py:231-233) */
+#define AZ_LEAF_ROLLOUT 3   /* random playout from the leaf board, back up the winner */
+#define AZ_LEAF_DRAW 4      /* finished game at the leaf: back up 0 */
+#define AZ_LEAF_BLACK 5     /* finished game, black (+1) won */
+#define AZ_LEAF_WHITE 6     /* finished game, white (-1) won */
+
+#define AZ_STATUS_OVERFLOW 1u /* node pool of this game is full: children could not be allocated */
+#define AZ_STATUS_DEPTH 2u    /* path longer than max_depth */
+#define AZ_STATUS_ILLEGAL 4u  /* az_tree_advance got an illegal action for this game */
+
+#define AZ_MODE_ROLLOUT 0
+#define AZ_MODE_NEURAL 1
+
+/* Descriptor of G concurrent game trees.  All pointers are device pointers owned by the caller. */
+typedef struct az_tree {
+    az_node* nodes;        /* [G][2][capacity]  per-game pool, two halves (re-rooting compacts into the other) */
+    uint8_t* half;         /* [G] active half */
+    uint32_t* n_alloc;     /* [G] nodes used in the active half (root is index 0) */
+    uint64_t* root_own;    /* [G] root position, side-relative */
+    uint64_t* root_opp;    /* [G] */
+    int8_t* root_player;   /* [G] +1 / -1 */
+    uint8_t* active;       /* [G] 1 = the game takes part in search / advance */
+    uint32_t* sims_done;   /* [G] simulations backed up since the search started (MCT.n_rollouts) */
+    uint32_t* rng_ctr;     /* [G] per-game random event counter */
+    uint32_t* status;      /* [G] AZ_STATUS_* bits, sticky */
+    uint32_t* leaf_node;   /* [G] */
+    uint8_t* leaf_kind;    /* [G] AZ_LEAF_* */
+    uint64_t* leaf_own;    /* [G] leaf position, side-relative */
+    uint64_t* leaf_opp;    /* [G] */
+    int8_t* leaf_player;   /* [G] */
+    uint32_t* path;        /* [G][max_depth] node indices root..leaf */
+    uint32_t* path_len;    /* [G] */
+    void* enc;             /* [G][n*n] network input, player*grid row-major (written by select) */
+    float* probs;          /* [G][n*n+1] network probabilities exp(log_softmax), pass last (read by finish) */
+    float* value;          /* [G] neural: network value, side to move's view; rollout: absolute winner id */
+    uint64_t seed;
+    int32_t G;
+    int32_t n;             /* board size 4/6/8 */
+    int32_t capacity;      /* nodes per half */
+    int32_t max_depth;
+    int32_t mode;          /* AZ_MODE_* */
+    int32_t tie_random;    /* 0: ties -> lowest action index (parity mode); 1: uniform among ties (fair_max) */
+    int32_t enc_dtype;     /* 0 float32, 1 bfloat16 */
+    float dirichlet_alpha; /* <= 0: no noise */
+    float dirichlet_eps;
+    int32_t reserved;
+} az_tree;
+
+/* Fresh trees (reference: MCT() / player.reset()) for the games with mask[g] != 0 (mask NULL = all):
+ * n_alloc = 1, zeroed root node, leaf_kind idle, sims_done 0.  Root boards are NOT touched. */
+int az_tree_reset(const az_tree* t, const uint8_t* mask, void* stream);
+
+/* One batched step of MCT.__search_iter (mcts.py:226-252) for every active game, one warp per game:
+ *   do_finish: consume the previous leaf: children + priors from probs (get_normalized_probs,
+ *              othello.py:384-402), back_propagate (mcts.py:197-223), sims_done++;
+ *   do_select: if sims_done < n_sim: root priming / Dirichlet noise / select_node (mcts.py:127-171), then write the
+ *              leaf (kind, board, path) and its network encoding.
+ * Between two calls the caller fills probs/value for the leaves (network, az_eval_hash or az_tree_rollout). */
+int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_select, void* stream);
+
+/* Rollout-mode leaf evaluation: value[g] = winner of one uniform random playout from the leaf board for every
+ * game whose leaf_kind is AZ_LEAF_ROLLOUT (MCT.rollout, mcts.py:173-180). */
+int az_tree_rollout(const az_tree* t, void* stream);
+
+/* Root statistics as the reference exposes them through root.children (mcts.py:88-116): for every canvas action a,
+ * N[g][a] = visits of the child (-1 if the root has no such child or is not expanded), Q, P likewise;
+ * root_N[g] = root visits.  Outputs may be NULL. */
+int az_tree_root_stats(const az_tree* t, int32_t* N, double* Q, float* P, uint32_t* root_N, void* stream);
+
+/* MCT.get_action_probs (mcts.py:95-116) + the sampling of MCTSPlayer.get_move (players.py:184-189):
+ * temp[g] == 0 -> argmax of visits (ties per tie_random), pi one-hot; else pi ~ N^(1/temp), action sampled.
+ * action[g] = chosen canvas action; pi[g][n*n+1] in network order (to_neural_output, othello.py:404-412). */
+int az_tree_choose(const az_tree* t, const float* temp, uint8_t* action, float* pi, void* stream);
+
+/* Plays action[g] (255 = none) on the root board of every active game and re-roots its tree like
+ * MCT.change_root (mcts.py:118-125): keep the child's subtree if the root was expanded, else a fresh root.
+ * The kept subtree is compacted breadth-first into the other pool half.  Illegal actions set
+ * AZ_STATUS_ILLEGAL and leave the game untouched. */
+int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream);
+
+/* Deterministic hash evaluator (test double for PolicyValueNetwork.evaluate, see tests/hash_eval.py):
+ * probs[g][a] = q/4096, value[g] in {-256..255}/256 from (own, opp, salt). */
+int az_eval_hash(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t salt, float* probs,
+                 float* value, void* stream);
 
 #ifdef __cplusplus
 }
