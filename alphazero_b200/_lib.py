@@ -102,7 +102,12 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+LAUNCH_CALLS = 0  # number of kernel-launching C-ABI calls made through check() (bench.py's gpu_launches)
+
+
 def check(rc: int, what: str = "") -> None:
+    global LAUNCH_CALLS
+    LAUNCH_CALLS += 1
     if rc == AZ_OK:
         return
     if rc == AZ_ERR_ARG:

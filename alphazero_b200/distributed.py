@@ -1,0 +1,41 @@
+"""Multi-GPU plumbing: games shard across ranks with no data-path collective; the single exchange is the
+all-gather of the self-play samples to the training rank.  One process per GPU, torch.distributed
+(NCCL on GPUs, gloo in the CPU tests)."""
+import torch
+import torch.distributed as dist
+
+from .selfplay import SampleBatch
+
+
+def shard_range(total: int, rank: int, world: int):
+    """Games [lo, hi) owned by `rank`: contiguous, sizes differ by at most one."""
+    base, rem = divmod(total, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def gather_samples(batch: SampleBatch, episode_offset: int = 0, group=None) -> SampleBatch:
+    """All-gathers variable-length sample batches: counts first, then payloads padded to the longest rank.
+    Every rank gets the concatenation in rank order (episode indices shifted by each rank's `episode_offset`)."""
+    world = dist.get_world_size(group)
+    dev = batch.own.device
+    count = torch.tensor([len(batch)], dtype=torch.int64, device=dev)
+    counts = [torch.zeros_like(count) for _ in range(world)]
+    dist.all_gather(counts, count, group=group)
+    counts = [int(c.item()) for c in counts]
+    m = max(counts)
+
+    def pad(t):
+        out = torch.zeros((m,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        out[: t.shape[0]] = t
+        return out
+
+    def gather(t):
+        mine = pad(t)
+        bufs = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(bufs, mine, group=group)
+        return torch.cat([b[:c] for b, c in zip(bufs, counts)], dim=0)
+
+    ep = batch.episode_idx + int(episode_offset)
+    return SampleBatch(gather(batch.own), gather(batch.opp), gather(batch.pi), gather(batch.z), gather(ep),
+                       gather(batch.move_idx), batch.n)

@@ -66,6 +66,7 @@ class TreeBatch:
         self.value = z(G, dtype=torch.float32)
         self.n_rollouts = 0
         self.simulation_time = 0.0
+        self.profile = None   # set to {"eval": [], "tree": []} to record (start, end) CUDA events per call
         self._desc = _lib.AzTree()
         d = self._desc
         for name in ("nodes", "half", "n_alloc", "root_own", "root_opp", "root_player", "active", "sims_done",
@@ -132,12 +133,24 @@ class TreeBatch:
         self.sims_done.zero_()
         self.step(n_sim, finish=False, select=True)
         steps = n_sim + (extra_steps if self.mode == "neural" else 0)
+        prof = self.profile
         for _ in range(steps):
+            if prof is not None:
+                e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                e0.record()
             if self.mode == "neural":
                 evaluator(self)
             else:
                 self.rollout_leaves()
+            if prof is not None:
+                e1.record()
             self.step(n_sim, finish=True, select=True)
+            if prof is not None:
+                e2.record()
+                prof["eval"].append((e0, e1))
+                prof["tree"].append((e1, e2))
+                prof["depth_sum"] += self.path_len[self.active.bool()].sum()
+                prof["depth_cnt"] += self.active.sum()
         self.n_rollouts = int(n_sim)
         if check:
             self.check_status()

@@ -1,0 +1,129 @@
+"""Batched self-play: the trainer's sequential episode loop (alphazero/trainer.py:215-286) for G concurrent games.
+
+Every game follows exactly the reference's per-episode procedure -- AlphaZeroPlayer.get_move with the temperature
+of the move index, Sample(state, pi, player), play_move, apply_move (tree reuse), outcome back-filled and
+normalised to player = +1 -- but all games advance in lock-step on the device: one TreeBatch.search per move for
+all live games, one leaf per game per simulation step, the network evaluated on the whole leaf batch.
+"""
+import dataclasses
+
+import numpy as np
+import torch
+
+from . import boardops as bo
+from .engine import TreeBatch
+from .evaluators import NetEvaluator
+from .schedulers import TEMP_SCHEDULERS
+
+
+@dataclasses.dataclass
+class SampleBatch:
+    """Normalised training samples (trainer.py:74-78): `own`/`opp` are the bitboards of the side to move / the other
+    side, i.e. state*player with own = +1; pi is in network order (pass last); z = winner * player in {-1,0,1}."""
+    own: torch.Tensor         # int64 [S]
+    opp: torch.Tensor         # int64 [S]
+    pi: torch.Tensor          # float32 [S, n*n+1]
+    z: torch.Tensor           # int8 [S]
+    episode_idx: torch.Tensor  # int32 [S]
+    move_idx: torch.Tensor     # int32 [S]
+    n: int
+
+    def __len__(self) -> int:
+        return int(self.own.numel())
+
+    def cpu(self) -> "SampleBatch":
+        return SampleBatch(self.own.cpu(), self.opp.cpu(), self.pi.cpu(), self.z.cpu(), self.episode_idx.cpu(),
+                           self.move_idx.cpu(), self.n)
+
+    def nbytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.own, self.opp, self.pi, self.z, self.episode_idx, self.move_idx))
+
+    def states(self) -> np.ndarray:
+        """float64 [S, n, n] grids as the reference's Sample.state after normalize()."""
+        own, opp = bo.bits_to_numpy(self.own), bo.bits_to_numpy(self.opp)
+        out = np.zeros((len(own), self.n, self.n))
+        for r in range(self.n):
+            for c in range(self.n):
+                bit = np.uint64(r * 8 + c)
+                out[:, r, c] = ((own >> bit) & np.uint64(1)).astype(np.float64) - ((opp >> bit) & np.uint64(1)).astype(np.float64)
+        return out
+
+
+class SelfPlayEngine:
+    """G concurrent AlphaZero self-play games on one GPU."""
+
+    def __init__(self, nn, G: int, n: int = 8, n_sim: int = 200, dirichlet_alpha: float = 0.03,
+                 dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
+                 temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
+                 tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None):
+        self.G, self.n, self.n_sim = G, n, n_sim
+        self.max_plies = max_plies
+        self.tree = TreeBatch(G, n=n, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
+                              tie_random=tie_random, dirichlet_alpha=dirichlet_alpha,
+                              dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
+        self.evaluator = evaluator if evaluator is not None else NetEvaluator(nn, self.tree, dtype=dtype)
+        self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, n * n - 4)
+        dev = self.tree.device
+        T, A = max_plies, n * n + 1
+        self.h_own = torch.zeros(T, G, dtype=torch.int64, device=dev)
+        self.h_opp = torch.zeros(T, G, dtype=torch.int64, device=dev)
+        self.h_player = torch.zeros(T, G, dtype=torch.int8, device=dev)
+        self.h_live = torch.zeros(T, G, dtype=torch.bool, device=dev)
+        self.h_pi = torch.zeros(T, G, A, dtype=torch.float32, device=dev)
+        self.winner = torch.zeros(G, dtype=torch.int8, device=dev)
+        self.total_sims = 0
+        self.total_moves = 0
+        self.plies_played = 0
+
+    def set_network(self, nn) -> None:
+        """trainer.update_network (trainer.py:383-387): refresh the device snapshot + CUDA graph."""
+        self.evaluator.refresh(nn)
+
+    def play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
+             start_player: torch.Tensor = None) -> SampleBatch:
+        """Plays G games to the end and returns their samples (device tensors)."""
+        tree, G, n = self.tree, self.G, self.n
+        if start_own is None:
+            tree.reset_roots()
+        else:
+            tree.set_roots(start_own, start_opp, start_player)
+            tree.active.fill_(1)
+        term, _, win = bo.terminal_score(tree.root_own, tree.root_opp, tree.root_player, n)
+        live = term == 0
+        self.winner.copy_(win)
+        tree.active.copy_(live.to(torch.uint8))
+        sims = torch.zeros((), dtype=torch.int64, device=tree.device)
+        t = 0
+        temp_t = torch.empty(G, dtype=torch.float32, device=tree.device)
+        while t < self.max_plies:
+            self.h_own[t].copy_(tree.root_own); self.h_opp[t].copy_(tree.root_opp)
+            self.h_player[t].copy_(tree.root_player); self.h_live[t].copy_(live)
+            # fresh roots only exist on the first move: afterwards the played child always carries visits
+            tree.search(self.n_sim, self.evaluator, extra_steps=1 if t == 0 else 0, check=False)
+            sims += tree.sims_done.to(torch.int64)[live].sum()
+            temp_t.fill_(float(self.temp[t]))
+            action, pi = tree.choose(temp_t)
+            self.h_pi[t].copy_(pi)
+            tree.advance(action)
+            term, _, win = bo.terminal_score(tree.root_own, tree.root_opp, tree.root_player, n)
+            newly = live & (term == 1)
+            self.winner = torch.where(newly, win, self.winner)
+            live = live & (term == 0)
+            tree.active.copy_(live.to(torch.uint8))
+            t += 1
+            if not bool(live.any().item()):
+                break
+        tree.check_status()
+        if bool(live.any().item()):
+            raise RuntimeError(f"self-play did not finish within max_plies={self.max_plies}")
+        self.plies_played = t
+        self.total_sims = int(sims.item())
+        mask = self.h_live[:t]                                   # [t, G]
+        self.total_moves = int(mask.sum().item())
+        move_idx, episode_idx = torch.nonzero(mask.t(), as_tuple=True)[::-1]   # ordered by episode, then move
+        own = self.h_own[:t].t()[mask.t()]
+        opp = self.h_opp[:t].t()[mask.t()]
+        player = self.h_player[:t].t()[mask.t()]
+        pi = self.h_pi[:t].transpose(0, 1)[mask.t()]
+        z = (self.winner[episode_idx] * player).to(torch.int8)   # outcome * player (trainer.py:77)
+        return SampleBatch(own, opp, pi, z, episode_idx.to(torch.int32), move_idx.to(torch.int32), n)

@@ -1,0 +1,300 @@
+#!/usr/bin/env python
+"""bench.py -- Othello MCTS simulations/s of batched AlphaZero self-play on B200 (BASELINE.json config 3).
+
+One "step" = one pass of the hot path over one batch: G concurrent Othello 8x8 self-play games played to the end
+with the reference net (random init, torch.manual_seed(0)), n_sim simulations per move, Dirichlet 0.03/0.25,
+linear temperature 4/4, tree reuse -- AlphaZeroTrainer.self_play (trainer.py:215-286) for G episodes at once.
+
+    python bench.py --gpus N --steps K --warmup W          # ours (under torchrun for N > 1, one rank per GPU)
+    python bench.py --impl reference --steps K --warmup W  # CPU oracle port of the reference path, all host cores
+
+Prints ONE JSON line (rank 0).  `value` = simulations/s with everything resident in HBM; `e2e` = the same through
+the public API with host buffers (pinned start positions in, all training samples out) inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "othello_mcts_simulations_per_sec"
+UNIT = "sims/s"
+FLOP_PER_EVAL = 2 * 2169856          # OthelloNet n=8 forward, SURVEY.md 3.5
+WORKLOAD = "othello8x8_alphazero_selfplay_neural_mcts"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--games", type=int, default=4096, help="concurrent games per GPU")
+    ap.add_argument("--sims", type=int, default=200)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons of one GPU every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(power),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        d = json.load(open(path))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def cpu_baseline(args, seconds):
+    """Oracle port of the reference's neural MCTS on all host cores (oracle/cpu_baseline.py), bounded sample."""
+    import cpu_baseline as cb
+    cores = os.cpu_count() or 1
+    # ~750 sims/s/core measured in the build container: size the sample to the time budget
+    moves = max(1, int(seconds * 600 / args.sims))
+    reps, procs, _ = cb.run(n=8, n_sim=args.sims, moves=moves, repeats=1, processes=cores)
+    sims, secs = reps[0]
+    return {"value": sims / secs, "unit": UNIT, "cores": procs, "kind": "port",
+            "sample": f"{procs} processes x {moves} self-play moves x {args.sims} sims from the start position "
+                      f"({sims} sims in {secs:.1f}s); C oracle tree + batch-1 fp32 torch CPU forward per simulation"}
+
+
+def run_reference(args):
+    """--impl reference: the CPU oracle port on all host cores; each step is a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import cpu_baseline as cb
+    cores = os.cpu_count() or 1
+    moves = 4
+    reps, procs, _ = cb.run(n=8, n_sim=args.sims, moves=moves, repeats=args.warmup + args.steps, processes=cores)
+    timed = reps[args.warmup:]
+    sims = sum(r[0] for r in timed)
+    secs = sum(r[1] for r in timed)
+    value = sims / secs
+    sample = (f"{procs} processes x {moves} self-play moves x {args.sims} sims per step from the start position; "
+              f"C oracle tree (oracle/az_oracle.c) + batch-1 fp32 torch CPU forward per simulation")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 * secs / max(1, args.steps), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "board": "8x8", "n_sim": args.sims, "net": "OthelloNet(n=8) random-init seed 0",
+                   "dirichlet": [0.03, 0.25], "note": "python reference cannot travel to the GPU box; oracle port timed"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from alphazero_b200 import _lib
+    from alphazero_b200 import boardops as bo
+    from alphazero_b200.games.othello import OthelloNet
+    from alphazero_b200.selfplay import SelfPlayEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    G, n, n_sim = args.games, 8, args.sims
+
+    torch.manual_seed(0)
+    net = OthelloNet(n=n)
+    engine = SelfPlayEngine(net, G, n=n, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
+                            temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4, seed=0x5EED + 7919 * rank,
+                            dtype=torch.bfloat16, device=dev)
+    black, white = bo.start_position(n)
+    h_own = torch.full((G,), bo.to_i64(black), dtype=torch.int64).pin_memory()
+    h_opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64).pin_memory()
+    h_player = torch.ones(G, dtype=torch.int8).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        batch = engine.play()
+        if world > 1:
+            from alphazero_b200.distributed import gather_samples
+            batch = gather_samples(batch, episode_offset=rank * G)
+        return batch
+
+    def step_e2e():
+        own = h_own.to(dev, non_blocking=True); opp = h_opp.to(dev, non_blocking=True)
+        player = h_player.to(dev, non_blocking=True)
+        batch = engine.play(own, opp, player)
+        if world > 1:
+            from alphazero_b200.distributed import gather_samples
+            batch = gather_samples(batch, episode_offset=rank * G)
+        host = batch.cpu() if rank == 0 or world == 1 else None
+        return batch, host
+
+    for _ in range(args.warmup):
+        step_device()
+
+    def timed(fn, steps):
+        sampler = ClockSampler(local_rank)
+        barrier()
+        sampler.start()
+        launches0 = _lib.LAUNCH_CALLS
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record()
+        sims = moves = games = 0
+        last = None
+        for _ in range(steps):
+            last = fn()
+            sims += engine.total_sims; moves += engine.total_moves; games += G
+        e1.record()
+        barrier()
+        wall = time.time() - t0
+        clocks = sampler.stop()
+        ms = max(e0.elapsed_time(e1), 0.0)
+        ms = max(ms, 0.0)
+        stats = torch.tensor([ms, wall * 1000.0], dtype=torch.float64, device=dev)
+        tot = torch.tensor([sims, moves, games], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        return {"ms": float(stats[0]), "wall_ms": float(stats[1]), "sims": float(tot[0]), "moves": float(tot[1]),
+                "games": float(tot[2]), "clocks": clocks, "launches": _lib.LAUNCH_CALLS - launches0, "last": last}
+
+    dev_run = timed(step_device, args.steps)
+    e2e_run = timed(step_e2e, args.steps)
+    # the e2e region includes host-side packing, so its clock is the wall clock between the two barriers
+    e2e_ms = max(e2e_run["ms"], e2e_run["wall_ms"])
+    batch, host = e2e_run["last"]
+    d2h = host.nbytes() if host is not None else 0
+    h2d = G * (8 + 8 + 1)
+
+    # ---- phase profile (one more self-play batch with CUDA events around every evaluator / tree-step call)
+    tree = engine.tree
+    tree.profile = {"eval": [], "tree": [], "depth_sum": torch.zeros((), dtype=torch.int64, device=dev),
+                    "depth_cnt": torch.zeros((), dtype=torch.int64, device=dev)}
+    engine.play()
+    torch.cuda.synchronize()
+    prof = tree.profile
+    tree.profile = None
+    t_eval = sum(a.elapsed_time(b) for a, b in prof["eval"])
+    t_tree = sum(a.elapsed_time(b) for a, b in prof["tree"])
+    n_calls = len(prof["eval"])
+    mean_depth = float(prof["depth_sum"].item()) / max(1.0, float(prof["depth_cnt"].item()))
+    peaks = measured_peaks()
+    eval_ms = t_eval / n_calls
+    tree_ms = t_tree / n_calls
+    tflops = G * FLOP_PER_EVAL / (eval_ms * 1e-3) / 1e12
+    roofline = {
+        "bound": "tensor", "kernel": "policy-value network forward over the leaf batch (bf16, CUDA graph)",
+        "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+        "frac": tflops / peaks["bf16_tflops_sustained"], "peak_source": peaks["source"] + " (sustained: timed inside a long step)",
+        "traffic": None, "ms_per_launch": eval_ms, "share_of_step": t_eval / (t_eval + t_tree),
+    }
+    # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
+    # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
+    b_mean = 10.0
+    bytes_per_sim = mean_depth * 32 * b_mean + mean_depth * 32 + 32 * b_mean + 32 + 128 + 260 + 4 + 40
+    tree_gbs = G * bytes_per_sim / (tree_ms * 1e-3) / 1e9
+    tree_roofline = {"bound": "hbm", "kernel": "k_tree_step (backup + expand + select + encode)", "achieved": tree_gbs,
+                     "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
+                     "ms_per_launch": tree_ms, "mean_depth": mean_depth, "bytes_per_sim": bytes_per_sim,
+                     "share_of_step": t_tree / (t_eval + t_tree), "traffic": None}
+
+    if rank == 0:
+        value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
+        e2e_value = e2e_run["sims"] / (e2e_ms * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_run["ms"] / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "board": "8x8", "games_per_gpu": G, "n_sim": n_sim,
+                       "net": "OthelloNet(n=8) random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
+                       "leaves_in_flight_per_game": 1, "tree_reuse": True,
+                       "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
+                       "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},
+            "games_per_hour": dev_run["games"] / (dev_run["ms"] * 1e-3) * 3600.0,
+            "moves_per_step": dev_run["moves"] / args.steps,
+            "clocks": dev_run["clocks"],
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / args.steps, "clocks": e2e_run["clocks"]},
+            "gpu_launches": dev_run["launches"],
+            "roofline": roofline,
+            "roofline_tree": tree_roofline,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
