@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "tree_kernels.cu"]
+SOURCES = ["board_kernels.cu", "tree_kernels.cu", "net_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
@@ -58,6 +58,9 @@ SIGNATURES = {
     "az_tree_choose": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_tree_advance": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p]),
     "az_eval_hash": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_u64, c_void_p, c_void_p, c_void_p]),
+    "az_net_wblob_bytes": (c_int, []),
+    "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "az_net_heads": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,398 @@
+// Fused convolution trunk of the Othello policy-value network on the 5th-gen tensor cores (tcgen05 + TMEM),
+// plus the fused policy/value head epilogue.  sm_100a only.
+//
+// Replaces, for the leaf batch of the MCTS step, conv1..conv4 + BatchNorm + ReLU of OthelloNet.forward
+// (alphazero/games/othello.py:366-374).  Design:
+//   * one persistent CTA per SM loops over groups of NB boards; all activations of a group stay in shared memory,
+//     nothing but the 16-byte bitboards is read from HBM and only the 32*(n-4)^2 features are written;
+//   * every board lives in a zero-ringed (n+2)x(n+2) frame, frames are stacked into one row space
+//     (row = board*F*F + r*F + c); a 3x3 convolution is then 9 row-shifted GEMMs: for tap (dr,dc) the A operand
+//     of `tcgen05.mma` is the SAME activation buffer with its descriptor start address moved by (dr*F+dc) rows
+//     (K-major, no-swizzle canonical layout: 16 bytes per row per 8-channel chunk, so a row shift is +16 B);
+//   * B operands (per-tap 32x32 weight tiles, BatchNorm folded in) sit in shared memory for the whole kernel;
+//   * accumulators (128 rows x 32 channels fp32) live in TMEM, double buffered; four epilogue warps read them with
+//     tcgen05.ld, add the folded bias, apply ReLU, round to bf16 and write the next layer's A operand;
+//   * conv1 (1 input channel, K = 9) runs on the CUDA cores straight from the bitboards.
+// Garbage computed on ring rows / tail rows is never read by a valid output ("trunk frame").
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#include "../../include/az_b200.h"
+#include "common.cuh"
+
+#define NET_CH 32                 // channels of every conv layer
+#define NET_TILE_M 128            // rows per MMA tile
+#define NET_TILES 6               // tiles per group
+#define NET_ROWS (NET_TILE_M * NET_TILES)   // 768 rows of activation per buffer
+#define NET_MARGIN 16             // zero rows before / after (|row shift| <= F + 1 <= 11)
+#define NET_BUF_ROWS (NET_ROWS + 2 * NET_MARGIN)   // 800
+#define NET_CHUNK_BYTES (NET_BUF_ROWS * 16)        // one 8-channel chunk plane: 12800 B  (= LBO of the A operand)
+#define NET_BUF_BYTES (4 * NET_CHUNK_BYTES)        // 51200 B per activation buffer
+#define NET_TAP_BYTES 2048        // one 32x32 bf16 weight tile
+#define NET_LAYER_BYTES (9 * NET_TAP_BYTES)        // 18432
+#define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES)  // conv2..conv4
+#define NET_WBLOB_F32 (32 * 9 + 4 * 32)            // conv1 weights [32][9], biases of conv1..conv4
+#define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
+#define NET_THREADS 160           // warps 0-3: conv1 + epilogue, warp 4: TMEM allocation + MMA issue
+#define NET_TMEM_COLS 64          // two accumulator stages of 32 columns
+
+// shared memory map (bytes)
+#define SM_BUF_A 0
+#define SM_BUF_B (SM_BUF_A + NET_BUF_BYTES)
+#define SM_W (SM_BUF_B + NET_BUF_BYTES)
+#define SM_BARS (SM_W + NET_WBLOB_BYTES)           // 4 mbarriers: full[2], empty[2]
+#define SM_TMEM_PTR (SM_BARS + 4 * 8)
+#define SM_BOARDS (SM_TMEM_PTR + 8)                // own/opp of the group's boards: 2 * 16 * 8 B
+#define SM_TOTAL (SM_BOARDS + 2 * 16 * 8)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(bar), "r"(parity) : "memory");
+}
+
+// K-major, no-swizzle shared memory matrix descriptor: 8-row core matrices of 16-byte rows, `lbo` bytes between
+// the two 16-byte K chunks of one MMA, `sbo` bytes between consecutive 8-row groups.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFFu);
+    d |= (uint64_t)((lbo >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
+    return d;                 // base_offset 0, lbo_mode 0, layout_type 0 = SWIZZLE_NONE
+}
+
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M = 128, N = 32.
+__device__ __forceinline__ uint32_t umma_idesc_bf16_m128_n32() {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+struct NetTrunkParams {
+    const uint64_t* own;       // [G] side-relative bitboards of the leaves
+    const uint64_t* opp;       // [G]
+    const uint8_t* wblob;      // NET_WBLOB_BYTES: packed weights (see alphazero_b200/fused_net.py)
+    __nv_bfloat16* features;   // [G][(n-4)^2 * 32]  position-major, channel-minor
+    __nv_bfloat16* debug;      // optional [n_groups][NET_ROWS][32] dump of the activations after `debug_layer`
+    int G;
+    int n;                     // board size 6 or 8
+    int boards_per_group;      // NB: NB * (n+2)^2 <= NET_ROWS
+    int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
+};
+
+// Row -> (board in group, frame row, frame col)
+__device__ __forceinline__ void net_row_coords(int row, int F, int& b, int& r, int& c) {
+    const int FF = F * F;
+    b = row / FF;
+    const int rem = row - b * FF;
+    r = rem / F;
+    c = rem - r * F;
+}
+
+// conv1 + folded BN + ReLU on the CUDA cores, straight from the bitboards, for the rows handled by this thread.
+__device__ __forceinline__ void net_conv1(const NetTrunkParams& p, uint8_t* smem, int tid, int n_boards) {
+    const int F = p.n + 2, rows = p.boards_per_group * F * F;
+    const float* w1 = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // [32][9]
+    const float* b1 = w1 + 32 * 9;
+    const uint64_t* s_own = reinterpret_cast<const uint64_t*>(smem + SM_BOARDS);
+    const uint64_t* s_opp = s_own + 16;
+    for (int row = tid; row < rows; row += 128) {
+        int b, r, c;
+        net_row_coords(row, F, b, r, c);
+        uint32_t out[16];
+        const bool interior = (b < n_boards) && r >= 1 && r <= p.n && c >= 1 && c <= p.n;
+        if (interior) {
+            const uint64_t own = s_own[b], opp = s_opp[b];
+            float v[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const int ur = r - 1 + (t / 3 - 1), uc = c - 1 + (t % 3 - 1);
+                float x = 0.f;
+                if (ur >= 0 && ur < p.n && uc >= 0 && uc < p.n) {
+                    const int bit = ur * 8 + uc;
+                    x = (float)((int)((own >> bit) & 1ULL) - (int)((opp >> bit) & 1ULL));
+                }
+                v[t] = x;
+            }
+#pragma unroll
+            for (int co = 0; co < 32; co += 2) {
+                float a0 = b1[co], a1 = b1[co + 1];
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    a0 = fmaf(w1[co * 9 + t], v[t], a0);
+                    a1 = fmaf(w1[(co + 1) * 9 + t], v[t], a1);
+                }
+                out[co >> 1] = pack_bf16x2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) out[i] = 0u;       // zero ring = the padding of conv2
+        }
+        uint8_t* dst = smem + SM_BUF_A + (NET_MARGIN + row) * 16;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch)
+            *reinterpret_cast<uint4*>(dst + ch * NET_CHUNK_BYTES) =
+                make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
+    }
+}
+
+__global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int F = p.n + 2, FF = F * F;
+    const int NB = p.boards_per_group;
+    const int n_groups = (p.G + NB - 1) / NB;
+    const uint32_t bar_full0 = smem_u32(smem + SM_BARS), bar_empty0 = bar_full0 + 16;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SM_TMEM_PTR);
+
+    // ---- one-time setup: zero the activation buffers, stage the weights, barriers, TMEM
+    for (int i = tid; i < 2 * NET_BUF_BYTES / 16; i += NET_THREADS)
+        reinterpret_cast<uint4*>(smem + SM_BUF_A)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < NET_WBLOB_BYTES / 16; i += NET_THREADS)
+        reinterpret_cast<uint4*>(smem + SM_W)[i] = reinterpret_cast<const uint4*>(p.wblob)[i];
+    if (tid == 0) {
+        mbar_init(bar_full0, 1); mbar_init(bar_full0 + 8, 1);
+        mbar_init(bar_empty0, 128); mbar_init(bar_empty0 + 8, 128);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(NET_TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_ptr_smem;
+    const uint32_t idesc = umma_idesc_bf16_m128_n32();
+    const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES) + 32 * 9 + 32;  // b2,b3,b4
+
+    uint32_t tile_it = 0;   // running tile counter (same sequence in the MMA thread and in the epilogue warps)
+
+    for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+        const int board0 = grp * NB;
+        const int n_boards = min(NB, p.G - board0);
+        // ---- stage the bitboards, conv1 -> buffer A
+        if (tid < 16) {
+            uint64_t* s_own = reinterpret_cast<uint64_t*>(smem + SM_BOARDS);
+            s_own[tid] = tid < n_boards ? p.own[board0 + tid] : 0ULL;
+            s_own[16 + tid] = tid < n_boards ? p.opp[board0 + tid] : 0ULL;
+        }
+        __syncthreads();
+        if (warp < 4) net_conv1(p, smem, tid, n_boards);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (p.debug && p.debug_layer == 1 && warp < 4) {
+            for (int row = tid; row < NET_ROWS; row += 128)
+                for (int ch = 0; ch < 4; ++ch)
+                    *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
+                        *reinterpret_cast<const uint4*>(smem + SM_BUF_A + ch * NET_CHUNK_BYTES + (NET_MARGIN + row) * 16);
+        }
+
+        // ---- conv2 (A -> B), conv3 (B -> A), conv4 (A -> features)
+        for (int layer = 0; layer < 3; ++layer) {
+            const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A));
+            uint8_t* dst = smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B);
+            const uint32_t wbase = smem_u32(smem + SM_W + layer * NET_LAYER_BYTES);
+            if (warp == 4) {
+                if (lane == 0) {
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    for (int t = 0; t < NET_TILES; ++t) {
+                        const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                        mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint32_t d_tmem = tmem_base + stage * 32u;
+                        uint32_t acc = 0u;
+#pragma unroll
+                        for (int tap = 0; tap < 9; ++tap) {
+                            const int shift = (tap / 3 - 1) * F + (tap % 3 - 1);
+                            const uint32_t a_row = src + (uint32_t)((NET_MARGIN + t * NET_TILE_M + shift) * 16);
+#pragma unroll
+                            for (int kk = 0; kk < 2; ++kk) {
+                                const uint64_t da = umma_desc(a_row + kk * 2 * NET_CHUNK_BYTES, NET_CHUNK_BYTES, 128);
+                                const uint64_t db = umma_desc(wbase + tap * NET_TAP_BYTES + kk * 2 * 512, 512, 128);
+                                umma_bf16(d_tmem, da, db, idesc, acc);
+                                acc = 1u;
+                            }
+                        }
+                        umma_commit(bar_full0 + 8 * stage);
+                    }
+                }
+                __syncwarp();
+            } else {
+                const float* bias = bias_all + layer * 32;
+                for (int t = 0; t < NET_TILES; ++t) {
+                    const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                    mbar_wait(bar_full0 + 8 * stage, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    uint32_t acc[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + stage * 32u, acc);
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(bar_empty0 + 8 * stage);
+                    const int row = t * NET_TILE_M + tid;           // tid = TMEM lane = row within the tile
+                    uint32_t out[16];
+#pragma unroll
+                    for (int co = 0; co < 32; co += 2)
+                        out[co >> 1] = pack_bf16x2(fmaxf(__uint_as_float(acc[co]) + bias[co], 0.f),
+                                                   fmaxf(__uint_as_float(acc[co + 1]) + bias[co + 1], 0.f));
+                    if (layer < 2) {
+                        uint8_t* d = dst + (NET_MARGIN + row) * 16;
+#pragma unroll
+                        for (int ch = 0; ch < 4; ++ch)
+                            *reinterpret_cast<uint4*>(d + ch * NET_CHUNK_BYTES) =
+                                make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
+                        if (p.debug && p.debug_layer == layer + 2)
+                            for (int ch = 0; ch < 4; ++ch)
+                                *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
+                                    make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
+                    } else {
+                        // conv4: only frame positions 3..n-2 are outputs; features[board][pos*32 + co]
+                        int b, r, c;
+                        net_row_coords(row, F, b, r, c);
+                        const int m = p.n - 4;
+                        if (row < NB * FF && b < n_boards && r >= 3 && r < 3 + m && c >= 3 && c < 3 + m) {
+                            const int pos = (r - 3) * m + (c - 3);
+                            uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (m * m) + pos) * 32);
+#pragma unroll
+                            for (int ch = 0; ch < 4; ++ch)
+                                f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
+                        }
+                    }
+                }
+            }
+            tile_it += NET_TILES;
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(NET_TMEM_COLS));
+}
+
+// ------------------------------------------------------------------------------------------------ heads epilogue
+
+// One warp per position: probs = softmax(logits[0 .. A)) in float32, value = tanh(logits[A]).
+// Fuses log_softmax + exp (PolicyValueNetwork.predict, base.py:350-355) and tanh (othello.py:382) and writes straight
+// into the tree's probs / value buffers.
+__global__ void __launch_bounds__(128) k_net_heads(const __nv_bfloat16* __restrict__ logits, int ld, int A, int64_t G,
+                                                   float* __restrict__ probs, float* __restrict__ value) {
+    const int64_t g = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= G) return;
+    const __nv_bfloat16* row = logits + g * ld;
+    float x[3];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int a = lane + 32 * i;
+        x[i] = a < A ? __bfloat162float(row[a]) : -INFINITY;
+        mx = fmaxf(mx, x[i]);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    float e[3], s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        e[i] = (lane + 32 * i) < A ? __expf(x[i] - mx) : 0.f;
+        s += e[i];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    const float inv = 1.f / s;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int a = lane + 32 * i;
+        if (a < A) probs[g * A + a] = e[i] * inv;
+    }
+    if (lane == 0) value[g] = tanhf(__bfloat162float(row[A]));
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+
+extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES; }
+
+extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob,
+                            void* features, void* debug, int debug_layer, void* stream) {
+    if ((n != 6 && n != 8) || G < 0 || (G > 0 && (!own || !opp || !wblob || !features))) return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    static int n_sms = 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        int dev = 0;
+        AZ_CUDA_TRY(cudaGetDevice(&dev));
+        AZ_CUDA_TRY(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        attr_set = true;
+    }
+    NetTrunkParams p;
+    p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
+    p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;
+    p.G = (int)G; p.n = n;
+    const int F = n + 2;
+    p.boards_per_group = NET_ROWS / (F * F);          // 7 boards (n = 8) or 12 boards (n = 6) per 768-row group
+    p.debug_layer = debug ? debug_layer : 0;
+    const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
+    const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM
+    k_net_trunk<<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    AZ_CHECK_LAUNCH("k_net_trunk");
+    return AZ_OK;
+}
+
+extern "C" int az_net_heads(const void* logits, int ld, int n, int64_t G, float* probs, float* value, void* stream) {
+    const int A = n * n + 1;
+    if (!az_valid_n(n) || G < 0 || ld < A + 1 || (G > 0 && (!logits || !probs || !value))) return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    k_net_heads<<<(unsigned)((G + 3) / 4), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits, ld, A, G, probs,
+                                                                       value);
+    AZ_CHECK_LAUNCH("k_net_heads");
+    return AZ_OK;
+}

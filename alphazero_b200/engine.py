@@ -82,6 +82,11 @@ class TreeBatch:
         self.reset_roots()
 
     # ------------------------------------------------------------------ configuration
+    def set_encoding(self, on: bool) -> None:
+        """Switches the float network encoding written by the select kernel on/off (evaluators that read the leaf
+        bitboards directly, e.g. FusedOthelloEvaluator, do not need it)."""
+        self._desc.enc = self.enc.data_ptr() if on else None
+
     def set_dirichlet(self, alpha, epsilon) -> None:
         """Both None (or <= 0) switches the root noise off (mcts.py:235)."""
         self.dirichlet_alpha, self.dirichlet_epsilon = alpha, epsilon

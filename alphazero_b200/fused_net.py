@@ -1,0 +1,135 @@
+"""Hand-written forward of the Othello policy-value network for the leaf batch (evaluator for TreeBatch.search).
+
+The weights are the reference module's own (any OthelloNet state_dict, alphazero/games/othello.py:341-359); this file
+only re-packs them for the kernels:
+  * eval-mode BatchNorm folded into the preceding conv / linear layer (y = s*(Wx + b - mu) + beta, s = g/sqrt(v+eps));
+  * conv2..conv4: per-tap 32x32 bf16 tiles in the tcgen05 K-major no-swizzle operand layout (csrc/net_kernels.cu);
+  * conv1 + all conv biases in float32;
+  * fc1 columns permuted from the reference's channel-major flatten (c*m*m + pos) to the trunk kernel's
+    position-major feature order (pos*32 + c);
+  * fc_probs and fc_value concatenated into one [n*n+2, 512] head.
+Per step:  az_net_trunk (tcgen05)  ->  fc1 + ReLU, fc2 + ReLU, heads (cuBLASLt GEMMs with fused bias/ReLU epilogues,
+plain library GEMMs)  ->  az_net_heads (softmax / tanh straight into tree.probs / tree.value), all in one CUDA graph.
+Input is the leaf bitboards (tree.leaf_own / leaf_opp): the float encoding of the board is never materialised.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .boardops import _ptr, _stream
+
+TAP_BYTES, LAYER_BYTES = 2048, 9 * 2048
+
+
+def _fold_bn(weight, bias, bn):
+    s = bn.weight.detach().double() / torch.sqrt(bn.running_var.detach().double() + bn.eps)
+    shape = [-1] + [1] * (weight.dim() - 1)
+    w = weight.detach().double() * s.reshape(shape)
+    b = (bias.detach().double() - bn.running_mean.detach().double()) * s + bn.bias.detach().double()
+    return w, b
+
+
+def pack_trunk_weights(net) -> torch.Tensor:
+    """uint8 blob for az_net_trunk: [conv2|conv3|conv4 MMA tiles][conv1 w f32 [32][9]][b1..b4 f32 [4][32]]."""
+    assert net.n_channels == 32
+    blob = np.zeros(int(_lib.lib().az_net_wblob_bytes()), dtype=np.uint8)
+    mma = np.zeros(3 * 9 * 4 * 32 * 8, dtype=np.uint16)      # [layer][tap][ci chunk][co][ci % 8] bf16 bits
+    mma = mma.reshape(3, 9, 4, 32, 8)
+    biases = np.zeros((4, 32), dtype=np.float32)
+    w1, b1 = _fold_bn(net.conv1.weight, net.conv1.bias, net.bn1)
+    biases[0] = b1.float().cpu().numpy()
+    for li, (conv, bn) in enumerate(((net.conv2, net.bn2), (net.conv3, net.bn3), (net.conv4, net.bn4))):
+        w, b = _fold_bn(conv.weight, conv.bias, bn)          # [co][ci][kh][kw]
+        biases[li + 1] = b.float().cpu().numpy()
+        wb = w.float().cpu().to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)   # bf16 bit patterns
+        for tap in range(9):
+            kh, kw = divmod(tap, 3)
+            t = wb[:, :, kh, kw]                              # [co][ci]
+            mma[li, tap] = t.reshape(32, 4, 8).transpose(1, 0, 2)   # -> [ci chunk][co][ci % 8]
+    n_mma = 3 * LAYER_BYTES
+    blob[:n_mma] = mma.reshape(-1).view(np.uint8)
+    f32 = np.concatenate([w1.float().cpu().numpy().reshape(32, 9).reshape(-1), biases.reshape(-1)]).astype(np.float32)
+    blob[n_mma:n_mma + f32.nbytes] = f32.view(np.uint8)
+    return torch.from_numpy(blob)
+
+
+class FusedOthelloEvaluator:
+    """evaluator(tree): fills tree.probs / tree.value for the leaves in tree.leaf_own / tree.leaf_opp."""
+
+    @staticmethod
+    def supports(nn) -> bool:
+        """True for the reference's Othello architecture (layer names / shapes of othello.py:341-359), n = 6 or 8."""
+        from .games.othello import OthelloNet
+        return isinstance(nn, OthelloNet) and nn.n in (6, 8) and nn.n_channels == 32
+
+    def __init__(self, nn, tree, use_cuda_graph: bool = True):
+        self.tree = tree
+        self.use_cuda_graph = use_cuda_graph
+        self.graph = None
+        self.n_calls = 0
+        self.refresh(nn)
+
+    def refresh(self, nn) -> None:
+        """(Re)packs the weights; call after the network changed (MCT.nn setter, mcts.py:78-83)."""
+        t = self.tree
+        n, dev, G = t.n, t.device, t.G
+        if nn.n != n:
+            raise ValueError(f"network is for n={nn.n}, tree for n={n}")
+        if n not in (6, 8):
+            raise ValueError("the fused trunk supports n = 6 or 8")
+        self.src = nn
+        m = n - 4
+        self.wblob = pack_trunk_weights(nn).to(dev)
+        w1, b1 = _fold_bn(nn.fc1.weight, nn.fc1.bias, nn.fc_bn1)               # [1024][32*m*m] channel-major
+        w1 = w1.reshape(1024, 32, m * m).permute(0, 2, 1).reshape(1024, m * m * 32)
+        w2, b2 = _fold_bn(nn.fc2.weight, nn.fc2.bias, nn.fc_bn2)
+        bf = lambda x: x.float().to(dev).to(torch.bfloat16).contiguous()
+        self.w1t, self.b1 = bf(w1.t()), bf(b1)                                  # [K][N] for addmm
+        self.w2t, self.b2 = bf(w2.t()), bf(b2)
+        A = n * n + 1
+        self.ld = ((A + 1 + 7) // 8) * 8                                        # head rows padded to a multiple of 8
+        wh = torch.zeros(self.ld, 512, dtype=torch.float64)
+        bh = torch.zeros(self.ld, dtype=torch.float64)
+        wh[:A] = nn.fc_probs.weight.detach().double().cpu(); bh[:A] = nn.fc_probs.bias.detach().double().cpu()
+        wh[A] = nn.fc_value.weight.detach().double().cpu()[0]; bh[A] = nn.fc_value.bias.detach().double().cpu()[0]
+        self.wht, self.bh = bf(wh.t()), bf(bh)
+        self.features = torch.zeros(G, m * m * 32, dtype=torch.bfloat16, device=dev)
+        self.h1 = torch.empty(G, 1024, dtype=torch.bfloat16, device=dev)
+        self.h2 = torch.empty(G, 512, dtype=torch.bfloat16, device=dev)
+        self.logits = torch.empty(G, self.ld, dtype=torch.bfloat16, device=dev)
+        self.graph = None
+        if self.use_cuda_graph:
+            self._capture()
+
+    def trunk(self, debug=None, debug_layer: int = 0) -> None:
+        t = self.tree
+        _lib.check(_lib.lib().az_net_trunk(_ptr(t.leaf_own), _ptr(t.leaf_opp), t.n, t.G, _ptr(self.wblob),
+                                           _ptr(self.features), _ptr(debug), int(debug_layer), _stream()), "az_net_trunk")
+
+    def _forward(self) -> None:
+        t = self.tree
+        self.trunk()
+        with torch.no_grad():
+            torch._addmm_activation(self.b1, self.features, self.w1t, out=self.h1)      # fused bias + ReLU epilogue
+            torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
+            torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
+        _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, t.n, t.G, _ptr(t.probs), _ptr(t.value), _stream()),
+                   "az_net_heads")
+
+    def _capture(self) -> None:
+        s = torch.cuda.Stream(device=self.tree.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                self._forward()
+        torch.cuda.current_stream().wait_stream(s)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._forward()
+
+    def __call__(self, tree=None) -> None:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._forward()
+        self.n_calls += 1

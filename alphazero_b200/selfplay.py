@@ -13,6 +13,7 @@ import torch
 from . import boardops as bo
 from .engine import TreeBatch
 from .evaluators import NetEvaluator
+from .fused_net import FusedOthelloEvaluator
 from .schedulers import TEMP_SCHEDULERS
 
 
@@ -55,13 +56,20 @@ class SelfPlayEngine:
     def __init__(self, nn, G: int, n: int = 8, n_sim: int = 200, dirichlet_alpha: float = 0.03,
                  dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
                  temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
-                 tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None):
+                 tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
+                 network_path: str = "auto"):
         self.G, self.n, self.n_sim = G, n, n_sim
         self.max_plies = max_plies
         self.tree = TreeBatch(G, n=n, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
                               tie_random=tie_random, dirichlet_alpha=dirichlet_alpha,
                               dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
-        self.evaluator = evaluator if evaluator is not None else NetEvaluator(nn, self.tree, dtype=dtype)
+        if evaluator is not None:
+            self.evaluator = evaluator
+        elif network_path == "fused" or (network_path == "auto" and FusedOthelloEvaluator.supports(nn)):
+            self.evaluator = FusedOthelloEvaluator(nn, self.tree)       # hand-written tcgen05 forward
+            self.tree.set_encoding(False)
+        else:
+            self.evaluator = NetEvaluator(nn, self.tree, dtype=dtype)   # any PolicyValueNetwork, bf16 CUDA graph
         self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, n * n - 4)
         dev = self.tree.device
         T, A = max_plies, n * n + 1

@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--net", default="fused", choices=["fused", "torch"],
+                    help="fused: hand-written tcgen05 trunk + fused heads; torch: the module's own bf16 forward")
     return ap.parse_args()
 
 
@@ -164,7 +166,7 @@ def run_ours(args):
     net = OthelloNet(n=n)
     engine = SelfPlayEngine(net, G, n=n, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
                             temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4, seed=0x5EED + 7919 * rank,
-                            dtype=torch.bfloat16, device=dev)
+                            dtype=torch.bfloat16, device=dev, network_path=args.net)
     black, white = bo.start_position(n)
     h_own = torch.full((G,), bo.to_i64(black), dtype=torch.int64).pin_memory()
     h_opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64).pin_memory()
@@ -248,7 +250,7 @@ def run_ours(args):
     tree_ms = t_tree / n_calls
     tflops = G * FLOP_PER_EVAL / (eval_ms * 1e-3) / 1e12
     roofline = {
-        "bound": "tensor", "kernel": "policy-value network forward over the leaf batch (bf16, CUDA graph)",
+        "bound": "tensor", "kernel": f"policy-value network forward over the leaf batch (bf16, CUDA graph, path={args.net})",
         "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": tflops / peaks["bf16_tflops_sustained"], "peak_source": peaks["source"] + " (sustained: timed inside a long step)",
         "traffic": None, "ms_per_launch": eval_ms, "share_of_step": t_eval / (t_eval + t_tree),
@@ -272,7 +274,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "board": "8x8", "games_per_gpu": G, "n_sim": n_sim,
                        "net": "OthelloNet(n=8) random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
-                       "leaves_in_flight_per_game": 1, "tree_reuse": True,
+                       "leaves_in_flight_per_game": 1, "network_path": args.net, "tree_reuse": True,
                        "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
                        "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},
             "games_per_hour": dev_run["games"] / (dev_run["ms"] * 1e-3) * 3600.0,

@@ -193,6 +193,24 @@ int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream);
 int az_eval_hash(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t salt, float* probs,
                  float* value, void* stream);
 
+/* ---------------------------------------------------------------- fused network kernels ---------------- */
+
+/* Bytes of the packed trunk weights expected by az_net_trunk (built by alphazero_b200/fused_net.py). */
+int az_net_wblob_bytes(void);
+
+/* Fused conv1..conv4 (+ folded BatchNorm + ReLU) of OthelloNet.forward (alphazero/games/othello.py:366-374) for G
+ * positions given as side-relative bitboards (the network input player*grid, base.py:363, is formed on the fly).
+ * features: bf16 [G][(n-4)^2 * 32], position-major / channel-minor (fc1's columns are permuted to match).
+ * tcgen05 implicit GEMM, activations resident in shared memory; n = 6 or 8.
+ * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>. */
+int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob, void* features,
+                 void* debug, int debug_layer, void* stream);
+
+/* probs[g][0 .. n*n+1) = softmax(logits[g][0 .. n*n+1)), value[g] = tanh(logits[g][n*n+1]); logits bf16, row
+ * stride ld.  Replaces log_softmax + exp + tanh of OthelloNet.forward / PolicyValueNetwork.predict
+ * (othello.py:382, base.py:350-355). */
+int az_net_heads(const void* logits, int ld, int n, int64_t G, float* probs, float* value, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
