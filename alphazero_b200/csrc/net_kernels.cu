@@ -12,11 +12,13 @@
 //   * B operands (per-tap 32x32 weight tiles, BatchNorm folded in) sit in shared memory for the whole kernel;
 //   * accumulators (128 rows x 32 channels fp32) live in TMEM, double buffered; four epilogue warps read them with
 //     tcgen05.ld, add the folded bias, apply ReLU, round to bf16 and write the next layer's A operand;
-//   * conv1 (1 input channel, K = 9) runs on the CUDA cores straight from the bitboards.
+//   * conv1 (1 input channel, K = 9 padded to 16) is one more MMA per tile on a 9-tap im2col built straight from
+//     the bitboards (values -1/0/+1 are exact in bf16); its epilogue writes the zero ring that pads conv2.
 // Garbage computed on ring rows / tail rows is never read by a valid output ("trunk frame").
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/az_b200.h"
 #include "common.cuh"
@@ -31,10 +33,12 @@
 #define NET_BUF_BYTES (4 * NET_CHUNK_BYTES)        // 51200 B per activation buffer
 #define NET_TAP_BYTES 2048        // one 32x32 bf16 weight tile
 #define NET_LAYER_BYTES (9 * NET_TAP_BYTES)        // 18432
-#define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES)  // conv2..conv4
-#define NET_WBLOB_F32 (32 * 9 + 4 * 32)            // conv1 weights [32][9], biases of conv1..conv4
+#define NET_CONV1_TILE_BYTES 1024 // conv1 as one K=16 MMA: [2 chunks][32 co][8] bf16 (taps 0..8, zero padded)
+#define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES + NET_CONV1_TILE_BYTES)  // conv2..conv4 tiles, then the conv1 tile
+#define NET_WBLOB_F32 (4 * 32)                     // folded biases of conv1..conv4
 #define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
-#define NET_THREADS 160           // warps 0-3: conv1 + epilogue, warp 4: TMEM allocation + MMA issue
+#define NET_WORKERS 256           // warps 0-7: im2col + epilogue (two teams of 4 warps, one per TMEM stage)
+#define NET_THREADS 288           // + warp 8: TMEM allocation + MMA issue
 #define NET_TMEM_COLS 64          // two accumulator stages of 32 columns
 
 // shared memory map (bytes)
@@ -109,6 +113,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// True in exactly one (elected) lane of a converged warp.
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred px;\n\t"
+        "elect.sync _|px, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, px;\n\t"
+        "}" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
@@ -135,61 +151,42 @@ __device__ __forceinline__ void net_row_coords(int row, int F, int& b, int& r, i
     c = rem - r * F;
 }
 
-// conv1 + folded BN + ReLU on the CUDA cores, straight from the bitboards, for the rows handled by this thread.
-__device__ __forceinline__ void net_conv1(const NetTrunkParams& p, uint8_t* smem, int tid, int n_boards) {
-    const int F = p.n + 2, rows = p.boards_per_group * F * F;
-    const float* w1 = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // [32][9]
-    const float* b1 = w1 + 32 * 9;
-    const uint64_t* s_own = reinterpret_cast<const uint64_t*>(smem + SM_BOARDS);
-    const uint64_t* s_opp = s_own + 16;
-    for (int row = tid; row < rows; row += 128) {
-        int b, r, c;
-        net_row_coords(row, F, b, r, c);
-        uint32_t out[16];
-        const bool interior = (b < n_boards) && r >= 1 && r <= p.n && c >= 1 && c <= p.n;
-        if (interior) {
-            const uint64_t own = s_own[b], opp = s_opp[b];
-            float v[9];
+// 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one frame row:
+// 16 bf16 = taps 0..8 then zeros, written as the two 16-byte K chunks of the conv1 A operand.
+__device__ __forceinline__ void net_im2col_row(const NetTrunkParams& p, uint8_t* smem, int row, int n_boards) {
+    const int F = p.n + 2;
+    int b, r, c;
+    net_row_coords(row, F, b, r, c);
+    uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};     // taps 0..8 as bf16 pairs (tap 8 in the low half of w[4])
+    if (row < p.boards_per_group * F * F && b < n_boards && r >= 1 && r <= p.n && c >= 1 && c <= p.n) {
+        const uint64_t* s_own = reinterpret_cast<const uint64_t*>(smem + SM_BOARDS);
+        const uint64_t own = s_own[b], opp = s_own[16 + b];
 #pragma unroll
-            for (int t = 0; t < 9; ++t) {
-                const int ur = r - 1 + (t / 3 - 1), uc = c - 1 + (t % 3 - 1);
-                float x = 0.f;
-                if (ur >= 0 && ur < p.n && uc >= 0 && uc < p.n) {
-                    const int bit = ur * 8 + uc;
-                    x = (float)((int)((own >> bit) & 1ULL) - (int)((opp >> bit) & 1ULL));
-                }
-                v[t] = x;
+        for (int t = 0; t < 9; ++t) {
+            const int ur = r - 1 + (t / 3 - 1), uc = c - 1 + (t % 3 - 1);
+            uint32_t v = 0u;
+            if (ur >= 0 && ur < p.n && uc >= 0 && uc < p.n) {
+                const int bit = ur * 8 + uc;
+                v = ((own >> bit) & 1ULL) ? 0x3F80u : (((opp >> bit) & 1ULL) ? 0xBF80u : 0u);   // +1.0 / -1.0 bf16
             }
-#pragma unroll
-            for (int co = 0; co < 32; co += 2) {
-                float a0 = b1[co], a1 = b1[co + 1];
-#pragma unroll
-                for (int t = 0; t < 9; ++t) {
-                    a0 = fmaf(w1[co * 9 + t], v[t], a0);
-                    a1 = fmaf(w1[(co + 1) * 9 + t], v[t], a1);
-                }
-                out[co >> 1] = pack_bf16x2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) out[i] = 0u;       // zero ring = the padding of conv2
+            w[t >> 1] |= v << ((t & 1) * 16);
         }
-        uint8_t* dst = smem + SM_BUF_A + (NET_MARGIN + row) * 16;
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch)
-            *reinterpret_cast<uint4*>(dst + ch * NET_CHUNK_BYTES) =
-                make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
     }
+    uint8_t* dst = smem + SM_BUF_B + (NET_MARGIN + row) * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(dst + NET_CHUNK_BYTES) = make_uint4(w[4], 0u, 0u, 0u);
 }
 
+template <int NBOARD>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int F = p.n + 2, FF = F * F;
+    constexpr int F = NBOARD + 2, FF = F * F;
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
     const uint32_t bar_full0 = smem_u32(smem + SM_BARS), bar_empty0 = bar_full0 + 16;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SM_TMEM_PTR);
+    constexpr int MMA_WARP = NET_WORKERS / 32;
 
     // ---- one-time setup: zero the activation buffers, stage the weights, barriers, TMEM
     for (int i = tid; i < 2 * NET_BUF_BYTES / 16; i += NET_THREADS)
@@ -201,7 +198,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
         mbar_init(bar_empty0, 128); mbar_init(bar_empty0 + 8, 128);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {
+    if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(NET_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
@@ -211,98 +208,110 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
     const uint32_t idesc = umma_idesc_bf16_m128_n32();
-    const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES) + 32 * 9 + 32;  // b2,b3,b4
+    const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
+    const int team = warp >> 2;            // epilogue team = TMEM stage it serves (workers only)
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may read
+    const int m_out = p.n - 4;
 
-    uint32_t tile_it = 0;   // running tile counter (same sequence in the MMA thread and in the epilogue warps)
+    uint32_t tile_it = 0;   // running tile counter (even at every layer start: NET_TILES is even)
 
     for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
         const int board0 = grp * NB;
         const int n_boards = min(NB, p.G - board0);
-        // ---- stage the bitboards, conv1 -> buffer A
         if (tid < 16) {
             uint64_t* s_own = reinterpret_cast<uint64_t*>(smem + SM_BOARDS);
             s_own[tid] = tid < n_boards ? p.own[board0 + tid] : 0ULL;
             s_own[16 + tid] = tid < n_boards ? p.opp[board0 + tid] : 0ULL;
         }
         __syncthreads();
-        if (warp < 4) net_conv1(p, smem, tid, n_boards);
+        if (warp < MMA_WARP)
+            for (int row = tid; row < NET_ROWS; row += NET_WORKERS) net_im2col_row(p, smem, row, n_boards);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
-        if (p.debug && p.debug_layer == 1 && warp < 4) {
-            for (int row = tid; row < NET_ROWS; row += 128)
-                for (int ch = 0; ch < 4; ++ch)
-                    *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
-                        *reinterpret_cast<const uint4*>(smem + SM_BUF_A + ch * NET_CHUNK_BYTES + (NET_MARGIN + row) * 16);
-        }
 
-        // ---- conv2 (A -> B), conv3 (B -> A), conv4 (A -> features)
-        for (int layer = 0; layer < 3; ++layer) {
-            const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A));
-            uint8_t* dst = smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B);
-            const uint32_t wbase = smem_u32(smem + SM_W + layer * NET_LAYER_BYTES);
-            if (warp == 4) {
-                if (lane == 0) {
+        // ---- layer 0: conv1 (im2col in B -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
+        for (int layer = 0; layer < 4; ++layer) {
+            const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B));
+            uint8_t* dst = smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A);
+            if (warp == MMA_WARP) {
+                // The whole warp stays converged; one elected lane issues the MMAs of a tile back to back
+                // (descriptors differ from the per-layer base only by an immediate in the start-address field).
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t a_layer = umma_desc(src + NET_MARGIN * 16, NET_CHUNK_BYTES, 128);
+                const uint64_t b_layer = umma_desc(smem_u32(smem + SM_W) + (layer == 0 ? 3 * NET_LAYER_BYTES
+                                                                                      : (layer - 1) * NET_LAYER_BYTES),
+                                                   512, 128);
+                for (int t = 0; t < NET_TILES; ++t) {
+                    const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                    mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    for (int t = 0; t < NET_TILES; ++t) {
-                        const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
-                        mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
-                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        const uint32_t d_tmem = tmem_base + stage * 32u;
-                        uint32_t acc = 0u;
+                    const uint32_t d_tmem = tmem_base + stage * 32u;
+                    const uint64_t a_tile = a_layer + (uint64_t)(t * (NET_TILE_M * 16 / 16));
+                    if (elect_one()) {
+                        if (layer == 0) {
+                            umma_bf16(d_tmem, a_tile, b_layer, idesc, 0u);
+                        } else {
 #pragma unroll
-                        for (int tap = 0; tap < 9; ++tap) {
-                            const int shift = (tap / 3 - 1) * F + (tap % 3 - 1);
-                            const uint32_t a_row = src + (uint32_t)((NET_MARGIN + t * NET_TILE_M + shift) * 16);
+                            for (int tap = 0; tap < 9; ++tap) {
+                                const int shift = (tap / 3 - 1) * F + (tap % 3 - 1);
 #pragma unroll
-                            for (int kk = 0; kk < 2; ++kk) {
-                                const uint64_t da = umma_desc(a_row + kk * 2 * NET_CHUNK_BYTES, NET_CHUNK_BYTES, 128);
-                                const uint64_t db = umma_desc(wbase + tap * NET_TAP_BYTES + kk * 2 * 512, 512, 128);
-                                umma_bf16(d_tmem, da, db, idesc, acc);
-                                acc = 1u;
+                                for (int kk = 0; kk < 2; ++kk) {
+                                    const int64_t a_off = shift + kk * (2 * NET_CHUNK_BYTES / 16);
+                                    const uint64_t b_off = (uint64_t)((tap * NET_TAP_BYTES + kk * 2 * 512) / 16);
+                                    umma_bf16(d_tmem, (uint64_t)((int64_t)a_tile + a_off), b_layer + b_off, idesc,
+                                              (tap | kk) ? 1u : 0u);
+                                }
                             }
                         }
                         umma_commit(bar_full0 + 8 * stage);
                     }
+                    __syncwarp();
                 }
-                __syncwarp();
             } else {
-                const float* bias = bias_all + layer * 32;
-                for (int t = 0; t < NET_TILES; ++t) {
+                float bias[32];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 v = reinterpret_cast<const float4*>(bias_all + layer * 32)[i];
+                    bias[4 * i] = v.x; bias[4 * i + 1] = v.y; bias[4 * i + 2] = v.z; bias[4 * i + 3] = v.w;
+                }
+                for (int t = team; t < NET_TILES; t += 2) {
                     const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
                     mbar_wait(bar_full0 + 8 * stage, phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     uint32_t acc[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + stage * 32u, acc);
+                    tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * 32u, acc);
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     mbar_arrive(bar_empty0 + 8 * stage);
-                    const int row = t * NET_TILE_M + tid;           // tid = TMEM lane = row within the tile
+                    const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
+                    int b, r, c;
+                    net_row_coords(row, F, b, r, c);
+                    const bool in_group = row < NB * FF && b < n_boards;
                     uint32_t out[16];
 #pragma unroll
                     for (int co = 0; co < 32; co += 2)
                         out[co >> 1] = pack_bf16x2(fmaxf(__uint_as_float(acc[co]) + bias[co], 0.f),
                                                    fmaxf(__uint_as_float(acc[co + 1]) + bias[co + 1], 0.f));
-                    if (layer < 2) {
+                    if (layer == 0 && !(in_group && r >= 1 && r <= p.n && c >= 1 && c <= p.n)) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) out[i] = 0u;             // zero ring = the padding of conv2
+                    }
+                    if (layer < 3) {
                         uint8_t* d = dst + (NET_MARGIN + row) * 16;
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
                             *reinterpret_cast<uint4*>(d + ch * NET_CHUNK_BYTES) =
                                 make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
-                        if (p.debug && p.debug_layer == layer + 2)
+                        if (p.debug && p.debug_layer == layer + 1)
                             for (int ch = 0; ch < 4; ++ch)
                                 *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
                                     make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
-                    } else {
+                    } else if (in_group && r >= 3 && r < 3 + m_out && c >= 3 && c < 3 + m_out) {
                         // conv4: only frame positions 3..n-2 are outputs; features[board][pos*32 + co]
-                        int b, r, c;
-                        net_row_coords(row, F, b, r, c);
-                        const int m = p.n - 4;
-                        if (row < NB * FF && b < n_boards && r >= 3 && r < 3 + m && c >= 3 && c < 3 + m) {
-                            const int pos = (r - 3) * m + (c - 3);
-                            uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (m * m) + pos) * 32);
+                        const int pos = (r - 3) * m_out + (c - 3);
+                        uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (m_out * m_out) + pos) * 32);
 #pragma unroll
-                            for (int ch = 0; ch < 4; ++ch)
-                                f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
-                        }
+                        for (int ch = 0; ch < 4; ++ch)
+                            f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                     }
                 }
             }
@@ -314,7 +323,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 4)
+    if (warp == MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(NET_TMEM_COLS));
 }
 
@@ -370,7 +379,8 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int
         int dev = 0;
         AZ_CUDA_TRY(cudaGetDevice(&dev));
         AZ_CUDA_TRY(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
-        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
         attr_set = true;
     }
     NetTrunkParams p;
@@ -382,7 +392,8 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int
     p.debug_layer = debug ? debug_layer : 0;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM
-    k_net_trunk<<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    if (n == 8) k_net_trunk<8><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    else k_net_trunk<6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
     AZ_CHECK_LAUNCH("k_net_trunk");
     return AZ_OK;
 }

@@ -27,6 +27,8 @@ class NetEvaluator:
     every simulation step; exp(log_softmax) is taken in float32 (PolicyValueNetwork.predict, base.py:350-355).
     Re-create (or call `refresh()`) after the weights change (mcts.py:78-83 nn setter)."""
 
+    own_kernels_per_call = 0   # library kernels only
+
     def __init__(self, nn, tree, dtype=torch.bfloat16, use_cuda_graph: bool = True):
         self.tree = tree
         self.dtype = dtype

@@ -4,7 +4,7 @@ The weights are the reference module's own (any OthelloNet state_dict, alphazero
 only re-packs them for the kernels:
   * eval-mode BatchNorm folded into the preceding conv / linear layer (y = s*(Wx + b - mu) + beta, s = g/sqrt(v+eps));
   * conv2..conv4: per-tap 32x32 bf16 tiles in the tcgen05 K-major no-swizzle operand layout (csrc/net_kernels.cu);
-  * conv1 + all conv biases in float32;
+  * conv1 as one more K=16 bf16 tile (9 taps, zero padded); all conv biases in float32;
   * fc1 columns permuted from the reference's channel-major flatten (c*m*m + pos) to the trunk kernel's
     position-major feature order (pos*32 + c);
   * fc_probs and fc_value concatenated into one [n*n+2, 512] head.
@@ -29,28 +29,34 @@ def _fold_bn(weight, bias, bn):
     return w, b
 
 
+def _bf16_bits(t: torch.Tensor) -> np.ndarray:
+    return t.float().cpu().to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+
+
 def pack_trunk_weights(net) -> torch.Tensor:
-    """uint8 blob for az_net_trunk: [conv2|conv3|conv4 MMA tiles][conv1 w f32 [32][9]][b1..b4 f32 [4][32]]."""
+    """uint8 blob for az_net_trunk:
+    [conv2|conv3|conv4: 9 taps x [ci chunk 4][co 32][ci%8] bf16][conv1: [k chunk 2][co 32][8] bf16, taps 0..8 then 0]
+    [b1..b4 float32 [4][32]]  -- all with eval-mode BatchNorm folded in."""
     assert net.n_channels == 32
-    blob = np.zeros(int(_lib.lib().az_net_wblob_bytes()), dtype=np.uint8)
-    mma = np.zeros(3 * 9 * 4 * 32 * 8, dtype=np.uint16)      # [layer][tap][ci chunk][co][ci % 8] bf16 bits
-    mma = mma.reshape(3, 9, 4, 32, 8)
+    n_bytes = int(_lib.lib().az_net_wblob_bytes())
+    mma = np.zeros((3, 9, 4, 32, 8), dtype=np.uint16)
     biases = np.zeros((4, 32), dtype=np.float32)
-    w1, b1 = _fold_bn(net.conv1.weight, net.conv1.bias, net.bn1)
+    w1, b1 = _fold_bn(net.conv1.weight, net.conv1.bias, net.bn1)     # [co][1][kh][kw]
     biases[0] = b1.float().cpu().numpy()
+    c1 = np.zeros((32, 16), dtype=np.uint16)
+    c1[:, :9] = _bf16_bits(w1.reshape(32, 9))
+    c1 = c1.reshape(32, 2, 8).transpose(1, 0, 2)                      # [k chunk][co][k % 8]
     for li, (conv, bn) in enumerate(((net.conv2, net.bn2), (net.conv3, net.bn3), (net.conv4, net.bn4))):
-        w, b = _fold_bn(conv.weight, conv.bias, bn)          # [co][ci][kh][kw]
+        w, b = _fold_bn(conv.weight, conv.bias, bn)                   # [co][ci][kh][kw]
         biases[li + 1] = b.float().cpu().numpy()
-        wb = w.float().cpu().to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)   # bf16 bit patterns
+        wb = _bf16_bits(w)
         for tap in range(9):
             kh, kw = divmod(tap, 3)
-            t = wb[:, :, kh, kw]                              # [co][ci]
-            mma[li, tap] = t.reshape(32, 4, 8).transpose(1, 0, 2)   # -> [ci chunk][co][ci % 8]
-    n_mma = 3 * LAYER_BYTES
-    blob[:n_mma] = mma.reshape(-1).view(np.uint8)
-    f32 = np.concatenate([w1.float().cpu().numpy().reshape(32, 9).reshape(-1), biases.reshape(-1)]).astype(np.float32)
-    blob[n_mma:n_mma + f32.nbytes] = f32.view(np.uint8)
-    return torch.from_numpy(blob)
+            mma[li, tap] = wb[:, :, kh, kw].reshape(32, 4, 8).transpose(1, 0, 2)   # [ci chunk][co][ci % 8]
+    packed = np.concatenate([mma.reshape(-1).view(np.uint8), np.ascontiguousarray(c1).reshape(-1).view(np.uint8),
+                             biases.reshape(-1).view(np.uint8)])
+    assert packed.nbytes == n_bytes, (packed.nbytes, n_bytes)
+    return torch.from_numpy(packed.copy())
 
 
 class FusedOthelloEvaluator:
@@ -61,6 +67,8 @@ class FusedOthelloEvaluator:
         """True for the reference's Othello architecture (layer names / shapes of othello.py:341-359), n = 6 or 8."""
         from .games.othello import OthelloNet
         return isinstance(nn, OthelloNet) and nn.n in (6, 8) and nn.n_channels == 32
+
+    own_kernels_per_call = 2   # k_net_trunk + k_net_heads (replayed inside the CUDA graph)
 
     def __init__(self, nn, tree, use_cuda_graph: bool = True):
         self.tree = tree

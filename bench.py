@@ -203,6 +203,8 @@ def run_ours(args):
         barrier()
         sampler.start()
         launches0 = _lib.LAUNCH_CALLS
+        ev = engine.evaluator
+        graph0 = getattr(ev, "n_calls", 0)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record()
@@ -223,7 +225,10 @@ def run_ours(args):
             dist.all_reduce(stats, op=dist.ReduceOp.MAX)
             dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         return {"ms": float(stats[0]), "wall_ms": float(stats[1]), "sims": float(tot[0]), "moves": float(tot[1]),
-                "games": float(tot[2]), "clocks": clocks, "launches": _lib.LAUNCH_CALLS - launches0, "last": last}
+                "games": float(tot[2]), "clocks": clocks, "last": last,
+                # C-ABI launches issued from Python + our kernels replayed inside the evaluator's CUDA graph
+                "launches": (_lib.LAUNCH_CALLS - launches0)
+                + (getattr(ev, "n_calls", 0) - graph0) * getattr(ev, "own_kernels_per_call", 0)}
 
     dev_run = timed(step_device, args.steps)
     e2e_run = timed(step_e2e, args.steps)

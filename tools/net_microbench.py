@@ -1,0 +1,39 @@
+"""Times the pieces of the fused network forward in isolation (CUDA events, G leaf positions)."""
+import sys
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from alphazero_b200 import _lib
+from alphazero_b200.engine import TreeBatch
+from alphazero_b200.fused_net import FusedOthelloEvaluator
+from alphazero_b200.games.othello import OthelloNet
+
+G = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 200
+torch.manual_seed(0)
+net = OthelloNet(n=8)
+tree = TreeBatch(G, n=8, mode="neural", capacity=64)
+tree.leaf_own.random_(0, 2**62); tree.leaf_opp.copy_(~tree.leaf_own & torch.randint(0, 2**62, (G,), device="cuda"))
+ev = FusedOthelloEvaluator(net, tree)
+
+
+def timeit(fn, name):
+    for _ in range(10):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"{name:28s} {1000 * e0.elapsed_time(e1) / iters:8.2f} us")
+
+
+timeit(ev.trunk, "trunk (tcgen05)")
+timeit(lambda: torch._addmm_activation(ev.b1, ev.features, ev.w1t, out=ev.h1), "fc1+relu (cuBLASLt)")
+timeit(lambda: torch._addmm_activation(ev.b2, ev.h1, ev.w2t, out=ev.h2), "fc2+relu (cuBLASLt)")
+timeit(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cuBLASLt)")
+timeit(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, 8, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
+timeit(ev, "whole forward (CUDA graph)")
+timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
