@@ -60,14 +60,18 @@ def _worker(args):
     L = orc.lib()
     out = []
     for rep in range(repeats):
-        h = L.orc_mct_new(n, 1, 1, 0, seed * 1000003 + wid * 101 + rep, ctypes.cast(cb, ctypes.c_void_p), None)
-        L.orc_mct_set_dirichlet(h, 0.03, 0.25)
-        b, w = orc.start(n)
-        black, white, player = np.array([b], np.uint64), np.array([w], np.uint64), np.array([1], np.int8)
-        sims, t0 = 0, time.time()
+        sims, t0, game = 0, time.time(), 0
+        h = None
         for _ in range(moves):
-            if orc.terminal(black, white, player, n)[0][0]:
-                break
+            if h is None or orc.terminal(black, white, player, n)[0][0]:
+                if h is not None:
+                    L.orc_mct_free(h)
+                game += 1
+                h = L.orc_mct_new(n, 1, 1, 0, seed * 1000003 + wid * 101 + rep * 17 + game,
+                                  ctypes.cast(cb, ctypes.c_void_p), None)
+                L.orc_mct_set_dirichlet(h, 0.03, 0.25)
+                b, w = orc.start(n)
+                black, white, player = np.array([b], np.uint64), np.array([w], np.uint64), np.array([1], np.int8)
             L.orc_mct_search(h, int(black[0]), int(white[0]), int(player[0]), n_sim)
             sims += n_sim
             a = L.orc_mct_best_action(h)
