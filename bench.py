@@ -104,6 +104,23 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
+def ncu_traffic(kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, from the committed ncu --set full
+    capture (profiles/r1_ncu_full_summary.json, same command at n_sim=8); None when the capture is absent."""
+    path = os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")
+    if not os.path.isfile(path):
+        return None
+    vals = []
+    for k in json.load(open(path)):
+        if kernel_substr in k["kernel"]:
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            tot = 0.0
+            for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += (k[m]["value"] or 0.0) * scale.get(k[m]["unit"], 1.0)
+            vals.append(tot)
+    return sum(vals) / len(vals) if vals else None
+
+
 def cpu_baseline(args, seconds):
     """Oracle port of the reference's neural MCTS on all host cores (oracle/cpu_baseline.py), bounded sample."""
     import cpu_baseline as cb
@@ -258,7 +275,10 @@ def run_ours(args):
         "bound": "tensor", "kernel": f"policy-value network forward over the leaf batch (bf16, CUDA graph, path={args.net})",
         "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": tflops / peaks["bf16_tflops_sustained"], "peak_source": peaks["source"] + " (sustained: timed inside a long step)",
-        "traffic": None, "ms_per_launch": eval_ms, "share_of_step": t_eval / (t_eval + t_tree),
+        "traffic": ncu_traffic("k_net_trunk") if args.net == "fused" else None,
+        "traffic_note": "DRAM bytes per k_net_trunk launch (ncu --set full, profiles/r1_ncu_full_summary.txt); "
+                        "activations never leave shared memory, features stay in L2 for the fc GEMMs",
+        "ms_per_launch": eval_ms, "share_of_step": t_eval / (t_eval + t_tree),
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
@@ -268,7 +288,7 @@ def run_ours(args):
     tree_roofline = {"bound": "hbm", "kernel": "k_tree_step (backup + expand + select + encode)", "achieved": tree_gbs,
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
                      "ms_per_launch": tree_ms, "mean_depth": mean_depth, "bytes_per_sim": bytes_per_sim,
-                     "share_of_step": t_tree / (t_eval + t_tree), "traffic": None}
+                     "share_of_step": t_tree / (t_eval + t_tree), "traffic": ncu_traffic("k_tree_step")}
 
     if rank == 0:
         value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
