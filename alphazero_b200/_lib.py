@@ -11,13 +11,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "tree_kernels.cu", "net_kernels.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tree_kernels.cu", "net_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
 LEAF_IDLE, LEAF_NN, LEAF_PRIME, LEAF_ROLLOUT, LEAF_DRAW, LEAF_BLACK, LEAF_WHITE = range(7)
 STATUS_OVERFLOW, STATUS_DEPTH, STATUS_ILLEGAL = 1, 2, 4
 MODE_ROLLOUT, MODE_NEURAL = 0, 1
+GAME_OTHELLO, GAME_CONNECT4 = 0, 1
 NODE_EVAL, NODE_EXPANDED, NODE_NOISED = 1, 2, 4
 
 c_void_p, c_int, c_i64, c_u64, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_size_t
@@ -32,7 +33,8 @@ class AzTree(ctypes.Structure):
         ("seed", ctypes.c_uint64),
         ("G", ctypes.c_int32), ("n", ctypes.c_int32), ("capacity", ctypes.c_int32), ("max_depth", ctypes.c_int32),
         ("mode", ctypes.c_int32), ("tie_random", ctypes.c_int32), ("enc_dtype", ctypes.c_int32),
-        ("dirichlet_alpha", ctypes.c_float), ("dirichlet_eps", ctypes.c_float), ("reserved", ctypes.c_int32),
+        ("dirichlet_alpha", ctypes.c_float), ("dirichlet_eps", ctypes.c_float), ("game", ctypes.c_int32),
+        ("height", ctypes.c_int32), ("reserved", ctypes.c_int32),
     ]
 
 
@@ -51,6 +53,16 @@ SIGNATURES = {
     "az_othello_playouts": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_i64, c_i64, c_u64, c_u64, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_othello_encode": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_void_p, c_int, c_void_p]),
+    "az_connect4_legal": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p]),
+    "az_connect4_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_void_p]),
+    "az_connect4_terminal_score": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p,
+                                           c_void_p, c_void_p]),
+    "az_connect4_playouts": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_i64, c_u64, c_u64, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "az_connect4_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_int, c_void_p]),
+    "az_connect4_perft": (c_int, [c_u64, c_u64, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
+                                  ctypes.POINTER(ctypes.c_uint64), c_void_p]),
     "az_tree_reset": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p]),
     "az_tree_step": (c_int, [ctypes.POINTER(AzTree), c_int, c_int, c_int, c_void_p]),
     "az_tree_rollout": (c_int, [ctypes.POINTER(AzTree), c_void_p]),

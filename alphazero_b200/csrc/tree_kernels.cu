@@ -21,6 +21,7 @@
 #include "othello_bits.cuh"
 #include "philox.cuh"
 #include "playout.cuh"
+#include "rules.cuh"
 
 static_assert(sizeof(az_node) == 32, "az_node must be 32 bytes");
 
@@ -80,9 +81,6 @@ __device__ __forceinline__ NodeRec az_bcast_node(const NodeRec& r, int src) {
     return o;
 }
 
-// Network action index (r*n+c, pass = n*n) of a canvas action (r*8+c, pass = 64).
-__device__ __forceinline__ int az_net_index(int a, int n) { return a == AZ_PASS ? n * n : (a >> 3) * n + (a & 7); }
-
 __device__ __forceinline__ double az_warp_sum(double v) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(AZ_FULL, v, off);
@@ -100,10 +98,11 @@ __device__ __forceinline__ az_u32x4 az_draw4(uint64_t seed, uint32_t g, uint32_t
 }
 
 // Writes the network encoding of a side-relative position: +1 own, -1 opp, 0 empty, row-major n x n.
-__device__ __forceinline__ void az_encode_leaf(const az_tree& t, int g, int lane, uint64_t own, uint64_t opp) {
-    const int n = t.n, cells = n * n;
+__device__ __forceinline__ void az_encode_leaf(const az_tree& t, const az_dims& d, int g, int lane, uint64_t own,
+                                               uint64_t opp) {
+    const int cells = d.rows * d.cols;
     for (int k = lane; k < cells; k += 32) {
-        int bit = (k / n) * 8 + (k % n);
+        int bit = (k / d.cols) * 8 + (k % d.cols);
         float v = (float)((int)((own >> bit) & 1ULL) - (int)((opp >> bit) & 1ULL));
         if (t.enc_dtype == 0) reinterpret_cast<float*>(t.enc)[(size_t)g * cells + k] = v;
         else reinterpret_cast<__nv_bfloat16*>(t.enc)[(size_t)g * cells + k] = __float2bfloat16(v);
@@ -116,12 +115,13 @@ __device__ __forceinline__ void az_encode_leaf(const az_tree& t, int g, int lane
 // neural: P = probs[idx]/sum over the legal moves in float32, uniform when sum < 1e-6
 //         (OthelloNet.get_normalized_probs, othello.py:384-402);  rollout: P = 0 (mcts.py:152-154).
 // Returns the first child index (0 on pool overflow).
-__device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, az_node* nodes, int g, int lane,
-                                                      uint32_t leaf, uint64_t own, uint64_t opp, bool with_priors,
-                                                      uint32_t extra_flags, int* k_out) {
-    const uint64_t bmask = az_board_mask(t.n);
-    const uint64_t legal = az_legal_mask(own, opp, bmask);
-    const int k = legal ? __popcll(legal) : 1;
+template <int GAME>
+__device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az_dims& d, az_node* nodes, int g,
+                                                      int lane, uint32_t leaf, uint64_t own, uint64_t opp,
+                                                      bool with_priors, uint32_t extra_flags, int* k_out) {
+    using R = az_rules<GAME>;
+    const uint64_t legal = R::legal(own, opp, d);
+    const int k = R::n_actions(legal);
     *k_out = k;
     const uint32_t base = t.n_alloc[g];
     if (base + (uint32_t)k > (uint32_t)t.capacity) {
@@ -132,12 +132,12 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, az_node*
     int a0 = AZ_PASS, a1 = AZ_PASS;
     float p0 = 0.f, p1 = 0.f;
     const bool has0 = lane < k, has1 = lane + 32 < k;
-    if (has0) a0 = legal ? az_nth_set_bit(legal, lane) : AZ_PASS;
-    if (has1) a1 = az_nth_set_bit(legal, lane + 32);
+    if (has0) a0 = R::nth_action(legal, lane);
+    if (has1) a1 = R::nth_action(legal, lane + 32);
     if (with_priors) {
-        const float* pr = t.probs + (size_t)g * (t.n * t.n + 1);
-        if (has0) p0 = pr[az_net_index(a0, t.n)];
-        if (has1) p1 = pr[az_net_index(a1, t.n)];
+        const float* pr = t.probs + (size_t)g * R::action_size(d);
+        if (has0) p0 = pr[R::net_index(a0, d)];
+        if (has1) p1 = pr[R::net_index(a1, d)];
         float sum = az_warp_sum(p0 + p1);
         if (sum < 1e-6f) {
             p0 = p1 = (float)(1.0 / (double)k);
@@ -187,14 +187,15 @@ __device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int 
     __syncwarp();
 }
 
-__device__ __forceinline__ void az_finish(const az_tree& t, az_node* nodes, int g, int lane) {
+template <int GAME>
+__device__ __forceinline__ void az_finish(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane) {
     const int kind = t.leaf_kind[g];
     if (kind == AZ_LEAF_IDLE) return;
     const uint32_t leaf = t.leaf_node[g];
     const int leaf_player = t.leaf_player[g];
     if (kind == AZ_LEAF_NN || kind == AZ_LEAF_PRIME) {
         int k;
-        az_alloc_children(t, nodes, g, lane, leaf, t.leaf_own[g], t.leaf_opp[g], true, 0u, &k);
+        az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, t.leaf_own[g], t.leaf_opp[g], true, 0u, &k);
     }
     if (kind != AZ_LEAF_PRIME) {
         double outcome;
@@ -322,14 +323,16 @@ __device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_nod
     return cur.first_child + (uint32_t)win;
 }
 
-__device__ __forceinline__ int az_terminal_kind(uint64_t own, uint64_t opp, int player) {
-    int w = az_winner(own, opp, player);
+template <int GAME>
+__device__ __forceinline__ int az_terminal_kind(uint64_t own, uint64_t opp, int player, const az_dims& d) {
+    int w = az_rules<GAME>::winner(own, opp, player, d);
     return w == 0 ? AZ_LEAF_DRAW : (w > 0 ? AZ_LEAF_BLACK : AZ_LEAF_WHITE);
 }
 
 // MCT.__search_iter up to the evaluation (mcts.py:226-248): priming, noise, select_node; writes the leaf buffers.
-__device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int g, int lane) {
-    const uint64_t bmask = az_board_mask(t.n);
+template <int GAME>
+__device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane) {
+    using R = az_rules<GAME>;
     uint64_t own = t.root_own[g], opp = t.root_opp[g];
     int player = t.root_player[g];
     uint32_t event = t.rng_ctr[g];
@@ -352,8 +355,8 @@ __device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int 
         while (true) {
             // invariant: cur is the root or a node with N > 0
             if (!(cur.flags() & AZ_NODE_EXPANDED)) {
-                if (az_is_terminal(own, opp, bmask)) {          // mcts.py:146-147
-                    kind = t.mode == AZ_MODE_NEURAL ? az_terminal_kind(own, opp, player) : AZ_LEAF_ROLLOUT;
+                if (R::is_terminal(own, opp, d)) {              // mcts.py:146-147
+                    kind = t.mode == AZ_MODE_NEURAL ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_ROLLOUT;
                     break;
                 }
                 if (t.mode == AZ_MODE_NEURAL) {
@@ -364,14 +367,15 @@ __device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int 
                     }
                 } else {
                     int k;
-                    uint32_t base = az_alloc_children(t, nodes, g, lane, cur_idx, own, opp, false, AZ_NODE_EXPANDED, &k);
+                    uint32_t base = az_alloc_children<GAME>(t, d, nodes, g, lane, cur_idx, own, opp, false,
+                                                            AZ_NODE_EXPANDED, &k);
                     if (base == 0u) { kind = AZ_LEAF_ROLLOUT; break; }                   // overflow: evaluate here
                     // mcts.py:163-165: uniform pick among the fresh children
                     az_u32x4 r = az_draw4(t.seed, (uint32_t)g, event, 0u, 0x45585044u);
                     event += 1u;
                     int j = (int)az_bounded(r.x, (uint32_t)k);
                     NodeRec c = az_load_node(&nodes[base + j]);
-                    az_apply(own, opp, c.move());
+                    R::apply(own, opp, c.move(), d);
                     player = -player;
                     cur_idx = base + (uint32_t)j;
                     if (len < t.max_depth) { if (lane == 0) path[len] = cur_idx; ++len; }
@@ -382,7 +386,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int 
             NodeRec child;
             uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child);
             event += 1u;
-            az_apply(own, opp, child.move());
+            R::apply(own, opp, child.move(), d);
             player = -player;
             if (len >= t.max_depth) {
                 if (lane == 0) t.status[g] |= AZ_STATUS_DEPTH;
@@ -395,7 +399,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int 
             cur_idx = child_idx;
             if (cur.N == 0u) {                                  // mcts.py:143-144: first visit = the leaf
                 if (t.mode == AZ_MODE_NEURAL)
-                    kind = az_is_terminal(own, opp, bmask) ? az_terminal_kind(own, opp, player) : AZ_LEAF_NN;
+                    kind = R::is_terminal(own, opp, d) ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_NN;
                 else
                     kind = AZ_LEAF_ROLLOUT;
                 break;
@@ -411,16 +415,18 @@ __device__ __forceinline__ void az_select(const az_tree& t, az_node* nodes, int 
         t.path_len[g] = (uint32_t)len;
         t.rng_ctr[g] = event;
     }
-    if (t.mode == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t, g, lane, own, opp);
+    if (t.mode == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t, d, g, lane, own, opp);
 }
 
+template <int GAME>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
+    const az_dims d = az_rules<GAME>::dims(t.n, t.height);
     az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
-    if (do_finish) az_finish(t, nodes, g, lane);
-    if (do_select && t.sims_done[g] < (uint32_t)n_sim) az_select(t, nodes, g, lane);
+    if (do_finish) az_finish<GAME>(t, d, nodes, g, lane);
+    if (do_select && t.sims_done[g] < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane);
 }
 
 // ------------------------------------------------------------------------------------------------ misc kernels
@@ -438,16 +444,19 @@ __global__ void __launch_bounds__(256) k_tree_reset(az_tree t, const uint8_t* __
 }
 
 // One thread per game: a uniform random playout from the leaf board (MCT.rollout, mcts.py:173-180).
+template <int GAME>
 __global__ void __launch_bounds__(128) k_tree_rollout(az_tree t) {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= t.G || !t.active[g] || t.leaf_kind[g] != AZ_LEAF_ROLLOUT) return;
+    const az_dims d = az_rules<GAME>::dims(t.n, t.height);
     uint64_t own = t.leaf_own[g], opp = t.leaf_opp[g];
     int player = t.leaf_player[g];
     const uint32_t ev = t.rng_ctr[g];
-    az_random_playout(own, opp, player, az_board_mask(t.n), ((uint64_t)(uint32_t)g << 32) | (uint64_t)ev,
-                      t.seed ^ 0x524F4C4C4F555421ULL);
+    const uint64_t id = ((uint64_t)(uint32_t)g << 32) | (uint64_t)ev, seed = t.seed ^ 0x524F4C4C4F555421ULL;
+    if (GAME == AZ_GAME_OTHELLO) az_random_playout(own, opp, player, d.bmask, id, seed);
+    else az_random_playout_g<GAME>(own, opp, player, d, id, seed);
     t.rng_ctr[g] = ev + 1u;
-    t.value[g] = (float)az_winner(own, opp, player);
+    t.value[g] = (float)az_rules<GAME>::winner(own, opp, player, d);
 }
 
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_root_stats(az_tree t, int32_t* __restrict__ N,
@@ -477,13 +486,16 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_root_stats(az_tr
 }
 
 // get_action_probs (mcts.py:95-116) + the categorical draw of MCTSPlayer.get_move (players.py:184-189).
+template <int GAME>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t, const float* __restrict__ temp,
                                                                      uint8_t* __restrict__ action,
                                                                      float* __restrict__ pi) {
+    using R = az_rules<GAME>;
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
-    const int A = t.n * t.n + 1;
+    const az_dims d = R::dims(t.n, t.height);
+    const int A = R::action_size(d);
     const az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
     if (pi) for (int a = lane; a < A; a += 32) pi[(size_t)g * A + a] = 0.f;
     __syncwarp();
@@ -511,7 +523,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
         az_warp_argmax((double)(second ? n1 : n0), second ? lane + 32 : lane, lane < k, t.tie_random != 0, t.seed,
                        (uint32_t)g, event, &src);
         chosen_move = __shfl_sync(AZ_FULL, second ? m1 : m0, src);
-        if (lane == 0 && pi) pi[(size_t)g * A + az_net_index(chosen_move, t.n)] = 1.f;
+        if (lane == 0 && pi) pi[(size_t)g * A + R::net_index(chosen_move, d)] = 1.f;
     } else {
         const double inv = 1.0 / (double)T;
         double w0 = lane < k ? pow((double)n0, inv) : 0.0;
@@ -520,8 +532,8 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
         const double sum = az_warp_sum(w0 + w1);
         const double p0 = w0 / sum, p1 = w1 / sum;
         if (pi) {
-            if (lane < k) pi[(size_t)g * A + az_net_index(m0, t.n)] = (float)p0;
-            if (lane + 32 < k) pi[(size_t)g * A + az_net_index(m1, t.n)] = (float)p1;
+            if (lane < k) pi[(size_t)g * A + R::net_index(m0, d)] = (float)p0;
+            if (lane + 32 < k) pi[(size_t)g * A + R::net_index(m1, d)] = (float)p1;
         }
         // inverse-CDF draw in child order: inclusive prefix sum of p0 over lanes, then the 33rd child
         double c = p0;
@@ -556,16 +568,17 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
 // node, an exclusive warp scan of their child counts assigns the destination blocks, then the child blocks are
 // copied with coalesced 32-byte-per-lane loads/stores), so the root is always node 0 and a game's tree stays
 // dense no matter how long the game lasts.
+template <int GAME>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree t, const uint8_t* __restrict__ action) {
+    using R = az_rules<GAME>;
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
     const int a = action[g];
     if (a == 255) return;
-    const uint64_t bmask = az_board_mask(t.n);
+    const az_dims d = R::dims(t.n, t.height);
     uint64_t own = t.root_own[g], opp = t.root_opp[g];
-    const uint64_t legal = az_legal_mask(own, opp, bmask);
-    const bool ok = (a == AZ_PASS) ? (legal == 0ULL) : (a < 64 && ((legal >> a) & 1ULL));
+    const bool ok = R::is_legal(R::legal(own, opp, d), a);
     if (!ok) {
         if (lane == 0) t.status[g] |= AZ_STATUS_ILLEGAL;
         return;
@@ -616,10 +629,10 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree 
                 const uint32_t db = __shfl_sync(AZ_FULL, my_base, l);
                 for (uint32_t j = lane; j < kc; j += 32) {
                     const uint4* s = reinterpret_cast<const uint4*>(&src[sfc + j]);
-                    uint4* d = reinterpret_cast<uint4*>(&dst[db + j]);
+                    uint4* dq = reinterpret_cast<uint4*>(&dst[db + j]);
                     uint4 x = s[0], y = s[1];
-                    d[0] = x;
-                    d[1] = y;
+                    dq[0] = x;
+                    dq[1] = y;
                 }
             }
             n_dst += total;
@@ -627,7 +640,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree 
             __syncwarp();
         }
     }
-    az_apply(own, opp, a);
+    R::apply(own, opp, a, d);
     if (lane == 0) {
         t.root_own[g] = own;
         t.root_opp[g] = opp;
@@ -649,13 +662,12 @@ __device__ __forceinline__ uint64_t az_mix64(uint64_t z) {
 
 // One warp per position: lane a computes probs[a], a + 32, ...; see tests/hash_eval.py for the definition.
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_eval_hash(const uint64_t* __restrict__ own,
-                                                                   const uint64_t* __restrict__ opp, int n, int64_t G,
+                                                                   const uint64_t* __restrict__ opp, int A, int64_t G,
                                                                    uint64_t salt, float* __restrict__ probs,
                                                                    float* __restrict__ value) {
     const int64_t g = (int64_t)blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= G) return;
-    const int A = n * n + 1;
     const uint64_t h = az_mix64(own[g] * 0x9E3779B97F4A7C15ULL + az_mix64(opp[g] + 0xD1B54A32D192ED03ULL) + salt);
     for (int a = lane; a < A; a += 32) {
         uint64_t q = ((az_mix64(h + (uint64_t)a * 0x632BE59BD9B4E019ULL) >> 40) & 31ULL) + 1ULL;
@@ -667,7 +679,14 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_eval_hash(const uint6
 // ------------------------------------------------------------------------------------------------ C ABI
 
 static int az_check_tree(const az_tree* t) {
-    if (!t || !az_valid_n(t->n) || t->G <= 0 || t->capacity < 64 || t->max_depth < 2) return AZ_ERR_ARG;
+    if (!t || t->G <= 0 || t->capacity < 64 || t->max_depth < 2) return AZ_ERR_ARG;
+    if (t->game == AZ_GAME_OTHELLO) {
+        if (!az_valid_n(t->n)) return AZ_ERR_ARG;
+    } else if (t->game == AZ_GAME_CONNECT4) {
+        if (t->n < 4 || t->n > 8 || t->height < 4 || t->height > 8) return AZ_ERR_ARG;
+    } else {
+        return AZ_ERR_ARG;
+    }
     if (!t->nodes || !t->half || !t->n_alloc || !t->root_own || !t->root_opp || !t->root_player || !t->active ||
         !t->sims_done || !t->rng_ctr || !t->status || !t->leaf_node || !t->leaf_kind || !t->leaf_own ||
         !t->leaf_opp || !t->leaf_player || !t->path || !t->path_len)
@@ -679,6 +698,13 @@ static int az_check_tree(const az_tree* t) {
 }
 
 static inline int az_warp_grid(int64_t G) { return (int)((G + AZ_WARPS_PER_CTA - 1) / AZ_WARPS_PER_CTA); }
+
+// Launches kernel<GAME><<<grid, block, 0, stream>>>(args...) for the game of the tree.
+#define AZ_LAUNCH_GAME(game, kernel, grid, block, stream, ...)                                     \
+    do {                                                                                           \
+        if ((game) == AZ_GAME_OTHELLO) kernel<AZ_GAME_OTHELLO><<<grid, block, 0, stream>>>(__VA_ARGS__); \
+        else kernel<AZ_GAME_CONNECT4><<<grid, block, 0, stream>>>(__VA_ARGS__);                     \
+    } while (0)
 
 extern "C" int az_tree_reset(const az_tree* t, const uint8_t* mask, void* stream) {
     int rc = az_check_tree(t);
@@ -692,7 +718,8 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
     int rc = az_check_tree(t);
     if (rc) return rc;
     if (n_sim < 0) return AZ_ERR_ARG;
-    k_tree_step<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, n_sim, do_finish, do_select);
+    AZ_LAUNCH_GAME(t->game, k_tree_step, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, n_sim,
+                   do_finish, do_select);
     AZ_CHECK_LAUNCH("k_tree_step");
     return AZ_OK;
 }
@@ -700,7 +727,7 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
 extern "C" int az_tree_rollout(const az_tree* t, void* stream) {
     int rc = az_check_tree(t);
     if (rc) return rc;
-    k_tree_rollout<<<(t->G + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*t);
+    AZ_LAUNCH_GAME(t->game, k_tree_rollout, (t->G + 127) / 128, 128, (cudaStream_t)stream, *t);
     AZ_CHECK_LAUNCH("k_tree_rollout");
     return AZ_OK;
 }
@@ -717,7 +744,8 @@ extern "C" int az_tree_choose(const az_tree* t, const float* temp, uint8_t* acti
     int rc = az_check_tree(t);
     if (rc) return rc;
     if (!action) return AZ_ERR_ARG;
-    k_tree_choose<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, temp, action, pi);
+    AZ_LAUNCH_GAME(t->game, k_tree_choose, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, temp,
+                   action, pi);
     AZ_CHECK_LAUNCH("k_tree_choose");
     return AZ_OK;
 }
@@ -726,16 +754,18 @@ extern "C" int az_tree_advance(const az_tree* t, const uint8_t* action, void* st
     int rc = az_check_tree(t);
     if (rc) return rc;
     if (!action) return AZ_ERR_ARG;
-    k_tree_advance<<<az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(*t, action);
+    AZ_LAUNCH_GAME(t->game, k_tree_advance, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, action);
     AZ_CHECK_LAUNCH("k_tree_advance");
     return AZ_OK;
 }
 
-extern "C" int az_eval_hash(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t salt, float* probs,
-                            float* value, void* stream) {
-    if (!az_valid_n(n) || G < 0 || (G > 0 && (!own || !opp || !probs || !value))) return AZ_ERR_ARG;
+extern "C" int az_eval_hash(const uint64_t* own, const uint64_t* opp, int action_size, int64_t G, uint64_t salt,
+                            float* probs, float* value, void* stream) {
+    if (action_size < 1 || action_size > AZ_CANVAS_ACTIONS || G < 0 || (G > 0 && (!own || !opp || !probs || !value)))
+        return AZ_ERR_ARG;
     if (G == 0) return AZ_OK;
-    k_eval_hash<<<az_warp_grid(G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(own, opp, n, G, salt, probs, value);
+    k_eval_hash<<<az_warp_grid(G), AZ_WARPS_PER_CTA * 32, 0, (cudaStream_t)stream>>>(own, opp, action_size, G, salt, probs,
+                                                                                    value);
     AZ_CHECK_LAUNCH("k_eval_hash");
     return AZ_OK;
 }

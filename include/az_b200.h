@@ -30,6 +30,9 @@ extern "C" {
 #define AZ_ACTION_PASS 64
 #define AZ_CANVAS_ACTIONS 65 /* 64 cells + pass on the 8-wide canvas */
 
+#define AZ_GAME_OTHELLO 0  /* alphazero/games/othello.py */
+#define AZ_GAME_CONNECT4 1 /* alphazero/games/connect4.py */
+
 /* ABI version, bumped when a signature changes. */
 int az_abi_version(void);
 /* Text of the last CUDA error seen by this library on the calling thread ("" if none). */
@@ -82,6 +85,46 @@ int az_othello_playouts(const uint64_t* own, const uint64_t* opp, const int8_t* 
 int az_othello_encode(const uint64_t* own, const uint64_t* opp, int n, int64_t G, void* out, int dtype,
                       void* stream);
 
+/* ---------------------------------------------------------------- Connect4 board kernels --------------- */
+/* Same canvas (bit r*8+c, row 0 = top of the reference's grid), width x height boards with 4 <= width, height <= 8;
+ * an action is a column index 0..width-1, there is no pass. */
+
+/* legal[g] = bit mask over COLUMN indices of the playable columns (free_rows[c] > 0).
+ * Replaces Connect4Board.get_moves / is_legal_move, alphazero/games/connect4.py:145-162. */
+int az_connect4_legal(const uint64_t* own, const uint64_t* opp, int width, int height, int64_t G, uint64_t* legal,
+                      void* stream);
+
+/* Drops a disc of the side to move in column action[g] and swaps sides (in-place allowed).
+ * status[g] = 0 ok, 1 illegal (column full or out of range; board unchanged) -- the reference raises ValueError.
+ * Replaces Connect4Board.play_move, alphazero/games/connect4.py:170-182. */
+int az_connect4_apply(const uint64_t* own, const uint64_t* opp, const int8_t* player, const uint8_t* action,
+                      int width, int height, int64_t G, uint64_t* out_own, uint64_t* out_opp, int8_t* out_player,
+                      uint8_t* status, void* stream);
+
+/* terminal[g] = 1 iff a colour has four aligned discs or the board is full; score[g] = #own - #opp (get_score());
+ * winner[g] = absolute id of the aligned colour, 0 for a draw (meaningful when terminal).
+ * Replaces __get_game_status / is_game_over / get_winner / get_score, alphazero/games/connect4.py:137-139, 184-258. */
+int az_connect4_terminal_score(const uint64_t* own, const uint64_t* opp, const int8_t* player, int width,
+                               int height, int64_t G, uint8_t* terminal, int8_t* score, int8_t* winner,
+                               void* stream);
+
+/* Uniform random playouts, same random stream convention as az_othello_playouts (k-th playable column in ascending
+ * order).  Replaces MCT.rollout + Connect4Board.get_random_move, mcts.py:173-180, connect4.py:164-168. */
+int az_connect4_playouts(const uint64_t* own, const uint64_t* opp, const int8_t* player, int width, int height,
+                         int64_t n_roots, int64_t per_root, uint64_t seed, uint64_t first_id,
+                         uint64_t* final_black, uint64_t* final_white, int8_t* winner, uint8_t* plies, void* stream);
+
+/* Network input player*grid, row-major [G][height][width] (Connect4Net.forward then VIEWS these height*width values
+ * as (width, height), connect4.py:399 -- a reinterpretation, not a transpose, reproduced by keeping this order).
+ * dtype: 0 = float32, 1 = bfloat16. */
+int az_connect4_encode(const uint64_t* own, const uint64_t* opp, int width, int height, int64_t G, void* out,
+                       int dtype, void* stream);
+
+/* perft from one position (host values): a finished game counts as one leaf.  Same scheme and scratch contract as
+ * az_othello_perft.  SYNCHRONOUS. */
+int az_connect4_perft(uint64_t own_h, uint64_t opp_h, int width, int height, int depth, int dfs_depth,
+                      uint64_t* scratch, size_t scratch_u64, uint64_t* count_h, void* stream);
+
 /* ---------------------------------------------------------------- MCTS tree kernels -------------------- */
 
 /* One tree node, 32 bytes, 32-byte aligned: a child block is a contiguous run of these, so a warp reads a whole
@@ -95,7 +138,7 @@ typedef struct az_node {
     uint32_t N;
     uint32_t first_child; /* index of the first child inside the game's pool half; 0 = no child block */
     uint8_t n_children;
-    uint8_t move;         /* action that led here (0..63, 64 = pass) */
+    uint8_t move;         /* action that led here (Othello: 0..63, 64 = pass; Connect4: column) */
     uint8_t flags;        /* AZ_NODE_* */
     uint8_t reserved0;
     uint32_t reserved1[2];
@@ -140,12 +183,12 @@ typedef struct az_tree {
     int8_t* leaf_player;   /* [G] */
     uint32_t* path;        /* [G][max_depth] node indices root..leaf */
     uint32_t* path_len;    /* [G] */
-    void* enc;             /* [G][n*n] network input, player*grid row-major (written by select) */
-    float* probs;          /* [G][n*n+1] network probabilities exp(log_softmax), pass last (read by finish) */
+    void* enc;             /* [G][rows*cols] network input, player*grid row-major (written by select) */
+    float* probs;          /* [G][A] network probabilities exp(log_softmax); A = n*n+1 (pass last) / width */
     float* value;          /* [G] neural: network value, side to move's view; rollout: absolute winner id */
     uint64_t seed;
     int32_t G;
-    int32_t n;             /* board size 4/6/8 */
+    int32_t n;             /* Othello: board size 4/6/8; Connect4: width (columns) */
     int32_t capacity;      /* nodes per half */
     int32_t max_depth;
     int32_t mode;          /* AZ_MODE_* */
@@ -153,6 +196,8 @@ typedef struct az_tree {
     int32_t enc_dtype;     /* 0 float32, 1 bfloat16 */
     float dirichlet_alpha; /* <= 0: no noise */
     float dirichlet_eps;
+    int32_t game;          /* AZ_GAME_* */
+    int32_t height;        /* Connect4: rows; ignored for Othello */
     int32_t reserved;
 } az_tree;
 
@@ -189,8 +234,8 @@ int az_tree_choose(const az_tree* t, const float* temp, uint8_t* action, float* 
 int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream);
 
 /* Deterministic hash evaluator (test double for PolicyValueNetwork.evaluate, see tests/hash_eval.py):
- * probs[g][a] = q/4096, value[g] in {-256..255}/256 from (own, opp, salt). */
-int az_eval_hash(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t salt, float* probs,
+ * probs[g][a] = q/4096 for a < action_size, value[g] in {-256..255}/256 from (own, opp, salt). */
+int az_eval_hash(const uint64_t* own, const uint64_t* opp, int action_size, int64_t G, uint64_t salt, float* probs,
                  float* value, void* stream);
 
 /* ---------------------------------------------------------------- fused network kernels ---------------- */

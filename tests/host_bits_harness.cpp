@@ -31,3 +31,25 @@ void hb_philox(const uint32_t* c, const uint32_t* k, uint32_t* o) {
     o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = r.w;
 }
 }
+
+// ---- Connect4 (connect4_bits.cuh / rules.cuh host side)
+#include "../include/az_b200.h"
+#include "../alphazero_b200/csrc/rules.cuh"
+
+extern "C" {
+void hb_c4_legal(const uint64_t* own, const uint64_t* opp, int width, int64_t G, uint64_t* legal) {
+    for (int64_t g = 0; g < G; ++g) legal[g] = az_c4_legal_cols(own[g], opp[g], width);
+}
+void hb_c4_apply(uint64_t* own, uint64_t* opp, const uint8_t* action, int width, int height, int64_t G) {
+    az_dims d = az_rules<AZ_GAME_CONNECT4>::dims(width, height);
+    for (int64_t g = 0; g < G; ++g) az_rules<AZ_GAME_CONNECT4>::apply(own[g], opp[g], action[g], d);
+}
+void hb_c4_terminal(const uint64_t* own, const uint64_t* opp, const int8_t* player, int width, int height, int64_t G,
+                    uint8_t* term, int8_t* winner) {
+    az_dims d = az_rules<AZ_GAME_CONNECT4>::dims(width, height);
+    for (int64_t g = 0; g < G; ++g) {
+        term[g] = az_rules<AZ_GAME_CONNECT4>::is_terminal(own[g], opp[g], d);
+        winner[g] = (int8_t)az_rules<AZ_GAME_CONNECT4>::winner(own[g], opp[g], player[g], d);
+    }
+}
+}

@@ -41,6 +41,14 @@ def lib():
         L.orc_mct_root_stats.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orc_mct_best_action.argtypes = [vp]
         L.orc_mct_best_action.restype = i32
+        L.orc_connect4_legal.argtypes = [vp, vp, vp, i32, i32, i64, vp]
+        L.orc_connect4_apply.argtypes = [vp, vp, vp, vp, i32, i32, i64, vp, vp, vp, vp]
+        L.orc_connect4_terminal.argtypes = [vp, vp, vp, i32, i32, i64, vp, vp, vp]
+        L.orc_connect4_perft.restype = u64
+        L.orc_connect4_perft.argtypes = [u64, u64, i32, i32, i32, i32]
+        L.orc_connect4_playouts.argtypes = [vp, vp, vp, i32, i32, i64, i64, u64, u64, vp, vp, vp, vp]
+        L.orc_mct_new_connect4.restype = vp
+        L.orc_mct_new_connect4.argtypes = [i32, i32, i32, i32, u64, u64, vp, vp]
         _lib = L
     return _lib
 
@@ -98,11 +106,52 @@ def hash_eval(own, opp, action_size, salt):
     return probs, float(v[0])
 
 
-class OracleMCT:
-    """Sequential pointer-tree MCT of the oracle (restates alphazero/mcts.py)."""
+# ---- Connect4 (boards are absolute black/white bitboards on the canvas, bit r*8+c, row 0 = top) ----
 
-    def __init__(self, n, mode="neural", tie_random=False, salt=0, seed=0, dirichlet=None):
-        self.h = lib().orc_mct_new(n, 1 if mode == "neural" else 0, int(tie_random), salt, seed, None, None)
+def c4_legal(black, white, player, width, height):
+    out = np.zeros(len(black), np.uint64)
+    lib().orc_connect4_legal(P(black), P(white), P(player), width, height, len(black), P(out))
+    return out
+
+
+def c4_apply(black, white, player, action, width, height):
+    G = len(black)
+    ob, ow = np.zeros(G, np.uint64), np.zeros(G, np.uint64)
+    op, st = np.zeros(G, np.int8), np.zeros(G, np.uint8)
+    lib().orc_connect4_apply(P(black), P(white), P(player), P(action), width, height, G, P(ob), P(ow), P(op), P(st))
+    return ob, ow, op, st
+
+
+def c4_terminal(black, white, player, width, height):
+    G = len(black)
+    t, s, w = np.zeros(G, np.uint8), np.zeros(G, np.int8), np.zeros(G, np.int8)
+    lib().orc_connect4_terminal(P(black), P(white), P(player), width, height, G, P(t), P(s), P(w))
+    return t, s, w
+
+
+def c4_perft(width, height, depth, black=0, white=0, player=1):
+    return int(lib().orc_connect4_perft(black, white, player, width, height, depth))
+
+
+def c4_playouts(black, white, player, width, height, per_root, seed, first_id=0):
+    T = len(black) * per_root
+    fb, fw = np.zeros(T, np.uint64), np.zeros(T, np.uint64)
+    win, pl = np.zeros(T, np.int8), np.zeros(T, np.uint8)
+    lib().orc_connect4_playouts(P(black), P(white), P(player), width, height, len(black), per_root, seed, first_id,
+                                P(fb), P(fw), P(win), P(pl))
+    return fb, fw, win, pl
+
+
+class OracleMCT:
+    """Sequential pointer-tree MCT of the oracle (restates alphazero/mcts.py).  `n` = Othello board size, or
+    (width, height) with game="connect4"."""
+
+    def __init__(self, n, mode="neural", tie_random=False, salt=0, seed=0, dirichlet=None, game="othello"):
+        if game == "connect4":
+            self.h = lib().orc_mct_new_connect4(n[0], n[1], 1 if mode == "neural" else 0, int(tie_random), salt, seed,
+                                                None, None)
+        else:
+            self.h = lib().orc_mct_new(n, 1 if mode == "neural" else 0, int(tie_random), salt, seed, None, None)
         if dirichlet:
             lib().orc_mct_set_dirichlet(self.h, dirichlet[0], dirichlet[1])
 
