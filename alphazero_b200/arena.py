@@ -15,6 +15,7 @@ from .base import Board, Player
 from .engine import TreeBatch
 from .evaluators import NetEvaluator
 from .fused_net import FusedOthelloEvaluator
+from .gamespec import spec_of
 from .players import AlphaZeroPlayer, MCTSPlayer, RandomPlayer
 
 
@@ -26,7 +27,7 @@ def _empty_stats() -> dict:
 class _BatchedSide:
     """Device-side move rule of one arena player for G concurrent games."""
 
-    def __init__(self, player: Player, G: int, n: int, seed: int):
+    def __init__(self, player: Player, G: int, spec, seed: int):
         self.player = player
         self.tree = None
         self.evaluator = None
@@ -35,7 +36,7 @@ class _BatchedSide:
         if isinstance(player, AlphaZeroPlayer):
             nn = player.mct.nn
             self.n_sim = player.n_sim
-            self.tree = TreeBatch(G, n=n, mode="neural", n_sim_hint=self.n_sim, seed=seed, tie_random=True,
+            self.tree = TreeBatch(G, n=spec, mode="neural", n_sim_hint=self.n_sim, seed=seed, tie_random=True,
                                   dirichlet_alpha=player.mct.dirichlet_alpha,
                                   dirichlet_epsilon=player.mct.dirichlet_epsilon, enc_dtype=torch.bfloat16)
             if FusedOthelloEvaluator.supports(nn):
@@ -45,14 +46,14 @@ class _BatchedSide:
                 self.evaluator = NetEvaluator(nn, self.tree)
         elif isinstance(player, MCTSPlayer):
             self.n_sim = player.n_sim
-            self.tree = TreeBatch(G, n=n, mode="rollout", n_sim_hint=self.n_sim, seed=seed, tie_random=True)
+            self.tree = TreeBatch(G, n=spec, mode="rollout", n_sim_hint=self.n_sim, seed=seed, tie_random=True)
         elif not isinstance(player, RandomPlayer):
             raise ValueError(f"{player} has no batched device implementation (supported: MCTSPlayer, "
                              "AlphaZeroPlayer, RandomPlayer); use play_games instead")
         if self.tree is not None and self.n_sim is None:
             raise ValueError("batched arena needs n_sim players (compute_time is wall-clock bound per game)")
 
-    def moves(self, own, opp, player, mask, n) -> torch.Tensor:
+    def moves(self, own, opp, player, mask, spec) -> torch.Tensor:
         """Actions (uint8, 255 where mask is False) for the games in `mask`."""
         G = own.numel()
         if self.tree is not None:
@@ -60,12 +61,11 @@ class _BatchedSide:
             self.tree.search(self.n_sim, self.evaluator, check=False)
             action, _ = self.tree.choose(None)        # temp = 0: MCTSPlayer.get_move default (players.py:161)
             return torch.where(mask, action, torch.full_like(action, 255))
-        legal = bo.legal(own, opp, n)
-        bits = ((legal.unsqueeze(1) >> torch.arange(64, device=own.device)) & 1).to(torch.float32)   # [G, 64]
+        bits, no_move_action = spec.legal_action_bits(spec.legal(own, opp))                         # [G, 64]
         has = bits.sum(dim=1) > 0
-        bits[~has, 0] = 1.0                                # dummy support for pass rows
+        bits[~has, 0] = 1.0                                # dummy support for rows without a move (Othello: pass)
         pick = torch.multinomial(bits, 1, generator=self.gen).squeeze(1).to(torch.uint8)
-        action = torch.where(has, pick, torch.full_like(pick, bo.PASS))
+        action = torch.where(has, pick, torch.full_like(pick, no_move_action))
         return torch.where(mask, action, torch.full_like(action, 255))
 
     def observe(self, action, live) -> None:
@@ -151,13 +151,11 @@ class Arena:
         the games is started by player 2, the second half by player 1 (the reference gives even-numbered workers
         start_player = 2, odd ones 1).  `n_process` only takes part in the reference's argument checks."""
         self._check_inputs(n_rounds, n_process if n_process is not None else 2)
-        if self.game != "othello":
-            raise NotImplementedError("batched arena: Othello boards")
-        n, G = self.board.n, n_rounds
+        spec, G = spec_of(self.board), n_rounds      # NotImplementedError for games without device rules
         seed = int(np.random.randint(1 << 31)) if seed is None else seed
-        sides = (_BatchedSide(self.player1, G, n, seed), _BatchedSide(self.player2, G, n, seed + 1))
+        sides = (_BatchedSide(self.player1, G, spec, seed), _BatchedSide(self.player2, G, spec, seed + 1))
         dev = torch.device("cuda")
-        black, white = bo.start_position(n)
+        black, white = spec.start_position()
         own = torch.full((G,), bo.to_i64(black), dtype=torch.int64, device=dev)
         opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64, device=dev)
         player = torch.ones(G, dtype=torch.int8, device=dev)
@@ -165,20 +163,20 @@ class Arena:
         # who moves: black (+1) is the starter
         live = torch.ones(G, dtype=torch.bool, device=dev)
         start = time()
-        for ply in range(2 * n * n + 2):
+        for ply in range(spec.max_plies + 2):
             starter_moves = player == 1
             p1_to_move = live & (starter_moves != p2_starts)
             p2_to_move = live & ~p1_to_move
-            a1 = sides[0].moves(own, opp, player, p1_to_move, n)
-            a2 = sides[1].moves(own, opp, player, p2_to_move, n)
+            a1 = sides[0].moves(own, opp, player, p1_to_move, spec)
+            a2 = sides[1].moves(own, opp, player, p2_to_move, spec)
             action = torch.where(p1_to_move, a1, a2)
             for s in sides:
                 s.observe(action, live)
-            own2, opp2, player2, st = bo.apply(own, opp, player, torch.where(live, action, torch.full_like(action, bo.PASS)), n)
+            own2, opp2, player2, st = spec.apply(own, opp, player, torch.where(live, action, torch.full_like(action, bo.PASS)))
             if bool((st[live] != 0).any().item()):
                 raise RuntimeError("batched arena produced an illegal move")
             own = torch.where(live, own2, own); opp = torch.where(live, opp2, opp); player = torch.where(live, player2, player)
-            term, _, _ = bo.terminal_score(own, opp, player, n)
+            term, _, _ = spec.terminal_score(own, opp, player)
             live = live & (term == 0)
             if not bool(live.any().item()):
                 break
@@ -186,7 +184,7 @@ class Arena:
             if s.tree is not None:
                 s.tree.status.bitwise_and_(~4)   # inactive games never advance; illegal-move bits cannot be set here
                 s.tree.check_status()
-        _, score, winner = bo.terminal_score(own, opp, player, n)
+        _, score, winner = spec.terminal_score(own, opp, player)
         score, winner, p2s = score.abs().cpu().numpy(), winner.cpu().numpy(), p2_starts.cpu().numpy()
         if verbose:
             print(f"Total time = {time() - start:.2f} seconds")

@@ -38,4 +38,4 @@ def gather_samples(batch: SampleBatch, episode_offset: int = 0, group=None) -> S
 
     ep = batch.episode_idx + int(episode_offset)
     return SampleBatch(gather(batch.own), gather(batch.opp), gather(batch.pi), gather(batch.z), gather(ep),
-                       gather(batch.move_idx), batch.n)
+                       gather(batch.move_idx), batch.n, batch.rows)

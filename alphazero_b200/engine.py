@@ -18,21 +18,24 @@ import numpy as np
 import torch
 
 from . import _lib
-from .boardops import PASS, _ptr, _stream, start_position, to_i64
+from .boardops import PASS, _ptr, _stream, to_i64
+from .gamespec import as_spec
 
 NODE_BYTES = 32
 
 
 class TreeBatch:
-    def __init__(self, G: int, n: int = 8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
+    def __init__(self, G: int, n=8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
                  device="cuda", seed: int = 0, tie_random: bool = True, dirichlet_alpha: float = None,
                  dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128):
         if not torch.cuda.is_available():
             raise RuntimeError("TreeBatch needs a CUDA device (alphazero_b200 has no CPU path)")
         if mode not in ("neural", "rollout"):
             raise ValueError(f"unknown mode {mode}")
-        self.G, self.n, self.mode = int(G), int(n), mode
-        self.A = n * n + 1
+        # `n`: Othello board size, or a GameSpec (gamespec.OthelloSpec / Connect4Spec)
+        self.spec = as_spec(n)
+        self.G, self.n, self.mode = int(G), self.spec.n, mode
+        self.A = self.spec.action_size
         self.device = torch.device(device)
         if capacity is None:
             # per search at most (n_sim + 1) child blocks are added; 4x head-room over an average branching of ~12
@@ -61,7 +64,7 @@ class TreeBatch:
         self.path = z(G * self.max_depth, dtype=torch.int32)
         self.path_len = z(G, dtype=torch.int32)
         self.enc_dtype = enc_dtype
-        self.enc = z(G, n, n, dtype=enc_dtype)
+        self.enc = z(G, self.spec.rows, self.spec.cols, dtype=enc_dtype)
         self.probs = z(G, self.A, dtype=torch.float32)
         self.value = z(G, dtype=torch.float32)
         self.n_rollouts = 0
@@ -75,6 +78,7 @@ class TreeBatch:
             setattr(d, name, getattr(self, name).data_ptr())
         d.seed = int(seed) & ((1 << 64) - 1)
         d.G, d.n, d.capacity, d.max_depth = self.G, self.n, self.capacity, self.max_depth
+        d.game, d.height = self.spec.game_id, self.spec.height
         d.mode = _lib.MODE_NEURAL if mode == "neural" else _lib.MODE_ROLLOUT
         d.tie_random = 1 if tie_random else 0
         d.enc_dtype = {torch.float32: 0, torch.bfloat16: 1}[enc_dtype]
@@ -101,7 +105,7 @@ class TreeBatch:
     # ------------------------------------------------------------------ roots
     def reset_roots(self, mask: torch.Tensor = None) -> None:
         """Start position + fresh trees for the masked games (board.reset() + player.reset())."""
-        black, white = start_position(self.n)
+        black, white = self.spec.start_position()
         if mask is None:
             self.root_own.fill_(to_i64(black)); self.root_opp.fill_(to_i64(white)); self.root_player.fill_(1)
             self.active.fill_(1)

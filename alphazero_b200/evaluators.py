@@ -14,7 +14,7 @@ class HashEvaluator:
         self.n_calls = 0
 
     def __call__(self, tree) -> None:
-        _lib.check(_lib.lib().az_eval_hash(_ptr(tree.leaf_own), _ptr(tree.leaf_opp), tree.n, tree.G, self.salt,
+        _lib.check(_lib.lib().az_eval_hash(_ptr(tree.leaf_own), _ptr(tree.leaf_opp), tree.A, tree.G, self.salt,
                                            _ptr(tree.probs), _ptr(tree.value), _stream()), "az_eval_hash")
         self.n_calls += 1
 

@@ -15,6 +15,7 @@ from .base import Board, PolicyValueNetwork, TreeEval
 from .engine import TreeBatch
 from .evaluators import NetEvaluator
 from .fused_net import FusedOthelloEvaluator
+from .gamespec import OthelloSpec, spec_of
 from .utils import fair_max
 
 
@@ -73,6 +74,7 @@ class MCT:
         self._evaluator = None
         self._pending = []      # change_root calls made before the first search (no device tree yet)
         self._n = None
+        self._spec = None
 
     # ---- attributes the reference's callers set directly (players.py:213-215, trainer.py:387) -------------
     @property
@@ -108,15 +110,13 @@ class MCT:
 
     # ---- device tree --------------------------------------------------------------------------------------
     def _ensure_tree(self, board: Board) -> None:
-        if getattr(board, "game", None) != "othello":
-            raise NotImplementedError("the B200 MCT supports Othello boards")
-        n = board.n
-        if self._tree is None or self._n != n:
+        spec = spec_of(board)    # NotImplementedError for games without device rules
+        if self._tree is None or self._spec != spec:
             mode = "neural" if self.eval_method == TreeEval.NEURAL else "rollout"
-            self._tree = TreeBatch(1, n=n, mode=mode, capacity=self.CAPACITY, seed=int(np.random.randint(1 << 31)),
+            self._tree = TreeBatch(1, n=spec, mode=mode, capacity=self.CAPACITY, seed=int(np.random.randint(1 << 31)),
                                    tie_random=self.TIE_RANDOM, dirichlet_alpha=self._dirichlet_alpha,
                                    dirichlet_epsilon=self._dirichlet_epsilon, enc_dtype=torch.bfloat16)
-            self._n = n
+            self._spec, self._n = spec, spec.n
             self._evaluator = None
             self._pending = []
         own, opp = (board.black, board.white) if board.player == 1 else (board.white, board.black)
@@ -145,7 +145,7 @@ class MCT:
         per game, players.py:151-152, 228-234); the tree itself starts fresh."""
         if old is None or old._tree is None or old.eval_method != self.eval_method:
             return
-        self._tree, self._n = old._tree, old._n
+        self._tree, self._n, self._spec = old._tree, old._n, old._spec
         self._tree.set_dirichlet(self._dirichlet_alpha, self._dirichlet_epsilon)
         if old._nn is self._nn:
             self._evaluator = old._evaluator
@@ -168,7 +168,7 @@ class MCT:
         neural = self.eval_method == TreeEval.NEURAL
         for a in range(65):
             if N[a] >= 0:
-                mv = action_to_move(a, self._n)
+                mv = self._spec.action_to_move(a)
                 node.children[mv] = Node(move=mv, parent=node, prob=np.float32(P[a]) if neural else None,
                                          N=int(N[a]), Q=float(Q[a]))
         return node
@@ -194,7 +194,7 @@ class MCT:
         """mcts.py:118-125: keep the subtree of `move` (played on the device root board as well)."""
         if self._tree is None:
             return                      # nothing searched yet: the next search starts from the board it is given
-        a = move_to_action(move, self._n)
+        a = self._spec.move_to_action(move)
         self._tree.advance(torch.tensor([a], dtype=torch.uint8))
         st = int(self._tree.status.item())
         if st & 4:

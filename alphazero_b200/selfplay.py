@@ -14,6 +14,7 @@ from . import boardops as bo
 from .engine import TreeBatch
 from .evaluators import NetEvaluator
 from .fused_net import FusedOthelloEvaluator
+from .gamespec import as_spec
 from .schedulers import TEMP_SCHEDULERS
 
 
@@ -23,27 +24,29 @@ class SampleBatch:
     side, i.e. state*player with own = +1; pi is in network order (pass last); z = winner * player in {-1,0,1}."""
     own: torch.Tensor         # int64 [S]
     opp: torch.Tensor         # int64 [S]
-    pi: torch.Tensor          # float32 [S, n*n+1]
+    pi: torch.Tensor          # float32 [S, action_size]
     z: torch.Tensor           # int8 [S]
     episode_idx: torch.Tensor  # int32 [S]
     move_idx: torch.Tensor     # int32 [S]
-    n: int
+    n: int                     # columns (Othello: board size; Connect4: width)
+    rows: int = None           # rows (None = n, a square Othello board)
 
     def __len__(self) -> int:
         return int(self.own.numel())
 
     def cpu(self) -> "SampleBatch":
         return SampleBatch(self.own.cpu(), self.opp.cpu(), self.pi.cpu(), self.z.cpu(), self.episode_idx.cpu(),
-                           self.move_idx.cpu(), self.n)
+                           self.move_idx.cpu(), self.n, self.rows)
 
     def nbytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.own, self.opp, self.pi, self.z, self.episode_idx, self.move_idx))
 
     def states(self) -> np.ndarray:
-        """float64 [S, n, n] grids as the reference's Sample.state after normalize()."""
+        """float64 [S, rows, cols] grids as the reference's Sample.state after normalize()."""
         own, opp = bo.bits_to_numpy(self.own), bo.bits_to_numpy(self.opp)
-        out = np.zeros((len(own), self.n, self.n))
-        for r in range(self.n):
+        rows = self.n if self.rows is None else self.rows
+        out = np.zeros((len(own), rows, self.n))
+        for r in range(rows):
             for c in range(self.n):
                 bit = np.uint64(r * 8 + c)
                 out[:, r, c] = ((own >> bit) & np.uint64(1)).astype(np.float64) - ((opp >> bit) & np.uint64(1)).astype(np.float64)
@@ -53,14 +56,16 @@ class SampleBatch:
 class SelfPlayEngine:
     """G concurrent AlphaZero self-play games on one GPU."""
 
-    def __init__(self, nn, G: int, n: int = 8, n_sim: int = 200, dirichlet_alpha: float = 0.03,
+    def __init__(self, nn, G: int, n=8, n_sim: int = 200, dirichlet_alpha: float = 0.03,
                  dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
                  temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
                  tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
                  network_path: str = "auto"):
-        self.G, self.n, self.n_sim = G, n, n_sim
+        # `n`: Othello board size or a GameSpec (gamespec.Connect4Spec(7, 6) for BASELINE config 5)
+        self.spec = spec = as_spec(n)
+        self.G, self.n, self.n_sim = G, spec.n, n_sim
         self.max_plies = max_plies
-        self.tree = TreeBatch(G, n=n, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
+        self.tree = TreeBatch(G, n=spec, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
                               tie_random=tie_random, dirichlet_alpha=dirichlet_alpha,
                               dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
         if evaluator is not None:
@@ -70,9 +75,9 @@ class SelfPlayEngine:
             self.tree.set_encoding(False)
         else:
             self.evaluator = NetEvaluator(nn, self.tree, dtype=dtype)   # any PolicyValueNetwork, bf16 CUDA graph
-        self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, n * n - 4)
+        self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, spec.max_moves)
         dev = self.tree.device
-        T, A = max_plies, n * n + 1
+        T, A = max_plies, spec.action_size
         self.h_own = torch.zeros(T, G, dtype=torch.int64, device=dev)
         self.h_opp = torch.zeros(T, G, dtype=torch.int64, device=dev)
         self.h_player = torch.zeros(T, G, dtype=torch.int8, device=dev)
@@ -90,13 +95,13 @@ class SelfPlayEngine:
     def play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
              start_player: torch.Tensor = None) -> SampleBatch:
         """Plays G games to the end and returns their samples (device tensors)."""
-        tree, G, n = self.tree, self.G, self.n
+        tree, G, spec = self.tree, self.G, self.spec
         if start_own is None:
             tree.reset_roots()
         else:
             tree.set_roots(start_own, start_opp, start_player)
             tree.active.fill_(1)
-        term, _, win = bo.terminal_score(tree.root_own, tree.root_opp, tree.root_player, n)
+        term, _, win = spec.terminal_score(tree.root_own, tree.root_opp, tree.root_player)
         live = term == 0
         self.winner.copy_(win)
         tree.active.copy_(live.to(torch.uint8))
@@ -113,7 +118,7 @@ class SelfPlayEngine:
             action, pi = tree.choose(temp_t)
             self.h_pi[t].copy_(pi)
             tree.advance(action)
-            term, _, win = bo.terminal_score(tree.root_own, tree.root_opp, tree.root_player, n)
+            term, _, win = spec.terminal_score(tree.root_own, tree.root_opp, tree.root_player)
             newly = live & (term == 1)
             self.winner = torch.where(newly, win, self.winner)
             live = live & (term == 0)
@@ -134,4 +139,4 @@ class SelfPlayEngine:
         player = self.h_player[:t].t()[mask.t()]
         pi = self.h_pi[:t].transpose(0, 1)[mask.t()]
         z = (self.winner[episode_idx] * player).to(torch.int8)   # outcome * player (trainer.py:77)
-        return SampleBatch(own, opp, pi, z, episode_idx.to(torch.int32), move_idx.to(torch.int32), n)
+        return SampleBatch(own, opp, pi, z, episode_idx.to(torch.int32), move_idx.to(torch.int32), spec.cols, spec.rows)

@@ -14,6 +14,7 @@ from .base import Config, DataTransf, dotdict
 from .games.registers import BOARDS_REGISTER, CONFIGS_REGISTER, DATA_AUGMENT_STRATEGIES, NETWORKS_REGISTER
 from .players import AlphaZeroPlayer
 from .schedulers import TEMP_SCHEDULERS
+from .gamespec import spec_of
 from .selfplay import SampleBatch, SelfPlayEngine
 
 
@@ -123,7 +124,7 @@ class AlphaZeroTrainer:
         if cfg.simulations is None:
             raise ValueError("batched self-play needs config.simulations (compute_time is wall-clock bound per game)")
         if self._engine is None or self._engine.G != cfg.episodes or self._engine.n_sim != cfg.simulations:
-            self._engine = SelfPlayEngine(self.nn, cfg.episodes, n=self.board.n, n_sim=cfg.simulations,
+            self._engine = SelfPlayEngine(self.nn, cfg.episodes, n=spec_of(self.board), n_sim=cfg.simulations,
                                           dirichlet_alpha=cfg.dirichlet_alpha, dirichlet_epsilon=cfg.dirichlet_epsilon,
                                           temp_scheduler_type=cfg.temp_scheduler_type, temp_max_step=cfg.temp_max_step,
                                           temp_min_step=cfg.temp_min_step,

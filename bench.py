@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--game", default="othello", choices=["othello", "connect4"],
+                    help="othello: BASELINE config 3/4 (the headline); connect4: config 5 (7x6, Connect4Net)")
     ap.add_argument("--net", default="fused", choices=["fused", "torch"],
                     help="fused: hand-written tcgen05 trunk + fused heads; torch: the module's own bf16 forward")
     return ap.parse_args()
@@ -180,11 +182,22 @@ def run_ours(args):
     G, n, n_sim = args.games, 8, args.sims
 
     torch.manual_seed(0)
-    net = OthelloNet(n=n)
-    engine = SelfPlayEngine(net, G, n=n, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
+    if args.game == "connect4":
+        from alphazero_b200.games.connect4 import Connect4Net
+        from alphazero_b200.gamespec import Connect4Spec
+        spec = Connect4Spec(7, 6)
+        net = Connect4Net(board_width=7, board_height=6)
+        args.net = "torch"                      # the fused tcgen05 trunk is Othello's; Connect4Net runs its own bf16 graph
+        flop_per_eval, workload, net_name = 2 * 653376, "connect4_7x6_alphazero_selfplay_neural_mcts", "Connect4Net(7x6)"
+    else:
+        from alphazero_b200.gamespec import OthelloSpec
+        spec = OthelloSpec(n)
+        net = OthelloNet(n=n)
+        flop_per_eval, workload, net_name = FLOP_PER_EVAL, WORKLOAD, "OthelloNet(n=8)"
+    engine = SelfPlayEngine(net, G, n=spec, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
                             temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4, seed=0x5EED + 7919 * rank,
                             dtype=torch.bfloat16, device=dev, network_path=args.net)
-    black, white = bo.start_position(n)
+    black, white = spec.start_position()
     h_own = torch.full((G,), bo.to_i64(black), dtype=torch.int64).pin_memory()
     h_opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64).pin_memory()
     h_player = torch.ones(G, dtype=torch.int8).pin_memory()
@@ -270,7 +283,7 @@ def run_ours(args):
     peaks = measured_peaks()
     eval_ms = t_eval / n_calls
     tree_ms = t_tree / n_calls
-    tflops = G * FLOP_PER_EVAL / (eval_ms * 1e-3) / 1e12
+    tflops = G * flop_per_eval / (eval_ms * 1e-3) / 1e12
     roofline = {
         "bound": "tensor", "kernel": f"policy-value network forward over the leaf batch (bf16, CUDA graph, path={args.net})",
         "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
@@ -282,8 +295,9 @@ def run_ours(args):
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
-    b_mean = 10.0
-    bytes_per_sim = mean_depth * 32 * b_mean + mean_depth * 32 + 32 * b_mean + 32 + 128 + 260 + 4 + 40
+    b_mean = spec.mean_branching
+    bytes_per_sim = (mean_depth * 32 * b_mean + mean_depth * 32 + 32 * b_mean + 32 + 2 * spec.rows * spec.cols
+                     + 4 * spec.action_size + 4 + 40)
     tree_gbs = G * bytes_per_sim / (tree_ms * 1e-3) / 1e9
     tree_roofline = {"bound": "hbm", "kernel": "k_tree_step (backup + expand + select + encode)", "achieved": tree_gbs,
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
@@ -297,8 +311,8 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_run["ms"] / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "board": "8x8", "games_per_gpu": G, "n_sim": n_sim,
-                       "net": "OthelloNet(n=8) random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
+            "config": {"workload": workload, "board": f"{spec.cols}x{spec.rows}", "games_per_gpu": G, "n_sim": n_sim,
+                       "net": net_name + " random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
                        "leaves_in_flight_per_game": 1, "network_path": args.net, "tree_reuse": True,
                        "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
                        "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},

@@ -24,7 +24,9 @@ def test_class_surfaces_match_reference():
     import alphazero.mcts as r_mcts
     import alphazero.players as r_players
     import alphazero.games.othello as r_oth
+    import alphazero.games.connect4 as r_c4
     import alphazero.trainer as r_trainer
+    import alphazero_b200.games.connect4 as c4
     import alphazero_b200.arena as arena
     import alphazero_b200.base as base
     import alphazero_b200.mcts as mcts
@@ -36,6 +38,7 @@ def test_class_surfaces_match_reference():
              (r_players.RandomPlayer, players.RandomPlayer), (r_players.GreedyPlayer, players.GreedyPlayer),
              (r_players.MCTSPlayer, players.MCTSPlayer), (r_players.AlphaZeroPlayer, players.AlphaZeroPlayer),
              (r_oth.OthelloBoard, oth.OthelloBoard), (r_oth.OthelloNet, oth.OthelloNet), (r_arena.Arena, arena.Arena),
+             (r_c4.Connect4Board, c4.Connect4Board), (r_c4.Connect4Net, c4.Connect4Net),
              (r_trainer.Sample, trainer.Sample)]
     skip = {"human_display", "pixel_display", "add_child", "select_node", "rollout", "nn_evaluation", "back_propagate"}
     for ref_cls, cls in pairs:
@@ -180,3 +183,58 @@ def test_fair_max_semantics():
     assert (np.random.get_state()[1] == state).all()
     picks = {fair_max([("a", 1), ("b", 1), ("c", 0)], key=lambda t: t[1])[0] for _ in range(60)}
     assert picks == {"a", "b"}
+
+
+@needs_ref
+@pytest.mark.parametrize("w,h", [(7, 6), (5, 8)])
+def test_connect4_net_and_config_match_reference(w, h):
+    import_reference()
+    import alphazero.games.connect4 as r_c4
+    import alphazero.games.registers as r_reg
+    import alphazero_b200.games.connect4 as c4
+    import alphazero_b200.games.registers as reg
+    assert dataclasses.asdict(c4.Connect4Config()) == dataclasses.asdict(r_c4.Connect4Config())
+    for name in ("CONFIGS_REGISTER", "BOARDS_REGISTER", "NETWORKS_REGISTER", "MOVE_FORMATS_REGISTER", "DATA_AUGMENT_STRATEGIES"):
+        assert set(getattr(reg, name)) == set(getattr(r_reg, name)) - {"tictactoe"}
+    assert reg.MOVE_FORMATS_REGISTER["connect4"].value == r_reg.MOVE_FORMATS_REGISTER["connect4"].value
+    assert [t.value for t in reg.DATA_AUGMENT_STRATEGIES["connect4"].rotations] == \
+        [t.value for t in r_reg.DATA_AUGMENT_STRATEGIES["connect4"].rotations] == []
+    torch.manual_seed(0)
+    net = c4.Connect4Net(board_width=w, board_height=h)
+    ref = r_c4.Connect4Net(board_width=w, board_height=h)
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    ref.load_state_dict(net.state_dict())
+    assert net.get_parameters_count() == ref.get_parameters_count()
+    if (w, h) == (7, 6):
+        assert net.get_parameters_count() == 43208
+    x = torch.randint(-1, 2, (9, h, w)).float()          # (height, width) grids, viewed as (width, height) inside
+    p, v = net.predict(x)
+    rp, rv = ref.predict(x)
+    assert torch.equal(p, rp) and torch.equal(v, rv)
+    rng = np.random.default_rng(0)
+    probs = rng.random(w).astype(np.float32)
+    legal = [np.int64(0), np.int64(2), np.int64(w - 1)]
+    a, b = net.get_normalized_probs(probs, legal), ref.get_normalized_probs(probs, legal)
+    assert a.keys() == b.keys() and all(a[k] == b[k] and type(a[k]) is type(b[k]) for k in a)
+    tiny = np.zeros(w, np.float32)
+    assert net.get_normalized_probs(tiny, legal) == ref.get_normalized_probs(tiny, legal)
+    mp = {np.int64(1): 0.25, np.int64(3): 0.75}
+    assert (net.to_neural_output(mp) == ref.to_neural_output(mp)).all()
+    out = rng.random(w)
+    assert (net.reflect_neural_output(out, 1) == ref.reflect_neural_output(out, 1)).all()
+    with pytest.raises(ValueError):
+        net.reflect_neural_output(out[:-1], 1)
+    with pytest.raises(ValueError):
+        c4.Connect4Net(board_width=3, board_height=6)
+
+
+def test_connect4_golden_net_loads(golden_dir=None):
+    """The committed reference state_dict + outputs (tests/golden/connect4_net_7x6.npz) reproduce on CPU."""
+    import os
+    from alphazero_b200.games.connect4 import Connect4Net
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "connect4_net_7x6.npz")
+    d = np.load(here)
+    net = Connect4Net(board_width=7, board_height=6)
+    net.load_state_dict({k[3:]: torch.from_numpy(d[k]) for k in d.files if k.startswith("sd.")})
+    p, v = net.predict(torch.from_numpy(d["input"]))
+    assert np.abs(p.numpy() - d["probs"]).max() < 1e-6 and np.abs(v.numpy() - d["value"]).max() < 1e-6
