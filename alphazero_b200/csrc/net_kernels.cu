@@ -5,16 +5,26 @@
 // (alphazero/games/othello.py:366-374).  Design:
 //   * one persistent CTA per SM loops over groups of NB boards; all activations of a group stay in shared memory,
 //     nothing but the 16-byte bitboards is read from HBM and only the 32*(n-4)^2 features are written;
-//   * every board lives in a zero-ringed (n+2)x(n+2) frame, frames are stacked into one row space
-//     (row = board*F*F + r*F + c); a 3x3 convolution is then 9 row-shifted GEMMs: for tap (dr,dc) the A operand
-//     of `tcgen05.mma` is the SAME activation buffer with its descriptor start address moved by (dr*F+dc) rows
-//     (K-major, no-swizzle canonical layout: 16 bytes per row per 8-channel chunk, so a row shift is +16 B);
-//   * B operands (per-tap 32x32 weight tiles, BatchNorm folded in) sit in shared memory for the whole kernel;
-//   * accumulators (128 rows x 32 channels fp32) live in TMEM, double buffered; four epilogue warps read them with
-//     tcgen05.ld, add the folded bias, apply ReLU, round to bf16 and write the next layer's A operand;
-//   * conv1 (1 input channel, K = 9 padded to 16) is one more MMA per tile on a 9-tap im2col built straight from
-//     the bitboards (values -1/0/+1 are exact in bf16); its epilogue writes the zero ring that pads conv2.
-// Garbage computed on ring rows / tail rows is never read by a valid output ("trunk frame").
+//   * row space: a board is n rows of 8 cells (pitch 8, pad cells zero) preceded by one zero "ring" row of 8 cells
+//     that it shares with the board before it: row = board*(n+1)*8 + (1+r)*8 + c.  32-lane warps and 8-row tensor
+//     core matrices therefore never straddle a board row;
+//   * a 3x3 convolution = 3 accumulating GEMM steps, one per kernel ROW dr: the A operand of `tcgen05.mma` is the
+//     activation buffer with its descriptor start moved by dr*8 rows (K-major no-swizzle layout, 16 bytes per row per
+//     8-channel chunk, so the shift is a whole number of 128-byte core matrices) and the B operand holds the THREE taps
+//     of that kernel row side by side: N = 96 = (dc, c_out).  The accumulator row p then holds, per dc, the partial
+//     sum that belongs to output p - dc; the epilogue adds the three blocks with two warp shuffles per channel
+//     (lane +-1 = column +-1; the zero padding / row wrap at columns 0 and 7 is a predicate, not data).
+//     Measured on B200, an M128 N32 K16 SS-mode MMA costs ~90 cycles of which ~50 are a per-instruction cost that
+//     does not depend on N, so tripling N per instruction is what pays (profiles/r1_trunk_experiments.txt);
+//   * B operands (BatchNorm folded in) sit in shared memory for the whole kernel;
+//   * accumulators (128 rows x 96 fp32 columns) live in TMEM, double buffered; two teams of four epilogue warps read
+//     them with tcgen05.ld, combine the dc blocks, add the folded bias, apply ReLU, round to bf16 and write the next
+//     layer's A operand;
+//   * conv1 (1 input channel, K = 9 padded to 16) is one N = 32 MMA per tile on a 9-tap im2col built straight from
+//     the bitboards (values -1/0/+1 are exact in bf16); its epilogue writes zeros outside the n x n cells, which is
+//     the zero padding conv2 reads.
+// Garbage computed on ring rows / pad cells / tail rows after conv1 is never read by a valid output: conv2 (pad 1)
+// reads only conv1's zeros there, conv3 / conv4 (no padding) produce valid outputs only at an inset of 1 / 2 cells.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -27,19 +37,23 @@
 #define NET_TILE_M 128            // rows per MMA tile
 #define NET_TILES 6               // tiles per group
 #define NET_ROWS (NET_TILE_M * NET_TILES)   // 768 rows of activation per buffer
-#define NET_MARGIN 16             // zero rows before / after (|row shift| <= F + 1 <= 11)
+#define NET_PITCH 8               // cells per board row in the row space
+#define NET_MARGIN 16             // zero rows before / after (|row shift| = 8)
 #define NET_BUF_ROWS (NET_ROWS + 2 * NET_MARGIN)   // 800
 #define NET_CHUNK_BYTES (NET_BUF_ROWS * 16)        // one 8-channel chunk plane: 12800 B  (= LBO of the A operand)
 #define NET_BUF_BYTES (4 * NET_CHUNK_BYTES)        // 51200 B per activation buffer
-#define NET_TAP_BYTES 2048        // one 32x32 bf16 weight tile
-#define NET_LAYER_BYTES (9 * NET_TAP_BYTES)        // 18432
+#define NET_N3 96                 // N of the conv2..4 MMAs: 3 taps (dc) x 32 output channels
+#define NET_DR_CHUNK_BYTES (NET_N3 * 16)           // one 8-input-channel chunk of a kernel row: 1536 B (= LBO of B)
+#define NET_DR_BYTES (4 * NET_DR_CHUNK_BYTES)      // one kernel row: [ci chunk 4][(dc, co) 96][ci % 8] bf16 = 6144 B
+#define NET_LAYER_BYTES (3 * NET_DR_BYTES)         // 18432
 #define NET_CONV1_TILE_BYTES 1024 // conv1 as one K=16 MMA: [2 chunks][32 co][8] bf16 (taps 0..8, zero padded)
 #define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES + NET_CONV1_TILE_BYTES)  // conv2..conv4 tiles, then the conv1 tile
 #define NET_WBLOB_F32 (4 * 32)                     // folded biases of conv1..conv4
 #define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
 #define NET_WORKERS 256           // warps 0-7: im2col + epilogue (two teams of 4 warps, one per TMEM stage)
 #define NET_THREADS 288           // + warp 8: TMEM allocation + MMA issue
-#define NET_TMEM_COLS 64          // two accumulator stages of 32 columns
+#define NET_STAGE_COLS 128        // TMEM columns per accumulator stage (96 used)
+#define NET_TMEM_COLS 256         // two stages
 
 // shared memory map (bytes)
 #define SM_BUF_A 0
@@ -81,9 +95,9 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, 
     return d;                 // base_offset 0, lbo_mode 0, layout_type 0 = SWIZZLE_NONE
 }
 
-// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M = 128, N = 32.
-__device__ __forceinline__ uint32_t umma_idesc_bf16_m128_n32() {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M = 128, N = n (multiple of 16).
+__device__ __forceinline__ uint32_t umma_idesc_bf16_m128(uint32_t n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((128u >> 4) << 24);
 }
 
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
@@ -138,32 +152,31 @@ struct NetTrunkParams {
     __nv_bfloat16* debug;      // optional [n_groups][NET_ROWS][32] dump of the activations after `debug_layer`
     int G;
     int n;                     // board size 6 or 8
-    int boards_per_group;      // NB: NB * (n+2)^2 <= NET_ROWS
+    int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= NET_ROWS
     int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
 };
 
-// Row -> (board in group, frame row, frame col)
-__device__ __forceinline__ void net_row_coords(int row, int F, int& b, int& r, int& c) {
-    const int FF = F * F;
-    b = row / FF;
-    const int rem = row - b * FF;
-    r = rem / F;
-    c = rem - r * F;
+// Row of the group's row space -> (board in group, board row r, column c); r = -1 on a ring row.
+// rpb = rows per board = (n + 1) * 8.
+__device__ __forceinline__ void net_row_coords(int row, int rpb, int& b, int& r, int& c) {
+    b = row / rpb;
+    const int rem = row - b * rpb;
+    r = (rem >> 3) - 1;
+    c = rem & 7;
 }
 
-// 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one frame row:
+// 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one row:
 // 16 bf16 = taps 0..8 then zeros, written as the two 16-byte K chunks of the conv1 A operand.
 __device__ __forceinline__ void net_im2col_row(const NetTrunkParams& p, uint8_t* smem, int row, int n_boards) {
-    const int F = p.n + 2;
     int b, r, c;
-    net_row_coords(row, F, b, r, c);
+    net_row_coords(row, (p.n + 1) * NET_PITCH, b, r, c);
     uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};     // taps 0..8 as bf16 pairs (tap 8 in the low half of w[4])
-    if (row < p.boards_per_group * F * F && b < n_boards && r >= 1 && r <= p.n && c >= 1 && c <= p.n) {
+    if (b < n_boards && r >= 0 && c < p.n) {
         const uint64_t* s_own = reinterpret_cast<const uint64_t*>(smem + SM_BOARDS);
         const uint64_t own = s_own[b], opp = s_own[16 + b];
 #pragma unroll
         for (int t = 0; t < 9; ++t) {
-            const int ur = r - 1 + (t / 3 - 1), uc = c - 1 + (t % 3 - 1);
+            const int ur = r + (t / 3 - 1), uc = c + (t % 3 - 1);
             uint32_t v = 0u;
             if (ur >= 0 && ur < p.n && uc >= 0 && uc < p.n) {
                 const int bit = ur * 8 + uc;
@@ -181,7 +194,7 @@ template <int NBOARD>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    constexpr int F = NBOARD + 2, FF = F * F;
+    constexpr int RPB = (NBOARD + 1) * NET_PITCH;      // rows per board: ring row + n board rows
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
     const uint32_t bar_full0 = smem_u32(smem + SM_BARS), bar_empty0 = bar_full0 + 16;
@@ -207,7 +220,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
-    const uint32_t idesc = umma_idesc_bf16_m128_n32();
+    const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc96 = umma_idesc_bf16_m128(NET_N3);
     const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
     const int team = warp >> 2;            // epilogue team = TMEM stage it serves (workers only)
     const int quarter = warp & 3;          // TMEM lane quarter this warp may read
@@ -238,28 +251,28 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 // (descriptors differ from the per-layer base only by an immediate in the start-address field).
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint64_t a_layer = umma_desc(src + NET_MARGIN * 16, NET_CHUNK_BYTES, 128);
-                const uint64_t b_layer = umma_desc(smem_u32(smem + SM_W) + (layer == 0 ? 3 * NET_LAYER_BYTES
-                                                                                      : (layer - 1) * NET_LAYER_BYTES),
-                                                   512, 128);
+                const uint64_t b_layer = layer == 0
+                    ? umma_desc(smem_u32(smem + SM_W) + 3 * NET_LAYER_BYTES, 512, 128)
+                    : umma_desc(smem_u32(smem + SM_W) + (layer - 1) * NET_LAYER_BYTES, NET_DR_CHUNK_BYTES, 128);
                 for (int t = 0; t < NET_TILES; ++t) {
                     const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
                     mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t d_tmem = tmem_base + stage * 32u;
+                    const uint32_t d_tmem = tmem_base + stage * NET_STAGE_COLS;
                     const uint64_t a_tile = a_layer + (uint64_t)(t * (NET_TILE_M * 16 / 16));
                     if (elect_one()) {
                         if (layer == 0) {
-                            umma_bf16(d_tmem, a_tile, b_layer, idesc, 0u);
+                            umma_bf16(d_tmem, a_tile, b_layer, idesc32, 0u);
                         } else {
 #pragma unroll
-                            for (int tap = 0; tap < 9; ++tap) {
-                                const int shift = (tap / 3 - 1) * F + (tap % 3 - 1);
+                            for (int dr = 0; dr < 3; ++dr) {
 #pragma unroll
                                 for (int kk = 0; kk < 2; ++kk) {
-                                    const int64_t a_off = shift + kk * (2 * NET_CHUNK_BYTES / 16);
-                                    const uint64_t b_off = (uint64_t)((tap * NET_TAP_BYTES + kk * 2 * 512) / 16);
-                                    umma_bf16(d_tmem, (uint64_t)((int64_t)a_tile + a_off), b_layer + b_off, idesc,
-                                              (tap | kk) ? 1u : 0u);
+                                    // A: rows shifted by (dr - 1) board rows, input channels 16*kk .. 16*kk + 15
+                                    const int64_t a_off = (dr - 1) * NET_PITCH + kk * (2 * NET_CHUNK_BYTES / 16);
+                                    const uint64_t b_off = (uint64_t)((dr * NET_DR_BYTES + kk * 2 * NET_DR_CHUNK_BYTES) / 16);
+                                    umma_bf16(d_tmem, (uint64_t)((int64_t)a_tile + a_off), b_layer + b_off, idesc96,
+                                              (dr | kk) ? 1u : 0u);
                                 }
                             }
                         }
@@ -276,24 +289,48 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 }
                 for (int t = team; t < NET_TILES; t += 2) {
                     const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
-                    mbar_wait(bar_full0 + 8 * stage, phase);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    uint32_t acc[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * 32u, acc);
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    mbar_arrive(bar_empty0 + 8 * stage);
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
-                    net_row_coords(row, F, b, r, c);
-                    const bool in_group = row < NB * FF && b < n_boards;
+                    net_row_coords(row, RPB, b, r, c);
+                    mbar_wait(bar_full0 + 8 * stage, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * NET_STAGE_COLS;
+                    uint32_t acc[32];
+                    float sum[32];
+                    if (layer == 0) {
+                        tmem_ld32(t_lane, acc);
+#pragma unroll
+                        for (int co = 0; co < 32; ++co) sum[co] = __uint_as_float(acc[co]);
+                    } else {
+                        // accumulator row p, block dc holds the contribution to output p - dc:
+                        //   out[p] = blk(-1)[p - 1] + blk(0)[p] + blk(+1)[p + 1]; column 0 / 7 have no left / right
+                        //   neighbour (zero padding for conv2, never-valid outputs for conv3 / conv4).
+                        tmem_ld32(t_lane, acc);                                   // dc = -1 block of this row
+#pragma unroll
+                        for (int co = 0; co < 32; ++co) {
+                            const float up = __shfl_up_sync(0xffffffffu, __uint_as_float(acc[co]), 1);
+                            sum[co] = c > 0 ? up : 0.f;
+                        }
+                        tmem_ld32(t_lane + 32u, acc);                             // dc = 0
+#pragma unroll
+                        for (int co = 0; co < 32; ++co) sum[co] += __uint_as_float(acc[co]);
+                        tmem_ld32(t_lane + 64u, acc);                             // dc = +1
+#pragma unroll
+                        for (int co = 0; co < 32; ++co) {
+                            const float dn = __shfl_down_sync(0xffffffffu, __uint_as_float(acc[co]), 1);
+                            sum[co] += c < 7 ? dn : 0.f;
+                        }
+                    }
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    mbar_arrive(bar_empty0 + 8 * stage);
+                    const bool on_board = b < n_boards && r >= 0 && c < p.n;
                     uint32_t out[16];
 #pragma unroll
                     for (int co = 0; co < 32; co += 2)
-                        out[co >> 1] = pack_bf16x2(fmaxf(__uint_as_float(acc[co]) + bias[co], 0.f),
-                                                   fmaxf(__uint_as_float(acc[co + 1]) + bias[co + 1], 0.f));
-                    if (layer == 0 && !(in_group && r >= 1 && r <= p.n && c >= 1 && c <= p.n)) {
+                        out[co >> 1] = pack_bf16x2(fmaxf(sum[co] + bias[co], 0.f), fmaxf(sum[co + 1] + bias[co + 1], 0.f));
+                    if (layer == 0 && !on_board) {
 #pragma unroll
-                        for (int i = 0; i < 16; ++i) out[i] = 0u;             // zero ring = the padding of conv2
+                        for (int i = 0; i < 16; ++i) out[i] = 0u;             // zero ring / pad cells = conv2's padding
                     }
                     if (layer < 3) {
                         uint8_t* d = dst + (NET_MARGIN + row) * 16;
@@ -305,9 +342,9 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             for (int ch = 0; ch < 4; ++ch)
                                 *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
                                     make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
-                    } else if (in_group && r >= 3 && r < 3 + m_out && c >= 3 && c < 3 + m_out) {
-                        // conv4: only frame positions 3..n-2 are outputs; features[board][pos*32 + co]
-                        const int pos = (r - 3) * m_out + (c - 3);
+                    } else if (on_board && r >= 2 && r < 2 + m_out && c >= 2 && c < 2 + m_out) {
+                        // conv4: the outputs are the cells at an inset of 2; features[board][pos*32 + co]
+                        const int pos = (r - 2) * m_out + (c - 2);
                         uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (m_out * m_out) + pos) * 32);
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
@@ -387,8 +424,8 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;
     p.G = (int)G; p.n = n;
-    const int F = n + 2;
-    p.boards_per_group = NET_ROWS / (F * F);          // 7 boards (n = 8) or 12 boards (n = 6) per 768-row group
+    // rows per board = (n + 1) * 8, plus the closing ring row: 10 boards (n = 8) or 13 boards (n = 6) per 768 rows
+    p.boards_per_group = (NET_ROWS - NET_PITCH) / ((n + 1) * NET_PITCH);
     p.debug_layer = debug ? debug_layer : 0;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM

@@ -3,7 +3,8 @@
 The weights are the reference module's own (any OthelloNet state_dict, alphazero/games/othello.py:341-359); this file
 only re-packs them for the kernels:
   * eval-mode BatchNorm folded into the preceding conv / linear layer (y = s*(Wx + b - mu) + beta, s = g/sqrt(v+eps));
-  * conv2..conv4: per-tap 32x32 bf16 tiles in the tcgen05 K-major no-swizzle operand layout (csrc/net_kernels.cu);
+  * conv2..conv4: per kernel ROW one 96x32 bf16 tile -- the three taps (dc) of the row side by side on the N side,
+    N = dc*32 + c_out -- in the tcgen05 K-major no-swizzle operand layout (csrc/net_kernels.cu);
   * conv1 as one more K=16 bf16 tile (9 taps, zero padded); all conv biases in float32;
   * fc1 columns permuted from the reference's channel-major flatten (c*m*m + pos) to the trunk kernel's
     position-major feature order (pos*32 + c);
@@ -35,11 +36,11 @@ def _bf16_bits(t: torch.Tensor) -> np.ndarray:
 
 def pack_trunk_weights(net) -> torch.Tensor:
     """uint8 blob for az_net_trunk:
-    [conv2|conv3|conv4: 9 taps x [ci chunk 4][co 32][ci%8] bf16][conv1: [k chunk 2][co 32][8] bf16, taps 0..8 then 0]
+    [conv2|conv3|conv4: 3 kernel rows x [ci chunk 4][(dc, co) 96][ci%8] bf16][conv1: [k chunk 2][co 32][8] bf16, taps 0..8 then 0]
     [b1..b4 float32 [4][32]]  -- all with eval-mode BatchNorm folded in."""
     assert net.n_channels == 32
     n_bytes = int(_lib.lib().az_net_wblob_bytes())
-    mma = np.zeros((3, 9, 4, 32, 8), dtype=np.uint16)
+    mma = np.zeros((3, 3, 4, 96, 8), dtype=np.uint16)
     biases = np.zeros((4, 32), dtype=np.float32)
     w1, b1 = _fold_bn(net.conv1.weight, net.conv1.bias, net.bn1)     # [co][1][kh][kw]
     biases[0] = b1.float().cpu().numpy()
@@ -50,9 +51,9 @@ def pack_trunk_weights(net) -> torch.Tensor:
         w, b = _fold_bn(conv.weight, conv.bias, bn)                   # [co][ci][kh][kw]
         biases[li + 1] = b.float().cpu().numpy()
         wb = _bf16_bits(w)
-        for tap in range(9):
-            kh, kw = divmod(tap, 3)
-            mma[li, tap] = wb[:, :, kh, kw].reshape(32, 4, 8).transpose(1, 0, 2)   # [ci chunk][co][ci % 8]
+        for kh in range(3):
+            for kw in range(3):
+                mma[li, kh, :, kw * 32:(kw + 1) * 32] = wb[:, :, kh, kw].reshape(32, 4, 8).transpose(1, 0, 2)   # [ci chunk][co][ci % 8]
     packed = np.concatenate([mma.reshape(-1).view(np.uint8), np.ascontiguousarray(c1).reshape(-1).view(np.uint8),
                              biases.reshape(-1).view(np.uint8)])
     assert packed.nbytes == n_bytes, (packed.nbytes, n_bytes)
