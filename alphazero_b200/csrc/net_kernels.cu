@@ -50,8 +50,9 @@
 #define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES + NET_CONV1_TILE_BYTES)  // conv2..conv4 tiles, then the conv1 tile
 #define NET_WBLOB_F32 (4 * 32)                     // folded biases of conv1..conv4
 #define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
-#define NET_WORKERS 256           // warps 0-7: im2col + epilogue (two teams of 4 warps, one per TMEM stage)
-#define NET_THREADS 288           // + warp 8: TMEM allocation + MMA issue
+#define NET_WORKERS 256           // warps 0-7: epilogue (two teams of 4 warps, one per TMEM stage)
+#define NET_PRODUCERS 64          // warps 9-10: im2col of the NEXT group while the current one is in conv4
+#define NET_THREADS (NET_WORKERS + 32 + NET_PRODUCERS)   // warp 8: TMEM allocation + MMA issue
 #define NET_STAGE_COLS 128        // TMEM columns per accumulator stage (96 used)
 #define NET_TMEM_COLS 256         // two stages
 
@@ -59,10 +60,19 @@
 #define SM_BUF_A 0
 #define SM_BUF_B (SM_BUF_A + NET_BUF_BYTES)
 #define SM_W (SM_BUF_B + NET_BUF_BYTES)
-#define SM_BARS (SM_W + NET_WBLOB_BYTES)           // 4 mbarriers: full[2], empty[2]
-#define SM_TMEM_PTR (SM_BARS + 4 * 8)
-#define SM_BOARDS (SM_TMEM_PTR + 8)                // own/opp of the group's boards: 2 * 16 * 8 B
-#define SM_TOTAL (SM_BOARDS + 2 * 16 * 8)
+// mbarriers: full[2] / empty[2] accumulator stages, ready[NET_TILES] "rows of tile t of this layer are in shared
+// memory", im2col "conv1's A operand of the group is in place", bufb "buffer B is no longer read" (conv3 done),
+// weights "the bulk copy of the weight blob has landed"
+#define SM_BARS (SM_W + NET_WBLOB_BYTES)
+#define BAR_FULL 0
+#define BAR_EMPTY 2
+#define BAR_READY 4
+#define BAR_IM2COL (BAR_READY + NET_TILES)
+#define BAR_BUFB (BAR_IM2COL + 1)
+#define BAR_WEIGHTS (BAR_BUFB + 1)
+#define NET_N_BARS (BAR_WEIGHTS + 1)
+#define SM_TMEM_PTR (SM_BARS + 16 * 8)
+#define SM_TOTAL (SM_TMEM_PTR + 16)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -127,6 +137,25 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// Three 32-column loads (columns +0, +32, +64 of the lane's row) and ONE wait, in a single asm statement so that no
+// consumer of the registers can be scheduled before tcgen05.wait::ld.
+__device__ __forceinline__ void tmem_ld96(uint32_t taddr, uint32_t (&a)[32], uint32_t (&b)[32], uint32_t (&c)[32]) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 t1, t2;\n\t"
+        "add.u32 t1, %96, 32;\n\t"
+        "add.u32 t2, %96, 64;\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%96];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, %48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [t1];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%64, %65, %66, %67, %68, %69, %70, %71, %72, %73, %74, %75, %76, %77, %78, %79, %80, %81, %82, %83, %84, %85, %86, %87, %88, %89, %90, %91, %92, %93, %94, %95}, [t2];\n\t"
+        "tcgen05.wait::ld.sync.aligned;\n\t"
+        "}"
+        : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]), "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15]), "=r"(a[16]), "=r"(a[17]), "=r"(a[18]), "=r"(a[19]), "=r"(a[20]), "=r"(a[21]), "=r"(a[22]), "=r"(a[23]), "=r"(a[24]), "=r"(a[25]), "=r"(a[26]), "=r"(a[27]), "=r"(a[28]), "=r"(a[29]), "=r"(a[30]), "=r"(a[31]),
+          "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]), "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15]), "=r"(b[16]), "=r"(b[17]), "=r"(b[18]), "=r"(b[19]), "=r"(b[20]), "=r"(b[21]), "=r"(b[22]), "=r"(b[23]), "=r"(b[24]), "=r"(b[25]), "=r"(b[26]), "=r"(b[27]), "=r"(b[28]), "=r"(b[29]), "=r"(b[30]), "=r"(b[31]),
+          "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]), "=r"(c[4]), "=r"(c[5]), "=r"(c[6]), "=r"(c[7]), "=r"(c[8]), "=r"(c[9]), "=r"(c[10]), "=r"(c[11]), "=r"(c[12]), "=r"(c[13]), "=r"(c[14]), "=r"(c[15]), "=r"(c[16]), "=r"(c[17]), "=r"(c[18]), "=r"(c[19]), "=r"(c[20]), "=r"(c[21]), "=r"(c[22]), "=r"(c[23]), "=r"(c[24]), "=r"(c[25]), "=r"(c[26]), "=r"(c[27]), "=r"(c[28]), "=r"(c[29]), "=r"(c[30]), "=r"(c[31])
+        : "r"(taddr) : "memory");
+}
+
 // True in exactly one (elected) lane of a converged warp.
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred = 0;
@@ -167,22 +196,26 @@ __device__ __forceinline__ void net_row_coords(int row, int rpb, int& b, int& r,
 
 // 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one row:
 // 16 bf16 = taps 0..8 then zeros, written as the two 16-byte K chunks of the conv1 A operand.
-__device__ __forceinline__ void net_im2col_row(const NetTrunkParams& p, uint8_t* smem, int row, int n_boards) {
-    int b, r, c;
-    net_row_coords(row, (p.n + 1) * NET_PITCH, b, r, c);
+// (b, r, c) are the row's coordinates; own/opp the bitboards of its board (0 when the board does not exist).
+__device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n, int r, int c, uint64_t own, uint64_t opp) {
     uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};     // taps 0..8 as bf16 pairs (tap 8 in the low half of w[4])
-    if (b < n_boards && r >= 0 && c < p.n) {
-        const uint64_t* s_own = reinterpret_cast<const uint64_t*>(smem + SM_BOARDS);
-        const uint64_t own = s_own[b], opp = s_own[16 + b];
+    if (r >= 0 && c < n) {
 #pragma unroll
-        for (int t = 0; t < 9; ++t) {
-            const int ur = r + (t / 3 - 1), uc = c + (t % 3 - 1);
-            uint32_t v = 0u;
-            if (ur >= 0 && ur < p.n && uc >= 0 && uc < p.n) {
-                const int bit = ur * 8 + uc;
-                v = ((own >> bit) & 1ULL) ? 0x3F80u : (((opp >> bit) & 1ULL) ? 0xBF80u : 0u);   // +1.0 / -1.0 bf16
+        for (int dr = 0; dr < 3; ++dr) {
+            const int ur = r + dr - 1;
+            // the three cells (ur, c-1 .. c+1) as bits 0..2; cells outside the n x n board are 0 in both bitboards
+            uint32_t o3 = 0u, p3 = 0u;
+            if (ur >= 0 && ur < n) {
+                const uint32_t orow = (uint32_t)(own >> (ur * 8)) & 0xFFu, prow = (uint32_t)(opp >> (ur * 8)) & 0xFFu;
+                o3 = ((orow << 1) >> c) & 7u;
+                p3 = ((prow << 1) >> c) & 7u;
             }
-            w[t >> 1] |= v << ((t & 1) * 16);
+#pragma unroll
+            for (int dc = 0; dc < 3; ++dc) {
+                const int t = dr * 3 + dc;
+                const uint32_t v = ((o3 >> dc) & 1u) ? 0x3F80u : (((p3 >> dc) & 1u) ? 0xBF80u : 0u);   // +1.0 / -1.0 bf16
+                w[t >> 1] |= v << ((t & 1) * 16);
+            }
         }
     }
     uint8_t* dst = smem + SM_BUF_B + (NET_MARGIN + row) * 16;
@@ -190,6 +223,11 @@ __device__ __forceinline__ void net_im2col_row(const NetTrunkParams& p, uint8_t*
     *reinterpret_cast<uint4*>(dst + NET_CHUNK_BYTES) = make_uint4(w[4], 0u, 0u, 0u);
 }
 
+// Warp roles (no block-wide barrier inside the group loop; everything is mbarrier-pipelined):
+//   warps 0-7   epilogue: team = warp / 4 serves TMEM stage `team`, quarter = warp % 4 is the TMEM lane quarter;
+//   warp 8      MMA issue (one elected lane) -- tiles of consecutive layers and groups follow each other without a
+//               drain: tile t of layer L+1 only waits for tiles t-1 .. t+1 of layer L (row shifts are +-8 rows);
+//   warps 9-10  producers: im2col of group g+1 into buffer B while group g is in conv4 (which reads buffer A).
 template <int NBOARD>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -197,20 +235,28 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     constexpr int RPB = (NBOARD + 1) * NET_PITCH;      // rows per board: ring row + n board rows
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
-    const uint32_t bar_full0 = smem_u32(smem + SM_BARS), bar_empty0 = bar_full0 + 16;
+    const uint32_t bars = smem_u32(smem + SM_BARS);
+    const uint32_t bar_full0 = bars + 8 * BAR_FULL, bar_empty0 = bars + 8 * BAR_EMPTY, bar_ready0 = bars + 8 * BAR_READY;
+    const uint32_t bar_im2col = bars + 8 * BAR_IM2COL, bar_bufb = bars + 8 * BAR_BUFB, bar_weights = bars + 8 * BAR_WEIGHTS;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SM_TMEM_PTR);
     constexpr int MMA_WARP = NET_WORKERS / 32;
 
-    // ---- one-time setup: zero the activation buffers, stage the weights, barriers, TMEM
-    for (int i = tid; i < 2 * NET_BUF_BYTES / 16; i += NET_THREADS)
-        reinterpret_cast<uint4*>(smem + SM_BUF_A)[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = tid; i < NET_WBLOB_BYTES / 16; i += NET_THREADS)
-        reinterpret_cast<uint4*>(smem + SM_W)[i] = reinterpret_cast<const uint4*>(p.wblob)[i];
+    // ---- one-time setup: barriers, async bulk copy of the weights, zeroed activation buffers, TMEM
     if (tid == 0) {
         mbar_init(bar_full0, 1); mbar_init(bar_full0 + 8, 1);
         mbar_init(bar_empty0, 128); mbar_init(bar_empty0 + 8, 128);
+        for (int t = 0; t < NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 128);
+        mbar_init(bar_im2col, NET_PRODUCERS);
+        mbar_init(bar_bufb, 1);
+        mbar_init(bar_weights, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
+                     ::"r"(bar_weights), "r"((uint32_t)NET_WBLOB_BYTES) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(smem + SM_W)), "l"(p.wblob), "r"((uint32_t)NET_WBLOB_BYTES), "r"(bar_weights) : "memory");
     }
+    for (int i = tid; i < 2 * NET_BUF_BYTES / 16; i += NET_THREADS)
+        reinterpret_cast<uint4*>(smem + SM_BUF_A)[i] = make_uint4(0u, 0u, 0u, 0u);
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(NET_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -220,42 +266,58 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
-    const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc96 = umma_idesc_bf16_m128(NET_N3);
-    const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
-    const int team = warp >> 2;            // epilogue team = TMEM stage it serves (workers only)
-    const int quarter = warp & 3;          // TMEM lane quarter this warp may read
-    const int m_out = p.n - 4;
 
-    uint32_t tile_it = 0;   // running tile counter (even at every layer start: NET_TILES is even)
-
-    for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
-        const int board0 = grp * NB;
-        const int n_boards = min(NB, p.G - board0);
-        if (tid < 16) {
-            uint64_t* s_own = reinterpret_cast<uint64_t*>(smem + SM_BOARDS);
-            s_own[tid] = tid < n_boards ? p.own[board0 + tid] : 0ULL;
-            s_own[16 + tid] = tid < n_boards ? p.opp[board0 + tid] : 0ULL;
+    if (warp > MMA_WARP) {
+        // ================================================================== producers: im2col of every group
+        const int ptid = tid - (NET_WORKERS + 32);
+        uint32_t gi = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+            const int board0 = grp * NB;
+            const int n_boards = min(NB, p.G - board0);
+            // bitboards of the rows this thread converts (global loads issued before waiting for the buffer)
+            constexpr int RPT = NET_ROWS / NET_PRODUCERS;
+            uint64_t own[RPT], opp[RPT];
+#pragma unroll
+            for (int k = 0; k < RPT; ++k) {
+                const int b = (ptid + k * NET_PRODUCERS) / RPB;
+                const bool ok = b < n_boards;
+                own[k] = ok ? p.own[board0 + b] : 0ULL;
+                opp[k] = ok ? p.opp[board0 + b] : 0ULL;
+            }
+            if (gi > 0) mbar_wait(bar_bufb, (gi - 1u) & 1u);      // conv3 of the previous group has read buffer B
+#pragma unroll
+            for (int k = 0; k < RPT; ++k) {
+                const int row = ptid + k * NET_PRODUCERS;
+                int b, r, c;
+                net_row_coords(row, RPB, b, r, c);
+                net_im2col_row(smem, row, NBOARD, r, c, own[k], opp[k]);
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(bar_im2col);
         }
-        __syncthreads();
-        if (warp < MMA_WARP)
-            for (int row = tid; row < NET_ROWS; row += NET_WORKERS) net_im2col_row(p, smem, row, n_boards);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncthreads();
-
-        // ---- layer 0: conv1 (im2col in B -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
-        for (int layer = 0; layer < 4; ++layer) {
-            const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B));
-            uint8_t* dst = smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A);
-            if (warp == MMA_WARP) {
-                // The whole warp stays converged; one elected lane issues the MMAs of a tile back to back
-                // (descriptors differ from the per-layer base only by an immediate in the start-address field).
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    } else if (warp == MMA_WARP) {
+        // ================================================================== MMA issue
+        const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc96 = umma_idesc_bf16_m128(NET_N3);
+        mbar_wait(bar_weights, 0u);
+        uint32_t gi = 0, tile_it = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+            mbar_wait(bar_im2col, gi & 1u);
+            // ---- layer 0: conv1 (im2col in B -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
+            for (int layer = 0; layer < 4; ++layer) {
+                const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B));
                 const uint64_t a_layer = umma_desc(src + NET_MARGIN * 16, NET_CHUNK_BYTES, 128);
                 const uint64_t b_layer = layer == 0
                     ? umma_desc(smem_u32(smem + SM_W) + 3 * NET_LAYER_BYTES, 512, 128)
                     : umma_desc(smem_u32(smem + SM_W) + (layer - 1) * NET_LAYER_BYTES, NET_DR_CHUNK_BYTES, 128);
-                for (int t = 0; t < NET_TILES; ++t) {
-                    const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                // ready[] barriers complete one phase per layer 0..2 of every group (conv4 writes no activations)
+                const uint32_t ready_parity = (gi * 3u + (uint32_t)(layer - 1)) & 1u;
+                for (int t = 0; t < NET_TILES; ++t, ++tile_it) {
+                    if (layer > 0) {
+                        // input rows of tile t: tiles t-1 .. t+1 of the previous layer; t-1 and t were awaited for tile t-1
+                        if (t == 0) mbar_wait(bar_ready0, ready_parity);
+                        if (t + 1 < NET_TILES) mbar_wait(bar_ready0 + 8 * (t + 1), ready_parity);
+                    }
+                    const uint32_t stage = tile_it & 1u, phase = (tile_it >> 1) & 1u;
                     mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t d_tmem = tmem_base + stage * NET_STAGE_COLS;
@@ -277,10 +339,25 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             }
                         }
                         umma_commit(bar_full0 + 8 * stage);
+                        if (layer == 2 && t == NET_TILES - 1) umma_commit(bar_bufb);   // buffer B free for the next im2col
                     }
                     __syncwarp();
                 }
-            } else {
+            }
+        }
+    } else {
+        // ================================================================== epilogue teams
+        const int team = warp >> 2;            // TMEM stage this team serves
+        const int quarter = warp & 3;          // TMEM lane quarter this warp may read
+        const int m_out = NBOARD - 4;
+        const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
+        mbar_wait(bar_weights, 0u);
+        uint32_t tile_base = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+            const int board0 = grp * NB;
+            const int n_boards = min(NB, p.G - board0);
+            for (int layer = 0; layer < 4; ++layer, tile_base += NET_TILES) {
+                uint8_t* dst = smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A);
                 float bias[32];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -288,49 +365,48 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     bias[4 * i] = v.x; bias[4 * i + 1] = v.y; bias[4 * i + 2] = v.z; bias[4 * i + 3] = v.w;
                 }
                 for (int t = team; t < NET_TILES; t += 2) {
-                    const uint32_t it = tile_it + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                    const uint32_t it = tile_base + t, stage = it & 1u, phase = (it >> 1) & 1u;
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
+                    const bool on_board = b < n_boards && r >= 0 && c < NBOARD;
                     mbar_wait(bar_full0 + 8 * stage, phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * NET_STAGE_COLS;
-                    uint32_t acc[32];
-                    float sum[32];
+                    uint32_t out[16];
                     if (layer == 0) {
+                        uint32_t acc[32];
                         tmem_ld32(t_lane, acc);
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        mbar_arrive(bar_empty0 + 8 * stage);
 #pragma unroll
-                        for (int co = 0; co < 32; ++co) sum[co] = __uint_as_float(acc[co]);
+                        for (int co = 0; co < 32; co += 2)
+                            out[co >> 1] = pack_bf16x2(fmaxf(__uint_as_float(acc[co]) + bias[co], 0.f),
+                                                       fmaxf(__uint_as_float(acc[co + 1]) + bias[co + 1], 0.f));
+                        if (!on_board) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) out[i] = 0u;         // zero ring / pad cells = conv2's padding
+                        }
                     } else {
                         // accumulator row p, block dc holds the contribution to output p - dc:
                         //   out[p] = blk(-1)[p - 1] + blk(0)[p] + blk(+1)[p + 1]; column 0 / 7 have no left / right
                         //   neighbour (zero padding for conv2, never-valid outputs for conv3 / conv4).
-                        tmem_ld32(t_lane, acc);                                   // dc = -1 block of this row
+                        uint32_t lo[32], mid[32], hi[32];
+                        tmem_ld96(t_lane, lo, mid, hi);                           // dc = -1, 0, +1 blocks of this row
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        mbar_arrive(bar_empty0 + 8 * stage);
+                        const bool has_left = c > 0, has_right = c < 7;
+                        float v[2];
 #pragma unroll
                         for (int co = 0; co < 32; ++co) {
-                            const float up = __shfl_up_sync(0xffffffffu, __uint_as_float(acc[co]), 1);
-                            sum[co] = c > 0 ? up : 0.f;
+                            const float up = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co]), 1);
+                            const float dn = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co]), 1);
+                            float x = __uint_as_float(mid[co]) + bias[co];
+                            x += has_left ? up : 0.f;
+                            x += has_right ? dn : 0.f;
+                            v[co & 1] = fmaxf(x, 0.f);
+                            if (co & 1) out[co >> 1] = pack_bf16x2(v[0], v[1]);
                         }
-                        tmem_ld32(t_lane + 32u, acc);                             // dc = 0
-#pragma unroll
-                        for (int co = 0; co < 32; ++co) sum[co] += __uint_as_float(acc[co]);
-                        tmem_ld32(t_lane + 64u, acc);                             // dc = +1
-#pragma unroll
-                        for (int co = 0; co < 32; ++co) {
-                            const float dn = __shfl_down_sync(0xffffffffu, __uint_as_float(acc[co]), 1);
-                            sum[co] += c < 7 ? dn : 0.f;
-                        }
-                    }
-                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    mbar_arrive(bar_empty0 + 8 * stage);
-                    const bool on_board = b < n_boards && r >= 0 && c < p.n;
-                    uint32_t out[16];
-#pragma unroll
-                    for (int co = 0; co < 32; co += 2)
-                        out[co >> 1] = pack_bf16x2(fmaxf(sum[co] + bias[co], 0.f), fmaxf(sum[co + 1] + bias[co + 1], 0.f));
-                    if (layer == 0 && !on_board) {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) out[i] = 0u;             // zero ring / pad cells = conv2's padding
                     }
                     if (layer < 3) {
                         uint8_t* d = dst + (NET_MARGIN + row) * 16;
@@ -338,6 +414,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         for (int ch = 0; ch < 4; ++ch)
                             *reinterpret_cast<uint4*>(d + ch * NET_CHUNK_BYTES) =
                                 make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        mbar_arrive(bar_ready0 + 8 * t);
                         if (p.debug && p.debug_layer == layer + 1)
                             for (int ch = 0; ch < 4; ++ch)
                                 *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
@@ -352,9 +430,6 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     }
                 }
             }
-            tile_it += NET_TILES;
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncthreads();
         }
     }
 
