@@ -173,6 +173,33 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// Packed fp32 pairs (Blackwell add/fma.f32x2: two channels per FP instruction).
+__device__ __forceinline__ uint64_t f32x2_pack(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f32x2_unpack(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f32x2_add(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t f32x2_fma(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
+// max(x, 0) rounded to bf16, two channels per instruction (cvt with the .relu modifier: ReLU costs nothing).
+__device__ __forceinline__ uint32_t pack_relu_bf16x2(float lo, float hi) {
+    uint32_t d;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+
 struct NetTrunkParams {
     const uint64_t* own;       // [G] side-relative bitboards of the leaves
     const uint64_t* opp;       // [G]
@@ -380,9 +407,12 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         mbar_arrive(bar_empty0 + 8 * stage);
 #pragma unroll
-                        for (int co = 0; co < 32; co += 2)
-                            out[co >> 1] = pack_bf16x2(fmaxf(__uint_as_float(acc[co]) + bias[co], 0.f),
-                                                       fmaxf(__uint_as_float(acc[co + 1]) + bias[co + 1], 0.f));
+                        for (int co = 0; co < 32; co += 2) {
+                            float x0, x1;
+                            f32x2_unpack(f32x2_add(f32x2_pack(__uint_as_float(acc[co]), __uint_as_float(acc[co + 1])),
+                                                   f32x2_pack(bias[co], bias[co + 1])), x0, x1);
+                            out[co >> 1] = pack_relu_bf16x2(x0, x1);
+                        }
                         if (!on_board) {
 #pragma unroll
                             for (int i = 0; i < 16; ++i) out[i] = 0u;         // zero ring / pad cells = conv2's padding
@@ -395,17 +425,22 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         tmem_ld96(t_lane, lo, mid, hi);                           // dc = -1, 0, +1 blocks of this row
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         mbar_arrive(bar_empty0 + 8 * stage);
-                        const bool has_left = c > 0, has_right = c < 7;
-                        float v[2];
+                        // 0/1 factors instead of selects: one FFMA per neighbour term (all operands are finite)
+                        const float hl = c > 0 ? 1.f : 0.f, hr = c < 7 ? 1.f : 0.f;
+                        const uint64_t has_left = f32x2_pack(hl, hl), has_right = f32x2_pack(hr, hr);
 #pragma unroll
-                        for (int co = 0; co < 32; ++co) {
-                            const float up = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co]), 1);
-                            const float dn = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co]), 1);
-                            float x = __uint_as_float(mid[co]) + bias[co];
-                            x += has_left ? up : 0.f;
-                            x += has_right ? dn : 0.f;
-                            v[co & 1] = fmaxf(x, 0.f);
-                            if (co & 1) out[co >> 1] = pack_bf16x2(v[0], v[1]);
+                        for (int co = 0; co < 32; co += 2) {
+                            const float up0 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co]), 1);
+                            const float up1 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co + 1]), 1);
+                            const float dn0 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co]), 1);
+                            const float dn1 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co + 1]), 1);
+                            uint64_t x = f32x2_add(f32x2_pack(__uint_as_float(mid[co]), __uint_as_float(mid[co + 1])),
+                                                   f32x2_pack(bias[co], bias[co + 1]));
+                            x = f32x2_fma(f32x2_pack(up0, up1), has_left, x);
+                            x = f32x2_fma(f32x2_pack(dn0, dn1), has_right, x);
+                            float x0, x1;
+                            f32x2_unpack(x, x0, x1);
+                            out[co >> 1] = pack_relu_bf16x2(x0, x1);
                         }
                     }
                     if (layer < 3) {
