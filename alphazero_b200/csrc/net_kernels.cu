@@ -208,7 +208,8 @@ struct NetTrunkParams {
     __nv_bfloat16* debug;      // optional [n_groups][NET_ROWS][32] dump of the activations after `debug_layer`
     int G;
     int n;                     // board size 6 or 8
-    int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= NET_ROWS
+    int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= n_tiles * 128
+    int n_tiles;               // 128-row tiles per group: 2, 4 or 6 (even: tile parity = TMEM stage = epilogue team)
     int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
 };
 
@@ -262,6 +263,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     constexpr int RPB = (NBOARD + 1) * NET_PITCH;      // rows per board: ring row + n board rows
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
+    const int n_tiles = p.n_tiles, n_rows = n_tiles * NET_TILE_M;
     const uint32_t bars = smem_u32(smem + SM_BARS);
     const uint32_t bar_full0 = bars + 8 * BAR_FULL, bar_empty0 = bars + 8 * BAR_EMPTY, bar_ready0 = bars + 8 * BAR_READY;
     const uint32_t bar_im2col = bars + 8 * BAR_IM2COL, bar_bufb = bars + 8 * BAR_BUFB, bar_weights = bars + 8 * BAR_WEIGHTS;
@@ -307,7 +309,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
 #pragma unroll
             for (int k = 0; k < RPT; ++k) {
                 const int b = (ptid + k * NET_PRODUCERS) / RPB;
-                const bool ok = b < n_boards;
+                const bool ok = b < n_boards && ptid + k * NET_PRODUCERS < n_rows;
                 own[k] = ok ? p.own[board0 + b] : 0ULL;
                 opp[k] = ok ? p.opp[board0 + b] : 0ULL;
             }
@@ -315,9 +317,11 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
 #pragma unroll
             for (int k = 0; k < RPT; ++k) {
                 const int row = ptid + k * NET_PRODUCERS;
-                int b, r, c;
-                net_row_coords(row, RPB, b, r, c);
-                net_im2col_row(smem, row, NBOARD, r, c, own[k], opp[k]);
+                if (row < n_rows) {
+                    int b, r, c;
+                    net_row_coords(row, RPB, b, r, c);
+                    net_im2col_row(smem, row, NBOARD, r, c, own[k], opp[k]);
+                }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(bar_im2col);
@@ -338,11 +342,11 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     : umma_desc(smem_u32(smem + SM_W) + (layer - 1) * NET_LAYER_BYTES, NET_DR_CHUNK_BYTES, 128);
                 // ready[] barriers complete one phase per layer 0..2 of every group (conv4 writes no activations)
                 const uint32_t ready_parity = (gi * 3u + (uint32_t)(layer - 1)) & 1u;
-                for (int t = 0; t < NET_TILES; ++t, ++tile_it) {
+                for (int t = 0; t < n_tiles; ++t, ++tile_it) {
                     if (layer > 0) {
                         // input rows of tile t: tiles t-1 .. t+1 of the previous layer; t-1 and t were awaited for tile t-1
                         if (t == 0) mbar_wait(bar_ready0, ready_parity);
-                        if (t + 1 < NET_TILES) mbar_wait(bar_ready0 + 8 * (t + 1), ready_parity);
+                        if (t + 1 < n_tiles) mbar_wait(bar_ready0 + 8 * (t + 1), ready_parity);
                     }
                     const uint32_t stage = tile_it & 1u, phase = (tile_it >> 1) & 1u;
                     mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
@@ -366,7 +370,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             }
                         }
                         umma_commit(bar_full0 + 8 * stage);
-                        if (layer == 2 && t == NET_TILES - 1) umma_commit(bar_bufb);   // buffer B free for the next im2col
+                        if (layer == 2 && t == n_tiles - 1) umma_commit(bar_bufb);   // buffer B free for the next im2col
                     }
                     __syncwarp();
                 }
@@ -383,7 +387,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
         for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const int board0 = grp * NB;
             const int n_boards = min(NB, p.G - board0);
-            for (int layer = 0; layer < 4; ++layer, tile_base += NET_TILES) {
+            for (int layer = 0; layer < 4; ++layer, tile_base += n_tiles) {
                 uint8_t* dst = smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A);
                 float bias[32];
 #pragma unroll
@@ -391,7 +395,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     const float4 v = reinterpret_cast<const float4*>(bias_all + layer * 32)[i];
                     bias[4 * i] = v.x; bias[4 * i + 1] = v.y; bias[4 * i + 2] = v.z; bias[4 * i + 3] = v.w;
                 }
-                for (int t = team; t < NET_TILES; t += 2) {
+                for (int t = team; t < n_tiles; t += 2) {
                     const uint32_t it = tile_base + t, stage = it & 1u, phase = (it >> 1) & 1u;
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
@@ -516,6 +520,34 @@ __global__ void __launch_bounds__(128) k_net_heads(const __nv_bfloat16* __restri
 
 extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES; }
 
+// Boards per group / tiles per group for a launch over G positions on n_sms persistent CTAs: a group is 2, 4 or 6
+// tiles of 128 rows (rows per board = (n + 1) * 8, plus one closing ring row); the shape that needs the fewest
+// tile-steps on the busiest CTA wins (8x8 on 148 SMs: 4096 positions -> 3 rounds of 10 boards / 6 tiles,
+// 2048 positions -> 2 rounds of 7 boards / 4 tiles).
+static void net_group_shape(int n, int64_t G, int n_sms, int* boards_per_group, int* n_tiles) {
+    const int rpb = (n + 1) * NET_PITCH;
+    int64_t best_cost = -1;
+    for (int tiles = 2; tiles <= NET_TILES; tiles += 2) {
+        const int nb = (tiles * NET_TILE_M - NET_PITCH) / rpb;
+        const int64_t groups = (G + nb - 1) / nb;
+        // + 1 tile-step per group for the pipeline ramp between groups: with few tiles per layer the next layer's
+        // first MMAs wait for the previous layer's epilogue latency (measured: 4 x 4 tiles is no faster than 3 x 6)
+        const int64_t cost = ((groups + n_sms - 1) / n_sms) * (tiles + 1);
+        if (best_cost < 0 || cost <= best_cost) { best_cost = cost; *boards_per_group = nb; *n_tiles = tiles; }
+    }
+}
+
+// Boards per group az_net_trunk uses for (n, G) on the current device (the layout of its debug dump depends on it).
+extern "C" int az_net_trunk_boards_per_group(int n, int64_t G) {
+    int dev = 0, n_sms = 0, nb = 0, tiles = 0;
+    if ((n != 6 && n != 8) || G <= 0) return AZ_ERR_ARG;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+        return AZ_ERR_CUDA;
+    net_group_shape(n, G, n_sms, &nb, &tiles);
+    return nb;
+}
+
 extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob,
                             void* features, void* debug, int debug_layer, void* stream) {
     if ((n != 6 && n != 8) || G < 0 || (G > 0 && (!own || !opp || !wblob || !features))) return AZ_ERR_ARG;
@@ -534,8 +566,7 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;
     p.G = (int)G; p.n = n;
-    // rows per board = (n + 1) * 8, plus the closing ring row: 10 boards (n = 8) or 13 boards (n = 6) per 768 rows
-    p.boards_per_group = (NET_ROWS - NET_PITCH) / ((n + 1) * NET_PITCH);
+    net_group_shape(n, G, n_sms, &p.boards_per_group, &p.n_tiles);
     p.debug_layer = debug ? debug_layer : 0;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM

@@ -247,9 +247,14 @@ int az_net_wblob_bytes(void);
  * positions given as side-relative bitboards (the network input player*grid, base.py:363, is formed on the fly).
  * features: bf16 [G][(n-4)^2 * 32], position-major / channel-minor (fc1's columns are permuted to match).
  * tcgen05 implicit GEMM, activations resident in shared memory; n = 6 or 8.
- * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>. */
+ * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>
+ * (az_net_trunk_boards_per_group gives boards_per_group). */
 int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob, void* features,
                  void* debug, int debug_layer, void* stream);
+
+/* Boards per group az_net_trunk uses for G positions of an n x n board on the current device (> 0; the layout of
+ * its optional debug dump depends on it: group = g / boards, row = (g % boards) * (n+1)*8 + (1+r)*8 + c). */
+int az_net_trunk_boards_per_group(int n, int64_t G);
 
 /* probs[g][0 .. n*n+1) = softmax(logits[g][0 .. n*n+1)), value[g] = tanh(logits[g][n*n+1]); logits bf16, row
  * stride ld.  Replaces log_softmax + exp + tanh of OthelloNet.forward / PolicyValueNetwork.predict

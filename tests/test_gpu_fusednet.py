@@ -46,7 +46,9 @@ def test_trunk_layers_match_fp32(n):
         a3 = F.relu(net.bn3(net.conv3(a2)))
         a4 = F.relu(net.bn4(net.conv4(a3)))
     rpb = (n + 1) * 8                      # rows per board in the kernel's row space: ring row + n rows of 8 cells
-    NB = (768 - 8) // rpb
+    from alphazero_b200 import _lib
+    NB = _lib.lib().az_net_trunk_boards_per_group(n, G)
+    assert NB in ((768 - 8) // rpb, (512 - 8) // rpb, (256 - 8) // rpb)
     n_groups = (G + NB - 1) // NB
     for layer, ref, off in ((1, a1, 0), (2, a2, 0), (3, a3, 1)):
         dbg = torch.zeros(n_groups, 768, 32, dtype=torch.bfloat16, device="cuda")
