@@ -169,3 +169,78 @@ AZ_HD int az_nth_set_bit(uint64_t m, int k) {
     if (k >= c) { pos += 1; }
     return pos;
 }
+
+#ifdef __CUDACC__
+// ------------------------------------------------------------------------------------------------ warp-cooperative forms
+// The tree kernels give one warp to one game, so every lane would repeat the same 8-direction ray computation.
+// These variants give one DIRECTION to a lane instead and OR the eight results with warp shuffles: ~1/5 of the
+// instructions of az_flips / az_legal_mask.  All lanes must be converged and hold the same (own, opp).
+//
+// Lanes 0..3 walk E, S, SE, SW with left shifts by 1, 8, 9, 7; lanes 4..7 walk the opposite directions W, N, NW, NE
+// as the SAME left shifts on the bit-reversed board (brev maps cell (r, c) to (7-r, 7-c)), so the code is uniform.
+// Lanes 8..15 repeat the pattern for a second position (used for "the other side's moves"); lanes 16..31 idle along.
+struct az_dirlane {
+    uint32_t s;        // left shift of this lane's direction
+    uint64_t keep;     // cells that may receive a shifted disc (column wrap guard)
+    bool rev;          // lane works on the bit-reversed board
+};
+
+__device__ __forceinline__ az_dirlane az_dirlane_of(int lane) {
+    const int k = lane & 3;
+    az_dirlane d;
+    d.s = k == 0 ? 1u : (k == 1 ? 8u : (k == 2 ? 9u : 7u));
+    d.keep = k == 1 ? ~0ULL : (k == 3 ? AZ_NOT_COL7 : AZ_NOT_COL0);
+    d.rev = (lane & 4) != 0;
+    return d;
+}
+
+__device__ __forceinline__ uint64_t az_or_reduce8(uint64_t x) {
+    x |= __shfl_xor_sync(0xffffffffu, x, 1);
+    x |= __shfl_xor_sync(0xffffffffu, x, 2);
+    x |= __shfl_xor_sync(0xffffffffu, x, 4);
+    return x;
+}
+
+// Discs flipped when the side owning `own` plays the single-bit square `mv` (same value in every lane).
+__device__ __forceinline__ uint64_t az_flips_warp(uint64_t mv, uint64_t own, uint64_t opp, int lane) {
+    const az_dirlane d = az_dirlane_of(lane);
+    const uint64_t o = d.rev ? __brevll(own) : own, p = d.rev ? __brevll(opp) : opp;
+    uint64_t x = ((d.rev ? __brevll(mv) : mv) << d.s) & d.keep & p;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) x |= (x << d.s) & d.keep & p;
+    x = ((x << d.s) & d.keep & o) ? x : 0ULL;
+    if (d.rev) x = __brevll(x);
+    if (lane & 8) x = 0ULL;                     // one position only: lanes 8..15 would duplicate lanes 0..7
+    x = az_or_reduce8(x);
+    return __shfl_sync(0xffffffffu, x, 0);
+}
+
+// Placement squares of the side owning `own` (result in every lane) and, through other_out, of the other side.
+__device__ __forceinline__ uint64_t az_legal_warp(uint64_t own, uint64_t opp, uint64_t board_mask, int lane,
+                                                  uint64_t* other_out) {
+    const az_dirlane d = az_dirlane_of(lane);
+    const bool second = (lane & 8) != 0;        // lanes 8..15: the roles of own / opp swapped
+    uint64_t o = second ? opp : own, p = second ? own : opp;
+    uint64_t empty = ~(own | opp) & board_mask;
+    if (d.rev) { o = __brevll(o); p = __brevll(p); empty = __brevll(empty); }
+    uint64_t x = (o << d.s) & d.keep & p;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) x |= (x << d.s) & d.keep & p;
+    x = (x << d.s) & d.keep & empty;
+    if (d.rev) x = __brevll(x);
+    x = az_or_reduce8(x);                       // lanes 0..7 hold legal(own, opp), lanes 8..15 legal(opp, own)
+    if (other_out) *other_out = __shfl_sync(0xffffffffu, x, 8);
+    return __shfl_sync(0xffffffffu, x, 0);
+}
+
+// Plays action `a` for the side to move and swaps sides; warp-cooperative twin of az_apply.
+__device__ __forceinline__ void az_apply_warp(uint64_t& own, uint64_t& opp, int a, int lane) {
+    if (a != AZ_PASS) {
+        const uint64_t mv = 1ULL << a;
+        const uint64_t f = az_flips_warp(mv, own, opp, lane);
+        own ^= f | mv;
+        opp ^= f;
+    }
+    const uint64_t t = own; own = opp; opp = t;
+}
+#endif

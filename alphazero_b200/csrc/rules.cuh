@@ -59,6 +59,37 @@ struct az_rules<AZ_GAME_CONNECT4> {
 };
 
 #ifdef __CUDACC__
+// Warp-cooperative rule queries for kernels that give a whole warp to one game (every lane holds the same position;
+// the warp must be converged).  Othello spreads the eight ray directions over lanes (othello_bits.cuh); Connect4's
+// rules are a handful of instructions, so every lane just evaluates them.
+template <int GAME>
+struct az_warp_rules;
+
+template <>
+struct az_warp_rules<AZ_GAME_OTHELLO> {
+    // legal actions of the side to move; *terminal = neither side has a placement (othello.py:212-219)
+    static __device__ __forceinline__ uint64_t legal(uint64_t own, uint64_t opp, const az_dims& d, int lane, bool* terminal) {
+        uint64_t other;
+        const uint64_t l = az_legal_warp(own, opp, d.bmask, lane, &other);
+        if (terminal) *terminal = l == 0ULL && other == 0ULL;
+        return l;
+    }
+    static __device__ __forceinline__ void apply(uint64_t& own, uint64_t& opp, int a, const az_dims&, int lane) {
+        az_apply_warp(own, opp, a, lane);
+    }
+};
+
+template <>
+struct az_warp_rules<AZ_GAME_CONNECT4> {
+    static __device__ __forceinline__ uint64_t legal(uint64_t own, uint64_t opp, const az_dims& d, int, bool* terminal) {
+        if (terminal) *terminal = az_c4_is_terminal(own, opp, d.bmask);
+        return az_c4_legal_cols(own, opp, d.cols);
+    }
+    static __device__ __forceinline__ void apply(uint64_t& own, uint64_t& opp, int a, const az_dims& d, int) {
+        az_c4_apply(own, opp, a, d.bmask);
+    }
+};
+
 // One uniform random playout to the end of the game from (own, opp, player); returns the plies played.
 // Random stream: philox4x32_10(ctr = {id_lo, id_hi, ply, 0}, key = seed).x per ply with a choice to make; the k-th
 // legal action in ascending order is played with k = mulhi(x, #legal).  A side without a move passes (Othello).

@@ -120,7 +120,7 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
                                                       int lane, uint32_t leaf, uint64_t own, uint64_t opp,
                                                       bool with_priors, uint32_t extra_flags, int* k_out) {
     using R = az_rules<GAME>;
-    const uint64_t legal = R::legal(own, opp, d);
+    const uint64_t legal = az_warp_rules<GAME>::legal(own, opp, d, lane, nullptr);
     const int k = R::n_actions(legal);
     *k_out = k;
     const uint32_t base = t.n_alloc[g];
@@ -332,7 +332,7 @@ __device__ __forceinline__ int az_terminal_kind(uint64_t own, uint64_t opp, int 
 // MCT.__search_iter up to the evaluation (mcts.py:226-248): priming, noise, select_node; writes the leaf buffers.
 template <int GAME>
 __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane) {
-    using R = az_rules<GAME>;
+    using W = az_warp_rules<GAME>;
     uint64_t own = t.root_own[g], opp = t.root_opp[g];
     int player = t.root_player[g];
     uint32_t event = t.rng_ctr[g];
@@ -355,7 +355,9 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
         while (true) {
             // invariant: cur is the root or a node with N > 0
             if (!(cur.flags() & AZ_NODE_EXPANDED)) {
-                if (R::is_terminal(own, opp, d)) {              // mcts.py:146-147
+                bool terminal;
+                W::legal(own, opp, d, lane, &terminal);
+                if (terminal) {                                 // mcts.py:146-147
                     kind = t.mode == AZ_MODE_NEURAL ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_ROLLOUT;
                     break;
                 }
@@ -375,7 +377,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
                     event += 1u;
                     int j = (int)az_bounded(r.x, (uint32_t)k);
                     NodeRec c = az_load_node(&nodes[base + j]);
-                    R::apply(own, opp, c.move(), d);
+                    W::apply(own, opp, c.move(), d, lane);
                     player = -player;
                     cur_idx = base + (uint32_t)j;
                     if (len < t.max_depth) { if (lane == 0) path[len] = cur_idx; ++len; }
@@ -386,7 +388,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             NodeRec child;
             uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child);
             event += 1u;
-            R::apply(own, opp, child.move(), d);
+            W::apply(own, opp, child.move(), d, lane);
             player = -player;
             if (len >= t.max_depth) {
                 if (lane == 0) t.status[g] |= AZ_STATUS_DEPTH;
@@ -398,9 +400,11 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             cur = child;
             cur_idx = child_idx;
             if (cur.N == 0u) {                                  // mcts.py:143-144: first visit = the leaf
-                if (t.mode == AZ_MODE_NEURAL)
-                    kind = R::is_terminal(own, opp, d) ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_NN;
-                else
+                if (t.mode == AZ_MODE_NEURAL) {
+                    bool terminal;
+                    W::legal(own, opp, d, lane, &terminal);
+                    kind = terminal ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_NN;
+                } else
                     kind = AZ_LEAF_ROLLOUT;
                 break;
             }
@@ -419,7 +423,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
 }
 
 template <int GAME>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, 8) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
@@ -578,7 +582,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree 
     if (a == 255) return;
     const az_dims d = R::dims(t.n, t.height);
     uint64_t own = t.root_own[g], opp = t.root_opp[g];
-    const bool ok = R::is_legal(R::legal(own, opp, d), a);
+    const bool ok = R::is_legal(az_warp_rules<GAME>::legal(own, opp, d, lane, nullptr), a);
     if (!ok) {
         if (lane == 0) t.status[g] |= AZ_STATUS_ILLEGAL;
         return;
@@ -640,7 +644,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree 
             __syncwarp();
         }
     }
-    R::apply(own, opp, a, d);
+    az_warp_rules<GAME>::apply(own, opp, a, d, lane);
     if (lane == 0) {
         t.root_own[g] = own;
         t.root_opp[g] = opp;
