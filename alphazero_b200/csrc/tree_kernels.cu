@@ -165,11 +165,10 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
 // MCT.back_propagate (mcts.py:197-223): reward for the leaf, sign alternating towards the root; every node on the
 // path gets Q = (N*Q + r)/(N+1) in float64 and N += 1.  Lane j updates path node j (nodes are distinct).
 __device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int g, int lane, int player_to_play,
-                                          double outcome) {
+                                          double outcome, int len) {
     double reward;
     if (fabs(outcome) < 1e-4) reward = 0.0;
     else reward = ((double)player_to_play * outcome > 0.0) ? -fabs(outcome) : fabs(outcome);
-    const int len = (int)t.path_len[g];
     const uint32_t* path = t.path + (size_t)g * t.max_depth;
     for (int j = lane; j < len; j += 32) {
         az_node* nd = &nodes[path[j]];
@@ -187,22 +186,44 @@ __device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int 
     __syncwarp();
 }
 
+// Per-game scalars of the pending leaf, loaded together at kernel entry: the loads are independent, so their
+// latencies overlap instead of forming a chain through az_finish.
+struct LeafRegs {
+    int kind, leaf_player;
+    uint32_t leaf, path_len;
+    uint64_t own, opp;
+    float value;
+};
+
+__device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, int g) {
+    LeafRegs r;
+    r.kind = t.leaf_kind[g];
+    r.leaf = t.leaf_node[g];
+    r.leaf_player = t.leaf_player[g];
+    r.path_len = t.path_len[g];
+    r.own = t.leaf_own[g];
+    r.opp = t.leaf_opp[g];
+    r.value = t.value[g];
+    return r;
+}
+
 template <int GAME>
-__device__ __forceinline__ void az_finish(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane) {
-    const int kind = t.leaf_kind[g];
+__device__ __forceinline__ void az_finish(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane,
+                                          const LeafRegs& lf) {
+    const int kind = lf.kind;
     if (kind == AZ_LEAF_IDLE) return;
-    const uint32_t leaf = t.leaf_node[g];
-    const int leaf_player = t.leaf_player[g];
+    const uint32_t leaf = lf.leaf;
+    const int leaf_player = lf.leaf_player;
     if (kind == AZ_LEAF_NN || kind == AZ_LEAF_PRIME) {
         int k;
-        az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, t.leaf_own[g], t.leaf_opp[g], true, 0u, &k);
+        az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, lf.own, lf.opp, true, 0u, &k);
     }
     if (kind != AZ_LEAF_PRIME) {
         double outcome;
-        if (kind == AZ_LEAF_NN) outcome = (double)((float)leaf_player * t.value[g]);   // base.py:366
-        else if (kind == AZ_LEAF_ROLLOUT) outcome = (double)t.value[g];                 // absolute winner id
+        if (kind == AZ_LEAF_NN) outcome = (double)((float)leaf_player * lf.value);     // base.py:366
+        else if (kind == AZ_LEAF_ROLLOUT) outcome = (double)lf.value;                   // absolute winner id
         else outcome = kind == AZ_LEAF_DRAW ? 0.0 : (kind == AZ_LEAF_BLACK ? 1.0 : -1.0);
-        az_backup(t, nodes, g, lane, leaf_player, outcome);
+        az_backup(t, nodes, g, lane, leaf_player, outcome, (int)lf.path_len);
         if (lane == 0) t.sims_done[g] += 1u;
     }
     if (lane == 0) t.leaf_kind[g] = AZ_LEAF_IDLE;
@@ -294,8 +315,10 @@ __device__ __forceinline__ void az_root_noise(const az_tree& t, az_node* nodes, 
 
 // Picks the child of `cur` that maximises PUCT (neural, mcts.py:44-46) or UCT (rollout, mcts.py:38-42).
 // Returns the child's pool index and its record (broadcast to all lanes).
+// `pre` = record of child `lane` (valid when lane < k), loaded by the caller ahead of time.
 __device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_node* nodes, int g, int lane,
-                                                  const NodeRec& cur, uint32_t event, NodeRec* child_out) {
+                                                  const NodeRec& cur, uint32_t event, NodeRec* child_out,
+                                                  const NodeRec& pre) {
     const int k = cur.n_children();
     const double parentN = (double)cur.N;
     // sqrt / log of the parent's visit count are shared by all children
@@ -306,7 +329,7 @@ __device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_nod
     double best_score = -INFINITY;
     int best_j = -1;
     for (int j = lane; j < k; j += 32) {
-        NodeRec c = az_load_node(&nodes[cur.first_child + j]);
+        const NodeRec c = j < 32 ? pre : az_load_node(&nodes[cur.first_child + j]);
         double s;
         if (t.mode == AZ_MODE_NEURAL) {
             // Q + c_puct * P * sqrt(N_parent) / (1 + N), c_puct = 1.0, evaluated left to right in float64
@@ -352,6 +375,9 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             az_root_noise(t, nodes, g, lane, cur, event);       // mcts.py:235-240
             event += 1u;
         }
+        NodeRec pre;                 // child `lane` of cur, loaded one level ahead (while the move is applied)
+        pre.Q = 0.0; pre.P = 0.f; pre.N = 0u; pre.first_child = 0u; pre.meta = 0u;
+        bool pre_ok = false;
         while (true) {
             // invariant: cur is the root or a node with N > 0
             if (!(cur.flags() & AZ_NODE_EXPANDED)) {
@@ -385,9 +411,13 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
                     break;
                 }
             }
+            if (!pre_ok && lane < cur.n_children()) pre = az_load_node(&nodes[cur.first_child + lane]);
             NodeRec child;
-            uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child);
+            uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child, pre);
             event += 1u;
+            // the chosen child's own children block (if it has one) is fetched now, under the move application
+            pre_ok = child.first_child != 0u;
+            if (pre_ok && lane < child.n_children()) pre = az_load_node(&nodes[child.first_child + lane]);
             W::apply(own, opp, child.move(), d, lane);
             player = -player;
             if (len >= t.max_depth) {
@@ -422,15 +452,24 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
     if (t.mode == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t, d, g, lane, own, opp);
 }
 
+#ifndef AZ_TREE_MIN_CTAS
+#define AZ_TREE_MIN_CTAS 8    // resident CTAs per SM the register budget is sized for (latency-bound kernel)
+#endif
 template <int GAME>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, 8) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
     const az_dims d = az_rules<GAME>::dims(t.n, t.height);
     az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
-    if (do_finish) az_finish<GAME>(t, d, nodes, g, lane);
-    if (do_select && t.sims_done[g] < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane);
+    const uint32_t sims_before = t.sims_done[g];
+    bool backed_up = false;
+    if (do_finish) {
+        const LeafRegs lf = az_load_leaf(t, g);
+        az_finish<GAME>(t, d, nodes, g, lane, lf);
+        backed_up = lf.kind != AZ_LEAF_IDLE && lf.kind != AZ_LEAF_PRIME;
+    }
+    if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane);
 }
 
 // ------------------------------------------------------------------------------------------------ misc kernels
