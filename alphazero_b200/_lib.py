@@ -72,7 +72,8 @@ SIGNATURES = {
     "az_eval_hash": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_u64, c_void_p, c_void_p, c_void_p]),
     "az_net_wblob_bytes": (c_int, []),
     "az_net_trunk_boards_per_group": (c_int, [c_int, c_i64]),
-    "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "az_connect4_image_bits": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_heads": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
 }
 

@@ -207,7 +207,7 @@ struct NetTrunkParams {
     __nv_bfloat16* features;   // [G][(n-4)^2 * 32]  position-major, channel-minor
     __nv_bfloat16* debug;      // optional [n_groups][NET_ROWS][32] dump of the activations after `debug_layer`
     int G;
-    int n;                     // board size 6 or 8
+    int rows, cols;            // image size: 8x8 / 6x6 (Othello) or 7x6 (Connect4Net's view of the 6x7 grid)
     int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= n_tiles * 128
     int n_tiles;               // 128-row tiles per group: 2, 4 or 6 (even: tile parity = TMEM stage = epilogue team)
     int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
@@ -225,15 +225,16 @@ __device__ __forceinline__ void net_row_coords(int row, int rpb, int& b, int& r,
 // 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one row:
 // 16 bf16 = taps 0..8 then zeros, written as the two 16-byte K chunks of the conv1 A operand.
 // (b, r, c) are the row's coordinates; own/opp the bitboards of its board (0 when the board does not exist).
-__device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n, int r, int c, uint64_t own, uint64_t opp) {
+__device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n_rows, int n_cols, int r, int c,
+                                               uint64_t own, uint64_t opp) {
     uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};     // taps 0..8 as bf16 pairs (tap 8 in the low half of w[4])
-    if (r >= 0 && c < n) {
+    if (r >= 0 && c < n_cols) {
 #pragma unroll
         for (int dr = 0; dr < 3; ++dr) {
             const int ur = r + dr - 1;
-            // the three cells (ur, c-1 .. c+1) as bits 0..2; cells outside the n x n board are 0 in both bitboards
+            // the three cells (ur, c-1 .. c+1) as bits 0..2; cells outside the image are 0 in both bitboards
             uint32_t o3 = 0u, p3 = 0u;
-            if (ur >= 0 && ur < n) {
+            if (ur >= 0 && ur < n_rows) {
                 const uint32_t orow = (uint32_t)(own >> (ur * 8)) & 0xFFu, prow = (uint32_t)(opp >> (ur * 8)) & 0xFFu;
                 o3 = ((orow << 1) >> c) & 7u;
                 p3 = ((prow << 1) >> c) & 7u;
@@ -256,11 +257,11 @@ __device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n, in
 //   warp 8      MMA issue (one elected lane) -- tiles of consecutive layers and groups follow each other without a
 //               drain: tile t of layer L+1 only waits for tiles t-1 .. t+1 of layer L (row shifts are +-8 rows);
 //   warps 9-10  producers: im2col of group g+1 into buffer B while group g is in conv4 (which reads buffer A).
-template <int NBOARD>
+template <int IMG_ROWS, int IMG_COLS>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    constexpr int RPB = (NBOARD + 1) * NET_PITCH;      // rows per board: ring row + n board rows
+    constexpr int RPB = (IMG_ROWS + 1) * NET_PITCH;    // rows per board: ring row + image rows
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
     const int n_tiles = p.n_tiles, n_rows = n_tiles * NET_TILE_M;
@@ -320,7 +321,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 if (row < n_rows) {
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
-                    net_im2col_row(smem, row, NBOARD, r, c, own[k], opp[k]);
+                    net_im2col_row(smem, row, IMG_ROWS, IMG_COLS, r, c, own[k], opp[k]);
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
         // ================================================================== epilogue teams
         const int team = warp >> 2;            // TMEM stage this team serves
         const int quarter = warp & 3;          // TMEM lane quarter this warp may read
-        const int m_out = NBOARD - 4;
+        constexpr int M_R = IMG_ROWS - 4, M_C = IMG_COLS - 4;   // conv4 output size
         const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
         mbar_wait(bar_weights, 0u);
         uint32_t tile_base = 0;
@@ -400,7 +401,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
-                    const bool on_board = b < n_boards && r >= 0 && c < NBOARD;
+                    const bool on_board = b < n_boards && r >= 0 && c < IMG_COLS;
                     mbar_wait(bar_full0 + 8 * stage, phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * NET_STAGE_COLS;
@@ -459,10 +460,10 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             for (int ch = 0; ch < 4; ++ch)
                                 *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
                                     make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
-                    } else if (on_board && r >= 2 && r < 2 + m_out && c >= 2 && c < 2 + m_out) {
+                    } else if (on_board && r >= 2 && r < 2 + M_R && c >= 2 && c < 2 + M_C) {
                         // conv4: the outputs are the cells at an inset of 2; features[board][pos*32 + co]
-                        const int pos = (r - 2) * m_out + (c - 2);
-                        uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (m_out * m_out) + pos) * 32);
+                        const int pos = (r - 2) * M_C + (c - 2);
+                        uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)(board0 + b) * (M_R * M_C) + pos) * 32);
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
                             f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
@@ -524,8 +525,8 @@ extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES; }
 // tiles of 128 rows (rows per board = (n + 1) * 8, plus one closing ring row); the shape that needs the fewest
 // tile-steps on the busiest CTA wins (8x8 on 148 SMs: 4096 positions -> 3 rounds of 10 boards / 6 tiles,
 // 2048 positions -> 2 rounds of 7 boards / 4 tiles).
-static void net_group_shape(int n, int64_t G, int n_sms, int* boards_per_group, int* n_tiles) {
-    const int rpb = (n + 1) * NET_PITCH;
+static void net_group_shape(int rows, int64_t G, int n_sms, int* boards_per_group, int* n_tiles) {
+    const int rpb = (rows + 1) * NET_PITCH;
     int64_t best_cost = -1;
     for (int tiles = 2; tiles <= NET_TILES; tiles += 2) {
         const int nb = (tiles * NET_TILE_M - NET_PITCH) / rpb;
@@ -537,20 +538,24 @@ static void net_group_shape(int n, int64_t G, int n_sms, int* boards_per_group, 
     }
 }
 
-// Boards per group az_net_trunk uses for (n, G) on the current device (the layout of its debug dump depends on it).
-extern "C" int az_net_trunk_boards_per_group(int n, int64_t G) {
+static bool net_valid_image(int rows, int cols) {
+    return (rows == 8 && cols == 8) || (rows == 6 && cols == 6) || (rows == 7 && cols == 6);
+}
+
+// Boards per group az_net_trunk uses for (rows, G) on the current device (the layout of its debug dump depends on it).
+extern "C" int az_net_trunk_boards_per_group(int rows, int64_t G) {
     int dev = 0, n_sms = 0, nb = 0, tiles = 0;
-    if ((n != 6 && n != 8) || G <= 0) return AZ_ERR_ARG;
+    if (rows < 6 || rows > 8 || G <= 0) return AZ_ERR_ARG;
     if (cudaGetDevice(&dev) != cudaSuccess ||
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
         return AZ_ERR_CUDA;
-    net_group_shape(n, G, n_sms, &nb, &tiles);
+    net_group_shape(rows, G, n_sms, &nb, &tiles);
     return nb;
 }
 
-extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob,
+extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob,
                             void* features, void* debug, int debug_layer, void* stream) {
-    if ((n != 6 && n != 8) || G < 0 || (G > 0 && (!own || !opp || !wblob || !features))) return AZ_ERR_ARG;
+    if (!net_valid_image(rows, cols) || G < 0 || (G > 0 && (!own || !opp || !wblob || !features))) return AZ_ERR_ARG;
     if (G == 0) return AZ_OK;
     static int n_sms = 0;
     static bool attr_set = false;
@@ -558,27 +563,60 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int
         int dev = 0;
         AZ_CUDA_TRY(cudaGetDevice(&dev));
         AZ_CUDA_TRY(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev));
-        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
-        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<6, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<7, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
         attr_set = true;
     }
     NetTrunkParams p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;
-    p.G = (int)G; p.n = n;
-    net_group_shape(n, G, n_sms, &p.boards_per_group, &p.n_tiles);
+    p.G = (int)G; p.rows = rows; p.cols = cols;
+    net_group_shape(rows, G, n_sms, &p.boards_per_group, &p.n_tiles);
     p.debug_layer = debug ? debug_layer : 0;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM
-    if (n == 8) k_net_trunk<8><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
-    else k_net_trunk<6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    if (rows == 8) k_net_trunk<8, 8><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    else if (rows == 6) k_net_trunk<6, 6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    else k_net_trunk<7, 6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
     AZ_CHECK_LAUNCH("k_net_trunk");
     return AZ_OK;
 }
 
-extern "C" int az_net_heads(const void* logits, int ld, int n, int64_t G, float* probs, float* value, void* stream) {
-    const int A = n * n + 1;
-    if (!az_valid_n(n) || G < 0 || ld < A + 1 || (G > 0 && (!logits || !probs || !value))) return AZ_ERR_ARG;
+// Connect4Net VIEWS the row-major (height, width) grid as a (width, height) image (connect4.py:399): image cell
+// (i, j) is flat index i*height + j of the grid, i.e. grid cell (flat / width, flat % width).  One thread per board
+// moves the canvas bits (grid r*8 + c) to image-canvas bits (i*8 + j) for az_net_trunk.
+__global__ void __launch_bounds__(256) k_connect4_image_bits(const uint64_t* __restrict__ own,
+                                                             const uint64_t* __restrict__ opp, int width, int height,
+                                                             int64_t G, uint64_t* __restrict__ own_img,
+                                                             uint64_t* __restrict__ opp_img) {
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < G; g += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t o = own[g], p = opp[g];
+        uint64_t oi = 0ULL, pi = 0ULL;
+        for (int flat = 0; flat < width * height; ++flat) {
+            const int src = (flat / width) * 8 + (flat % width), dst = (flat / height) * 8 + (flat % height);
+            oi |= ((o >> src) & 1ULL) << dst;
+            pi |= ((p >> src) & 1ULL) << dst;
+        }
+        own_img[g] = oi;
+        opp_img[g] = pi;
+    }
+}
+
+extern "C" int az_connect4_image_bits(const uint64_t* own, const uint64_t* opp, int width, int height, int64_t G,
+                                      uint64_t* own_img, uint64_t* opp_img, void* stream) {
+    if (width < 4 || width > 8 || height < 4 || height > 8 || G < 0 || (G > 0 && (!own || !opp || !own_img || !opp_img)))
+        return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    k_connect4_image_bits<<<az_grid_for(G, 256), 256, 0, (cudaStream_t)stream>>>(own, opp, width, height, G, own_img, opp_img);
+    AZ_CHECK_LAUNCH("k_connect4_image_bits");
+    return AZ_OK;
+}
+
+extern "C" int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* probs, float* value,
+                            void* stream) {
+    const int A = action_size;
+    if (A < 1 || A > 96 || G < 0 || ld < A + 1 || (G > 0 && (!logits || !probs || !value))) return AZ_ERR_ARG;
     if (G == 0) return AZ_OK;
     k_net_heads<<<(unsigned)((G + 3) / 4), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits, ld, A, G, probs,
                                                                        value);

@@ -1,6 +1,8 @@
-"""Hand-written forward of the Othello policy-value network for the leaf batch (evaluator for TreeBatch.search).
+"""Hand-written forward of the convolutional policy-value networks (OthelloNet, Connect4Net) for the leaf batch
+(evaluator for TreeBatch.search).
 
-The weights are the reference module's own (any OthelloNet state_dict, alphazero/games/othello.py:341-359); this file
+The weights are the reference module's own (any OthelloNet / Connect4Net state_dict, alphazero/games/othello.py:341-359,
+connect4.py:369-390); this file
 only re-packs them for the kernels:
   * eval-mode BatchNorm folded into the preceding conv / linear layer (y = s*(Wx + b - mu) + beta, s = g/sqrt(v+eps));
   * conv2..conv4: per kernel ROW one 96x32 bf16 tile -- the three taps (dc) of the row side by side on the N side,
@@ -60,14 +62,29 @@ def pack_trunk_weights(net) -> torch.Tensor:
     return torch.from_numpy(packed.copy())
 
 
-class FusedOthelloEvaluator:
-    """evaluator(tree): fills tree.probs / tree.value for the leaves in tree.leaf_own / tree.leaf_opp."""
+def _image_shape(nn):
+    """(rows, cols) of the image the network's first convolution sees, or None if the fused trunk has no kernel for it."""
+    from .games.connect4 import Connect4Net
+    from .games.othello import OthelloNet
+    if getattr(nn, "n_channels", None) != 32:
+        return None
+    if isinstance(nn, OthelloNet) and nn.n in (6, 8):
+        return nn.n, nn.n
+    if isinstance(nn, Connect4Net) and (nn.width, nn.height) == (7, 6):
+        return nn.width, nn.height          # the (height, width) grid VIEWED as (width, height), connect4.py:399
+    return None
+
+
+class FusedNetEvaluator:
+    """evaluator(tree): fills tree.probs / tree.value for the leaves in tree.leaf_own / tree.leaf_opp.
+
+    Handles the reference's two convolutional architectures -- OthelloNet (n = 6, 8) and Connect4Net (7 x 6) -- which
+    share the trunk (4 x conv3x3/32 + BN + ReLU, pads 1,1,0,0) and differ in the image shape and the fc sizes."""
 
     @staticmethod
     def supports(nn) -> bool:
-        """True for the reference's Othello architecture (layer names / shapes of othello.py:341-359), n = 6 or 8."""
-        from .games.othello import OthelloNet
-        return isinstance(nn, OthelloNet) and nn.n in (6, 8) and nn.n_channels == 32
+        """True for the reference's architectures (layer names / shapes of othello.py:341-359, connect4.py:369-390)."""
+        return _image_shape(nn) is not None
 
     own_kernels_per_call = 2   # k_net_trunk + k_net_heads (replayed inside the CUDA graph)
 
@@ -81,38 +98,53 @@ class FusedOthelloEvaluator:
     def refresh(self, nn) -> None:
         """(Re)packs the weights; call after the network changed (MCT.nn setter, mcts.py:78-83)."""
         t = self.tree
-        n, dev, G = t.n, t.device, t.G
-        if nn.n != n:
-            raise ValueError(f"network is for n={nn.n}, tree for n={n}")
-        if n not in (6, 8):
-            raise ValueError("the fused trunk supports n = 6 or 8")
+        dev, G = t.device, t.G
+        shape = _image_shape(nn)
+        if shape is None:
+            raise ValueError(f"the fused trunk has no kernel for {nn}")
+        self.rows, self.cols = shape
+        self.connect4 = t.spec.game == "connect4"
+        self.own_kernels_per_call = 3 if self.connect4 else 2     # (+ az_connect4_image_bits)
+        if nn.action_size != t.A or (not self.connect4 and nn.n != t.n) or \
+                (self.connect4 and (nn.width, nn.height) != (t.spec.cols, t.spec.rows)):
+            raise ValueError(f"network {nn} does not match the tree's game {t.spec}")
         self.src = nn
-        m = n - 4
+        m = (self.rows - 4) * (self.cols - 4)
+        h1, h2 = nn.fc1.out_features, nn.fc2.out_features
         self.wblob = pack_trunk_weights(nn).to(dev)
-        w1, b1 = _fold_bn(nn.fc1.weight, nn.fc1.bias, nn.fc_bn1)               # [1024][32*m*m] channel-major
-        w1 = w1.reshape(1024, 32, m * m).permute(0, 2, 1).reshape(1024, m * m * 32)
+        w1, b1 = _fold_bn(nn.fc1.weight, nn.fc1.bias, nn.fc_bn1)               # [h1][32*m] channel-major
+        w1 = w1.reshape(h1, 32, m).permute(0, 2, 1).reshape(h1, m * 32)
         w2, b2 = _fold_bn(nn.fc2.weight, nn.fc2.bias, nn.fc_bn2)
         bf = lambda x: x.float().to(dev).to(torch.bfloat16).contiguous()
         self.w1t, self.b1 = bf(w1.t()), bf(b1)                                  # [K][N] for addmm
         self.w2t, self.b2 = bf(w2.t()), bf(b2)
-        A = n * n + 1
+        A = self.A = nn.action_size
         self.ld = ((A + 1 + 7) // 8) * 8                                        # head rows padded to a multiple of 8
-        wh = torch.zeros(self.ld, 512, dtype=torch.float64)
+        wh = torch.zeros(self.ld, h2, dtype=torch.float64)
         bh = torch.zeros(self.ld, dtype=torch.float64)
         wh[:A] = nn.fc_probs.weight.detach().double().cpu(); bh[:A] = nn.fc_probs.bias.detach().double().cpu()
         wh[A] = nn.fc_value.weight.detach().double().cpu()[0]; bh[A] = nn.fc_value.bias.detach().double().cpu()[0]
         self.wht, self.bh = bf(wh.t()), bf(bh)
-        self.features = torch.zeros(G, m * m * 32, dtype=torch.bfloat16, device=dev)
-        self.h1 = torch.empty(G, 1024, dtype=torch.bfloat16, device=dev)
-        self.h2 = torch.empty(G, 512, dtype=torch.bfloat16, device=dev)
+        self.features = torch.zeros(G, m * 32, dtype=torch.bfloat16, device=dev)
+        self.h1 = torch.empty(G, h1, dtype=torch.bfloat16, device=dev)
+        self.h2 = torch.empty(G, h2, dtype=torch.bfloat16, device=dev)
         self.logits = torch.empty(G, self.ld, dtype=torch.bfloat16, device=dev)
+        if self.connect4:
+            self.img_own = torch.zeros(G, dtype=torch.int64, device=dev)
+            self.img_opp = torch.zeros(G, dtype=torch.int64, device=dev)
         self.graph = None
         if self.use_cuda_graph:
             self._capture()
 
     def trunk(self, debug=None, debug_layer: int = 0) -> None:
         t = self.tree
-        _lib.check(_lib.lib().az_net_trunk(_ptr(t.leaf_own), _ptr(t.leaf_opp), t.n, t.G, _ptr(self.wblob),
+        own, opp = t.leaf_own, t.leaf_opp
+        if self.connect4:
+            _lib.check(_lib.lib().az_connect4_image_bits(_ptr(own), _ptr(opp), t.spec.cols, t.spec.rows, t.G,
+                                                         _ptr(self.img_own), _ptr(self.img_opp), _stream()),
+                       "az_connect4_image_bits")
+            own, opp = self.img_own, self.img_opp
+        _lib.check(_lib.lib().az_net_trunk(_ptr(own), _ptr(opp), self.rows, self.cols, t.G, _ptr(self.wblob),
                                            _ptr(self.features), _ptr(debug), int(debug_layer), _stream()), "az_net_trunk")
 
     def _forward(self) -> None:
@@ -122,7 +154,7 @@ class FusedOthelloEvaluator:
             torch._addmm_activation(self.b1, self.features, self.w1t, out=self.h1)      # fused bias + ReLU epilogue
             torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
             torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
-        _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, t.n, t.G, _ptr(t.probs), _ptr(t.value), _stream()),
+        _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, self.A, t.G, _ptr(t.probs), _ptr(t.value), _stream()),
                    "az_net_heads")
 
     def _capture(self) -> None:
@@ -142,3 +174,6 @@ class FusedOthelloEvaluator:
         else:
             self._forward()
         self.n_calls += 1
+
+
+FusedOthelloEvaluator = FusedNetEvaluator   # name used before Connect4Net was covered

@@ -187,7 +187,6 @@ def run_ours(args):
         from alphazero_b200.gamespec import Connect4Spec
         spec = Connect4Spec(7, 6)
         net = Connect4Net(board_width=7, board_height=6)
-        args.net = "torch"                      # the fused tcgen05 trunk is Othello's; Connect4Net runs its own bf16 graph
         flop_per_eval, workload, net_name = 2 * 653376, "connect4_7x6_alphazero_selfplay_neural_mcts", "Connect4Net(7x6)"
     else:
         from alphazero_b200.gamespec import OthelloSpec
@@ -308,7 +307,8 @@ def run_ours(args):
         value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
         e2e_value = e2e_run["sims"] / (e2e_ms * 1e-3)
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": METRIC if args.game == "othello" else "connect4_mcts_simulations_per_sec", "value": value,
+            "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_run["ms"] / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload, "board": f"{spec.cols}x{spec.rows}", "games_per_gpu": G, "n_sim": n_sim,

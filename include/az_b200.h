@@ -243,23 +243,33 @@ int az_eval_hash(const uint64_t* own, const uint64_t* opp, int action_size, int6
 /* Bytes of the packed trunk weights expected by az_net_trunk (built by alphazero_b200/fused_net.py). */
 int az_net_wblob_bytes(void);
 
-/* Fused conv1..conv4 (+ folded BatchNorm + ReLU) of OthelloNet.forward (alphazero/games/othello.py:366-374) for G
- * positions given as side-relative bitboards (the network input player*grid, base.py:363, is formed on the fly).
- * features: bf16 [G][(n-4)^2 * 32], position-major / channel-minor (fc1's columns are permuted to match).
- * tcgen05 implicit GEMM, activations resident in shared memory; n = 6 or 8.
+/* Fused conv1..conv4 (+ folded BatchNorm + ReLU) of OthelloNet.forward / Connect4Net.forward
+ * (alphazero/games/othello.py:366-374, connect4.py:397-403) for G positions given as side-relative bitboards in IMAGE
+ * layout: bit i*8 + j = cell (i, j) of the rows x cols image the first convolution sees (the network input
+ * player*grid, base.py:363, is formed on the fly).  Othello: the image is the board, (rows, cols) = (8, 8) or (6, 6).
+ * Connect4 7x6: Connect4Net views the (height, width) grid as a (width, height) image, (rows, cols) = (7, 6); make
+ * the bitboards with az_connect4_image_bits.
+ * features: bf16 [G][(rows-4)*(cols-4) * 32], position-major / channel-minor (fc1's columns are permuted to match).
+ * tcgen05 implicit GEMM, activations resident in shared memory.
  * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>
  * (az_net_trunk_boards_per_group gives boards_per_group). */
-int az_net_trunk(const uint64_t* own, const uint64_t* opp, int n, int64_t G, const void* wblob, void* features,
-                 void* debug, int debug_layer, void* stream);
+int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob,
+                 void* features, void* debug, int debug_layer, void* stream);
 
-/* Boards per group az_net_trunk uses for G positions of an n x n board on the current device (> 0; the layout of
- * its optional debug dump depends on it: group = g / boards, row = (g % boards) * (n+1)*8 + (1+r)*8 + c). */
-int az_net_trunk_boards_per_group(int n, int64_t G);
+/* Boards per group az_net_trunk uses for G images of `rows` rows on the current device (> 0; the layout of its
+ * optional debug dump depends on it: group = g / boards, row = (g % boards) * (rows+1)*8 + (1+i)*8 + j). */
+int az_net_trunk_boards_per_group(int rows, int64_t G);
 
-/* probs[g][0 .. n*n+1) = softmax(logits[g][0 .. n*n+1)), value[g] = tanh(logits[g][n*n+1]); logits bf16, row
- * stride ld.  Replaces log_softmax + exp + tanh of OthelloNet.forward / PolicyValueNetwork.predict
- * (othello.py:382, base.py:350-355). */
-int az_net_heads(const void* logits, int ld, int n, int64_t G, float* probs, float* value, void* stream);
+/* Image-layout bitboards for az_net_trunk from canvas bitboards of a width x height Connect4 grid: image cell (i, j)
+ * (i < width, j < height) = flat element i*height + j of the row-major grid -- the .view(-1, 1, width, height) of
+ * Connect4Net.forward, alphazero/games/connect4.py:399 (a reinterpretation, not a transpose). */
+int az_connect4_image_bits(const uint64_t* own, const uint64_t* opp, int width, int height, int64_t G,
+                           uint64_t* own_img, uint64_t* opp_img, void* stream);
+
+/* probs[g][0 .. A) = softmax(logits[g][0 .. A)), value[g] = tanh(logits[g][A]); A = action_size <= 96; logits bf16,
+ * row stride ld.  Replaces log_softmax + exp + tanh of the network forward / PolicyValueNetwork.predict
+ * (othello.py:382, connect4.py:411, base.py:350-355). */
+int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* probs, float* value, void* stream);
 
 #ifdef __cplusplus
 }

@@ -507,3 +507,57 @@ def test_self_play_engine_and_trainer_connect4():
     s0 = next(s for s in base if s.move_idx >= 2)
     tw = next(s for s in aug if s.episode_idx == s0.episode_idx and s.move_idx == s0.move_idx)
     assert (tw.state == s0.state[:, ::-1]).all() and (tw.pi == s0.pi[::-1]).all()
+
+
+def test_fused_connect4_net_matches_reference_outputs(golden_dir):
+    """The hand-written forward (az_connect4_image_bits -> tcgen05 trunk on the 7x6 image -> fc GEMMs -> fused heads)
+    on the reference's own weights: conv features against the fp32 module, probs / value within 1e-2 of the
+    reference's fp32 predict (BASELINE.json north_star tolerance), with and without the CUDA graph."""
+    import torch.nn.functional as F
+    from alphazero_b200.fused_net import FusedNetEvaluator
+    net, d = _golden_net(golden_dir)
+    assert FusedNetEvaluator.supports(net)
+    player = d["player"].astype(np.int8)
+    own, opp = _rel(d["black"], d["white"], player)
+    G = len(own)
+    tree = _mk_tree(G, 7, 6)
+    tree.leaf_own.copy_(_dev(own)); tree.leaf_opp.copy_(_dev(opp))
+    for graph in (False, True):
+        ev = FusedNetEvaluator(net, tree, use_cuda_graph=graph)
+        tree.probs.zero_(); tree.value.zero_()
+        ev(tree)
+        torch.cuda.synchronize()
+        assert np.abs(tree.probs.cpu().numpy() - d["probs"]).max() < 1e-2
+        assert np.abs(tree.value.cpu().numpy() - d["value"].reshape(-1)).max() < 1e-2
+        assert torch.allclose(tree.probs.sum(dim=1).cpu(), torch.ones(G), atol=1e-4)
+    x = torch.from_numpy(d["input"]).reshape(-1, 1, 7, 6)      # the (width, height) view of Connect4Net.forward
+    with torch.no_grad():
+        a = F.relu(net.bn1(net.conv1(x))); a = F.relu(net.bn2(net.conv2(a)))
+        a = F.relu(net.bn3(net.conv3(a))); a4 = F.relu(net.bn4(net.conv4(a)))     # [G, 32, 3, 2]
+    feat = ev.features.float().cpu().reshape(G, 6, 32).permute(0, 2, 1).reshape(G, 32, 3, 2)
+    assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
+    # a batch larger than one round of CTAs, with a partially filled last group
+    G2 = 4099
+    idx = np.arange(G2) % G
+    big = _mk_tree(G2, 7, 6, capacity=64)
+    big.leaf_own.copy_(_dev(own[idx])); big.leaf_opp.copy_(_dev(opp[idx]))
+    ev2 = FusedNetEvaluator(net, big)
+    ev2(big)
+    torch.cuda.synchronize()
+    p = big.probs.cpu().numpy()
+    assert np.abs(p[:G] - d["probs"]).max() < 1e-2 and (p[G:2 * G] == p[:G]).all()
+
+
+def test_self_play_connect4_fused_path_is_used():
+    from alphazero_b200.fused_net import FusedNetEvaluator
+    from alphazero_b200.games.connect4 import Connect4Net
+    from alphazero_b200.gamespec import Connect4Spec
+    from alphazero_b200.selfplay import SelfPlayEngine
+    torch.manual_seed(1)
+    eng = SelfPlayEngine(Connect4Net(board_width=7, board_height=6), 32, n=Connect4Spec(7, 6), n_sim=16, seed=3)
+    assert isinstance(eng.evaluator, FusedNetEvaluator)
+    batch = eng.play()
+    assert eng.total_sims == eng.total_moves * 16 and len(batch) == eng.total_moves
+    other = SelfPlayEngine(Connect4Net(board_width=5, board_height=6), 8, n=Connect4Spec(5, 6), n_sim=8, seed=3)
+    assert not isinstance(other.evaluator, FusedNetEvaluator)      # no fused kernel for this size: module's own graph
+    other.play()
