@@ -34,6 +34,6 @@ timeit(ev.trunk, "trunk (tcgen05)")
 timeit(lambda: torch._addmm_activation(ev.b1, ev.features, ev.w1t, out=ev.h1), "fc1+relu (cuBLASLt)")
 timeit(lambda: torch._addmm_activation(ev.b2, ev.h1, ev.w2t, out=ev.h2), "fc2+relu (cuBLASLt)")
 timeit(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cuBLASLt)")
-timeit(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, 8, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
+timeit(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
 timeit(ev, "whole forward (CUDA graph)")
 timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
