@@ -305,6 +305,14 @@ int az_samples_batch(const uint64_t* own, const uint64_t* opp, const float* pi, 
                      const int64_t* index, int64_t S, int64_t B, int rows, int cols, int action_size, float* input,
                      float* pi_out, float* z_out, int32_t* bad_index, void* stream);
 
+/* ---------------------------------------------------------------- measurement only --------------------- */
+
+/* Integer-ALU issue-rate micro-benchmark (the roofline denominator of the board kernels):
+ * launches 148*8 CTAs of 256 threads, each thread running `iters` x 32 instructions of one kind in 8 independent
+ * chains.  kind 0 LOP3, 1 SHF, 2 IADD3, 3 shift-mask-or (the movegen step, 2 instructions).  out: >= 148*8*256
+ * uint32 (sink).  *ops_per_thread (host, optional) = instructions each thread executed in the timed loop. */
+int az_peak_int32(int kind, int iters, uint32_t* out, int64_t out_len, int64_t* ops_per_thread, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -17,7 +17,9 @@ METRICS = [
     "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.sum.pct_of_peak_sustained_elapsed",
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "launch__registers_per_thread", "launch__grid_size",
     "launch__block_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
-    "smsp__inst_executed.sum", "smsp__cycles_active.avg", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
+    "smsp__inst_executed.sum", "smsp__inst_executed_pipe_alu.sum", "smsp__inst_executed_pipe_fmaheavy.sum",
+    "smsp__inst_executed_pipe_fmalite.sum", "smsp__inst_executed_pipe_fma.sum", "smsp__inst_executed_pipe_lsu.sum",
+    "smsp__inst_executed_pipe_fp64.sum", "smsp__cycles_active.avg", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
     "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
     "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct", "smsp__issue_active.avg.pct_of_peak_sustained_active",
 ]
