@@ -11,14 +11,14 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "sample_kernels.cu", "peak_kernels.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "sample_kernels.cu", "peak_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
 LEAF_IDLE, LEAF_NN, LEAF_PRIME, LEAF_ROLLOUT, LEAF_DRAW, LEAF_BLACK, LEAF_WHITE = range(7)
 STATUS_OVERFLOW, STATUS_DEPTH, STATUS_ILLEGAL = 1, 2, 4
 MODE_ROLLOUT, MODE_NEURAL = 0, 1
-GAME_OTHELLO, GAME_CONNECT4 = 0, 1
+GAME_OTHELLO, GAME_CONNECT4, GAME_TICTACTOE = 0, 1, 2
 NODE_EVAL, NODE_EXPANDED, NODE_NOISED = 1, 2, 4
 
 c_void_p, c_int, c_i64, c_u64, c_size_t = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_size_t
@@ -63,6 +63,16 @@ SIGNATURES = {
     "az_connect4_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_int, c_void_p]),
     "az_connect4_perft": (c_int, [c_u64, c_u64, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
                                   ctypes.POINTER(ctypes.c_uint64), c_void_p]),
+    "az_tictactoe_legal": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "az_tictactoe_apply": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p]),
+    "az_tictactoe_terminal_score": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p,
+                                            c_void_p]),
+    "az_tictactoe_encode": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_int, c_void_p]),
+    "az_tictactoe_playouts": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_i64, c_u64, c_u64, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p]),
+    "az_tictactoe_net_floats": (c_int, []),
+    "az_tictactoe_net": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_tree_reset": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p]),
     "az_tree_step": (c_int, [ctypes.POINTER(AzTree), c_int, c_int, c_int, c_void_p]),
     "az_tree_rollout": (c_int, [ctypes.POINTER(AzTree), c_void_p]),

@@ -13,8 +13,7 @@ import torch
 from . import boardops as bo
 from .base import Board, Player
 from .engine import TreeBatch
-from .evaluators import NetEvaluator
-from .fused_net import FusedOthelloEvaluator
+from .fused_net import make_evaluator
 from .gamespec import spec_of
 from .players import AlphaZeroPlayer, MCTSPlayer, RandomPlayer
 
@@ -39,11 +38,7 @@ class _BatchedSide:
             self.tree = TreeBatch(G, n=spec, mode="neural", n_sim_hint=self.n_sim, seed=seed, tie_random=True,
                                   dirichlet_alpha=player.mct.dirichlet_alpha,
                                   dirichlet_epsilon=player.mct.dirichlet_epsilon, enc_dtype=torch.bfloat16)
-            if FusedOthelloEvaluator.supports(nn):
-                self.evaluator = FusedOthelloEvaluator(nn, self.tree)
-                self.tree.set_encoding(False)
-            else:
-                self.evaluator = NetEvaluator(nn, self.tree)
+            self.evaluator = make_evaluator(nn, self.tree)
         elif isinstance(player, MCTSPlayer):
             self.n_sim = player.n_sim
             self.tree = TreeBatch(G, n=spec, mode="rollout", n_sim_hint=self.n_sim, seed=seed, tie_random=True)

@@ -3,6 +3,7 @@
 //
 //   az_rules<AZ_GAME_OTHELLO>   alphazero/games/othello.py   actions 0..63 = cell r*8+c, 64 = pass
 //   az_rules<AZ_GAME_CONNECT4>  alphazero/games/connect4.py  actions 0..width-1 = column, no pass
+//   az_rules<AZ_GAME_TICTACTOE> alphazero/games/tictactoe.py actions = cell r*8+c (r, c < 3), no pass
 //
 // `legal()` returns a 64-bit set of action ids (Othello: placement cells; Connect4: playable columns);
 // children are created in ascending action order.  An empty set means "pass only" for Othello and cannot occur at
@@ -10,6 +11,7 @@
 #pragma once
 #include "connect4_bits.cuh"
 #include "othello_bits.cuh"
+#include "tictactoe_bits.cuh"
 #include "philox.cuh"
 
 // member-function flavour of AZ_HD (a class member cannot be `static inline` twice on the host build)
@@ -58,6 +60,21 @@ struct az_rules<AZ_GAME_CONNECT4> {
     static AZ_HDM int net_index(int a, const az_dims& d) { return a < d.cols ? a : 0; }
 };
 
+template <>
+struct az_rules<AZ_GAME_TICTACTOE> {
+    static AZ_HDM az_dims dims(int, int) { return az_dims{3, 3, AZ_TTT_BOARD}; }
+    static AZ_HDM int action_size(const az_dims&) { return 9; }
+    static AZ_HDM uint64_t legal(uint64_t own, uint64_t opp, const az_dims&) { return az_ttt_legal(own, opp); }
+    static AZ_HDM int n_actions(uint64_t legal) { return legal ? az_popc64(legal) : 1; }
+    static AZ_HDM int nth_action(uint64_t legal, int j) { return legal ? az_nth_set_bit(legal, j) : 0; }
+    static AZ_HDM bool is_legal(uint64_t legal, int a) { return a < 64 && ((legal >> a) & 1ULL); }
+    static AZ_HDM void apply(uint64_t& own, uint64_t& opp, int a, const az_dims&) { az_ttt_apply(own, opp, a); }
+    static AZ_HDM bool is_terminal(uint64_t own, uint64_t opp, const az_dims&) { return az_ttt_is_terminal(own, opp); }
+    static AZ_HDM int winner(uint64_t own, uint64_t opp, int player, const az_dims&) { return az_ttt_winner(own, opp, player); }
+    // tictactoe.py:325, 340: index 3*r + c
+    static AZ_HDM int net_index(int a, const az_dims&) { return (a >> 3) * 3 + (a & 7); }
+};
+
 #ifdef __CUDACC__
 // Warp-cooperative rule queries for kernels that give a whole warp to one game (every lane holds the same position;
 // the warp must be converged).  Othello spreads the eight ray directions over lanes (othello_bits.cuh); Connect4's
@@ -87,6 +104,17 @@ struct az_warp_rules<AZ_GAME_CONNECT4> {
     }
     static __device__ __forceinline__ void apply(uint64_t& own, uint64_t& opp, int a, const az_dims& d, int) {
         az_c4_apply(own, opp, a, d.bmask);
+    }
+};
+
+template <>
+struct az_warp_rules<AZ_GAME_TICTACTOE> {
+    static __device__ __forceinline__ uint64_t legal(uint64_t own, uint64_t opp, const az_dims&, int, bool* terminal) {
+        if (terminal) *terminal = az_ttt_is_terminal(own, opp);
+        return az_ttt_legal(own, opp);
+    }
+    static __device__ __forceinline__ void apply(uint64_t& own, uint64_t& opp, int a, const az_dims&, int) {
+        az_ttt_apply(own, opp, a);
     }
 };
 

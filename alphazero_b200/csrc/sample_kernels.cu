@@ -218,6 +218,7 @@ static bool az_valid_sample_game(int game, int rows, int cols, int action_size) 
     if (game == AZ_GAME_OTHELLO) return az_valid_n(cols) && rows == cols && action_size == cols * cols + 1;
     if (game == AZ_GAME_CONNECT4)
         return cols >= 4 && cols <= 8 && rows >= 4 && rows <= 8 && action_size == cols;
+    if (game == AZ_GAME_TICTACTOE) return rows == 3 && cols == 3 && action_size == 9;
     return false;
 }
 
@@ -228,7 +229,7 @@ extern "C" int64_t az_augment_scratch_bytes(int64_t S) {
 }
 
 extern "C" int az_augment_twins(int game) {
-    return game == AZ_GAME_OTHELLO ? 7 : game == AZ_GAME_CONNECT4 ? 1 : AZ_ERR_ARG;
+    return (game == AZ_GAME_OTHELLO || game == AZ_GAME_TICTACTOE) ? 7 : game == AZ_GAME_CONNECT4 ? 1 : AZ_ERR_ARG;
 }
 
 extern "C" int az_augment_plan(const int32_t* move_idx, int64_t S, int min_move_idx, void* scratch, int64_t* total,
@@ -265,7 +266,7 @@ extern "C" int az_augment_apply(const uint64_t* own, const uint64_t* opp, const 
     p.out_episode = out_episode; p.out_move = out_move; p.out_transf = out_transf;
     p.S = S; p.rows = rows; p.cols = cols; p.action_size = action_size;
     p.n_twins = az_augment_twins(game);
-    p.board_actions = game == AZ_GAME_OTHELLO ? cols * cols : 0;
+    p.board_actions = game == AZ_GAME_CONNECT4 ? 0 : cols * cols;       // TicTacToe: all 9 entries are cells
     k_augment_apply<<<az_sample_grid(S), AZ_SAMPLE_WARPS * 32, 0, stream>>>(p);
     AZ_CHECK_LAUNCH("k_augment_apply");
     return AZ_OK;

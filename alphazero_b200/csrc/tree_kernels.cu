@@ -727,6 +727,8 @@ static int az_check_tree(const az_tree* t) {
         if (!az_valid_n(t->n)) return AZ_ERR_ARG;
     } else if (t->game == AZ_GAME_CONNECT4) {
         if (t->n < 4 || t->n > 8 || t->height < 4 || t->height > 8) return AZ_ERR_ARG;
+    } else if (t->game == AZ_GAME_TICTACTOE) {
+        if (t->n != 3 || t->height != 3) return AZ_ERR_ARG;
     } else {
         return AZ_ERR_ARG;
     }
@@ -746,7 +748,8 @@ static inline int az_warp_grid(int64_t G) { return (int)((G + AZ_WARPS_PER_CTA -
 #define AZ_LAUNCH_GAME(game, kernel, grid, block, stream, ...)                                     \
     do {                                                                                           \
         if ((game) == AZ_GAME_OTHELLO) kernel<AZ_GAME_OTHELLO><<<grid, block, 0, stream>>>(__VA_ARGS__); \
-        else kernel<AZ_GAME_CONNECT4><<<grid, block, 0, stream>>>(__VA_ARGS__);                     \
+        else if ((game) == AZ_GAME_CONNECT4) kernel<AZ_GAME_CONNECT4><<<grid, block, 0, stream>>>(__VA_ARGS__); \
+        else kernel<AZ_GAME_TICTACTOE><<<grid, block, 0, stream>>>(__VA_ARGS__);                    \
     } while (0)
 
 extern "C" int az_tree_reset(const az_tree* t, const uint8_t* mask, void* stream) {

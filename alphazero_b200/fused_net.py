@@ -177,3 +177,58 @@ class FusedNetEvaluator:
 
 
 FusedOthelloEvaluator = FusedNetEvaluator   # name used before Connect4Net was covered
+
+
+class TicTacToeNetEvaluator:
+    """evaluator(tree) for the reference's TicTacToeNet (tictactoe.py:262-316): the whole forward -- 9 -> 9 -> 9 ->
+    (9 + 1) units with the eval-mode BatchNorm1d layers folded in, softmax, tanh -- is one fp32 kernel reading the leaf
+    bitboards (az_tictactoe_net), one thread per position."""
+
+    own_kernels_per_call = 1
+
+    @staticmethod
+    def supports(nn) -> bool:
+        from .games.tictactoe import TicTacToeNet
+        return isinstance(nn, TicTacToeNet)
+
+    def __init__(self, nn, tree, use_cuda_graph: bool = False):
+        if tree.spec.game != "tictactoe":
+            raise ValueError(f"network {nn} does not match the tree's game {tree.spec}")
+        self.tree = tree
+        self.n_calls = 0
+        self.refresh(nn)
+
+    def refresh(self, nn) -> None:
+        self.src = nn
+        w1, b1 = _fold_bn(nn.fc1.weight, nn.fc1.bias, nn.bn1)
+        w2, b2 = _fold_bn(nn.fc2.weight, nn.fc2.bias, nn.bn2)
+        parts = [w1, b1, w2, b2, nn.fc_probs.weight.detach().double(), nn.fc_probs.bias.detach().double(),
+                 nn.fc_value.weight.detach().double(), nn.fc_value.bias.detach().double()]
+        flat = torch.cat([p.reshape(-1).cpu() for p in parts]).float()
+        assert flat.numel() == int(_lib.lib().az_tictactoe_net_floats())
+        self.weights = flat.to(self.tree.device).contiguous()
+
+    def __call__(self, tree=None) -> None:
+        t = self.tree
+        _lib.check(_lib.lib().az_tictactoe_net(_ptr(t.leaf_own), _ptr(t.leaf_opp), t.G, _ptr(self.weights),
+                                               _ptr(t.probs), _ptr(t.value), _stream()), "az_tictactoe_net")
+        self.n_calls += 1
+
+
+def make_evaluator(nn, tree, dtype=torch.bfloat16, path: str = "auto"):
+    """The leaf evaluator for `nn` on `tree`: the hand-written kernels when there is one for the architecture
+    (OthelloNet 6/8, Connect4Net 7x6: tcgen05 trunk; TicTacToeNet: fused MLP) -- these read the leaf bitboards, so the
+    select kernel's encoding is switched off -- else the module's own forward under a CUDA graph.  path: "auto" |
+    "fused" (raise if there is no kernel) | "torch"."""
+    from .evaluators import NetEvaluator
+    if path not in ("auto", "fused", "torch"):
+        raise ValueError(f"unknown network path {path!r}")
+    if path != "torch":
+        for cls in (FusedNetEvaluator, TicTacToeNetEvaluator):
+            if cls.supports(nn):
+                ev = cls(nn, tree)
+                tree.set_encoding(False)
+                return ev
+        if path == "fused":
+            raise ValueError(f"there is no hand-written forward kernel for {nn}")
+    return NetEvaluator(nn, tree, dtype=dtype)

@@ -204,6 +204,75 @@ class Connect4Spec(GameSpec):
         return int(count.value)
 
 
+class TicTacToeSpec(GameSpec):
+    """alphazero/games/tictactoe.py: 3 x 3, actions = canvas cell r*8+c (the reference's (r, c)), no pass."""
+
+    game, game_id = "tictactoe", _lib.GAME_TICTACTOE
+
+    def __init__(self):
+        self.n = self.height = self.rows = self.cols = 3
+        self.action_size = 9
+        self.max_moves = 9
+        self.max_plies = 9
+        self.mean_branching = 5.0
+
+    def __repr__(self):
+        return "TicTacToeSpec()"
+
+    def start_position(self):
+        return 0, 0
+
+    def legal(self, own, opp):
+        out = torch.empty_like(own)
+        _lib.check(_lib.lib().az_tictactoe_legal(_ptr(own), _ptr(opp), own.numel(), _ptr(out), _stream()),
+                   "az_tictactoe_legal")
+        return out
+
+    def apply(self, own, opp, player, action):
+        o2, p2, pl2 = torch.empty_like(own), torch.empty_like(opp), torch.empty_like(player)
+        st = torch.empty(own.numel(), dtype=torch.uint8, device=own.device)
+        _lib.check(_lib.lib().az_tictactoe_apply(_ptr(own), _ptr(opp), _ptr(player), _ptr(action), own.numel(),
+                                                 _ptr(o2), _ptr(p2), _ptr(pl2), _ptr(st), _stream()), "az_tictactoe_apply")
+        return o2, p2, pl2, st
+
+    def terminal_score(self, own, opp, player):
+        term, score, winner = self._outs(own)
+        _lib.check(_lib.lib().az_tictactoe_terminal_score(_ptr(own), _ptr(opp), _ptr(player), own.numel(), _ptr(term),
+                                                          _ptr(score), _ptr(winner), _stream()),
+                   "az_tictactoe_terminal_score")
+        return term, score, winner
+
+    def encode(self, own, opp, dtype=torch.float32):
+        out = torch.empty((own.numel(), 3, 3), dtype=dtype, device=own.device)
+        code = {torch.float32: 0, torch.bfloat16: 1}[dtype]
+        _lib.check(_lib.lib().az_tictactoe_encode(_ptr(own), _ptr(opp), own.numel(), _ptr(out), code, _stream()),
+                   "az_tictactoe_encode")
+        return out
+
+    def legal_action_bits(self, legal):
+        bits = ((legal.unsqueeze(1) >> torch.arange(64, device=legal.device)) & 1).to(torch.float32)
+        return bits, 0
+
+    def action_to_move(self, a: int):
+        return (a // 8, a % 8)
+
+    def move_to_action(self, move) -> int:
+        r, c = int(move[0]), int(move[1])
+        return r * 8 + c if 0 <= r < 3 and 0 <= c < 3 else 255
+
+    def playouts(self, own, opp, player, per_root: int, seed: int, first_id: int = 0):
+        R = own.numel()
+        T = R * per_root
+        fb = torch.empty(T, dtype=torch.int64, device=own.device)
+        fw = torch.empty(T, dtype=torch.int64, device=own.device)
+        win = torch.empty(T, dtype=torch.int8, device=own.device)
+        pl = torch.empty(T, dtype=torch.uint8, device=own.device)
+        _lib.check(_lib.lib().az_tictactoe_playouts(_ptr(own), _ptr(opp), _ptr(player), R, per_root, _to_u64(seed),
+                                                    _to_u64(first_id), _ptr(fb), _ptr(fw), _ptr(win), _ptr(pl),
+                                                    _stream()), "az_tictactoe_playouts")
+        return fb, fw, win, pl
+
+
 def spec_of(board) -> GameSpec:
     """Spec of a drop-in Board object (games/othello.py, games/connect4.py)."""
     game = getattr(board, "game", None)
@@ -211,7 +280,9 @@ def spec_of(board) -> GameSpec:
         return OthelloSpec(board.n)
     if game == "connect4":
         return Connect4Spec(board.width, board.height)
-    raise NotImplementedError(f"the B200 engine supports Othello and Connect4 boards, got {game!r}")
+    if game == "tictactoe":
+        return TicTacToeSpec()
+    raise NotImplementedError(f"the B200 engine supports Othello, Connect4 and TicTacToe boards, got {game!r}")
 
 
 def as_spec(n_or_spec) -> GameSpec:

@@ -13,8 +13,7 @@ import torch
 from . import boardops as bo
 from .base import Board, PolicyValueNetwork, TreeEval
 from .engine import TreeBatch
-from .evaluators import NetEvaluator
-from .fused_net import FusedOthelloEvaluator
+from .fused_net import make_evaluator
 from .gamespec import OthelloSpec, spec_of
 from .utils import fair_max
 
@@ -133,12 +132,9 @@ class MCT:
                 raise ValueError("MCT in neural mode needs a network before search")
             if hasattr(self._nn, "make_batched_evaluator"):      # evaluator supplied by the network object itself
                 self._evaluator = self._nn.make_batched_evaluator(t)
-            elif FusedOthelloEvaluator.supports(self._nn):
-                self._evaluator = FusedOthelloEvaluator(self._nn, t)
-                t.set_encoding(False)
             else:
-                self._evaluator = NetEvaluator(self._nn, t)
                 t.set_encoding(True)
+                self._evaluator = make_evaluator(self._nn, t)     # switches the encoding off when it reads bitboards
 
     def _adopt(self, old: "MCT") -> None:
         """Re-uses the device pools / CUDA graph of a discarded MCT of the same kind (player.reset() builds a new MCT

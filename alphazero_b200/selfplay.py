@@ -13,8 +13,7 @@ import torch
 from . import _lib
 from . import boardops as bo
 from .engine import TreeBatch
-from .evaluators import NetEvaluator
-from .fused_net import FusedOthelloEvaluator
+from .fused_net import make_evaluator
 from .gamespec import as_spec
 from .schedulers import TEMP_SCHEDULERS
 
@@ -59,7 +58,7 @@ class SampleBatch:
         if self.transformation is not None:
             raise ValueError("the batch is already augmented")
         L, dev, S = _lib.lib(), self.own.device, len(self)
-        game_id = {"othello": _lib.GAME_OTHELLO, "connect4": _lib.GAME_CONNECT4}[self.game]
+        game_id = {"othello": _lib.GAME_OTHELLO, "connect4": _lib.GAME_CONNECT4, "tictactoe": _lib.GAME_TICTACTOE}[self.game]
         stream = torch.cuda.current_stream().cuda_stream
         A = self.pi.shape[1]
         scratch = torch.empty(L.az_augment_scratch_bytes(S), dtype=torch.uint8, device=dev)
@@ -135,11 +134,8 @@ class SelfPlayEngine:
                               dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
         if evaluator is not None:
             self.evaluator = evaluator
-        elif network_path == "fused" or (network_path == "auto" and FusedOthelloEvaluator.supports(nn)):
-            self.evaluator = FusedOthelloEvaluator(nn, self.tree)       # hand-written tcgen05 forward
-            self.tree.set_encoding(False)
         else:
-            self.evaluator = NetEvaluator(nn, self.tree, dtype=dtype)   # any PolicyValueNetwork, bf16 CUDA graph
+            self.evaluator = make_evaluator(nn, self.tree, dtype=dtype, path=network_path)
         self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, spec.max_moves)
         dev = self.tree.device
         T, A = max_plies, spec.action_size

@@ -32,6 +32,7 @@ extern "C" {
 
 #define AZ_GAME_OTHELLO 0  /* alphazero/games/othello.py */
 #define AZ_GAME_CONNECT4 1 /* alphazero/games/connect4.py */
+#define AZ_GAME_TICTACTOE 2 /* alphazero/games/tictactoe.py */
 
 /* ABI version, bumped when a signature changes. */
 int az_abi_version(void);
@@ -270,6 +271,42 @@ int az_connect4_image_bits(const uint64_t* own, const uint64_t* opp, int width, 
  * row stride ld.  Replaces log_softmax + exp + tanh of the network forward / PolicyValueNetwork.predict
  * (othello.py:382, connect4.py:411, base.py:350-355). */
 int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* probs, float* value, void* stream);
+
+/* ---------------------------------------------------------------- TicTacToe ----------------------------- */
+/* 3 x 3 board on the same canvas (bit r*8+c, r, c < 3); an action is the canvas cell, there is no pass; the policy
+ * vector index of cell (r, c) is 3*r + c (alphazero/games/tictactoe.py:325, 340).  The tree kernels take
+ * az_tree.game = AZ_GAME_TICTACTOE with n = height = 3. */
+
+/* legal[g] = mask of the empty cells.  Replaces TicTacToeBoard.get_moves / is_legal_move, tictactoe.py:139-150. */
+int az_tictactoe_legal(const uint64_t* own, const uint64_t* opp, int64_t G, uint64_t* legal, void* stream);
+
+/* Places a piece of the side to move on action[g]; status 1 = occupied cell or not a cell (the reference raises
+ * ValueError), board unchanged.  Replaces TicTacToeBoard.play_move, tictactoe.py:157-164. */
+int az_tictactoe_apply(const uint64_t* own, const uint64_t* opp, const int8_t* player, const uint8_t* action,
+                       int64_t G, uint64_t* out_own, uint64_t* out_opp, int8_t* out_player, uint8_t* status,
+                       void* stream);
+
+/* terminal = an alignment of three or a full board; score = 127 (the reference's float("inf")) when the side to move
+ * has two on an alignment whose third cell is free, else 0; winner = absolute id (0 when live or drawn).
+ * Replaces is_game_over / get_score / get_winner, tictactoe.py:127-133, 166-184. */
+int az_tictactoe_terminal_score(const uint64_t* own, const uint64_t* opp, const int8_t* player, int64_t G,
+                                uint8_t* terminal, int8_t* score, int8_t* winner, void* stream);
+
+/* Network input player*grid, [G][3][3]; dtype 0 = float32, 1 = bfloat16 (base.py:363). */
+int az_tictactoe_encode(const uint64_t* own, const uint64_t* opp, int64_t G, void* out, int dtype, void* stream);
+
+/* Uniform random playouts (same random stream convention as az_othello_playouts).  Replaces MCT.rollout +
+ * TicTacToeBoard.get_random_move, mcts.py:173-180, tictactoe.py:152-155. */
+int az_tictactoe_playouts(const uint64_t* own, const uint64_t* opp, const int8_t* player, int64_t n_roots,
+                          int64_t per_root, uint64_t seed, uint64_t first_id, uint64_t* final_black,
+                          uint64_t* final_white, int8_t* winner, uint8_t* plies, void* stream);
+
+/* TicTacToeNet.forward + predict (tictactoe.py:302-316, base.py:350-355) for G positions given as bitboards, fp32:
+ * probs[g][9] = softmax, value[g] = tanh.  weights: az_tictactoe_net_floats() float32 values
+ * W1[9][9] b1[9] W2[9][9] b2[9] Wp[9][9] bp[9] Wv[9] bv with the eval-mode BatchNorm1d layers folded into fc1 / fc2. */
+int az_tictactoe_net_floats(void);
+int az_tictactoe_net(const uint64_t* own, const uint64_t* opp, int64_t G, const float* weights, float* probs,
+                     float* value, void* stream);
 
 /* ---------------------------------------------------------------- training samples ---------------------- */
 

@@ -8,7 +8,7 @@ UNMODIFIED reference (tests/test_samples_cpu.py checks this file against them).
 Follows (file:line relative to /root/reference):
   alphazero/trainer.py:80-118     Sample.create_reflection_twin / create_rotation_twin
   alphazero/trainer.py:275-284    the augmentation loop of AlphaZeroTrainer.self_play
-  alphazero/games/othello.py:414-450, connect4.py:437-445   reflect/rotate_neural_output
+  alphazero/games/othello.py:414-450, connect4.py:437-445, tictactoe.py:343-368   reflect/rotate_neural_output
   alphazero/games/registers.py:37-50   DATA_AUGMENT_STRATEGIES
   alphazero/trainer.py:288-322    _batch_generator
   alphazero/trainer.py:324-381    optimize_network
@@ -27,13 +27,17 @@ CODES = (None, "reflection_horizontal", "rotation_90", "reflection_horizontal+ro
 def _reflect_pi(game, pi, rows, cols):
     if game == "connect4":                      # connect4.py:445: np.flip of the whole vector
         return pi[::-1].copy()
+    if game == "tictactoe":                     # tictactoe.py:353: all 9 entries are cells
+        return np.flip(pi.reshape(rows, cols), axis=1).flatten()
     out = np.zeros_like(pi)                     # othello.py:424-428: flip the board part along axis 1, keep the tail
     out[:-1] = np.flip(pi[:-1].reshape(rows, cols), axis=1).flatten()
     out[-1:] = pi[-1:]
     return out
 
 
-def _rotate_pi(pi, n, angle):
+def _rotate_pi(game, pi, n, angle):
+    if game == "tictactoe":                     # tictactoe.py:368
+        return np.rot90(pi.reshape(n, n), k=angle // 90).flatten()
     out = np.zeros_like(pi)                     # othello.py:444-448
     out[:-1] = np.rot90(pi[:-1].reshape(n, n), k=angle // 90).flatten()
     out[-1:] = pi[-1:]
@@ -45,7 +49,7 @@ def augment(game, state, pi, z, episode_idx, move_idx, min_move_idx=2):
     (originals, then per eligible sample: reflection, then for each rotation the rotated sample and the rotated
     reflection) as a dict of arrays with a `transformation` code per sample."""
     rows, cols = state.shape[1:]
-    rotations = (ROT90, ROT180, ROT270) if game == "othello" else ()
+    rotations = (ROT90, ROT180, ROT270) if game in ("othello", "tictactoe") else ()
     out = [(state[i], pi[i], z[i], episode_idx[i], move_idx[i], 0) for i in range(len(z))]
     for i in range(len(z)):
         if move_idx[i] < min_move_idx:
@@ -53,9 +57,9 @@ def augment(game, state, pi, z, episode_idx, move_idx, min_move_idx=2):
         rs, rp = np.flip(state[i], axis=1), _reflect_pi(game, pi[i], rows, cols)
         out.append((rs, rp, z[i], episode_idx[i], move_idx[i], 1))
         for k, angle in enumerate(rotations):
-            out.append((np.rot90(state[i], k=angle // 90), _rotate_pi(pi[i], cols, angle), z[i], episode_idx[i],
+            out.append((np.rot90(state[i], k=angle // 90), _rotate_pi(game, pi[i], cols, angle), z[i], episode_idx[i],
                         move_idx[i], 2 + 2 * k))
-            out.append((np.rot90(rs, k=angle // 90), _rotate_pi(rp, cols, angle), z[i], episode_idx[i], move_idx[i],
+            out.append((np.rot90(rs, k=angle // 90), _rotate_pi(game, rp, cols, angle), z[i], episode_idx[i], move_idx[i],
                         3 + 2 * k))
     return dict(state=np.stack([o[0] for o in out]), pi=np.stack([o[1] for o in out]),
                 z=np.array([o[2] for o in out], dtype=np.int8),

@@ -30,6 +30,7 @@ import alphazero.trainer as ref_trainer  # noqa: E402
 from alphazero.games.connect4 import Connect4Board, Connect4Config, Connect4Net  # noqa: E402
 from alphazero.games.othello import OthelloBoard, OthelloConfig, OthelloNet  # noqa: E402
 from alphazero.games.registers import DATA_AUGMENT_STRATEGIES  # noqa: E402
+from alphazero.games.tictactoe import TicTacToeNet  # noqa: E402
 
 TAGS = [None, "reflection_horizontal", "rotation_90", "reflection_horizontal+rotation_90", "rotation_180",
         "reflection_horizontal+rotation_180", "rotation_270", "reflection_horizontal+rotation_270"]
@@ -128,6 +129,7 @@ def main():
     make_augment("othello_n8", "othello", OthelloNet(n=8), 8, 8, 11)
     make_augment("othello_n6", "othello", OthelloNet(n=6), 6, 6, 12)
     make_augment("connect4_7x6", "connect4", Connect4Net(board_width=7, board_height=6), 6, 7, 13)
+    make_augment("tictactoe", "tictactoe", TicTacToeNet(), 3, 3, 14)
     make_train("connect4_7x6", "connect4", Connect4Config(batch_size=16, epochs=3, learning_rate=0.01), Connect4Net,
                Connect4Board, 6, 7, 21, full_state=True)
     make_train("othello_n6", "othello", OthelloConfig(board_size=6, batch_size=16, epochs=2, learning_rate=0.01),

@@ -47,6 +47,14 @@ def lib():
         L.orc_connect4_perft.restype = u64
         L.orc_connect4_perft.argtypes = [u64, u64, i32, i32, i32, i32]
         L.orc_connect4_playouts.argtypes = [vp, vp, vp, i32, i32, i64, i64, u64, u64, vp, vp, vp, vp]
+        L.orc_tictactoe_legal.argtypes = [vp, vp, vp, i64, vp]
+        L.orc_tictactoe_apply.argtypes = [vp, vp, vp, vp, i64, vp, vp, vp, vp]
+        L.orc_tictactoe_terminal.argtypes = [vp, vp, vp, i64, vp, vp, vp]
+        L.orc_tictactoe_perft.restype = u64
+        L.orc_tictactoe_perft.argtypes = [u64, u64, i32, i32]
+        L.orc_tictactoe_playouts.argtypes = [vp, vp, vp, i64, i64, u64, u64, vp, vp, vp, vp]
+        L.orc_mct_new_tictactoe.restype = vp
+        L.orc_mct_new_tictactoe.argtypes = [i32, i32, u64, u64, vp, vp]
         L.orc_mct_new_connect4.restype = vp
         L.orc_mct_new_connect4.argtypes = [i32, i32, i32, i32, u64, u64, vp, vp]
         _lib = L
@@ -142,12 +150,50 @@ def c4_playouts(black, white, player, width, height, per_root, seed, first_id=0)
     return fb, fw, win, pl
 
 
+# ---- TicTacToe (3 x 3 on the canvas, action = canvas cell r*8+c) ----
+
+def ttt_legal(black, white, player):
+    out = np.zeros(len(black), np.uint64)
+    lib().orc_tictactoe_legal(P(black), P(white), P(player), len(black), P(out))
+    return out
+
+
+def ttt_apply(black, white, player, action):
+    G = len(black)
+    ob, ow = np.zeros(G, np.uint64), np.zeros(G, np.uint64)
+    op, st = np.zeros(G, np.int8), np.zeros(G, np.uint8)
+    lib().orc_tictactoe_apply(P(black), P(white), P(player), P(action), G, P(ob), P(ow), P(op), P(st))
+    return ob, ow, op, st
+
+
+def ttt_terminal(black, white, player):
+    G = len(black)
+    t, s, w = np.zeros(G, np.uint8), np.zeros(G, np.int8), np.zeros(G, np.int8)
+    lib().orc_tictactoe_terminal(P(black), P(white), P(player), G, P(t), P(s), P(w))
+    return t, s, w
+
+
+def ttt_perft(depth, black=0, white=0, player=1):
+    return int(lib().orc_tictactoe_perft(black, white, player, depth))
+
+
+def ttt_playouts(black, white, player, per_root, seed, first_id=0):
+    T = len(black) * per_root
+    fb, fw = np.zeros(T, np.uint64), np.zeros(T, np.uint64)
+    win, pl = np.zeros(T, np.int8), np.zeros(T, np.uint8)
+    lib().orc_tictactoe_playouts(P(black), P(white), P(player), len(black), per_root, seed, first_id,
+                                 P(fb), P(fw), P(win), P(pl))
+    return fb, fw, win, pl
+
+
 class OracleMCT:
     """Sequential pointer-tree MCT of the oracle (restates alphazero/mcts.py).  `n` = Othello board size, or
     (width, height) with game="connect4"."""
 
     def __init__(self, n, mode="neural", tie_random=False, salt=0, seed=0, dirichlet=None, game="othello"):
-        if game == "connect4":
+        if game == "tictactoe":
+            self.h = lib().orc_mct_new_tictactoe(1 if mode == "neural" else 0, int(tie_random), salt, seed, None, None)
+        elif game == "connect4":
             self.h = lib().orc_mct_new_connect4(n[0], n[1], 1 if mode == "neural" else 0, int(tie_random), salt, seed,
                                                 None, None)
         else:

@@ -197,7 +197,8 @@ def test_connect4_net_and_config_match_reference(w, h):
     import alphazero_b200.games.registers as reg
     assert dataclasses.asdict(c4.Connect4Config()) == dataclasses.asdict(r_c4.Connect4Config())
     for name in ("CONFIGS_REGISTER", "BOARDS_REGISTER", "NETWORKS_REGISTER", "MOVE_FORMATS_REGISTER", "DATA_AUGMENT_STRATEGIES"):
-        assert set(getattr(reg, name)) == set(getattr(r_reg, name)) - {"tictactoe"}
+        assert set(getattr(reg, name)) == set(getattr(r_reg, name))
+    assert reg.GAMES_SET == r_reg.GAMES_SET
     assert reg.MOVE_FORMATS_REGISTER["connect4"].value == r_reg.MOVE_FORMATS_REGISTER["connect4"].value
     assert [t.value for t in reg.DATA_AUGMENT_STRATEGIES["connect4"].rotations] == \
         [t.value for t in r_reg.DATA_AUGMENT_STRATEGIES["connect4"].rotations] == []
@@ -240,3 +241,47 @@ def test_connect4_golden_net_loads(golden_dir=None):
     net.load_state_dict({k[3:]: torch.from_numpy(d[k]) for k in d.files if k.startswith("sd.")})
     p, v = net.predict(torch.from_numpy(d["input"]))
     assert np.abs(p.numpy() - d["probs"]).max() < 1e-6 and np.abs(v.numpy() - d["value"]).max() < 1e-6
+
+
+@needs_ref
+def test_tictactoe_classes_match_reference():
+    """TicTacToeConfig defaults, class surface, network parameter names, outputs and the policy-vector helpers."""
+    import_reference()
+    import alphazero.games.tictactoe as r_ttt
+    import alphazero.games.registers as r_reg
+    import alphazero_b200.games.tictactoe as ttt
+    import alphazero_b200.games.registers as reg
+    assert dataclasses.asdict(ttt.TicTacToeConfig()) == dataclasses.asdict(r_ttt.TicTacToeConfig())
+    assert [t.value for t in reg.DATA_AUGMENT_STRATEGIES["tictactoe"].rotations] == \
+        [t.value for t in r_reg.DATA_AUGMENT_STRATEGIES["tictactoe"].rotations]
+    for ref_cls, cls in ((r_ttt.TicTacToeBoard, ttt.TicTacToeBoard), (r_ttt.TicTacToeNet, ttt.TicTacToeNet)):
+        for name, fn in _public_methods(ref_cls).items():
+            if name in ("human_display", "pixel_display", "get_alignments_sums", "get_nb_free_cells_on_alignments"):
+                continue      # rendering / NumPy helpers of the reference's rule code
+            assert hasattr(cls, name), name
+            ref_params = list(inspect.signature(fn).parameters)
+            assert list(inspect.signature(getattr(cls, name)).parameters)[:len(ref_params)] == ref_params, name
+        assert list(inspect.signature(cls.__init__).parameters) == list(inspect.signature(ref_cls.__init__).parameters)
+    torch.manual_seed(0)
+    net, ref = ttt.TicTacToeNet(), r_ttt.TicTacToeNet()
+    assert list(net.state_dict().keys()) == list(ref.state_dict().keys())
+    ref.load_state_dict(net.state_dict())
+    assert net.get_parameters_count() == ref.get_parameters_count()
+    x = torch.randint(-1, 2, (11, 3, 3)).float()
+    p, v = net.predict(x)
+    rp, rv = ref.predict(x)
+    assert torch.equal(p, rp) and torch.equal(v, rv)
+    p1, _ = net.predict(x[0])                       # a single 3x3 input gets a batch dimension (tictactoe.py:305-306)
+    assert p1.shape == (1, 9)
+    probs = np.random.RandomState(0).rand(9).astype(np.float32)
+    moves = [(0, 1), (2, 2), (1, 0)]
+    assert net.get_normalized_probs(probs, moves) == ref.get_normalized_probs(probs, moves)
+    assert net.get_normalized_probs(np.zeros(9, np.float32), moves) == {m: 1 / 3 for m in moves}
+    mp = {(0, 1): 0.25, (2, 2): 0.75}
+    assert (net.to_neural_output(mp) == ref.to_neural_output(mp)).all()
+    for axis in (0, 1):
+        assert (net.reflect_neural_output(probs, axis) == ref.reflect_neural_output(probs, axis)).all()
+    for angle in (90, 180, 270):
+        assert (net.rotate_neural_output(probs, angle) == ref.rotate_neural_output(probs, angle)).all()
+    with pytest.raises(ValueError):
+        net.reflect_neural_output(np.zeros(10), 1)

@@ -15,14 +15,15 @@ GOLDEN = os.path.join(HERE, "golden")
 import samples_oracle as so  # noqa: E402
 
 
-@pytest.mark.parametrize("name,game", [("othello_n8", "othello"), ("othello_n6", "othello"), ("connect4_7x6", "connect4")])
+@pytest.mark.parametrize("name,game", [("othello_n8", "othello"), ("othello_n6", "othello"), ("connect4_7x6", "connect4"),
+                                       ("tictactoe", "tictactoe")])
 def test_oracle_augmentation_matches_reference_fixture(name, game):
     d = np.load(os.path.join(GOLDEN, f"augment_{name}.npz"))
     got = so.augment(game, d["in_state"], d["in_pi"], d["in_z"], d["in_episode_idx"], d["in_move_idx"])
     for k in ("state", "pi", "z", "episode_idx", "move_idx", "transformation"):
         assert np.array_equal(got[k], d[f"out_{k}"]), k
     eligible = int((d["in_move_idx"] >= 2).sum())
-    assert len(got["z"]) == len(d["in_z"]) + eligible * (7 if game == "othello" else 1)
+    assert len(got["z"]) == len(d["in_z"]) + eligible * (1 if game == "connect4" else 7)
 
 
 def test_state_bits_round_trip():
