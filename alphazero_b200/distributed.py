@@ -24,6 +24,8 @@ def broadcast_network(nn: torch.nn.Module, src: int = 0, group=None) -> None:
         by_dtype.setdefault(t.dtype, []).append(t)
     for dtype, ts in by_dtype.items():
         flat = torch.cat([t.detach().reshape(-1) for t in ts])
+        if dist.get_backend(group) == "nccl" and not flat.is_cuda:      # a network kept on the CPU (config.device)
+            flat = flat.cuda()
         dist.broadcast(flat, src=src, group=group)
         off = 0
         with torch.no_grad():
