@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "sample_kernels.cu", "peak_kernels.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "sample_kernels.cu", "peak_kernels.cu", "mma_probe.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
@@ -90,6 +90,7 @@ SIGNATURES = {
     "az_augment_plan": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p]),
     "az_augment_apply": (c_int, [c_void_p] * 6 + [c_i64, c_int, c_int, c_int, c_int] + [c_void_p] * 9),
     "az_peak_int32": (c_int, [c_int, c_int, c_void_p, c_i64, ctypes.POINTER(ctypes.c_int64), c_void_p]),
+    "az_peak_mma": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "az_samples_batch": (c_int, [c_void_p] * 5 + [c_i64, c_i64, c_int, c_int, c_int] + [c_void_p] * 5),
 }
 

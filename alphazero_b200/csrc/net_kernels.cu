@@ -17,7 +17,7 @@
 //     Measured on B200, an M128 N32 K16 SS-mode MMA costs ~90 cycles of which ~50 are a per-instruction cost that
 //     does not depend on N, so tripling N per instruction is what pays (profiles/r1_trunk_experiments.txt);
 //   * B operands (BatchNorm folded in) sit in shared memory for the whole kernel;
-//   * accumulators (128 rows x 96 fp32 columns) live in TMEM, double buffered; two teams of four epilogue warps read
+//   * accumulators (128 rows x 96 fp32 columns) live in TMEM in four stages; two teams of four epilogue warps read
 //     them with tcgen05.ld, combine the dc blocks, add the folded bias, apply ReLU, round to bf16 and write the next
 //     layer's A operand;
 //   * conv1 (1 input channel, K = 9 padded to 16) is one N = 32 MMA per tile on a 9-tap im2col built straight from
@@ -50,28 +50,36 @@
 #define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES + NET_CONV1_TILE_BYTES)  // conv2..conv4 tiles, then the conv1 tile
 #define NET_WBLOB_F32 (4 * 32)                     // folded biases of conv1..conv4
 #define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
-#define NET_WORKERS 256           // warps 0-7: epilogue (two teams of 4 warps, one per TMEM stage)
-#define NET_PRODUCERS 64          // warps 9-10: im2col of the NEXT group while the current one is in conv4
-#define NET_THREADS (NET_WORKERS + 32 + NET_PRODUCERS)   // warp 8: TMEM allocation + MMA issue
+#define NET_WORKERS 256           // warps 0-7: epilogue (two teams of 4 warps; team k serves the tiles t = k mod 2)
+#define NET_MMA_WARPS 2           // warps 8-9 issue the MMAs of the even / odd tiles: issuing a tile costs one thread
+                                  // ~700 cycles (60 per tcgen05.mma + barrier bookkeeping) against ~290 cycles of
+                                  // tensor-pipe time, so two issuers are needed to keep the pipe fed
+#define NET_PRODUCERS 64          // warps 10-11: im2col of the NEXT group while the current one is in conv4
+#define NET_THREADS (NET_WORKERS + 32 * NET_MMA_WARPS + NET_PRODUCERS)
 #define NET_STAGE_COLS 128        // TMEM columns per accumulator stage (96 used)
-#define NET_TMEM_COLS 256         // two stages
+#define NET_STAGES 4              // accumulator stages: the MMA warp may run a whole layer of a 4-tile group ahead
+#define NET_TMEM_COLS (NET_STAGES * NET_STAGE_COLS)   // 512: all of the SM's TMEM (one CTA per SM)
 
 // shared memory map (bytes)
 #define SM_BUF_A 0
 #define SM_BUF_B (SM_BUF_A + NET_BUF_BYTES)
-#define SM_W (SM_BUF_B + NET_BUF_BYTES)
+#define SM_IM2COL (SM_BUF_B + NET_BUF_BYTES)          // conv1's A operand (K = 16: two chunk planes), own buffer so that
+#define NET_IM2COL_BYTES (2 * NET_CHUNK_BYTES)        // the producers can fill it for group g+1 while group g computes
+#define SM_W (SM_IM2COL + NET_IM2COL_BYTES)
 // mbarriers: full[2] / empty[2] accumulator stages, ready[NET_TILES] "rows of tile t of this layer are in shared
-// memory", im2col "conv1's A operand of the group is in place", bufb "buffer B is no longer read" (conv3 done),
+// memory", im2col "conv1's A operand of the group is in place", bufb "the im2col buffer is no longer read" (conv1
+// done), afree "buffer A is no longer read" (conv4 done),
 // weights "the bulk copy of the weight blob has landed"
 #define SM_BARS (SM_W + NET_WBLOB_BYTES)
 #define BAR_FULL 0
-#define BAR_EMPTY 2
-#define BAR_READY 4
+#define BAR_EMPTY NET_STAGES
+#define BAR_READY (2 * NET_STAGES)
 #define BAR_IM2COL (BAR_READY + NET_TILES)
 #define BAR_BUFB (BAR_IM2COL + 1)
 #define BAR_WEIGHTS (BAR_BUFB + 1)
-#define NET_N_BARS (BAR_WEIGHTS + 1)
-#define SM_TMEM_PTR (SM_BARS + 16 * 8)
+#define BAR_AFREE (BAR_WEIGHTS + 1)
+#define NET_N_BARS (BAR_AFREE + 1)
+#define SM_TMEM_PTR (SM_BARS + 24 * 8)   // room for NET_N_BARS = 17 barriers
 #define SM_TOTAL (SM_TMEM_PTR + 16)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -247,7 +255,7 @@ __device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n_row
             }
         }
     }
-    uint8_t* dst = smem + SM_BUF_B + (NET_MARGIN + row) * 16;
+    uint8_t* dst = smem + SM_IM2COL + (NET_MARGIN + row) * 16;
     *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
     *reinterpret_cast<uint4*>(dst + NET_CHUNK_BYTES) = make_uint4(w[4], 0u, 0u, 0u);
 }
@@ -256,7 +264,8 @@ __device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n_row
 //   warps 0-7   epilogue: team = warp / 4 serves TMEM stage `team`, quarter = warp % 4 is the TMEM lane quarter;
 //   warp 8      MMA issue (one elected lane) -- tiles of consecutive layers and groups follow each other without a
 //               drain: tile t of layer L+1 only waits for tiles t-1 .. t+1 of layer L (row shifts are +-8 rows);
-//   warps 9-10  producers: im2col of group g+1 into buffer B while group g is in conv4 (which reads buffer A).
+//   warps 8-9   MMA issue, even / odd tiles;
+//   warps 10-11 producers: im2col of group g+1 into its own buffer while group g runs conv2..conv4.
 template <int IMG_ROWS, int IMG_COLS>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -268,16 +277,17 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     const uint32_t bars = smem_u32(smem + SM_BARS);
     const uint32_t bar_full0 = bars + 8 * BAR_FULL, bar_empty0 = bars + 8 * BAR_EMPTY, bar_ready0 = bars + 8 * BAR_READY;
     const uint32_t bar_im2col = bars + 8 * BAR_IM2COL, bar_bufb = bars + 8 * BAR_BUFB, bar_weights = bars + 8 * BAR_WEIGHTS;
+    const uint32_t bar_afree = bars + 8 * BAR_AFREE;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SM_TMEM_PTR);
     constexpr int MMA_WARP = NET_WORKERS / 32;
 
     // ---- one-time setup: barriers, async bulk copy of the weights, zeroed activation buffers, TMEM
     if (tid == 0) {
-        mbar_init(bar_full0, 1); mbar_init(bar_full0 + 8, 1);
-        mbar_init(bar_empty0, 128); mbar_init(bar_empty0 + 8, 128);
+        for (int st = 0; st < NET_STAGES; ++st) { mbar_init(bar_full0 + 8 * st, 1); mbar_init(bar_empty0 + 8 * st, 128); }
         for (int t = 0; t < NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 128);
         mbar_init(bar_im2col, NET_PRODUCERS);
-        mbar_init(bar_bufb, 1);
+        mbar_init(bar_bufb, NET_MMA_WARPS);
+        mbar_init(bar_afree, NET_MMA_WARPS);
         mbar_init(bar_weights, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
@@ -297,9 +307,9 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
 
-    if (warp > MMA_WARP) {
+    if (warp >= MMA_WARP + NET_MMA_WARPS) {
         // ================================================================== producers: im2col of every group
-        const int ptid = tid - (NET_WORKERS + 32);
+        const int ptid = tid - (NET_WORKERS + 32 * NET_MMA_WARPS);
         uint32_t gi = 0;
         for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
             const int board0 = grp * NB;
@@ -314,7 +324,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 own[k] = ok ? p.own[board0 + b] : 0ULL;
                 opp[k] = ok ? p.opp[board0 + b] : 0ULL;
             }
-            if (gi > 0) mbar_wait(bar_bufb, (gi - 1u) & 1u);      // conv3 of the previous group has read buffer B
+            if (gi > 0) mbar_wait(bar_bufb, (gi - 1u) & 1u);      // conv1 of the previous group has read the im2col buffer
 #pragma unroll
             for (int k = 0; k < RPT; ++k) {
                 const int row = ptid + k * NET_PRODUCERS;
@@ -327,31 +337,44 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_arrive(bar_im2col);
         }
-    } else if (warp == MMA_WARP) {
-        // ================================================================== MMA issue
+    } else if (warp >= MMA_WARP) {
+        // ================================================================== MMA issue: this warp takes the tiles
+        // t = mma_id (mod NET_MMA_WARPS) of every layer
+        const int mma_id = warp - MMA_WARP;
         const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc96 = umma_idesc_bf16_m128(NET_N3);
         mbar_wait(bar_weights, 0u);
-        uint32_t gi = 0, tile_it = 0;
+        uint32_t gi = 0, tile_base = 0;
+        // debug_layer == 100: cycle accounting of this warp into debug[blockIdx.x][0..3] (int64)
+        const bool timing = p.debug && p.debug_layer == 100;
+        long long tm_ready = 0, tm_empty = 0, tm_issue = 0, tm_im2col = 0;
+        const long long tm_start = clock64();
         for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+            long long c0 = timing ? clock64() : 0;
             mbar_wait(bar_im2col, gi & 1u);
-            // ---- layer 0: conv1 (im2col in B -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
-            for (int layer = 0; layer < 4; ++layer) {
-                const uint32_t src = smem_u32(smem + ((layer & 1) ? SM_BUF_A : SM_BUF_B));
+            if (timing) tm_im2col += clock64() - c0;
+            // ---- layer 0: conv1 (im2col buffer -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
+            for (int layer = 0; layer < 4; ++layer, tile_base += n_tiles) {
+                const uint32_t src = smem_u32(smem + (layer == 0 ? SM_IM2COL : (layer & 1) ? SM_BUF_A : SM_BUF_B));
                 const uint64_t a_layer = umma_desc(src + NET_MARGIN * 16, NET_CHUNK_BYTES, 128);
                 const uint64_t b_layer = layer == 0
                     ? umma_desc(smem_u32(smem + SM_W) + 3 * NET_LAYER_BYTES, 512, 128)
                     : umma_desc(smem_u32(smem + SM_W) + (layer - 1) * NET_LAYER_BYTES, NET_DR_CHUNK_BYTES, 128);
                 // ready[] barriers complete one phase per layer 0..2 of every group (conv4 writes no activations)
                 const uint32_t ready_parity = (gi * 3u + (uint32_t)(layer - 1)) & 1u;
-                for (int t = 0; t < n_tiles; ++t, ++tile_it) {
+                for (int t = mma_id; t < n_tiles; t += NET_MMA_WARPS) {
+                    const uint32_t tile_it = tile_base + (uint32_t)t;
+                    long long c1 = timing ? clock64() : 0;
                     if (layer > 0) {
-                        // input rows of tile t: tiles t-1 .. t+1 of the previous layer; t-1 and t were awaited for tile t-1
-                        if (t == 0) mbar_wait(bar_ready0, ready_parity);
+                        // input rows of tile t: tiles t-1 .. t+1 of the previous layer
+                        if (t > 0) mbar_wait(bar_ready0 + 8 * (t - 1), ready_parity);
+                        mbar_wait(bar_ready0 + 8 * t, ready_parity);
                         if (t + 1 < n_tiles) mbar_wait(bar_ready0 + 8 * (t + 1), ready_parity);
                     }
-                    const uint32_t stage = tile_it & 1u, phase = (tile_it >> 1) & 1u;
+                    long long c2 = timing ? clock64() : 0;
+                    const uint32_t stage = tile_it % NET_STAGES, phase = (tile_it / NET_STAGES) & 1u;
                     mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    long long c3 = timing ? clock64() : 0;
                     const uint32_t d_tmem = tmem_base + stage * NET_STAGE_COLS;
                     const uint64_t a_tile = a_layer + (uint64_t)(t * (NET_TILE_M * 16 / 16));
                     if (elect_one()) {
@@ -371,11 +394,24 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             }
                         }
                         umma_commit(bar_full0 + 8 * stage);
-                        if (layer == 2 && t == n_tiles - 1) umma_commit(bar_bufb);   // buffer B free for the next im2col
+                        // conv1 has read the im2col buffer once the last conv1 tile of BOTH issuers is done: the
+                        // producers may then build the next group's im2col (while this group runs conv2..conv4)
+                        if (layer == 0 && t + NET_MMA_WARPS >= n_tiles) umma_commit(bar_bufb);
+                        // conv4 has read buffer A once the last conv4 tile of both issuers is done: conv1's epilogue of
+                        // the next group may overwrite it (the two issuers are not ordered against each other)
+                        if (layer == 3 && t + NET_MMA_WARPS >= n_tiles) umma_commit(bar_afree);
                     }
                     __syncwarp();
+                    if (timing) {
+                        const long long c4 = clock64();
+                        tm_ready += c2 - c1; tm_empty += c3 - c2; tm_issue += c4 - c3;
+                    }
                 }
             }
+        }
+        if (timing && (threadIdx.x & 31) == 0 && mma_id == 0) {
+            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 8;
+            o[0] = tm_ready; o[1] = tm_empty; o[2] = tm_issue; o[3] = clock64() - tm_start; o[4] = tm_im2col;
         }
     } else {
         // ================================================================== epilogue teams
@@ -385,7 +421,10 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
         const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
         mbar_wait(bar_weights, 0u);
         uint32_t tile_base = 0;
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+        const bool timing = p.debug && p.debug_layer == 100;
+        long long te_full = 0, te_work = 0;
+        uint32_t gi = 0;
+        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
             const int board0 = grp * NB;
             const int n_boards = min(NB, p.G - board0);
             for (int layer = 0; layer < 4; ++layer, tile_base += n_tiles) {
@@ -397,13 +436,16 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                     bias[4 * i] = v.x; bias[4 * i + 1] = v.y; bias[4 * i + 2] = v.z; bias[4 * i + 3] = v.w;
                 }
                 for (int t = team; t < n_tiles; t += 2) {
-                    const uint32_t it = tile_base + t, stage = it & 1u, phase = (it >> 1) & 1u;
+                    const uint32_t it = tile_base + t, stage = it % NET_STAGES, phase = (it / NET_STAGES) & 1u;
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
                     const bool on_board = b < n_boards && r >= 0 && c < IMG_COLS;
+                    const long long e0 = timing ? clock64() : 0;
                     mbar_wait(bar_full0 + 8 * stage, phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const long long e1 = timing ? clock64() : 0;
+                    te_full += e1 - e0;
                     const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16) + stage * NET_STAGE_COLS;
                     uint32_t out[16];
                     if (layer == 0) {
@@ -449,6 +491,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         }
                     }
                     if (layer < 3) {
+                        // buffer A still holds conv3's output of the previous group until its conv4 MMAs are done
+                        if (layer == 0 && gi > 0) mbar_wait(bar_afree, (gi - 1u) & 1u);
                         uint8_t* d = dst + (NET_MARGIN + row) * 16;
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
@@ -468,8 +512,14 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         for (int ch = 0; ch < 4; ++ch)
                             f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                     }
+                    if (timing) te_work += clock64() - e1;
                 }
             }
+        }
+        if (timing && (threadIdx.x & 31) == 0 && (warp == 0 || warp == 4)) {
+            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 8;
+            o[5 + (warp >> 2)] = te_full;
+            if (warp == 0) o[7] = te_work;
         }
     }
 

@@ -350,6 +350,14 @@ int az_samples_batch(const uint64_t* own, const uint64_t* opp, const float* pi, 
  * uint32 (sink).  *ops_per_thread (host, optional) = instructions each thread executed in the timed loop. */
 int az_peak_int32(int kind, int iters, uint32_t* out, int64_t out_len, int64_t* ops_per_thread, void* stream);
 
+/* tcgen05.mma issue-rate probe (the evidence behind the trunk's N = 96 design): every SM issues
+ * `reps` x `k_steps` MMAs of shape m x n x 16 (bf16 from shared memory, K-major no-swizzle, fp32 in TMEM), the
+ * k_steps of a rep accumulating into one of `regions` (1 or 2) accumulators; cycles[sm] (device, 148 int64) = SM
+ * clocks from the first issue to the completion of the last.
+ * flags: 1 = every MMA accumulates (no zero-initialising MMA), 2 = tcgen05.commit after every chain, 4 = three warps
+ * keep reading 96 accumulator columns with tcgen05.ld meanwhile. */
+int az_peak_mma(int m, int n, int k_steps, int reps, int regions, int flags, int64_t* cycles, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,3 +37,14 @@ timeit(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cu
 timeit(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
 timeit(ev, "whole forward (CUDA graph)")
 timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
+
+# cycle accounting of the trunk's MMA warp / epilogue warps (debug_layer = 100)
+dbg = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+_lib.check(_lib.lib().az_net_trunk(tree.leaf_own.data_ptr(), tree.leaf_opp.data_ptr(), 8, 8, G, ev.wblob.data_ptr(),
+                                   ev.features.data_ptr(), dbg.data_ptr(), 100, torch.cuda.current_stream().cuda_stream), "trunk timing")
+torch.cuda.synchronize()
+d = dbg.reshape(148, 8).double()
+names = ["mma: wait ready", "mma: wait empty", "mma: issue+commit", "mma: total", "mma: wait im2col", "epi team0: wait full",
+         "epi team1: wait full", "epi warp0: work"]
+for i, nm in enumerate(names):
+    print(f"{nm:24s} median {d[:, i].median().item():9.0f} cycles   max {d[:, i].max().item():9.0f}")
