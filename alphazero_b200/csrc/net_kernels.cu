@@ -35,13 +35,15 @@
 
 #define NET_CH 32                 // channels of every conv layer
 #define NET_TILE_M 128            // rows per MMA tile
-#define NET_TILES 6               // tiles per group
-#define NET_ROWS (NET_TILE_M * NET_TILES)   // 768 rows of activation per buffer
+#define NET_TILES 4               // tiles per group (at most)
+#define NET_ROWS (NET_TILE_M * NET_TILES)   // 512 rows of activation per buffer
+#define NET_DEBUG_ROWS 768        // row stride of the optional debug dump (kept from the 6-tile version of the ABI)
+#define NET_SLOTS 2               // groups in flight per CTA, each with its own buffers, MMA warp and epilogue team
 #define NET_PITCH 8               // cells per board row in the row space
 #define NET_MARGIN 16             // zero rows before / after (|row shift| = 8)
-#define NET_BUF_ROWS (NET_ROWS + 2 * NET_MARGIN)   // 800
-#define NET_CHUNK_BYTES (NET_BUF_ROWS * 16)        // one 8-channel chunk plane: 12800 B  (= LBO of the A operand)
-#define NET_BUF_BYTES (4 * NET_CHUNK_BYTES)        // 51200 B per activation buffer
+#define NET_BUF_ROWS (NET_ROWS + 2 * NET_MARGIN)   // 544
+#define NET_CHUNK_BYTES (NET_BUF_ROWS * 16)        // one 8-channel chunk plane: 8704 B  (= LBO of the A operand)
+#define NET_BUF_BYTES (4 * NET_CHUNK_BYTES)        // 34816 B per activation buffer
 #define NET_N3 96                 // N of the conv2..4 MMAs: 3 taps (dc) x 32 output channels
 #define NET_DR_CHUNK_BYTES (NET_N3 * 16)           // one 8-input-channel chunk of a kernel row: 1536 B (= LBO of B)
 #define NET_DR_BYTES (4 * NET_DR_CHUNK_BYTES)      // one kernel row: [ci chunk 4][(dc, co) 96][ci % 8] bf16 = 6144 B
@@ -50,37 +52,37 @@
 #define NET_WBLOB_MMA_BYTES (3 * NET_LAYER_BYTES + NET_CONV1_TILE_BYTES)  // conv2..conv4 tiles, then the conv1 tile
 #define NET_WBLOB_F32 (4 * 32)                     // folded biases of conv1..conv4
 #define NET_WBLOB_BYTES (NET_WBLOB_MMA_BYTES + NET_WBLOB_F32 * 4)
-#define NET_WORKERS 256           // warps 0-7: epilogue (two teams of 4 warps; team k serves the tiles t = k mod 2)
-#define NET_MMA_WARPS 2           // warps 8-9 issue the MMAs of the even / odd tiles: issuing a tile costs one thread
-                                  // ~700 cycles (60 per tcgen05.mma + barrier bookkeeping) against ~290 cycles of
-                                  // tensor-pipe time, so two issuers are needed to keep the pipe fed
-#define NET_PRODUCERS 64          // warps 10-11: im2col of the NEXT group while the current one is in conv4
+#define NET_WORKERS 256           // warps 0-7: epilogue, one team of 4 warps per slot (warp % 4 = TMEM lane quarter)
+#define NET_MMA_WARPS NET_SLOTS   // warps 8-9: MMA issue, one warp per slot.  Issuing a tile costs the thread ~700 cycles
+                                  // (60 per tcgen05.mma + barrier bookkeeping) against ~340 cycles of tensor-pipe time
+                                  // and ~730 of epilogue per team, so two independent slot pipelines keep all three busy
+#define NET_PRODUCERS 64          // warps 10-11: im2col of the slot's NEXT group while the current one runs conv2..conv4
 #define NET_THREADS (NET_WORKERS + 32 * NET_MMA_WARPS + NET_PRODUCERS)
 #define NET_STAGE_COLS 128        // TMEM columns per accumulator stage (96 used)
-#define NET_STAGES 4              // accumulator stages: the MMA warp may run a whole layer of a 4-tile group ahead
+#define NET_STAGES 4              // accumulator stages: two per slot
 #define NET_TMEM_COLS (NET_STAGES * NET_STAGE_COLS)   // 512: all of the SM's TMEM (one CTA per SM)
 
-// shared memory map (bytes)
-#define SM_BUF_A 0
-#define SM_BUF_B (SM_BUF_A + NET_BUF_BYTES)
-#define SM_IM2COL (SM_BUF_B + NET_BUF_BYTES)          // conv1's A operand (K = 16: two chunk planes), own buffer so that
-#define NET_IM2COL_BYTES (2 * NET_CHUNK_BYTES)        // the producers can fill it for group g+1 while group g computes
-#define SM_W (SM_IM2COL + NET_IM2COL_BYTES)
-// mbarriers: full[2] / empty[2] accumulator stages, ready[NET_TILES] "rows of tile t of this layer are in shared
-// memory", im2col "conv1's A operand of the group is in place", bufb "the im2col buffer is no longer read" (conv1
-// done), afree "buffer A is no longer read" (conv4 done),
-// weights "the bulk copy of the weight blob has landed"
+// shared memory map (bytes): per slot two activation buffers (A, B), per slot one im2col buffer (conv1's A operand,
+// K = 16: two chunk planes), the weight blob, the barriers
+#define SM_BUF(slot, which) (((slot) * 2 + (which)) * NET_BUF_BYTES)
+#define NET_IM2COL_BYTES (2 * NET_CHUNK_BYTES)
+#define SM_IM2COL(slot) (2 * NET_SLOTS * NET_BUF_BYTES + (slot) * NET_IM2COL_BYTES)
+#define SM_W (SM_IM2COL(NET_SLOTS))
+// mbarriers: full / empty per accumulator stage; ready[slot][tile] "rows of tile t of this layer are in shared
+// memory"; im2col[slot] "conv1's A operand of the slot's next group is in place"; i2free[slot] "the slot's im2col
+// buffer is no longer read" (conv1 MMAs done); weights "the bulk copy of the weight blob has landed"
 #define SM_BARS (SM_W + NET_WBLOB_BYTES)
 #define BAR_FULL 0
 #define BAR_EMPTY NET_STAGES
 #define BAR_READY (2 * NET_STAGES)
-#define BAR_IM2COL (BAR_READY + NET_TILES)
-#define BAR_BUFB (BAR_IM2COL + 1)
-#define BAR_WEIGHTS (BAR_BUFB + 1)
-#define BAR_AFREE (BAR_WEIGHTS + 1)
-#define NET_N_BARS (BAR_AFREE + 1)
-#define SM_TMEM_PTR (SM_BARS + 24 * 8)   // room for NET_N_BARS = 17 barriers
+#define BAR_IM2COL (BAR_READY + NET_SLOTS * NET_TILES)
+#define BAR_I2FREE (BAR_IM2COL + NET_SLOTS)
+#define BAR_WEIGHTS (BAR_I2FREE + NET_SLOTS)
+#define NET_N_BARS (BAR_WEIGHTS + 1)
+#define SM_TMEM_PTR (SM_BARS + 24 * 8)   // room for NET_N_BARS = 21 barriers
 #define SM_TOTAL (SM_TMEM_PTR + 16)
+static_assert(NET_N_BARS <= 24, "barrier area");
+static_assert(SM_TOTAL <= 232448, "shared memory per CTA on sm_100");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -164,6 +166,32 @@ __device__ __forceinline__ void tmem_ld96(uint32_t taddr, uint32_t (&a)[32], uin
         : "r"(taddr) : "memory");
 }
 
+// Three 16-column loads (columns +0, +32, +64 of the lane's row: the dc = -1, 0, +1 blocks of 16 channels) WITHOUT a
+// wait, and the matching wait.  The wait takes the destination registers as read-write operands so that no consumer
+// can be scheduled before it, while independent work (the other half's arithmetic) overlaps the TMEM read.
+__device__ __forceinline__ void tmem_ld48_issue(uint32_t taddr, uint32_t (&a)[16], uint32_t (&b)[16], uint32_t (&c)[16]) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 t1, t2;\n\t"
+        "add.u32 t1, %48, 32;\n\t"
+        "add.u32 t2, %48, 64;\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%48];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [t1];\n\t"
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47}, [t2];\n\t"
+        "}"
+        : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]), "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15]),
+          "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]), "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15]),
+          "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3]), "=r"(c[4]), "=r"(c[5]), "=r"(c[6]), "=r"(c[7]), "=r"(c[8]), "=r"(c[9]), "=r"(c[10]), "=r"(c[11]), "=r"(c[12]), "=r"(c[13]), "=r"(c[14]), "=r"(c[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld48_wait(uint32_t (&a)[16], uint32_t (&b)[16], uint32_t (&c)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+        : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]), "+r"(a[8]), "+r"(a[9]), "+r"(a[10]), "+r"(a[11]), "+r"(a[12]), "+r"(a[13]), "+r"(a[14]), "+r"(a[15]),
+          "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]), "+r"(b[8]), "+r"(b[9]), "+r"(b[10]), "+r"(b[11]), "+r"(b[12]), "+r"(b[13]), "+r"(b[14]), "+r"(b[15]),
+          "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]), "+r"(c[4]), "+r"(c[5]), "+r"(c[6]), "+r"(c[7]), "+r"(c[8]), "+r"(c[9]), "+r"(c[10]), "+r"(c[11]), "+r"(c[12]), "+r"(c[13]), "+r"(c[14]), "+r"(c[15])
+        :: "memory");
+}
+
 // True in exactly one (elected) lane of a converged warp.
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred = 0;
@@ -217,7 +245,7 @@ struct NetTrunkParams {
     int G;
     int rows, cols;            // image size: 8x8 / 6x6 (Othello) or 7x6 (Connect4Net's view of the 6x7 grid)
     int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= n_tiles * 128
-    int n_tiles;               // 128-row tiles per group: 2, 4 or 6 (even: tile parity = TMEM stage = epilogue team)
+    int n_tiles;               // 128-row tiles per group: 2 or 4
     int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
 };
 
@@ -233,7 +261,7 @@ __device__ __forceinline__ void net_row_coords(int row, int rpb, int& b, int& r,
 // 9-tap im2col of the network input (player*grid: +1 own, -1 opp, 0 empty / off-board) for one row:
 // 16 bf16 = taps 0..8 then zeros, written as the two 16-byte K chunks of the conv1 A operand.
 // (b, r, c) are the row's coordinates; own/opp the bitboards of its board (0 when the board does not exist).
-__device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n_rows, int n_cols, int r, int c,
+__device__ __forceinline__ void net_im2col_row(uint8_t* im2col, int row, int n_rows, int n_cols, int r, int c,
                                                uint64_t own, uint64_t opp) {
     uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};     // taps 0..8 as bf16 pairs (tap 8 in the low half of w[4])
     if (r >= 0 && c < n_cols) {
@@ -255,39 +283,43 @@ __device__ __forceinline__ void net_im2col_row(uint8_t* smem, int row, int n_row
             }
         }
     }
-    uint8_t* dst = smem + SM_IM2COL + (NET_MARGIN + row) * 16;
+    uint8_t* dst = im2col + (NET_MARGIN + row) * 16;
     *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
     *reinterpret_cast<uint4*>(dst + NET_CHUNK_BYTES) = make_uint4(w[4], 0u, 0u, 0u);
 }
 
-// Warp roles (no block-wide barrier inside the group loop; everything is mbarrier-pipelined):
-//   warps 0-7   epilogue: team = warp / 4 serves TMEM stage `team`, quarter = warp % 4 is the TMEM lane quarter;
-//   warp 8      MMA issue (one elected lane) -- tiles of consecutive layers and groups follow each other without a
-//               drain: tile t of layer L+1 only waits for tiles t-1 .. t+1 of layer L (row shifts are +-8 rows);
-//   warps 8-9   MMA issue, even / odd tiles;
-//   warps 10-11 producers: im2col of group g+1 into its own buffer while group g runs conv2..conv4.
+// Warp roles (no block-wide barrier inside the group loop; everything is mbarrier-pipelined).  The CTA keeps
+// NET_SLOTS = 2 groups in flight; slot s owns the CTA's groups k = s, s + 2, ... with its own activation buffers,
+// im2col buffer, two TMEM stages and barriers, so that the two pipelines never wait for each other:
+//   warps 0-3 / 4-7   epilogue team of slot 0 / 1 (warp % 4 = TMEM lane quarter);
+//   warp 8 / 9        MMA issue of slot 0 / 1 (one elected lane): tile t of layer L+1 only waits for tiles t-1 .. t+1 of
+//                     layer L (row shifts are +-8 rows), so layers and groups of a slot follow each other without a drain;
+//   warps 10-11       producers: im2col of the next group of either slot while that slot runs conv2..conv4.
+// Measured per tile (B200): 6 MMAs occupy the tensor pipe ~340 cycles (operand fetch, 128 B per clock), cost the issuing
+// thread ~700 cycles, and the epilogue team ~730 cycles (TMEM read of 96 columns + 64 shuffles per row) -- one slot
+// alone leaves each of the three idle most of the time (profiles/r1_trunk_experiments.txt).
 template <int IMG_ROWS, int IMG_COLS>
 __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long t_entry = clock64();
+    unsigned long long g_entry;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g_entry));
     constexpr int RPB = (IMG_ROWS + 1) * NET_PITCH;    // rows per board: ring row + image rows
     const int NB = p.boards_per_group;
     const int n_groups = (p.G + NB - 1) / NB;
     const int n_tiles = p.n_tiles, n_rows = n_tiles * NET_TILE_M;
     const uint32_t bars = smem_u32(smem + SM_BARS);
     const uint32_t bar_full0 = bars + 8 * BAR_FULL, bar_empty0 = bars + 8 * BAR_EMPTY, bar_ready0 = bars + 8 * BAR_READY;
-    const uint32_t bar_im2col = bars + 8 * BAR_IM2COL, bar_bufb = bars + 8 * BAR_BUFB, bar_weights = bars + 8 * BAR_WEIGHTS;
-    const uint32_t bar_afree = bars + 8 * BAR_AFREE;
+    const uint32_t bar_im2col0 = bars + 8 * BAR_IM2COL, bar_i2free0 = bars + 8 * BAR_I2FREE, bar_weights = bars + 8 * BAR_WEIGHTS;
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SM_TMEM_PTR);
     constexpr int MMA_WARP = NET_WORKERS / 32;
 
     // ---- one-time setup: barriers, async bulk copy of the weights, zeroed activation buffers, TMEM
     if (tid == 0) {
         for (int st = 0; st < NET_STAGES; ++st) { mbar_init(bar_full0 + 8 * st, 1); mbar_init(bar_empty0 + 8 * st, 128); }
-        for (int t = 0; t < NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 128);
-        mbar_init(bar_im2col, NET_PRODUCERS);
-        mbar_init(bar_bufb, NET_MMA_WARPS);
-        mbar_init(bar_afree, NET_MMA_WARPS);
+        for (int t = 0; t < NET_SLOTS * NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 128);
+        for (int sl = 0; sl < NET_SLOTS; ++sl) { mbar_init(bar_im2col0 + 8 * sl, NET_PRODUCERS); mbar_init(bar_i2free0 + 8 * sl, 1); }
         mbar_init(bar_weights, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
@@ -295,8 +327,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(smem_u32(smem + SM_W)), "l"(p.wblob), "r"((uint32_t)NET_WBLOB_BYTES), "r"(bar_weights) : "memory");
     }
-    for (int i = tid; i < 2 * NET_BUF_BYTES / 16; i += NET_THREADS)
-        reinterpret_cast<uint4*>(smem + SM_BUF_A)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 2 * NET_SLOTS * NET_BUF_BYTES / 16; i += NET_THREADS)
+        reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
     if (warp == MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(NET_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -306,72 +338,74 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
+    const bool timing = p.debug && p.debug_layer == 100;   // cycle accounting into debug[blockIdx.x][0..15] (int64)
+    const long long t_setup = clock64();
 
     if (warp >= MMA_WARP + NET_MMA_WARPS) {
-        // ================================================================== producers: im2col of every group
+        // ================================================================== producers: im2col of every group, in the
+        // order the CTA starts them (k = 0, 1, 2, ...: slot k & 1, the slot's j-th group with j = k >> 1)
         const int ptid = tid - (NET_WORKERS + 32 * NET_MMA_WARPS);
-        uint32_t gi = 0;
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+        // (the first group of each slot is converted by the slot's epilogue team, which has nothing else to do yet)
+        uint32_t k = NET_SLOTS;
+        for (int grp = blockIdx.x + NET_SLOTS * gridDim.x; grp < n_groups; grp += gridDim.x, ++k) {
+            const uint32_t slot = k & 1u, j = k >> 1;
             const int board0 = grp * NB;
             const int n_boards = min(NB, p.G - board0);
             // bitboards of the rows this thread converts (global loads issued before waiting for the buffer)
             constexpr int RPT = NET_ROWS / NET_PRODUCERS;
             uint64_t own[RPT], opp[RPT];
 #pragma unroll
-            for (int k = 0; k < RPT; ++k) {
-                const int b = (ptid + k * NET_PRODUCERS) / RPB;
-                const bool ok = b < n_boards && ptid + k * NET_PRODUCERS < n_rows;
-                own[k] = ok ? p.own[board0 + b] : 0ULL;
-                opp[k] = ok ? p.opp[board0 + b] : 0ULL;
+            for (int q = 0; q < RPT; ++q) {
+                const int b = (ptid + q * NET_PRODUCERS) / RPB;
+                const bool ok = b < n_boards && ptid + q * NET_PRODUCERS < n_rows;
+                own[q] = ok ? p.own[board0 + b] : 0ULL;
+                opp[q] = ok ? p.opp[board0 + b] : 0ULL;
             }
-            if (gi > 0) mbar_wait(bar_bufb, (gi - 1u) & 1u);      // conv1 of the previous group has read the im2col buffer
+            mbar_wait(bar_i2free0 + 8 * slot, (j - 1u) & 1u);   // conv1 of the slot's previous group has read it
+            uint8_t* im2col = smem + SM_IM2COL(slot);
 #pragma unroll
-            for (int k = 0; k < RPT; ++k) {
-                const int row = ptid + k * NET_PRODUCERS;
+            for (int q = 0; q < RPT; ++q) {
+                const int row = ptid + q * NET_PRODUCERS;
                 if (row < n_rows) {
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
-                    net_im2col_row(smem, row, IMG_ROWS, IMG_COLS, r, c, own[k], opp[k]);
+                    net_im2col_row(im2col, row, IMG_ROWS, IMG_COLS, r, c, own[q], opp[q]);
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_arrive(bar_im2col);
+            mbar_arrive(bar_im2col0 + 8 * slot);
         }
     } else if (warp >= MMA_WARP) {
-        // ================================================================== MMA issue: this warp takes the tiles
-        // t = mma_id (mod NET_MMA_WARPS) of every layer
-        const int mma_id = warp - MMA_WARP;
+        // ================================================================== MMA issue of slot `slot`
+        const uint32_t slot = (uint32_t)(warp - MMA_WARP);
         const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc96 = umma_idesc_bf16_m128(NET_N3);
+        const uint32_t bar_ready = bar_ready0 + 8 * NET_TILES * slot;
         mbar_wait(bar_weights, 0u);
-        uint32_t gi = 0, tile_base = 0;
-        // debug_layer == 100: cycle accounting of this warp into debug[blockIdx.x][0..3] (int64)
-        const bool timing = p.debug && p.debug_layer == 100;
+        uint32_t j = 0, tile_it = 0;
         long long tm_ready = 0, tm_empty = 0, tm_issue = 0, tm_im2col = 0;
         const long long tm_start = clock64();
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+        for (int grp = blockIdx.x + (int)slot * gridDim.x; grp < n_groups; grp += NET_SLOTS * gridDim.x, ++j) {
             long long c0 = timing ? clock64() : 0;
-            mbar_wait(bar_im2col, gi & 1u);
+            mbar_wait(bar_im2col0 + 8 * slot, j & 1u);
             if (timing) tm_im2col += clock64() - c0;
             // ---- layer 0: conv1 (im2col buffer -> A), 1: conv2 (A -> B), 2: conv3 (B -> A), 3: conv4 (A -> features)
-            for (int layer = 0; layer < 4; ++layer, tile_base += n_tiles) {
-                const uint32_t src = smem_u32(smem + (layer == 0 ? SM_IM2COL : (layer & 1) ? SM_BUF_A : SM_BUF_B));
+            for (int layer = 0; layer < 4; ++layer) {
+                const uint32_t src = smem_u32(smem + (layer == 0 ? SM_IM2COL(slot) : SM_BUF(slot, (layer & 1) ? 0 : 1)));
                 const uint64_t a_layer = umma_desc(src + NET_MARGIN * 16, NET_CHUNK_BYTES, 128);
                 const uint64_t b_layer = layer == 0
                     ? umma_desc(smem_u32(smem + SM_W) + 3 * NET_LAYER_BYTES, 512, 128)
                     : umma_desc(smem_u32(smem + SM_W) + (layer - 1) * NET_LAYER_BYTES, NET_DR_CHUNK_BYTES, 128);
-                // ready[] barriers complete one phase per layer 0..2 of every group (conv4 writes no activations)
-                const uint32_t ready_parity = (gi * 3u + (uint32_t)(layer - 1)) & 1u;
-                for (int t = mma_id; t < n_tiles; t += NET_MMA_WARPS) {
-                    const uint32_t tile_it = tile_base + (uint32_t)t;
+                // ready[] barriers complete one phase per layer 0..2 of every group of the slot (conv4 writes no activations)
+                const uint32_t ready_parity = (j * 3u + (uint32_t)(layer - 1)) & 1u;
+                for (int t = 0; t < n_tiles; ++t, ++tile_it) {
                     long long c1 = timing ? clock64() : 0;
                     if (layer > 0) {
-                        // input rows of tile t: tiles t-1 .. t+1 of the previous layer
-                        if (t > 0) mbar_wait(bar_ready0 + 8 * (t - 1), ready_parity);
-                        mbar_wait(bar_ready0 + 8 * t, ready_parity);
-                        if (t + 1 < n_tiles) mbar_wait(bar_ready0 + 8 * (t + 1), ready_parity);
+                        // input rows of tile t: tiles t-1 .. t+1 of the previous layer; t-1 and t were awaited for tile t-1
+                        if (t == 0) mbar_wait(bar_ready, ready_parity);
+                        if (t + 1 < n_tiles) mbar_wait(bar_ready + 8 * (t + 1), ready_parity);
                     }
                     long long c2 = timing ? clock64() : 0;
-                    const uint32_t stage = tile_it % NET_STAGES, phase = (tile_it / NET_STAGES) & 1u;
+                    const uint32_t stage = slot * 2u + (tile_it & 1u), phase = (tile_it >> 1) & 1u;
                     mbar_wait(bar_empty0 + 8 * stage, phase ^ 1u);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     long long c3 = timing ? clock64() : 0;
@@ -394,12 +428,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             }
                         }
                         umma_commit(bar_full0 + 8 * stage);
-                        // conv1 has read the im2col buffer once the last conv1 tile of BOTH issuers is done: the
-                        // producers may then build the next group's im2col (while this group runs conv2..conv4)
-                        if (layer == 0 && t + NET_MMA_WARPS >= n_tiles) umma_commit(bar_bufb);
-                        // conv4 has read buffer A once the last conv4 tile of both issuers is done: conv1's epilogue of
-                        // the next group may overwrite it (the two issuers are not ordered against each other)
-                        if (layer == 3 && t + NET_MMA_WARPS >= n_tiles) umma_commit(bar_afree);
+                        // conv1 has read the im2col buffer: the producers may build the slot's next group
+                        if (layer == 0 && t == n_tiles - 1) umma_commit(bar_i2free0 + 8 * slot);
                     }
                     __syncwarp();
                     if (timing) {
@@ -409,34 +439,55 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 }
             }
         }
-        if (timing && (threadIdx.x & 31) == 0 && mma_id == 0) {
-            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 8;
+        if (timing && lane == 0 && slot == 0) {
+            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 16;
             o[0] = tm_ready; o[1] = tm_empty; o[2] = tm_issue; o[3] = clock64() - tm_start; o[4] = tm_im2col;
+            o[8] = t_setup - t_entry; o[9] = tm_start - t_entry; o[10] = (long long)g_entry;
         }
     } else {
-        // ================================================================== epilogue teams
-        const int team = warp >> 2;            // TMEM stage this team serves
+        // ================================================================== epilogue team of slot `slot`
+        const uint32_t slot = (uint32_t)(warp >> 2);
         const int quarter = warp & 3;          // TMEM lane quarter this warp may read
         constexpr int M_R = IMG_ROWS - 4, M_C = IMG_COLS - 4;   // conv4 output size
         const float* bias_all = reinterpret_cast<const float*>(smem + SM_W + NET_WBLOB_MMA_BYTES);   // b1..b4
+        const uint32_t bar_ready = bar_ready0 + 8 * NET_TILES * slot;
+        {   // im2col of the slot's first group by this team (128 threads, 4 rows each): halves the start-up latency
+            const int grp0 = blockIdx.x + (int)slot * gridDim.x;
+            if (grp0 < n_groups) {
+                const int tt = tid - (int)slot * 128, board0 = grp0 * NB, n_boards = min(NB, p.G - board0);
+                uint8_t* im2col = smem + SM_IM2COL(slot);
+#pragma unroll
+                for (int q = 0; q < NET_ROWS / 128; ++q) {
+                    const int row = tt + q * 128;
+                    if (row < n_rows) {
+                        int b, r, c;
+                        net_row_coords(row, RPB, b, r, c);
+                        const bool ok = b < n_boards;
+                        net_im2col_row(im2col, row, IMG_ROWS, IMG_COLS, r, c, ok ? p.own[board0 + b] : 0ULL,
+                                       ok ? p.opp[board0 + b] : 0ULL);
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + (int)slot) : "memory");     // the team's named barrier
+                if (tt < NET_PRODUCERS) mbar_arrive(bar_im2col0 + 8 * slot);
+            }
+        }
         mbar_wait(bar_weights, 0u);
-        uint32_t tile_base = 0;
-        const bool timing = p.debug && p.debug_layer == 100;
+        uint32_t it = 0;
         long long te_full = 0, te_work = 0;
-        uint32_t gi = 0;
-        for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++gi) {
+        for (int grp = blockIdx.x + (int)slot * gridDim.x; grp < n_groups; grp += NET_SLOTS * gridDim.x) {
             const int board0 = grp * NB;
             const int n_boards = min(NB, p.G - board0);
-            for (int layer = 0; layer < 4; ++layer, tile_base += n_tiles) {
-                uint8_t* dst = smem + ((layer & 1) ? SM_BUF_B : SM_BUF_A);
+            for (int layer = 0; layer < 4; ++layer) {
+                uint8_t* dst = smem + SM_BUF(slot, (layer & 1) ? 1 : 0);
                 float bias[32];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const float4 v = reinterpret_cast<const float4*>(bias_all + layer * 32)[i];
                     bias[4 * i] = v.x; bias[4 * i + 1] = v.y; bias[4 * i + 2] = v.z; bias[4 * i + 3] = v.w;
                 }
-                for (int t = team; t < n_tiles; t += 2) {
-                    const uint32_t it = tile_base + t, stage = it % NET_STAGES, phase = (it / NET_STAGES) & 1u;
+                for (int t = 0; t < n_tiles; ++t, ++it) {
+                    const uint32_t stage = slot * 2u + (it & 1u), phase = (it >> 1) & 1u;
                     const int row = t * NET_TILE_M + quarter * 32 + lane;     // TMEM lane = row within the tile
                     int b, r, c;
                     net_row_coords(row, RPB, b, r, c);
@@ -468,20 +519,21 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         // accumulator row p, block dc holds the contribution to output p - dc:
                         //   out[p] = blk(-1)[p - 1] + blk(0)[p] + blk(+1)[p + 1]; column 0 / 7 have no left / right
                         //   neighbour (zero padding for conv2, never-valid outputs for conv3 / conv4).
-                        uint32_t lo[32], mid[32], hi[32];
-                        tmem_ld96(t_lane, lo, mid, hi);                           // dc = -1, 0, +1 blocks of this row
-                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                        mbar_arrive(bar_empty0 + 8 * stage);
+                        // two halves of 16 channels: the TMEM read of the second overlaps the arithmetic of the first
+                        uint32_t lo0[16], mid0[16], hi0[16], lo1[16], mid1[16], hi1[16];
+                        tmem_ld48_issue(t_lane, lo0, mid0, hi0);
+                        tmem_ld48_wait(lo0, mid0, hi0);
+                        tmem_ld48_issue(t_lane + 16, lo1, mid1, hi1);
                         // 0/1 factors instead of selects: one FFMA per neighbour term (all operands are finite)
                         const float hl = c > 0 ? 1.f : 0.f, hr = c < 7 ? 1.f : 0.f;
                         const uint64_t has_left = f32x2_pack(hl, hl), has_right = f32x2_pack(hr, hr);
 #pragma unroll
-                        for (int co = 0; co < 32; co += 2) {
-                            const float up0 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co]), 1);
-                            const float up1 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo[co + 1]), 1);
-                            const float dn0 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co]), 1);
-                            const float dn1 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi[co + 1]), 1);
-                            uint64_t x = f32x2_add(f32x2_pack(__uint_as_float(mid[co]), __uint_as_float(mid[co + 1])),
+                        for (int co = 0; co < 16; co += 2) {
+                            const float up0 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo0[co]), 1);
+                            const float up1 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo0[co + 1]), 1);
+                            const float dn0 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi0[co]), 1);
+                            const float dn1 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi0[co + 1]), 1);
+                            uint64_t x = f32x2_add(f32x2_pack(__uint_as_float(mid0[co]), __uint_as_float(mid0[co + 1])),
                                                    f32x2_pack(bias[co], bias[co + 1]));
                             x = f32x2_fma(f32x2_pack(up0, up1), has_left, x);
                             x = f32x2_fma(f32x2_pack(dn0, dn1), has_right, x);
@@ -489,20 +541,35 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             f32x2_unpack(x, x0, x1);
                             out[co >> 1] = pack_relu_bf16x2(x0, x1);
                         }
+                        tmem_ld48_wait(lo1, mid1, hi1);
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        mbar_arrive(bar_empty0 + 8 * stage);
+#pragma unroll
+                        for (int co = 0; co < 16; co += 2) {
+                            const float up0 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo1[co]), 1);
+                            const float up1 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo1[co + 1]), 1);
+                            const float dn0 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi1[co]), 1);
+                            const float dn1 = __shfl_down_sync(0xffffffffu, __uint_as_float(hi1[co + 1]), 1);
+                            uint64_t x = f32x2_add(f32x2_pack(__uint_as_float(mid1[co]), __uint_as_float(mid1[co + 1])),
+                                                   f32x2_pack(bias[16 + co], bias[17 + co]));
+                            x = f32x2_fma(f32x2_pack(up0, up1), has_left, x);
+                            x = f32x2_fma(f32x2_pack(dn0, dn1), has_right, x);
+                            float x0, x1;
+                            f32x2_unpack(x, x0, x1);
+                            out[8 + (co >> 1)] = pack_relu_bf16x2(x0, x1);
+                        }
                     }
                     if (layer < 3) {
-                        // buffer A still holds conv3's output of the previous group until its conv4 MMAs are done
-                        if (layer == 0 && gi > 0) mbar_wait(bar_afree, (gi - 1u) & 1u);
                         uint8_t* d = dst + (NET_MARGIN + row) * 16;
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
                             *reinterpret_cast<uint4*>(d + ch * NET_CHUNK_BYTES) =
                                 make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        mbar_arrive(bar_ready0 + 8 * t);
+                        mbar_arrive(bar_ready + 8 * t);
                         if (p.debug && p.debug_layer == layer + 1)
                             for (int ch = 0; ch < 4; ++ch)
-                                *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_ROWS + row) * 32 + ch * 8) =
+                                *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_DEBUG_ROWS + row) * 32 + ch * 8) =
                                     make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                     } else if (on_board && r >= 2 && r < 2 + M_R && c >= 2 && c < 2 + M_C) {
                         // conv4: the outputs are the cells at an inset of 2; features[board][pos*32 + co]
@@ -516,10 +583,10 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 }
             }
         }
-        if (timing && (threadIdx.x & 31) == 0 && (warp == 0 || warp == 4)) {
-            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 8;
-            o[5 + (warp >> 2)] = te_full;
-            if (warp == 0) o[7] = te_work;
+        if (timing && lane == 0 && quarter == 0) {
+            long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 16;
+            o[5 + slot] = te_full;
+            if (slot == 0) o[7] = te_work;
         }
     }
 
@@ -527,6 +594,12 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     __syncthreads();
     if (warp == MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(NET_TMEM_COLS));
+    if (timing && tid == 0) {
+        unsigned long long g_end;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(g_end));
+        long long* o = reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 16;
+        o[11] = (long long)g_end; o[12] = clock64() - t_entry;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ heads epilogue
@@ -581,9 +654,9 @@ static void net_group_shape(int rows, int64_t G, int n_sms, int* boards_per_grou
     for (int tiles = 2; tiles <= NET_TILES; tiles += 2) {
         const int nb = (tiles * NET_TILE_M - NET_PITCH) / rpb;
         const int64_t groups = (G + nb - 1) / nb;
-        // + 1 tile-step per group for the pipeline ramp between groups: with few tiles per layer the next layer's
-        // first MMAs wait for the previous layer's epilogue latency (measured: 4 x 4 tiles is no faster than 3 x 6)
-        const int64_t cost = ((groups + n_sms - 1) / n_sms) * (tiles + 1);
+        // a CTA runs its groups two at a time (NET_SLOTS pipelines); + 1 tile-step per group for the ramp
+        const int64_t per_cta = (groups + n_sms - 1) / n_sms;
+        const int64_t cost = ((per_cta + NET_SLOTS - 1) / NET_SLOTS) * (tiles + 1);
         if (best_cost < 0 || cost <= best_cost) { best_cost = cost; *boards_per_group = nb; *n_tiles = tiles; }
     }
 }

@@ -211,8 +211,11 @@ def test_optimize_network_reproduces_reference_othello6(golden_dir, exact_fp32):
     lv = np.array([tr.loss_values[0][e]["v"] for e in range(E)])
     _assert_losses_close(lp, lv, d)
     for k, v in tr.nn_twin.state_dict().items():
-        got = [v.double().sum().item(), v.double().norm().item()]
-        assert np.allclose(got, d[f"finalsum_{k}"], rtol=2e-3, atol=2e-2), k
+        # per-tensor checksums of the trained twin: the L2 norm within 0.5 %, the sum within what per-element
+        # differences of ~1e-3 (see _assert_losses_close) add up to over the tensor
+        want_sum, want_norm = d[f"finalsum_{k}"]
+        assert abs(v.double().norm().item() - want_norm) <= 5e-3 * want_norm + 1e-6, k
+        assert abs(v.double().sum().item() - want_sum) <= 1e-3 * (v.numel() ** 0.5) + 5e-2, k
 
 
 def test_too_few_samples_raises():

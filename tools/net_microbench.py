@@ -39,12 +39,17 @@ timeit(ev, "whole forward (CUDA graph)")
 timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
 
 # cycle accounting of the trunk's MMA warp / epilogue warps (debug_layer = 100)
-dbg = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
-_lib.check(_lib.lib().az_net_trunk(tree.leaf_own.data_ptr(), tree.leaf_opp.data_ptr(), 8, 8, G, ev.wblob.data_ptr(),
-                                   ev.features.data_ptr(), dbg.data_ptr(), 100, torch.cuda.current_stream().cuda_stream), "trunk timing")
+dbg = torch.zeros(148 * 16, dtype=torch.int64, device="cuda")
+for _ in range(3):      # back to back, like the search loop: the last launch is reported
+    _lib.check(_lib.lib().az_net_trunk(tree.leaf_own.data_ptr(), tree.leaf_opp.data_ptr(), 8, 8, G, ev.wblob.data_ptr(),
+                                       ev.features.data_ptr(), dbg.data_ptr(), 100, torch.cuda.current_stream().cuda_stream), "trunk timing")
 torch.cuda.synchronize()
-d = dbg.reshape(148, 8).double()
-names = ["mma: wait ready", "mma: wait empty", "mma: issue+commit", "mma: total", "mma: wait im2col", "epi team0: wait full",
-         "epi team1: wait full", "epi warp0: work"]
+d = dbg.reshape(148, 16).double()
+names = ["mma: wait ready", "mma: wait empty", "mma: issue+commit", "mma: loop total", "mma: wait im2col", "epi team0: wait full",
+         "epi team1: wait full", "epi warp0: work", "entry -> setup done", "entry -> weights landed", None, None, "entry -> exit"]
 for i, nm in enumerate(names):
-    print(f"{nm:24s} median {d[:, i].median().item():9.0f} cycles   max {d[:, i].max().item():9.0f}")
+    if nm:
+        print(f"{nm:24s} median {d[:, i].median().item():9.0f} cycles   max {d[:, i].max().item():9.0f}")
+g0, g1 = d[:, 10], d[:, 11]
+print(f"globaltimer: first CTA entry -> last CTA entry {(g0.max() - g0.min()).item() / 1e3:6.2f} us, "
+      f"first entry -> last exit {(g1.max() - g0.min()).item() / 1e3:6.2f} us")
