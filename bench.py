@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--capacity", type=int, default=None, help="nodes per tree-pool half (default 48 * (sims + 1))")
     ap.add_argument("--game", default="othello", choices=["othello", "connect4"],
                     help="othello: BASELINE config 3/4 (the headline); connect4: config 5 (7x6, Connect4Net)")
     ap.add_argument("--net", default="fused", choices=["fused", "torch"],
@@ -195,7 +196,7 @@ def run_ours(args):
         flop_per_eval, workload, net_name = FLOP_PER_EVAL, WORKLOAD, "OthelloNet(n=8)"
     engine = SelfPlayEngine(net, G, n=spec, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
                             temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4, seed=0x5EED + 7919 * rank,
-                            dtype=torch.bfloat16, device=dev, network_path=args.net)
+                            dtype=torch.bfloat16, device=dev, network_path=args.net, capacity=args.capacity)
     black, white = spec.start_position()
     h_own = torch.full((G,), bo.to_i64(black), dtype=torch.int64).pin_memory()
     h_opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64).pin_memory()
