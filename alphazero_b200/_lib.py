@@ -85,6 +85,8 @@ SIGNATURES = {
     "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "az_connect4_image_bits": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_heads": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
+    "az_net_headgemm_blob_bytes": (c_i64, [c_int, c_int]),
+    "az_net_headgemm": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_augment_scratch_bytes": (c_i64, [c_i64]),
     "az_augment_twins": (c_int, [c_int]),
     "az_augment_plan": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p]),

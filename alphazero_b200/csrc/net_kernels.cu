@@ -640,6 +640,176 @@ __global__ void __launch_bounds__(128) k_net_heads(const __nv_bfloat16* __restri
     if (lane == 0) value[g] = tanhf(__bfloat162float(row[A]));
 }
 
+// ------------------------------------------------------------------------------------------------ heads GEMM
+
+// logits = h2 x Wh^T + bh, probs = softmax(policy logits), value = tanh(value logit) in ONE kernel: the two output
+// layers fc_probs / fc_value (othello.py:361-362, 379-382; connect4.py:389-390, 408-411) as a tcgen05 GEMM whose
+// epilogue is PolicyValueNetwork.predict's exp(log_softmax) / tanh (base.py:350-355).  Replaces a library GEMM + the
+// k_net_heads launch; the logits stay fp32 (they never exist in memory).
+//
+// One CTA per 128 positions.  A = h2 tile, K-major no-swizzle [K/8][128][8] bf16, filled by 8 warps (lane = 8 rows x
+// 4 K-chunks: 64-byte row segments from global, 128-byte contiguous shared-memory stores) in four K quarters, each
+// with its mbarrier, so that the MMAs of a quarter start while the next one is still loading; B = the packed head
+// weights [K/8][NH][8] by one bulk async copy.  K/16 MMAs of shape 128 x NH x 16 into NH TMEM columns.
+#define HG_ROWS 128
+#define HG_LOAD_WARPS 8
+#define HG_THREADS (32 * (HG_LOAD_WARPS + 1))
+#define HG_MAX_K 512
+#define HG_MAX_NH 96
+#define HG_QUARTERS 4
+
+struct HeadGemmParams {
+    const __nv_bfloat16* h2;   // [G][K]
+    const uint8_t* wblob;      // [K/8][NH][8] bf16, then float bias[NH]
+    float* probs;              // [G][A]
+    float* value;              // [G]
+    int64_t G;
+    int K, NH, A;
+};
+
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+
+template <int NH>
+__global__ void __launch_bounds__(HG_THREADS, 1) k_net_headgemm(HeadGemmParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int K = p.K, n_kc = K >> 3;                       // 8-element K chunks
+    const uint32_t a_plane = HG_ROWS * 16, b_plane = NH * 16;
+    uint8_t* a_smem = smem;                                 // n_kc planes of 2 KB
+    // the A region doubles as the probs staging area of the epilogue ([128][A] floats): sized for the larger of the two
+    const uint32_t a_bytes = max((uint32_t)n_kc * a_plane, (uint32_t)(HG_ROWS * NH * 4));
+    uint8_t* b_smem = smem + a_bytes;                       // n_kc planes of NH*16 B, then float bias[NH]
+    const uint32_t w_bytes = (uint32_t)n_kc * b_plane + NH * 4u;
+    uint8_t* tail = b_smem + ((w_bytes + 127u) & ~127u);
+    const uint32_t bars = smem_u32(tail);                   // quarter[4], weights, full
+    const uint32_t bar_w = bars + 8 * HG_QUARTERS, bar_full = bar_w + 8;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tail + 64);
+    const int64_t row0 = (int64_t)blockIdx.x * HG_ROWS;
+
+    if (tid == 0) {
+        for (int q = 0; q < HG_QUARTERS; ++q) mbar_init(bars + 8 * q, HG_LOAD_WARPS * 32);
+        mbar_init(bar_w, 1);
+        mbar_init(bar_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
+                     ::"r"(bar_w), "r"(w_bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(smem_u32(b_smem)), "l"(p.wblob), "r"(w_bytes), "r"(bar_w) : "memory");
+    }
+    if (warp == HG_LOAD_WARPS) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(128));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp < HG_LOAD_WARPS) {
+        // ---- A tile: blocks of 8 rows x 4 K-chunks, K-chunk-block major so that the quarters complete in order
+        const int r8 = lane & 7, k4 = lane >> 3;
+        const int kc_blocks = n_kc >> 2, per_q = (kc_blocks + HG_QUARTERS - 1) / HG_QUARTERS;
+        for (int q = 0; q < HG_QUARTERS; ++q) {
+            const int kb0 = q * per_q, kb1 = min(kc_blocks, kb0 + per_q);
+            const int n_blocks = (kb1 - kb0) * (HG_ROWS / 8);
+            // 8 independent 16-byte loads in flight per lane before the first store (latency-bound otherwise)
+            for (int b0 = warp; b0 < n_blocks; b0 += 8 * HG_LOAD_WARPS) {
+                uint4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int b = b0 + u * HG_LOAD_WARPS;
+                    const int kc = (kb0 + b / (HG_ROWS / 8)) * 4 + k4, row = (b % (HG_ROWS / 8)) * 8 + r8;
+                    v[u] = make_uint4(0u, 0u, 0u, 0u);
+                    if (b < n_blocks && row0 + row < p.G)
+                        v[u] = *reinterpret_cast<const uint4*>(p.h2 + (row0 + row) * K + kc * 8);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int b = b0 + u * HG_LOAD_WARPS;
+                    const int kc = (kb0 + b / (HG_ROWS / 8)) * 4 + k4, row = (b % (HG_ROWS / 8)) * 8 + r8;
+                    if (b < n_blocks) *reinterpret_cast<uint4*>(a_smem + (size_t)kc * a_plane + row * 16) = v[u];
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(bars + 8 * q);
+        }
+    } else {
+        // ---- MMA issue
+        const uint32_t idesc = umma_idesc_bf16_m128(NH);
+        const int kc_blocks = n_kc >> 2, per_q = (kc_blocks + HG_QUARTERS - 1) / HG_QUARTERS;
+        mbar_wait(bar_w, 0u);
+        for (int q = 0; q < HG_QUARTERS; ++q) {
+            mbar_wait(bars + 8 * q, 0u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int ks0 = q * per_q * 2, ks1 = min(n_kc >> 1, (q + 1) * per_q * 2);   // K = 16 steps of this quarter
+            if (elect_one()) {
+                for (int ks = ks0; ks < ks1; ++ks) {
+                    const uint64_t ad = umma_desc(smem_u32(a_smem) + (uint32_t)ks * 2u * a_plane, a_plane, 128);
+                    const uint64_t bd = umma_desc(smem_u32(b_smem) + (uint32_t)ks * 2u * b_plane, b_plane, 128);
+                    umma_bf16(tmem_base, ad, bd, idesc, ks > 0 ? 1u : 0u);
+                }
+                if (q == HG_QUARTERS - 1) umma_commit(bar_full);
+            }
+            __syncwarp();
+        }
+    }
+
+    // ---- epilogue: warps 0-3, thread = row (TMEM lane); logits + bias -> softmax / tanh -> staged -> coalesced stores
+    if (warp < 4) {
+        const float* bias = reinterpret_cast<const float*>(b_smem + (size_t)n_kc * b_plane);
+        mbar_wait(bar_full, 0u);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        uint32_t acc[NH];
+#pragma unroll
+        for (int c = 0; c < NH / 16; ++c) {
+            uint32_t (&blk)[16] = *reinterpret_cast<uint32_t (*)[16]>(&acc[c * 16]);
+            tmem_ld16_issue(tmem_base + ((uint32_t)(warp * 32) << 16) + c * 16, blk);
+        }
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int A = p.A;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int a = 0; a < NH; ++a) {
+            const float x = __uint_as_float(acc[a]) + bias[a];
+            acc[a] = __float_as_uint(x);
+            if (a < A) mx = fmaxf(mx, x);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int a = 0; a < NH; ++a)
+            if (a < A) {
+                const float e = __expf(__uint_as_float(acc[a]) - mx);
+                acc[a] = __float_as_uint(e);
+                sum += e;
+            }
+        const float inv = 1.f / sum;
+        // the A operand is dead once the accumulator is complete: stage probs [128][A] there for coalesced stores
+        float* stage = reinterpret_cast<float*>(a_smem);
+        const int row = warp * 32 + lane;
+        float v = 0.f;
+#pragma unroll
+        for (int a = 0; a < NH; ++a) {
+            if (a < A) stage[row * A + a] = __uint_as_float(acc[a]) * inv;
+            else if (a == A) v = __uint_as_float(acc[a]);
+        }
+        if (row0 + row < p.G) p.value[row0 + row] = tanhf(v);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int64_t n_valid = min((int64_t)HG_ROWS, p.G - row0) * A;
+        float* out = p.probs + row0 * A;
+        for (int i = tid; i < n_valid; i += 128) out[i] = stage[i];
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == HG_LOAD_WARPS)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128));
+}
+
 // ------------------------------------------------------------------------------------------------ C ABI
 
 extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES; }
@@ -744,5 +914,44 @@ extern "C" int az_net_heads(const void* logits, int ld, int action_size, int64_t
     k_net_heads<<<(unsigned)((G + 3) / 4), 128, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)logits, ld, A, G, probs,
                                                                        value);
     AZ_CHECK_LAUNCH("k_net_heads");
+    return AZ_OK;
+}
+
+static size_t hg_smem_bytes(int K, int NH) {
+    const size_t w = (size_t)(K / 8) * NH * 16 + NH * 4;
+    const size_t a = (size_t)(K / 8) * HG_ROWS * 16, stage = (size_t)HG_ROWS * NH * 4;
+    return (a > stage ? a : stage) + ((w + 127) & ~(size_t)127) + 128;
+}
+
+extern "C" int64_t az_net_headgemm_blob_bytes(int K, int NH) {
+    if (K < 16 || K > HG_MAX_K || (K % 32) || NH < 16 || NH > HG_MAX_NH || (NH % 16)) return AZ_ERR_ARG;
+    return (int64_t)(K / 8) * NH * 16 + NH * 4;
+}
+
+extern "C" int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action_size, int64_t G,
+                               float* probs, float* value, void* stream) {
+    if (az_net_headgemm_blob_bytes(K, NH) < 0 || action_size < 1 || action_size + 1 > NH || G < 0 ||
+        (G > 0 && (!h2 || !wblob || !probs || !value)))
+        return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    HeadGemmParams p;
+    p.h2 = (const __nv_bfloat16*)h2; p.wblob = (const uint8_t*)wblob; p.probs = probs; p.value = value;
+    p.G = G; p.K = K; p.NH = NH; p.A = action_size;
+    const size_t bytes = hg_smem_bytes(K, NH);
+    const unsigned grid = (unsigned)((G + HG_ROWS - 1) / HG_ROWS);
+    static size_t attr_bytes[HG_MAX_NH / 16 + 1] = {0};     // opt-in shared memory already granted per instantiation
+#define HG_CASE(N)                                                                                              \
+    case N:                                                                                                     \
+        if (attr_bytes[N / 16] < bytes) {                                                                       \
+            AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_headgemm<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)); \
+            attr_bytes[N / 16] = bytes;                                                                         \
+        }                                                                                                       \
+        k_net_headgemm<N><<<grid, HG_THREADS, bytes, (cudaStream_t)stream>>>(p);                                \
+        break;
+    switch (NH) {
+        HG_CASE(16) HG_CASE(32) HG_CASE(48) HG_CASE(64) HG_CASE(80) HG_CASE(96)
+        default: return AZ_ERR_ARG;
+    }
+    AZ_CHECK_LAUNCH("k_net_headgemm");
     return AZ_OK;
 }

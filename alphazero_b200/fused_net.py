@@ -88,9 +88,12 @@ class FusedNetEvaluator:
 
     own_kernels_per_call = 2   # k_net_trunk + k_net_heads (replayed inside the CUDA graph)
 
-    def __init__(self, nn, tree, use_cuda_graph: bool = True):
+    def __init__(self, nn, tree, use_cuda_graph: bool = True, heads: str = "library"):
+        if heads not in ("fused", "library"):
+            raise ValueError("heads must be 'fused' (az_net_headgemm) or 'library' (cuBLASLt GEMM + az_net_heads)")
         self.tree = tree
         self.use_cuda_graph = use_cuda_graph
+        self.heads = heads
         self.graph = None
         self.n_calls = 0
         self.refresh(nn)
@@ -124,7 +127,17 @@ class FusedNetEvaluator:
         bh = torch.zeros(self.ld, dtype=torch.float64)
         wh[:A] = nn.fc_probs.weight.detach().double().cpu(); bh[:A] = nn.fc_probs.bias.detach().double().cpu()
         wh[A] = nn.fc_value.weight.detach().double().cpu()[0]; bh[A] = nn.fc_value.bias.detach().double().cpu()[0]
-        self.wht, self.bh = bf(wh.t()), bf(bh)
+        self.wht, self.bh = bf(wh.t()), bf(bh)                                  # library-GEMM form (heads="library")
+        # fused heads kernel (az_net_headgemm): bf16 [h2/8][NH][8] K-major tiles + float bias[NH]
+        self.NH = ((A + 1 + 15) // 16) * 16
+        tiles = np.zeros((h2 // 8, self.NH, 8), dtype=np.uint16)
+        tiles[:, :A + 1, :] = _bf16_bits(wh[:A + 1].float()).reshape(A + 1, h2 // 8, 8).transpose(1, 0, 2)
+        bias = np.zeros(self.NH, dtype=np.float32)
+        bias[:A + 1] = bh[:A + 1].float().numpy()
+        blob = np.concatenate([tiles.reshape(-1).view(np.uint8), bias.view(np.uint8)])
+        assert blob.nbytes == int(_lib.lib().az_net_headgemm_blob_bytes(h2, self.NH))
+        self.head_blob = torch.from_numpy(blob.copy()).to(dev)
+        self.h2_features = h2
         self.features = torch.zeros(G, m * 32, dtype=torch.bfloat16, device=dev)
         self.h1 = torch.empty(G, h1, dtype=torch.bfloat16, device=dev)
         self.h2 = torch.empty(G, h2, dtype=torch.bfloat16, device=dev)
@@ -153,9 +166,14 @@ class FusedNetEvaluator:
         with torch.no_grad():
             torch._addmm_activation(self.b1, self.features, self.w1t, out=self.h1)      # fused bias + ReLU epilogue
             torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
-            torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
-        _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, self.A, t.G, _ptr(t.probs), _ptr(t.value), _stream()),
-                   "az_net_heads")
+            if self.heads == "library":
+                torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
+        if self.heads == "library":
+            _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, self.A, t.G, _ptr(t.probs), _ptr(t.value),
+                                               _stream()), "az_net_heads")
+        else:       # fc_probs / fc_value + softmax / tanh in one tcgen05 kernel
+            _lib.check(_lib.lib().az_net_headgemm(_ptr(self.h2), self.h2_features, _ptr(self.head_blob), self.NH, self.A,
+                                                  t.G, _ptr(t.probs), _ptr(t.value), _stream()), "az_net_headgemm")
 
     def _capture(self) -> None:
         s = torch.cuda.Stream(device=self.tree.device)

@@ -272,6 +272,17 @@ int az_connect4_image_bits(const uint64_t* own, const uint64_t* opp, int width, 
  * (othello.py:382, connect4.py:411, base.py:350-355). */
 int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* probs, float* value, void* stream);
 
+/* The two output layers and predict's exp(log_softmax) / tanh in one kernel: logits = h2 x Wh^T + bh (tcgen05 GEMM,
+ * fp32 logits that never reach memory), probs[g][0 .. A) = softmax(logits[0 .. A)), value[g] = tanh(logits[A]).
+ * h2: bf16 [G][K] (K a multiple of 32, <= 512).  wblob: az_net_headgemm_blob_bytes(K, NH) bytes =
+ * bf16 [K/8][NH][8] with blob[kc][n][j] = Wh[n][kc*8 + j] (rows 0 .. A-1 = fc_probs, row A = fc_value, the rest zero),
+ * then float bias[NH]; NH a multiple of 16 with A + 1 <= NH <= 96.
+ * Replaces fc_probs / fc_value + log_softmax / tanh (othello.py:361-362, 379-382; connect4.py:389-390, 408-411) and
+ * PolicyValueNetwork.predict (base.py:350-355). */
+int64_t az_net_headgemm_blob_bytes(int K, int NH);
+int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action_size, int64_t G, float* probs,
+                    float* value, void* stream);
+
 /* ---------------------------------------------------------------- TicTacToe ----------------------------- */
 /* 3 x 3 board on the same canvas (bit r*8+c, r, c < 3); an action is the canvas cell, there is no pass; the policy
  * vector index of cell (r, c) is 3*r + c (alphazero/games/tictactoe.py:325, 340).  The tree kernels take

@@ -112,3 +112,63 @@ def test_fused_forward_large_batch_and_tail_groups():
     # identical positions give identical outputs wherever they sit in the batch / group / tile
     assert (p[idx == 5] == p[5]).all() and (v[idx == 5] == v[5]).all()
     assert (p[-3:] == p[(G - 3) % len(own):(G - 3) % len(own) + 3]).all()
+
+
+@pytest.mark.parametrize("n,G", [(8, 4096), (8, 300), (6, 1000)])
+def test_fused_heads_kernel_matches_library_heads(n, G):
+    """az_net_headgemm (tcgen05 GEMM + softmax / tanh epilogue, fp32 logits) against the cuBLASLt GEMM + az_net_heads
+    path it replaces (bf16 logits): same inputs, outputs within the bf16 rounding of the logits; ragged last tile."""
+    from alphazero_b200.engine import TreeBatch
+    from alphazero_b200.fused_net import FusedNetEvaluator
+    from alphazero_b200.games.othello import OthelloNet
+    torch.manual_seed(n + G)
+    net = OthelloNet(n=n)
+    with torch.no_grad():
+        net.fc_probs.weight.mul_(4.0)          # spread the policy so that the comparison is not between uniform vectors
+    tree = TreeBatch(G, n=n, mode="neural", capacity=64)
+    bmask = sum(1 << (r * 8 + c) for r in range(n) for c in range(n))
+    a = torch.randint(0, 2**62, (G,), device="cuda") & bmask
+    b = torch.randint(0, 2**62, (G,), device="cuda") & bmask & ~a
+    tree.leaf_own.copy_(a); tree.leaf_opp.copy_(b)
+    outs = {}
+    for heads in ("library", "fused"):
+        ev = FusedNetEvaluator(net, tree, heads=heads)
+        tree.probs.zero_(); tree.value.zero_()
+        ev()
+        torch.cuda.synchronize()
+        outs[heads] = (tree.probs.clone(), tree.value.clone())
+    assert (outs["fused"][0].sum(1) - 1).abs().max() < 1e-5
+    assert (outs["fused"][0] - outs["library"][0]).abs().max() < 3e-3
+    assert (outs["fused"][1] - outs["library"][1]).abs().max() < 5e-3
+    # against the module itself in fp32: the north star's 1e-2
+    net32 = net.to("cuda"); net32.device = torch.device("cuda")
+    from alphazero_b200.gamespec import OthelloSpec
+    p32, v32 = net32.predict(OthelloSpec(n).encode(a, b))
+    assert (outs["fused"][0] - p32).abs().max() < 1e-2 and (outs["fused"][1] - v32.reshape(-1)).abs().max() < 1e-2
+
+
+@pytest.mark.parametrize("K,A,G", [(32, 65, 200), (64, 7, 129), (512, 37, 1000), (256, 95, 64)])
+def test_headgemm_raw_shapes(K, A, G):
+    """az_net_headgemm through the C ABI on random operands, over the feature / action sizes it accepts (including
+    feature counts whose operand tile is smaller than the probs staging area), against float64 torch."""
+    from alphazero_b200 import _lib
+    torch.manual_seed(K + A)
+    NH = ((A + 1 + 15) // 16) * 16
+    h2 = torch.randn(G, K, device="cuda").to(torch.bfloat16)
+    w = (torch.randn(A + 1, K) / K ** 0.5).to(torch.bfloat16)
+    bias = torch.randn(A + 1)
+    tiles = np.zeros((K // 8, NH, 8), dtype=np.uint16)
+    tiles[:, :A + 1, :] = w.view(torch.int16).numpy().view(np.uint16).reshape(A + 1, K // 8, 8).transpose(1, 0, 2)
+    b = np.zeros(NH, dtype=np.float32); b[:A + 1] = bias.numpy()
+    blob = torch.from_numpy(np.concatenate([tiles.reshape(-1).view(np.uint8), b.view(np.uint8)]).copy()).cuda()
+    assert blob.numel() == _lib.lib().az_net_headgemm_blob_bytes(K, NH)
+    probs = torch.full((G, A), -1.0, device="cuda"); value = torch.full((G,), -9.0, device="cuda")
+    _lib.check(_lib.lib().az_net_headgemm(h2.data_ptr(), K, blob.data_ptr(), NH, A, G, probs.data_ptr(), value.data_ptr(),
+                                          torch.cuda.current_stream().cuda_stream), "az_net_headgemm")
+    torch.cuda.synchronize()
+    logits = h2.double().cpu() @ w.double().t() + bias.double()
+    assert (probs.cpu().double() - torch.softmax(logits[:, :A], 1)).abs().max() < 1e-5
+    assert (value.cpu().double() - torch.tanh(logits[:, A])).abs().max() < 1e-5
+    # argument checks: unsupported sizes are refused, not mis-launched
+    assert _lib.lib().az_net_headgemm(h2.data_ptr(), K + 8, blob.data_ptr(), NH, A, G, probs.data_ptr(), value.data_ptr(), 0) != 0
+    assert _lib.lib().az_net_headgemm(h2.data_ptr(), K, blob.data_ptr(), NH, NH, G, probs.data_ptr(), value.data_ptr(), 0) != 0

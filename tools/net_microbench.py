@@ -30,12 +30,42 @@ def timeit(fn, name):
     print(f"{name:28s} {1000 * e0.elapsed_time(e1) / iters:8.2f} us")
 
 
+def timeit_graph(fn, name, reps=20):
+    """Same, with `reps` launches captured in one CUDA graph: removes the ctypes/launch floor (~12 us) of the loop above."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        fn()
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(max(1, iters // reps)):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"{name:28s} {1000 * e0.elapsed_time(e1) / (max(1, iters // reps) * reps):8.2f} us  (in a graph)")
+
+
 timeit(ev.trunk, "trunk (tcgen05)")
 timeit(lambda: torch._addmm_activation(ev.b1, ev.features, ev.w1t, out=ev.h1), "fc1+relu (cuBLASLt)")
 timeit(lambda: torch._addmm_activation(ev.b2, ev.h1, ev.w2t, out=ev.h2), "fc2+relu (cuBLASLt)")
 timeit(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cuBLASLt)")
 timeit(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
-timeit(ev, "whole forward (CUDA graph)")
+timeit_graph(lambda: torch._addmm_activation(ev.b1, ev.features, ev.w1t, out=ev.h1), "fc1+relu (cuBLASLt)")
+timeit_graph(lambda: torch._addmm_activation(ev.b2, ev.h1, ev.w2t, out=ev.h2), "fc2+relu (cuBLASLt)")
+timeit_graph(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cuBLASLt)")
+timeit_graph(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
+timeit_graph(lambda: _lib.check(_lib.lib().az_net_headgemm(ev.h2.data_ptr(), ev.h2_features, ev.head_blob.data_ptr(), ev.NH, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads fused (tcgen05)")
+timeit(ev, f"whole forward (graph, {ev.heads})")
+ev_fused = FusedOthelloEvaluator(net, tree, heads="fused")
+timeit(ev_fused, "whole forward (graph, fused)")
 timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
 
 # cycle accounting of the trunk's MMA warp / epilogue warps (debug_layer = 100)
