@@ -27,7 +27,8 @@ NODE_BYTES = 32
 class TreeBatch:
     def __init__(self, G: int, n=8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
                  device="cuda", seed: int = 0, tie_random: bool = True, dirichlet_alpha: float = None,
-                 dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128):
+                 dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128,
+                 graph_search: bool = True):
         if not torch.cuda.is_available():
             raise RuntimeError("TreeBatch needs a CUDA device (alphazero_b200 has no CPU path)")
         if mode not in ("neural", "rollout"):
@@ -70,6 +71,10 @@ class TreeBatch:
         self.n_rollouts = 0
         self.simulation_time = 0.0
         self.profile = None   # set to {"eval": [], "tree": []} to record (start, end) CUDA events per call
+        # a whole search (steps x (leaf evaluation, tree step)) as ONE CUDA graph from its second use on: one launch
+        # per move instead of 2 * n_sim, so a busy host cannot starve the device
+        self.graph_search = bool(graph_search)
+        self._search_graphs = {}      # (n_sim, steps, id(evaluator), evaluator.version) -> CUDAGraph | None (seen once)
         self._desc = _lib.AzTree()
         d = self._desc
         for name in ("nodes", "half", "n_alloc", "root_own", "root_opp", "root_player", "active", "sims_done",
@@ -143,6 +148,12 @@ class TreeBatch:
         self.step(n_sim, finish=False, select=True)
         steps = n_sim + (extra_steps if self.mode == "neural" else 0)
         prof = self.profile
+        graph = self._search_graph(n_sim, steps, evaluator) if (self.graph_search and prof is None) else None
+        if graph is not None:
+            graph.replay()
+            if evaluator is not None and hasattr(evaluator, "n_calls"):
+                evaluator.n_calls += steps
+            steps = 0
         for _ in range(steps):
             if prof is not None:
                 e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
@@ -164,6 +175,34 @@ class TreeBatch:
         if check:
             self.check_status()
             self.simulation_time = time.time() - start
+
+    def _search_graph(self, n_sim: int, steps: int, evaluator):
+        """The CUDA graph of `steps` x (leaf evaluation, az_tree_step) for this evaluator, captured the second time the
+        same search is asked for (a one-off search never pays the instantiation); None = run the loop.  Everything a
+        step reads that changes between searches (roots, pools, random counters, network outputs) lives in device
+        buffers whose addresses are fixed for the life of the tree, so a replay is a fresh search.  Evaluators carry
+        a `version` that changes when their buffers do (refresh())."""
+        if self.mode == "neural":
+            enqueue = getattr(evaluator, "enqueue", None)
+            if enqueue is None:
+                return None
+            key = (int(n_sim), int(steps), id(evaluator), getattr(evaluator, "version", 0))
+        else:
+            enqueue = self.rollout_leaves
+            key = (int(n_sim), int(steps), 0, 0)
+        if key not in self._search_graphs:
+            for k in [k for k in self._search_graphs if k[2] == key[2] and k[3] != key[3]]:
+                del self._search_graphs[k]                      # graphs over a refreshed evaluator's old buffers
+            self._search_graphs[key] = None
+            return None
+        if self._search_graphs[key] is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(steps):
+                    enqueue()
+                    self.step(n_sim, finish=True, select=True)
+            self._search_graphs[key] = g
+        return self._search_graphs[key]
 
     def check_status(self) -> None:
         """Raises if any game hit a pool overflow / depth overflow / illegal move (synchronises)."""

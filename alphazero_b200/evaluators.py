@@ -9,14 +9,24 @@ class HashEvaluator:
     """Deterministic test double (see tests/hash_eval.py): priors and values are a hash of the leaf position.
     Used for visit-count identity tests against the reference MCT; runs on the device (az_eval_hash)."""
 
-    def __init__(self, salt: int = 0):
+    def __init__(self, salt: int = 0, tree=None):
         self.salt = to_u64(salt)
         self.n_calls = 0
+        self.tree = tree          # bound to one tree: TreeBatch.search may capture it into a whole-search graph
+        self.version = 0
 
     def __call__(self, tree) -> None:
         _lib.check(_lib.lib().az_eval_hash(_ptr(tree.leaf_own), _ptr(tree.leaf_opp), tree.A, tree.G, self.salt,
                                            _ptr(tree.probs), _ptr(tree.value), _stream()), "az_eval_hash")
         self.n_calls += 1
+
+    @property
+    def enqueue(self):
+        if self.tree is None:     # not bound to one tree: TreeBatch.search runs it from the host loop
+            return None
+        t = self.tree
+        return lambda: _lib.check(_lib.lib().az_eval_hash(_ptr(t.leaf_own), _ptr(t.leaf_opp), t.A, t.G, self.salt,
+                                                          _ptr(t.probs), _ptr(t.value), _stream()), "az_eval_hash")
 
 
 class NetEvaluator:
@@ -35,10 +45,12 @@ class NetEvaluator:
         self.use_cuda_graph = use_cuda_graph
         self.graph = None
         self.n_calls = 0
+        self.version = 0
         self.refresh(nn)
 
     def refresh(self, nn) -> None:
         import copy
+        self.version += 1            # TreeBatch drops whole-search graphs captured over the old weights
         self.src = nn
         self.net = copy.deepcopy(nn).to(device=self.tree.device, dtype=self.dtype).eval()
         for p in self.net.parameters():
@@ -67,6 +79,10 @@ class NetEvaluator:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._forward()
+
+    def enqueue(self) -> None:
+        """The forward's kernels on the current stream, no graph replay: what TreeBatch captures into a search graph."""
+        self._forward()
 
     def __call__(self, tree=None) -> None:
         if self.graph is not None:

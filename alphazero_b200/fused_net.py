@@ -96,10 +96,12 @@ class FusedNetEvaluator:
         self.heads = heads
         self.graph = None
         self.n_calls = 0
+        self.version = 0
         self.refresh(nn)
 
     def refresh(self, nn) -> None:
         """(Re)packs the weights; call after the network changed (MCT.nn setter, mcts.py:78-83)."""
+        self.version += 1            # TreeBatch drops whole-search graphs captured over the old buffers
         t = self.tree
         dev, G = t.device, t.G
         shape = _image_shape(nn)
@@ -186,6 +188,10 @@ class FusedNetEvaluator:
         with torch.cuda.graph(self.graph):
             self._forward()
 
+    def enqueue(self) -> None:
+        """The forward's kernels on the current stream, no graph replay: what TreeBatch captures into a search graph."""
+        self._forward()
+
     def __call__(self, tree=None) -> None:
         if self.graph is not None:
             self.graph.replay()
@@ -214,9 +220,11 @@ class TicTacToeNetEvaluator:
             raise ValueError(f"network {nn} does not match the tree's game {tree.spec}")
         self.tree = tree
         self.n_calls = 0
+        self.version = 0
         self.refresh(nn)
 
     def refresh(self, nn) -> None:
+        self.version += 1
         self.src = nn
         w1, b1 = _fold_bn(nn.fc1.weight, nn.fc1.bias, nn.bn1)
         w2, b2 = _fold_bn(nn.fc2.weight, nn.fc2.bias, nn.bn2)
@@ -226,10 +234,13 @@ class TicTacToeNetEvaluator:
         assert flat.numel() == int(_lib.lib().az_tictactoe_net_floats())
         self.weights = flat.to(self.tree.device).contiguous()
 
-    def __call__(self, tree=None) -> None:
+    def enqueue(self) -> None:
         t = self.tree
         _lib.check(_lib.lib().az_tictactoe_net(_ptr(t.leaf_own), _ptr(t.leaf_opp), t.G, _ptr(self.weights),
                                                _ptr(t.probs), _ptr(t.value), _stream()), "az_tictactoe_net")
+
+    def __call__(self, tree=None) -> None:
+        self.enqueue()
         self.n_calls += 1
 
 

@@ -65,10 +65,13 @@ def test_visit_counts_identical_to_reference_fixture(golden_dir, n):
             tree.check_status()
 
 
-@pytest.mark.parametrize("n,n_sim,G", [(8, 1, 256), (8, 2, 256), (8, 50, 512), (8, 200, 256), (8, 400, 64), (6, 64, 256), (4, 40, 128)])
-def test_visit_counts_identical_to_oracle(n, n_sim, G):
+@pytest.mark.parametrize("n,n_sim,G,graph", [(8, 1, 256, False), (8, 2, 256, True), (8, 50, 512, True), (8, 50, 512, False),
+                                             (8, 200, 256, True), (8, 400, 64, False), (6, 64, 256, True),
+                                             (4, 40, 128, False)])
+def test_visit_counts_identical_to_oracle(n, n_sim, G, graph):
     """>= 1000 roots overall: random mid-game roots, several consecutive searches with tree reuse, then an
-    unexplored opponent move (fresh root) -- compared node statistics must be bit-identical."""
+    unexplored opponent move (fresh root) -- compared node statistics must be bit-identical.  graph=True: the
+    evaluator is bound to the tree, so the searches from the second on replay the whole-search CUDA graph."""
     from alphazero_b200.evaluators import HashEvaluator
     rng = np.random.default_rng(n * 1000 + n_sim)
     salt = 4242 + n_sim
@@ -89,7 +92,7 @@ def test_visit_counts_identical_to_oracle(n, n_sim, G):
         black, white, player = np.where(go, ob, black), np.where(go, ow, white), np.where(go, op, player)
     term, _, _ = orc.terminal(black, white, player, n)
     tree = _mk_tree(G, n, n_sim_hint=n_sim)
-    ev = HashEvaluator(salt)
+    ev = HashEvaluator(salt, tree if graph else None)
     _set_roots(tree, black, white, player)
     tree.active.copy_(torch.from_numpy((term == 0).astype(np.uint8)).cuda())
     oracles = [orc.OracleMCT(n, "neural", tie_random=False, salt=salt) for _ in range(G)]
@@ -132,6 +135,8 @@ def test_visit_counts_identical_to_oracle(n, n_sim, G):
         term, _, _ = orc.terminal(black, white, player, n)
         alive = alive & (term == 0)
         tree.active.copy_(torch.from_numpy(alive.astype(np.uint8)).cuda())
+    assert any(g is not None for g in tree._search_graphs.values()) == graph
+    assert ev.n_calls == 4 * (n_sim + 1)
 
 
 def test_advance_illegal_move_and_overflow_are_loud():

@@ -5,3 +5,6 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k "regex:k_net_trunk|k_tree_step|k_net_heads" -s 600 -c 6 -o gpurun_out/r1c_full -f python bench.py --games 4096 --sims 8 --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu rc=$?"
 tail -3 gpurun_out/pytest_gpu.log; tail -2 gpurun_out/smoke.log; cat gpurun_out/bench.json
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 2000 -c 400 --csv --log-file gpurun_out/r1d_launches.csv python bench.py --games 4096 --sims 8 --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
+timeout 600 python bench.py --game connect4 --no-cpu-baseline > gpurun_out/bench_connect4.json 2> gpurun_out/bench_connect4.err; echo "connect4 rc=$?"; cat gpurun_out/bench_connect4.json
+timeout 600 python bench.py --impl reference --steps 1 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "reference rc=$?"; cat gpurun_out/bench_reference.json
