@@ -338,6 +338,9 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
+    // launched with az_launch_pdl: everything above (barriers, TMEM, the weight copy in flight) may run beside the tail
+    // of the tree step that selects this launch's leaves; nothing below may
+    az_pdl_wait();
     const bool timing = p.debug && p.debug_layer == 100;   // cycle accounting into debug[blockIdx.x][0..15] (int64)
     const long long t_setup = clock64();
 
@@ -609,6 +612,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
 // into the tree's probs / value buffers.
 __global__ void __launch_bounds__(128) k_net_heads(const __nv_bfloat16* __restrict__ logits, int ld, int A, int64_t G,
                                                    float* __restrict__ probs, float* __restrict__ value) {
+    az_pdl_trigger();   // the tree step that follows (az_launch_pdl) waits for this grid's completion before reading
     const int64_t g = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= G) return;
@@ -869,9 +873,11 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
     p.debug_layer = debug ? debug_layer : 0;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM
-    if (rows == 8) k_net_trunk<8, 8><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
-    else if (rows == 6) k_net_trunk<6, 6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
-    else k_net_trunk<7, 6><<<grid, NET_THREADS, SM_TOTAL, (cudaStream_t)stream>>>(p);
+    cudaError_t e;
+    if (rows == 8) e = az_launch_pdl(k_net_trunk<8, 8>, dim3(grid), dim3(NET_THREADS), SM_TOTAL, (cudaStream_t)stream, p);
+    else if (rows == 6) e = az_launch_pdl(k_net_trunk<6, 6>, dim3(grid), dim3(NET_THREADS), SM_TOTAL, (cudaStream_t)stream, p);
+    else e = az_launch_pdl(k_net_trunk<7, 6>, dim3(grid), dim3(NET_THREADS), SM_TOTAL, (cudaStream_t)stream, p);
+    if (e != cudaSuccess) return az_set_cuda_error(e, "k_net_trunk");
     AZ_CHECK_LAUNCH("k_net_trunk");
     return AZ_OK;
 }

@@ -457,6 +457,11 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
 #endif
 template <int GAME>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
+    // launched with az_launch_pdl: every warp waits for the evaluator's outputs (probs / value) before anything else --
+    // also the warps of finished games, so that this grid never completes before its predecessor has -- and then lets
+    // the next kernel (the network trunk of the following step) start its prologue beside the tail of this one
+    az_pdl_wait();
+    az_pdl_trigger();
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G || !t.active[g]) return;
@@ -764,8 +769,15 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
     int rc = az_check_tree(t);
     if (rc) return rc;
     if (n_sim < 0) return AZ_ERR_ARG;
-    AZ_LAUNCH_GAME(t->game, k_tree_step, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, n_sim,
-                   do_finish, do_select);
+    const dim3 grid(az_warp_grid(t->G)), block(AZ_WARPS_PER_CTA * 32);
+    cudaError_t e;
+    if (t->game == AZ_GAME_OTHELLO)
+        e = az_launch_pdl(k_tree_step<AZ_GAME_OTHELLO>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+    else if (t->game == AZ_GAME_CONNECT4)
+        e = az_launch_pdl(k_tree_step<AZ_GAME_CONNECT4>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+    else
+        e = az_launch_pdl(k_tree_step<AZ_GAME_TICTACTOE>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+    if (e != cudaSuccess) return az_set_cuda_error(e, "k_tree_step");
     AZ_CHECK_LAUNCH("k_tree_step");
     return AZ_OK;
 }
