@@ -32,6 +32,7 @@
 
 #include "../../include/az_b200.h"
 #include "common.cuh"
+#include "net_heads.cuh"
 
 #define NET_CH 32                 // channels of every conv layer
 #define NET_TILE_M 128            // rows per MMA tile
@@ -617,31 +618,16 @@ __global__ void __launch_bounds__(128) k_net_heads(const __nv_bfloat16* __restri
     const int lane = threadIdx.x & 31;
     if (g >= G) return;
     const __nv_bfloat16* row = logits + g * ld;
-    float x[3];
-    float mx = -INFINITY;
+    float x[3], pr[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) x[i] = (lane + 32 * i) < A ? __bfloat162float(row[lane + 32 * i]) : 0.f;
+    az_heads_softmax(x, lane, A, pr);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         const int a = lane + 32 * i;
-        x[i] = a < A ? __bfloat162float(row[a]) : -INFINITY;
-        mx = fmaxf(mx, x[i]);
+        if (a < A) probs[g * A + a] = pr[i];
     }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    float e[3], s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        e[i] = (lane + 32 * i) < A ? __expf(x[i] - mx) : 0.f;
-        s += e[i];
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
-    const float inv = 1.f / s;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        const int a = lane + 32 * i;
-        if (a < A) probs[g * A + a] = e[i] * inv;
-    }
-    if (lane == 0) value[g] = tanhf(__bfloat162float(row[A]));
+    if (lane == 0) value[g] = az_heads_value(row[A]);
 }
 
 // ------------------------------------------------------------------------------------------------ heads GEMM

@@ -148,6 +148,7 @@ class SelfPlayEngine:
         self.total_sims = 0
         self.total_moves = 0
         self.plies_played = 0
+        self.max_nodes_used = 0      # high-water mark of any game's node pool half over the last play()
 
     def set_network(self, nn) -> None:
         """trainer.update_network (trainer.py:383-387): refresh the device snapshot + CUDA graph."""
@@ -167,6 +168,7 @@ class SelfPlayEngine:
         self.winner.copy_(win)
         tree.active.copy_(live.to(torch.uint8))
         sims = torch.zeros((), dtype=torch.int64, device=tree.device)
+        peak = torch.zeros((), dtype=torch.int32, device=tree.device)
         t = 0
         temp_t = torch.empty(G, dtype=torch.float32, device=tree.device)
         while t < self.max_plies:
@@ -175,6 +177,7 @@ class SelfPlayEngine:
             # fresh roots only exist on the first move: afterwards the played child always carries visits
             tree.search(self.n_sim, self.evaluator, extra_steps=1 if t == 0 else 0, check=False)
             sims += tree.sims_done.to(torch.int64)[live].sum()
+            peak = torch.maximum(peak, tree.n_alloc.max())
             temp_t.fill_(float(self.temp[t]))
             action, pi = tree.choose(temp_t)
             self.h_pi[t].copy_(pi)
@@ -192,6 +195,7 @@ class SelfPlayEngine:
             raise RuntimeError(f"self-play did not finish within max_plies={self.max_plies}")
         self.plies_played = t
         self.total_sims = int(sims.item())
+        self.max_nodes_used = int(peak.item())
         mask = self.h_live[:t]                                   # [t, G]
         self.total_moves = int(mask.sum().item())
         move_idx, episode_idx = torch.nonzero(mask.t(), as_tuple=True)[::-1]   # ordered by episode, then move

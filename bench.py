@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--capacity", type=int, default=None, help="nodes per tree-pool half (default 48 * (sims + 1))")
+    ap.add_argument("--capacity", type=int, default=None, help="nodes per tree-pool half (default 192 * (sims + 1))")
     ap.add_argument("--game", default="othello", choices=["othello", "connect4"],
                     help="othello: BASELINE config 3/4 (the headline); connect4: config 5 (7x6, Connect4Net)")
     ap.add_argument("--net", default="fused", choices=["fused", "torch"],
@@ -316,6 +316,7 @@ def run_ours(args):
                        "net": net_name + " random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
                        "leaves_in_flight_per_game": 1, "network_path": args.net, "tree_reuse": True,
                        "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
+                       "node_pool": {"capacity_per_game": tree.capacity, "peak_used_last_step": engine.max_nodes_used},
                        "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},
             "games_per_hour": dev_run["games"] / (dev_run["ms"] * 1e-3) * 3600.0,
             "moves_per_step": dev_run["moves"] / args.steps,
