@@ -34,7 +34,7 @@ class AzTree(ctypes.Structure):
         ("G", ctypes.c_int32), ("n", ctypes.c_int32), ("capacity", ctypes.c_int32), ("max_depth", ctypes.c_int32),
         ("mode", ctypes.c_int32), ("tie_random", ctypes.c_int32), ("enc_dtype", ctypes.c_int32),
         ("dirichlet_alpha", ctypes.c_float), ("dirichlet_eps", ctypes.c_float), ("game", ctypes.c_int32),
-        ("height", ctypes.c_int32), ("reserved", ctypes.c_int32),
+        ("height", ctypes.c_int32), ("logits_ld", ctypes.c_int32), ("logits", c_void_p),
     ]
 
 

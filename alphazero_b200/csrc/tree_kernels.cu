@@ -22,6 +22,7 @@
 #include "philox.cuh"
 #include "playout.cuh"
 #include "rules.cuh"
+#include "net_heads.cuh"
 
 static_assert(sizeof(az_node) == 32, "az_node must be 32 bytes");
 
@@ -115,15 +116,32 @@ __device__ __forceinline__ void az_encode_leaf(const az_tree& t, const az_dims& 
 // neural: P = probs[idx]/sum over the legal moves in float32, uniform when sum < 1e-6
 //         (OthelloNet.get_normalized_probs, othello.py:384-402);  rollout: P = 0 (mcts.py:152-154).
 // Returns the first child index (0 on pool overflow).
+// What az_alloc_children needs from memory, loaded by the caller ahead of time (k_tree_step issues these together with
+// the other per-game loads, so that their latencies overlap instead of forming a chain through the expansion).
+struct AllocPre {
+    uint32_t base;      // n_alloc[g]
+    uint32_t meta;      // word 5 of the leaf's node record
+    float row[3];       // network probabilities of actions lane, lane + 32, lane + 64 (0 beyond the action size)
+};
+
+// probs[idx] out of a row held lane-wise; every lane of the warp must call it.
+__device__ __forceinline__ float az_row_gather(const float (&row)[3], int idx) {
+    const float v0 = __shfl_sync(AZ_FULL, row[0], idx & 31), v1 = __shfl_sync(AZ_FULL, row[1], idx & 31),
+                v2 = __shfl_sync(AZ_FULL, row[2], idx & 31);
+    const int s = idx >> 5;
+    return s == 0 ? v0 : (s == 1 ? v1 : v2);
+}
+
 template <int GAME>
 __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az_dims& d, az_node* nodes, int g,
                                                       int lane, uint32_t leaf, uint64_t own, uint64_t opp,
-                                                      bool with_priors, uint32_t extra_flags, int* k_out) {
+                                                      bool with_priors, uint32_t extra_flags, int* k_out,
+                                                      const AllocPre* pre = nullptr) {
     using R = az_rules<GAME>;
     const uint64_t legal = az_warp_rules<GAME>::legal(own, opp, d, lane, nullptr);
     const int k = R::n_actions(legal);
     *k_out = k;
-    const uint32_t base = t.n_alloc[g];
+    const uint32_t base = pre ? pre->base : t.n_alloc[g];
     if (base + (uint32_t)k > (uint32_t)t.capacity) {
         if (lane == 0) t.status[g] |= AZ_STATUS_OVERFLOW;
         return 0u;
@@ -135,9 +153,18 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
     if (has0) a0 = R::nth_action(legal, lane);
     if (has1) a1 = R::nth_action(legal, lane + 32);
     if (with_priors) {
-        const float* pr = t.probs + (size_t)g * R::action_size(d);
-        if (has0) p0 = pr[R::net_index(a0, d)];
-        if (has1) p1 = pr[R::net_index(a1, d)];
+        if (pre) {
+            const float q0 = az_row_gather(pre->row, has0 ? R::net_index(a0, d) : 0);
+            if (has0) p0 = q0;
+            if (k > 32) {                                       // warp-uniform
+                const float q1 = az_row_gather(pre->row, has1 ? R::net_index(a1, d) : 0);
+                if (has1) p1 = q1;
+            }
+        } else {
+            const float* pr = t.probs + (size_t)g * R::action_size(d);
+            if (has0) p0 = pr[R::net_index(a0, d)];
+            if (has1) p1 = pr[R::net_index(a1, d)];
+        }
         float sum = az_warp_sum(p0 + p1);
         if (sum < 1e-6f) {
             p0 = p1 = (float)(1.0 / (double)k);
@@ -152,7 +179,7 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
     if (lane == 0) {
         // leaf record: keep Q/P/N, set the child block and flags (second 16 bytes only)
         uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[leaf]);
-        uint32_t meta = w[5];
+        uint32_t meta = pre ? pre->meta : w[5];
         uint32_t flags = ((meta >> 16) & 0xffu) | AZ_NODE_EVAL | extra_flags;
         w[4] = base;
         w[5] = az_make_meta(k, (int)((meta >> 8) & 0xffu), flags);
@@ -164,16 +191,19 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
 
 // MCT.back_propagate (mcts.py:197-223): reward for the leaf, sign alternating towards the root; every node on the
 // path gets Q = (N*Q + r)/(N+1) in float64 and N += 1.  Lane j updates path node j (nodes are distinct).
+// `path_lane` = path[lane] and `rec_lane` = the first 16 bytes (Q, P, N) of that node, loaded by the caller ahead of
+// time (valid for lane < min(len, 32)): nothing between that load and here writes those bytes -- the expansion only
+// touches the second half of the leaf's record and records that are not on the path.
 __device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int g, int lane, int player_to_play,
-                                          double outcome, int len) {
+                                          double outcome, int len, uint32_t path_lane, uint4 rec_lane) {
     double reward;
     if (fabs(outcome) < 1e-4) reward = 0.0;
     else reward = ((double)player_to_play * outcome > 0.0) ? -fabs(outcome) : fabs(outcome);
     const uint32_t* path = t.path + (size_t)g * t.max_depth;
     for (int j = lane; j < len; j += 32) {
-        az_node* nd = &nodes[path[j]];
+        az_node* nd = &nodes[j < 32 ? path_lane : path[j]];
         uint4* q = reinterpret_cast<uint4*>(nd);
-        uint4 a = q[0];
+        uint4 a = j < 32 ? rec_lane : q[0];
         double Q = __hiloint2double((int)a.y, (int)a.x);
         uint32_t N = a.w;
         double r = ((len - 1 - j) & 1) ? -reward : reward;
@@ -193,9 +223,15 @@ struct LeafRegs {
     uint32_t leaf, path_len;
     uint64_t own, opp;
     float value;
+    uint32_t path_lane;     // path[lane]
+    AllocPre alloc;         // n_alloc, network row (first round of loads); leaf meta word (second round)
+    uint4 rec_lane;         // first half of node path[lane] (second round)
 };
 
-__device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, int g) {
+// First round: everything that only depends on g.  With az_tree.logits the evaluator's raw bf16 row is turned into
+// probabilities / value here (net_heads.cuh: the arithmetic of az_net_heads).
+template <int GAME>
+__device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, const az_dims& d, int g, int lane) {
     LeafRegs r;
     r.kind = t.leaf_kind[g];
     r.leaf = t.leaf_node[g];
@@ -203,8 +239,38 @@ __device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, int g) {
     r.path_len = t.path_len[g];
     r.own = t.leaf_own[g];
     r.opp = t.leaf_opp[g];
-    r.value = t.value[g];
+    r.alloc.base = t.n_alloc[g];
+    r.path_lane = lane < t.max_depth ? t.path[(size_t)g * t.max_depth + lane] : 0u;
+    r.alloc.row[0] = r.alloc.row[1] = r.alloc.row[2] = 0.f;
+    if (t.mode == AZ_MODE_NEURAL) {
+        const int A = az_rules<GAME>::action_size(d);
+        if (t.logits) {
+            const __nv_bfloat16* row = reinterpret_cast<const __nv_bfloat16*>(t.logits) + (size_t)g * t.logits_ld;
+            float x[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) x[i] = (lane + 32 * i) < A ? __bfloat162float(row[lane + 32 * i]) : 0.f;
+            const __nv_bfloat16 v = row[A];
+            az_heads_softmax(x, lane, A, r.alloc.row);
+            r.value = az_heads_value(v);
+        } else {
+            const float* pr = t.probs + (size_t)g * A;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) if (lane + 32 * i < A) r.alloc.row[i] = pr[lane + 32 * i];
+            r.value = t.value[g];
+        }
+    } else {
+        r.value = t.value[g];
+    }
     return r;
+}
+
+// Second round: the two node reads whose addresses the first round produced.
+__device__ __forceinline__ void az_load_leaf_nodes(LeafRegs& r, const az_node* nodes, int lane) {
+    r.alloc.meta = 0u;
+    r.rec_lane = make_uint4(0u, 0u, 0u, 0u);
+    if (r.kind == AZ_LEAF_IDLE) return;
+    r.alloc.meta = reinterpret_cast<const uint32_t*>(&nodes[r.leaf])[5];
+    if (r.kind != AZ_LEAF_PRIME && lane < (int)r.path_len) r.rec_lane = reinterpret_cast<const uint4*>(&nodes[r.path_lane])[0];
 }
 
 template <int GAME>
@@ -216,14 +282,14 @@ __device__ __forceinline__ void az_finish(const az_tree& t, const az_dims& d, az
     const int leaf_player = lf.leaf_player;
     if (kind == AZ_LEAF_NN || kind == AZ_LEAF_PRIME) {
         int k;
-        az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, lf.own, lf.opp, true, 0u, &k);
+        az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, lf.own, lf.opp, true, 0u, &k, &lf.alloc);
     }
     if (kind != AZ_LEAF_PRIME) {
         double outcome;
         if (kind == AZ_LEAF_NN) outcome = (double)((float)leaf_player * lf.value);     // base.py:366
         else if (kind == AZ_LEAF_ROLLOUT) outcome = (double)lf.value;                   // absolute winner id
         else outcome = kind == AZ_LEAF_DRAW ? 0.0 : (kind == AZ_LEAF_BLACK ? 1.0 : -1.0);
-        az_backup(t, nodes, g, lane, leaf_player, outcome, (int)lf.path_len);
+        az_backup(t, nodes, g, lane, leaf_player, outcome, (int)lf.path_len, lf.path_lane, lf.rec_lane);
         if (lane == 0) t.sims_done[g] += 1u;
     }
     if (lane == 0) t.leaf_kind[g] = AZ_LEAF_IDLE;
@@ -353,12 +419,24 @@ __device__ __forceinline__ int az_terminal_kind(uint64_t own, uint64_t opp, int 
 }
 
 // MCT.__search_iter up to the evaluation (mcts.py:226-248): priming, noise, select_node; writes the leaf buffers.
+struct RootRegs {       // per-game inputs of the selection, loaded with the first round of k_tree_step
+    uint64_t own, opp;
+    int player;
+    uint32_t event;
+};
+__device__ __forceinline__ RootRegs az_load_root(const az_tree& t, int g) {
+    RootRegs r;
+    r.own = t.root_own[g]; r.opp = t.root_opp[g]; r.player = t.root_player[g]; r.event = t.rng_ctr[g];
+    return r;
+}
+
 template <int GAME>
-__device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane) {
+__device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane,
+                                          const RootRegs& root) {
     using W = az_warp_rules<GAME>;
-    uint64_t own = t.root_own[g], opp = t.root_opp[g];
-    int player = t.root_player[g];
-    uint32_t event = t.rng_ctr[g];
+    uint64_t own = root.own, opp = root.opp;
+    int player = root.player;
+    uint32_t event = root.event;
     uint32_t* path = t.path + (size_t)g * t.max_depth;
     NodeRec cur = az_load_node(&nodes[0]);
     uint32_t cur_idx = 0u;
@@ -453,7 +531,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
 }
 
 #ifndef AZ_TREE_MIN_CTAS
-#define AZ_TREE_MIN_CTAS 8    // resident CTAs per SM the register budget is sized for (latency-bound kernel)
+#define AZ_TREE_MIN_CTAS 7    // resident CTAs per SM the register budget is sized for: 1024 CTAs / 148 SMs = one wave at 7
 #endif
 template <int GAME>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
@@ -464,17 +542,25 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tre
     az_pdl_trigger();
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (g >= t.G || !t.active[g]) return;
+    if (g >= t.G) return;
     const az_dims d = az_rules<GAME>::dims(t.n, t.height);
-    az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    // first round: every load whose address only depends on g, issued before the first use of any of them
+    const uint8_t active = t.active[g];
+    const uint8_t half = t.half[g];
     const uint32_t sims_before = t.sims_done[g];
+    LeafRegs lf;
+    if (do_finish) lf = az_load_leaf<GAME>(t, d, g, lane);
+    RootRegs root;
+    if (do_select) root = az_load_root(t, g);
+    if (!active) return;
+    az_node* nodes = t.nodes + ((size_t)g * 2 + half) * (size_t)t.capacity;
     bool backed_up = false;
     if (do_finish) {
-        const LeafRegs lf = az_load_leaf(t, g);
+        az_load_leaf_nodes(lf, nodes, lane);       // second round
         az_finish<GAME>(t, d, nodes, g, lane, lf);
         backed_up = lf.kind != AZ_LEAF_IDLE && lf.kind != AZ_LEAF_PRIME;
     }
-    if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane);
+    if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane, root);
 }
 
 // ------------------------------------------------------------------------------------------------ misc kernels
@@ -744,6 +830,10 @@ static int az_check_tree(const az_tree* t) {
     if (t->mode != AZ_MODE_ROLLOUT && t->mode != AZ_MODE_NEURAL) return AZ_ERR_ARG;
     if (t->mode == AZ_MODE_NEURAL && (!t->probs || !t->value)) return AZ_ERR_ARG;
     if (t->mode == AZ_MODE_ROLLOUT && !t->value) return AZ_ERR_ARG;
+    if (t->logits) {                                            // raw network rows: A policy logits + the value logit
+        const int A = t->game == AZ_GAME_OTHELLO ? t->n * t->n + 1 : (t->game == AZ_GAME_CONNECT4 ? t->n : 9);
+        if (t->mode != AZ_MODE_NEURAL || t->logits_ld < A + 1) return AZ_ERR_ARG;
+    }
     return AZ_OK;
 }
 

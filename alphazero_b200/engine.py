@@ -76,6 +76,7 @@ class TreeBatch:
         # a whole search (steps x (leaf evaluation, tree step)) as ONE CUDA graph from its second use on: one launch
         # per move instead of 2 * n_sim, so a busy host cannot starve the device
         self.graph_search = bool(graph_search)
+        self.graph_step_launches = 0  # az_tree_step kernels replayed inside search graphs (not seen by _lib.LAUNCH_CALLS)
         self._search_graphs = {}      # (n_sim, steps, id(evaluator), evaluator.version) -> CUDAGraph | None (seen once)
         self._desc = _lib.AzTree()
         d = self._desc
@@ -146,6 +147,9 @@ class TreeBatch:
         if self.mode == "neural" and evaluator is None:
             raise ValueError("neural mode needs an evaluator")
         start = time.time()
+        # an evaluator whose raw output rows the tree step reads itself (az_tree.logits); else probs / value
+        binding = getattr(evaluator, "logits_binding", None) if self.mode == "neural" else None
+        self._desc.logits, self._desc.logits_ld = (binding[0], int(binding[1])) if binding else (None, 0)
         self.sims_done.zero_()
         self.step(n_sim, finish=False, select=True)
         steps = n_sim + (extra_steps if self.mode == "neural" else 0)
@@ -153,8 +157,11 @@ class TreeBatch:
         graph = self._search_graph(n_sim, steps, evaluator) if (self.graph_search and prof is None) else None
         if graph is not None:
             graph.replay()
+            self.graph_step_launches += steps
             if evaluator is not None and hasattr(evaluator, "n_calls"):
                 evaluator.n_calls += steps
+                if hasattr(evaluator, "own_launches"):
+                    evaluator.own_launches += steps * evaluator.own_kernels_per_enqueue
             steps = 0
         for _ in range(steps):
             if prof is not None:

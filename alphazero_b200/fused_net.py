@@ -88,12 +88,17 @@ class FusedNetEvaluator:
 
     own_kernels_per_call = 2   # k_net_trunk + k_net_heads (replayed inside the CUDA graph)
 
-    def __init__(self, nn, tree, use_cuda_graph: bool = True, heads: str = "library"):
+    def __init__(self, nn, tree, use_cuda_graph: bool = True, heads: str = "library", heads_in_tree: bool = True):
+        """heads_in_tree: inside a whole-search graph (TreeBatch.search -> enqueue()) the softmax / tanh of the heads is
+        left to the tree step, which reads the bf16 logits row itself (az_tree.logits, same arithmetic and bits as
+        az_net_heads); a plain call still runs az_net_heads so that tree.probs / tree.value are always valid."""
         if heads not in ("fused", "library"):
             raise ValueError("heads must be 'fused' (az_net_headgemm) or 'library' (cuBLASLt GEMM + az_net_heads)")
         self.tree = tree
         self.use_cuda_graph = use_cuda_graph
         self.heads = heads
+        self.heads_in_tree = bool(heads_in_tree) and heads == "library"
+        self.own_launches = 0
         self.graph = None
         self.n_calls = 0
         self.version = 0
@@ -144,6 +149,8 @@ class FusedNetEvaluator:
         self.h1 = torch.empty(G, h1, dtype=torch.bfloat16, device=dev)
         self.h2 = torch.empty(G, h2, dtype=torch.bfloat16, device=dev)
         self.logits = torch.empty(G, self.ld, dtype=torch.bfloat16, device=dev)
+        # (pointer, row pitch) TreeBatch.search puts into az_tree.logits for this evaluator, or None
+        self.logits_binding = (self.logits.data_ptr(), self.ld) if self.heads_in_tree else None
         if self.connect4:
             self.img_own = torch.zeros(G, dtype=torch.int64, device=dev)
             self.img_opp = torch.zeros(G, dtype=torch.int64, device=dev)
@@ -162,7 +169,7 @@ class FusedNetEvaluator:
         _lib.check(_lib.lib().az_net_trunk(_ptr(own), _ptr(opp), self.rows, self.cols, t.G, _ptr(self.wblob),
                                            _ptr(self.features), _ptr(debug), int(debug_layer), _stream()), "az_net_trunk")
 
-    def _forward(self) -> None:
+    def _forward(self, output_transform: bool = True) -> None:
         t = self.tree
         self.trunk()
         with torch.no_grad():
@@ -170,6 +177,8 @@ class FusedNetEvaluator:
             torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
             if self.heads == "library":
                 torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
+        if not output_transform:
+            return
         if self.heads == "library":
             _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, self.A, t.G, _ptr(t.probs), _ptr(t.value),
                                                _stream()), "az_net_heads")
@@ -188,9 +197,14 @@ class FusedNetEvaluator:
         with torch.cuda.graph(self.graph):
             self._forward()
 
+    @property
+    def own_kernels_per_enqueue(self) -> int:
+        return self.own_kernels_per_call - (1 if self.logits_binding is not None else 0)
+
     def enqueue(self) -> None:
-        """The forward's kernels on the current stream, no graph replay: what TreeBatch captures into a search graph."""
-        self._forward()
+        """The forward's kernels on the current stream, no graph replay: what TreeBatch captures into a search graph
+        (without az_net_heads when the tree step reads the logits itself)."""
+        self._forward(output_transform=self.logits_binding is None)
 
     def __call__(self, tree=None) -> None:
         if self.graph is not None:
@@ -198,6 +212,7 @@ class FusedNetEvaluator:
         else:
             self._forward()
         self.n_calls += 1
+        self.own_launches += self.own_kernels_per_call
 
 
 FusedOthelloEvaluator = FusedNetEvaluator   # name used before Connect4Net was covered

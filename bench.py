@@ -235,6 +235,7 @@ def run_ours(args):
         launches0 = _lib.LAUNCH_CALLS
         ev = engine.evaluator
         graph0 = getattr(ev, "n_calls", 0)
+        own0, steps0 = getattr(ev, "own_launches", None), engine.tree.graph_step_launches
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record()
@@ -257,8 +258,10 @@ def run_ours(args):
         return {"ms": float(stats[0]), "wall_ms": float(stats[1]), "sims": float(tot[0]), "moves": float(tot[1]),
                 "games": float(tot[2]), "clocks": clocks, "last": last,
                 # C-ABI launches issued from Python + our kernels replayed inside the evaluator's CUDA graph
-                "launches": (_lib.LAUNCH_CALLS - launches0)
-                + (getattr(ev, "n_calls", 0) - graph0) * getattr(ev, "own_kernels_per_call", 0)}
+                # and the tree steps / evaluator kernels replayed inside whole-search graphs
+                "launches": (_lib.LAUNCH_CALLS - launches0) + (engine.tree.graph_step_launches - steps0)
+                + ((ev.own_launches - own0) if own0 is not None
+                   else (getattr(ev, "n_calls", 0) - graph0) * getattr(ev, "own_kernels_per_call", 0))}
 
     dev_run = timed(step_device, args.steps)
     e2e_run = timed(step_e2e, args.steps)

@@ -199,7 +199,11 @@ typedef struct az_tree {
     float dirichlet_eps;
     int32_t game;          /* AZ_GAME_* */
     int32_t height;        /* Connect4: rows; ignored for Othello */
-    int32_t reserved;
+    int32_t logits_ld;     /* row pitch of `logits` in elements (>= A + 1) */
+    const void* logits;    /* optional, neural mode: bf16 [G][logits_ld] raw network outputs (policy logits 0 .. A-1, value
+                              logit at A).  When not NULL az_tree_step takes priors = softmax(logits[0 .. A)) and
+                              value = tanh(logits[A]) -- the arithmetic of az_net_heads, same bits -- from here and
+                              ignores probs / value: the evaluator then needs no output-transform launch. */
 } az_tree;
 
 /* Fresh trees (reference: MCT() / player.reset()) for the games with mask[g] != 0 (mask NULL = all):

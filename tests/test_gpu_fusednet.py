@@ -172,3 +172,46 @@ def test_headgemm_raw_shapes(K, A, G):
     # argument checks: unsupported sizes are refused, not mis-launched
     assert _lib.lib().az_net_headgemm(h2.data_ptr(), K + 8, blob.data_ptr(), NH, A, G, probs.data_ptr(), value.data_ptr(), 0) != 0
     assert _lib.lib().az_net_headgemm(h2.data_ptr(), K, blob.data_ptr(), NH, NH, G, probs.data_ptr(), value.data_ptr(), 0) != 0
+
+
+@pytest.mark.parametrize("game", ["othello8", "othello6", "connect4"])
+def test_tree_step_reading_logits_gives_identical_search(game):
+    """az_tree.logits: the tree step takes softmax / tanh of the evaluator's raw bf16 rows itself (inside the
+    whole-search graph az_net_heads is not launched at all) -- node statistics, priors and chosen moves must be
+    bit-identical to the search that reads az_net_heads' probs / value."""
+    from alphazero_b200.engine import TreeBatch
+    from alphazero_b200.fused_net import FusedNetEvaluator
+    from alphazero_b200.gamespec import Connect4Spec, OthelloSpec
+    from alphazero_b200.games.connect4 import Connect4Net
+    from alphazero_b200.games.othello import OthelloNet
+    torch.manual_seed(5)
+    if game == "connect4":
+        spec, net = Connect4Spec(7, 6), Connect4Net(board_width=7, board_height=6)
+    else:
+        n = int(game[-1])
+        spec, net = OthelloSpec(n), OthelloNet(n=n)
+    with torch.no_grad():
+        net.fc_probs.weight.mul_(4.0)
+    G, n_sim = 300, 60
+    stats = {}
+    for in_tree in (False, True):
+        tree = TreeBatch(G, n=spec, mode="neural", n_sim_hint=n_sim, seed=11, tie_random=False)
+        tree.reset_roots()
+        ev = FusedNetEvaluator(net, tree, heads_in_tree=in_tree)
+        assert (ev.logits_binding is not None) == in_tree
+        rec = []
+        for move in range(4):
+            tree.search(n_sim, ev)
+            N, Q, P, rn = tree.root_stats()
+            action, pi = tree.choose(None)
+            rec.append((N.clone(), Q.clone(), P.clone(), rn.clone(), action.clone()))
+            tree.advance(action)
+            tree.check_status()
+        assert any(g is not None for g in tree._search_graphs.values())      # moves 1.. replayed the search graph
+        # first search from the host loop (trunk + az_net_heads per step), three from the graph
+        per_call = 3 if game == "connect4" else 2                          # (+ az_connect4_image_bits)
+        assert ev.own_launches == (n_sim + 1) * per_call + 3 * (n_sim + 1) * (per_call - (1 if in_tree else 0))
+        stats[in_tree] = rec
+    for a, b in zip(stats[False], stats[True]):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
