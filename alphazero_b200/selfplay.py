@@ -149,6 +149,7 @@ class SelfPlayEngine:
         self.total_moves = 0
         self.plies_played = 0
         self.max_nodes_used = 0      # high-water mark of any game's node pool half over the last play()
+        self.search_events = None    # set to [] to record (start event, end event, steps) of every search of play()
 
     def set_network(self, nn) -> None:
         """trainer.update_network (trainer.py:383-387): refresh the device snapshot + CUDA graph."""
@@ -175,7 +176,13 @@ class SelfPlayEngine:
             self.h_own[t].copy_(tree.root_own); self.h_opp[t].copy_(tree.root_opp)
             self.h_player[t].copy_(tree.root_player); self.h_live[t].copy_(live)
             # fresh roots only exist on the first move: afterwards the played child always carries visits
+            if self.search_events is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             tree.search(self.n_sim, self.evaluator, extra_steps=1 if t == 0 else 0, check=False)
+            if self.search_events is not None:
+                e1.record()
+                self.search_events.append((e0, e1, self.n_sim + (1 if t == 0 else 0)))
             sims += tree.sims_done.to(torch.int64)[live].sum()
             peak = torch.maximum(peak, tree.n_alloc.max())
             temp_t.fill_(float(self.temp[t]))

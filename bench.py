@@ -284,8 +284,38 @@ def run_ours(args):
     n_calls = len(prof["eval"])
     mean_depth = float(prof["depth_sum"].item()) / max(1.0, float(prof["depth_cnt"].item()))
     peaks = measured_peaks()
-    eval_ms = t_eval / n_calls
-    tree_ms = t_tree / n_calls
+    eager_eval_ms = t_eval / n_calls      # one evaluator-graph replay per call: includes the launch of that graph
+    eager_tree_ms = t_tree / n_calls
+    # ---- the same phases as the product runs them, i.e. inside the whole-search CUDA graph: (1) every search of one
+    # more self-play batch between CUDA events -> device time per simulation step; (2) the evaluator's kernels alone,
+    # K forwards back to back in one graph -> device time per network forward; the tree step is the difference
+    engine.search_events = []
+    engine.play()
+    torch.cuda.synchronize()
+    search_ms = sum(a.elapsed_time(b) for a, b, _ in engine.search_events)
+    search_steps = sum(k for _, _, k in engine.search_events)
+    engine.search_events = None
+    step_ms = search_ms / max(1, search_steps)
+    eval_ms, tree_ms, timing = eager_eval_ms, eager_tree_ms, "eager calls between CUDA events"
+    if hasattr(engine.evaluator, "enqueue") and tree.graph_search:
+        K = 64
+        net_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(net_graph):
+            for _ in range(K):
+                engine.evaluator.enqueue()
+        net_graph.replay()
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(8):
+            net_graph.replay()
+        g1.record()
+        torch.cuda.synchronize()
+        eval_ms = g0.elapsed_time(g1) / (8 * K)
+        tree_ms = max(step_ms - eval_ms, 1e-6)
+        timing = ("inside CUDA graphs: forward = 64 forwards back to back in one graph; tree step = "
+                  "(search time / simulation steps) - forward")
+        del net_graph
     tflops = G * flop_per_eval / (eval_ms * 1e-3) / 1e12
     roofline = {
         "bound": "tensor", "kernel": f"policy-value network forward over the leaf batch (bf16, CUDA graph, path={args.net})",
@@ -294,7 +324,9 @@ def run_ours(args):
         "traffic": ncu_traffic("k_net_trunk") if args.net == "fused" else None,
         "traffic_note": "DRAM bytes per k_net_trunk launch (ncu --set full, profiles/r1_ncu_full_summary.txt); "
                         "activations never leave shared memory, features stay in L2 for the fc GEMMs",
-        "ms_per_launch": eval_ms, "share_of_step": t_eval / (t_eval + t_tree),
+        "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
+        "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
+        "search_share_of_batch": search_ms / (dev_run["ms"] / args.steps),
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
@@ -305,7 +337,8 @@ def run_ours(args):
     tree_roofline = {"bound": "hbm", "kernel": "k_tree_step (backup + expand + select + encode)", "achieved": tree_gbs,
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
                      "ms_per_launch": tree_ms, "mean_depth": mean_depth, "bytes_per_sim": bytes_per_sim,
-                     "share_of_step": t_tree / (t_eval + t_tree), "traffic": ncu_traffic("k_tree_step")}
+                     "share_of_step": tree_ms / (eval_ms + tree_ms), "ms_per_launch_eager": eager_tree_ms,
+                     "traffic": ncu_traffic("k_tree_step")}
 
     if rank == 0:
         value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
