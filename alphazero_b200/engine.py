@@ -28,7 +28,7 @@ class TreeBatch:
     def __init__(self, G: int, n=8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
                  device="cuda", seed: int = 0, tie_random: bool = True, dirichlet_alpha: float = None,
                  dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128,
-                 graph_search: bool = True):
+                 graph_search: bool = True, graph_first_use: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("TreeBatch needs a CUDA device (alphazero_b200 has no CPU path)")
         if mode not in ("neural", "rollout"):
@@ -76,6 +76,7 @@ class TreeBatch:
         # a whole search (steps x (leaf evaluation, tree step)) as ONE CUDA graph from its second use on: one launch
         # per move instead of 2 * n_sim, so a busy host cannot starve the device
         self.graph_search = bool(graph_search)
+        self.graph_first_use = bool(graph_first_use)   # capture at the first use (batches that exist to be reused)
         self.graph_step_launches = 0  # az_tree_step kernels replayed inside search graphs (not seen by _lib.LAUNCH_CALLS)
         self._search_graphs = {}      # (n_sim, steps, id(evaluator), evaluator.version) -> CUDAGraph | None (seen once)
         self._desc = _lib.AzTree()
@@ -127,6 +128,30 @@ class TreeBatch:
         self.root_own.copy_(own); self.root_opp.copy_(opp); self.root_player.copy_(player)
         if fresh_trees:
             self.reset_trees()
+
+    def adopt(self, src: "TreeBatch", sel: torch.Tensor, n_nodes: int = None) -> None:
+        """Moves the games `sel` (indices into `src`) into slots 0..k-1 of this batch: root position, kept search tree
+        (the live half of the node pool, its first `n_nodes` records -- default the whole half), random counter and
+        sticky status.  Slots k.. are switched off.  Used by SelfPlayEngine to carry the last live games of a batch
+        over to a smaller batch (smaller leaf batches for the network) when most games have ended."""
+        if (src.spec.game_id, src.n, src.spec.height, src.capacity, src.mode) != \
+                (self.spec.game_id, self.n, self.spec.height, self.capacity, self.mode):
+            raise ValueError("adopt: the two tree batches differ in game, pool capacity or mode")
+        k = int(sel.numel())
+        if k > self.G:
+            raise ValueError(f"adopt: {k} games do not fit {self.G} slots")
+        sel = sel.to(device=src.device, dtype=torch.int64)
+        for name in ("root_own", "root_opp", "root_player", "n_alloc", "rng_ctr", "status"):
+            getattr(self, name)[:k] = getattr(src, name)[sel]
+        words = self.capacity * NODE_BYTES // 8
+        m = words if n_nodes is None else min(words, int(n_nodes) * NODE_BYTES // 8)
+        sv = src.nodes.view(torch.int64).view(src.G, 2, words)
+        dv = self.nodes.view(torch.int64).view(self.G, 2, words)
+        dv[:k, 0, :m] = sv[sel, src.half[sel].to(torch.int64), :m]
+        self.half[:k] = 0
+        self.leaf_kind.zero_()
+        self.active.zero_()
+        self.active[:k] = 1
 
     def reset_trees(self, mask: torch.Tensor = None) -> None:
         m = None if mask is None else mask.to(torch.uint8).contiguous()
@@ -203,7 +228,8 @@ class TreeBatch:
             for k in [k for k in self._search_graphs if k[2] == key[2] and k[3] != key[3]]:
                 del self._search_graphs[k]                      # graphs over a refreshed evaluator's old buffers
             self._search_graphs[key] = None
-            return None
+            if not self.graph_first_use:
+                return None
         if self._search_graphs[key] is None:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):

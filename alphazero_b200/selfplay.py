@@ -124,7 +124,7 @@ class SelfPlayEngine:
                  dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
                  temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
                  tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
-                 network_path: str = "auto"):
+                 network_path: str = "auto", tail_tiers="auto"):
         # `n`: Othello board size or a GameSpec (gamespec.Connect4Spec(7, 6) for BASELINE config 5)
         self.spec = spec = as_spec(n)
         self.G, self.n, self.n_sim = G, spec.n, n_sim
@@ -136,6 +136,18 @@ class SelfPlayEngine:
             self.evaluator = evaluator
         else:
             self.evaluator = make_evaluator(nn, self.tree, dtype=dtype, path=network_path)
+        # Tail of a batch: games of one batch end within a few plies of each other, and the last plies would run the
+        # full-size leaf batch through the network for a handful of live games (Othello 8x8, 4096 games: 1481 / 285 /
+        # 29 / 8 / 1 / 1 games live after plies 60..65).  `tail_tiers` = sizes of smaller TreeBatches (own pools,
+        # evaluator and search graph, built on first use) the live games are moved to once they fit:
+        # "auto" = G/2, G/8, G/64 for G >= 1024, nothing below; () switches it off.  A caller-supplied evaluator is
+        # bound to the main tree, so it switches it off too.
+        if tail_tiers == "auto":
+            tail_tiers = tuple(G // d for d in (2, 8, 64)) if G >= 1024 else ()
+        self.tail_tiers = tuple(sorted({int(x) for x in (tail_tiers or ()) if 0 < int(x) < G})) if evaluator is None else ()
+        self._tiers = {}             # size -> (TreeBatch, evaluator)
+        self._tier_args = dict(nn=nn, dtype=dtype, network_path=network_path, seed=seed, tie_random=tie_random,
+                               dirichlet_alpha=dirichlet_alpha, dirichlet_epsilon=dirichlet_epsilon, device=device)
         self.temp = TEMP_SCHEDULERS[temp_scheduler_type](temp_max_step, temp_min_step, spec.max_moves)
         dev = self.tree.device
         T, A = max_plies, spec.action_size
@@ -149,11 +161,29 @@ class SelfPlayEngine:
         self.total_moves = 0
         self.plies_played = 0
         self.max_nodes_used = 0      # high-water mark of any game's node pool half over the last play()
-        self.search_events = None    # set to [] to record (start event, end event, steps) of every search of play()
+        self.search_events = None    # set to [] to record (start event, end event, steps, batch size) of every search of play()
 
     def set_network(self, nn) -> None:
         """trainer.update_network (trainer.py:383-387): refresh the device snapshot + CUDA graph."""
         self.evaluator.refresh(nn)
+        self._tier_args["nn"] = nn
+        for _, ev in self._tiers.values():
+            ev.refresh(nn)
+
+    def _tier(self, size: int):
+        """(TreeBatch, evaluator) of `size` slots for the tail of a batch, built on first use."""
+        if size not in self._tiers:
+            a = self._tier_args
+            tree = TreeBatch(size, n=self.spec, mode="neural", capacity=self.tree.capacity, n_sim_hint=self.n_sim,
+                             device=a["device"], seed=a["seed"] + 0x9E3779B9 * size, tie_random=a["tie_random"],
+                             dirichlet_alpha=a["dirichlet_alpha"], dirichlet_epsilon=a["dirichlet_epsilon"],
+                             enc_dtype=a["dtype"], max_depth=self.tree.max_depth, graph_first_use=True)
+            self._tiers[size] = (tree, make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"]))
+        return self._tiers[size]
+
+    def trees(self):
+        """The main TreeBatch and the tail tiers built so far (with their evaluators)."""
+        return [(self.tree, self.evaluator)] + list(self._tiers.values())
 
     def play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
              start_player: torch.Tensor = None) -> SampleBatch:
@@ -171,34 +201,60 @@ class SelfPlayEngine:
         sims = torch.zeros((), dtype=torch.int64, device=tree.device)
         peak = torch.zeros((), dtype=torch.int32, device=tree.device)
         t = 0
-        temp_t = torch.empty(G, dtype=torch.float32, device=tree.device)
+        # `tree` / `evaluator` = the batch the live games are in (the main one, later a tail tier); `idx` = game id of
+        # each of its first k slots (None = identity)
+        evaluator, idx, k = self.evaluator, None, G
+        used = [tree]
+        n_live = G
         while t < self.max_plies:
-            self.h_own[t].copy_(tree.root_own); self.h_opp[t].copy_(tree.root_opp)
-            self.h_player[t].copy_(tree.root_player); self.h_live[t].copy_(live)
+            if idx is None:
+                self.h_own[t].copy_(tree.root_own); self.h_opp[t].copy_(tree.root_opp)
+                self.h_player[t].copy_(tree.root_player); self.h_live[t].copy_(live)
+            else:
+                self.h_own[t].index_copy_(0, idx, tree.root_own[:k]); self.h_opp[t].index_copy_(0, idx, tree.root_opp[:k])
+                self.h_player[t].index_copy_(0, idx, tree.root_player[:k])
+                self.h_live[t].zero_(); self.h_live[t].index_copy_(0, idx, live[:k])
             # fresh roots only exist on the first move: afterwards the played child always carries visits
             if self.search_events is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-            tree.search(self.n_sim, self.evaluator, extra_steps=1 if t == 0 else 0, check=False)
+            tree.search(self.n_sim, evaluator, extra_steps=1 if t == 0 else 0, check=False)
             if self.search_events is not None:
                 e1.record()
-                self.search_events.append((e0, e1, self.n_sim + (1 if t == 0 else 0)))
-            sims += tree.sims_done.to(torch.int64)[live].sum()
-            peak = torch.maximum(peak, tree.n_alloc.max())
-            temp_t.fill_(float(self.temp[t]))
+                self.search_events.append((e0, e1, self.n_sim + (1 if t == 0 else 0), tree.G))
+            sims += (tree.sims_done.to(torch.int64) * live).sum()
+            peak = torch.maximum(peak, tree.n_alloc[:k].max())
+            temp_t = torch.full((tree.G,), float(self.temp[t]), dtype=torch.float32, device=tree.device)
             action, pi = tree.choose(temp_t)
-            self.h_pi[t].copy_(pi)
+            if idx is None:
+                self.h_pi[t].copy_(pi)
+            else:
+                self.h_pi[t].index_copy_(0, idx, pi[:k])
             tree.advance(action)
             term, _, win = spec.terminal_score(tree.root_own, tree.root_opp, tree.root_player)
             newly = live & (term == 1)
-            self.winner = torch.where(newly, win, self.winner)
+            if idx is None:
+                self.winner = torch.where(newly, win, self.winner)
+            else:
+                self.winner.index_copy_(0, idx, torch.where(newly[:k], win[:k], self.winner[idx]))
             live = live & (term == 0)
             tree.active.copy_(live.to(torch.uint8))
             t += 1
-            if not bool(live.any().item()):
+            n_live, n_nodes = torch.stack([live.sum(), (tree.n_alloc * live).max().to(torch.int64)]).tolist()
+            if n_live == 0:
                 break
-        tree.check_status()
-        if bool(live.any().item()):
+            size = next((x for x in self.tail_tiers if n_live <= x < tree.G), None)
+            if size is not None:
+                sel = torch.nonzero(live).flatten()
+                sub, evaluator = self._tier(size)
+                sub.adopt(tree, sel, n_nodes)
+                idx = sel if idx is None else idx[sel]
+                tree, k = sub, n_live
+                used.append(tree)
+                live = tree.active.bool()
+        for tr in used:
+            tr.check_status()
+        if n_live > 0:
             raise RuntimeError(f"self-play did not finish within max_plies={self.max_plies}")
         self.plies_played = t
         self.total_sims = int(sims.item())

@@ -40,6 +40,7 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=200)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tail-tiers", action="store_true", help="keep the last live games of a batch in the full-size batch")
     ap.add_argument("--capacity", type=int, default=None, help="nodes per tree-pool half (default 192 * (sims + 1))")
     ap.add_argument("--game", default="othello", choices=["othello", "connect4"],
                     help="othello: BASELINE config 3/4 (the headline); connect4: config 5 (7x6, Connect4Net)")
@@ -196,7 +197,8 @@ def run_ours(args):
         flop_per_eval, workload, net_name = FLOP_PER_EVAL, WORKLOAD, "OthelloNet(n=8)"
     engine = SelfPlayEngine(net, G, n=spec, n_sim=n_sim, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
                             temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4, seed=0x5EED + 7919 * rank,
-                            dtype=torch.bfloat16, device=dev, network_path=args.net, capacity=args.capacity)
+                            dtype=torch.bfloat16, device=dev, network_path=args.net, capacity=args.capacity,
+                            tail_tiers=() if args.no_tail_tiers else "auto")
     black, white = spec.start_position()
     h_own = torch.full((G,), bo.to_i64(black), dtype=torch.int64).pin_memory()
     h_opp = torch.full((G,), bo.to_i64(white), dtype=torch.int64).pin_memory()
@@ -228,14 +230,21 @@ def run_ours(args):
     for _ in range(args.warmup):
         step_device()
 
+    def counted_launches():
+        # C-ABI launches issued from Python + our kernels replayed inside CUDA graphs (the evaluators' own graphs and
+        # the whole-search graphs), over the main tree batch and the tail tiers
+        c = _lib.LAUNCH_CALLS
+        for tr, ev in engine.trees():
+            c += tr.graph_step_launches
+            c += ev.own_launches if hasattr(ev, "own_launches") else \
+                getattr(ev, "n_calls", 0) * getattr(ev, "own_kernels_per_call", 0)
+        return c
+
     def timed(fn, steps):
         sampler = ClockSampler(local_rank)
         barrier()
         sampler.start()
-        launches0 = _lib.LAUNCH_CALLS
-        ev = engine.evaluator
-        graph0 = getattr(ev, "n_calls", 0)
-        own0, steps0 = getattr(ev, "own_launches", None), engine.tree.graph_step_launches
+        launches0 = counted_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.time()
         e0.record()
@@ -259,9 +268,7 @@ def run_ours(args):
                 "games": float(tot[2]), "clocks": clocks, "last": last,
                 # C-ABI launches issued from Python + our kernels replayed inside the evaluator's CUDA graph
                 # and the tree steps / evaluator kernels replayed inside whole-search graphs
-                "launches": (_lib.LAUNCH_CALLS - launches0) + (engine.tree.graph_step_launches - steps0)
-                + ((ev.own_launches - own0) if own0 is not None
-                   else (getattr(ev, "n_calls", 0) - graph0) * getattr(ev, "own_kernels_per_call", 0))}
+                "launches": counted_launches() - launches0}
 
     dev_run = timed(step_device, args.steps)
     e2e_run = timed(step_e2e, args.steps)
@@ -292,10 +299,12 @@ def run_ours(args):
     engine.search_events = []
     engine.play()
     torch.cuda.synchronize()
-    search_ms = sum(a.elapsed_time(b) for a, b, _ in engine.search_events)
-    search_steps = sum(k for _, _, k in engine.search_events)
+    search_ms = sum(a.elapsed_time(b) for a, b, _, _ in engine.search_events)
+    full = [(a, b, k) for a, b, k, size in engine.search_events if size == G]    # searches over the full batch
+    search_steps = sum(k for _, _, k in full)
+    full_ms = sum(a.elapsed_time(b) for a, b, _ in full)
     engine.search_events = None
-    step_ms = search_ms / max(1, search_steps)
+    step_ms = full_ms / max(1, search_steps)
     eval_ms, tree_ms, timing = eager_eval_ms, eager_tree_ms, "eager calls between CUDA events"
     if hasattr(engine.evaluator, "enqueue") and tree.graph_search:
         K = 64
@@ -351,6 +360,7 @@ def run_ours(args):
             "config": {"workload": workload, "board": f"{spec.cols}x{spec.rows}", "games_per_gpu": G, "n_sim": n_sim,
                        "net": net_name + " random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
                        "leaves_in_flight_per_game": 1, "network_path": args.net, "tree_reuse": True,
+                       "tail_tiers": list(engine.tail_tiers),
                        "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
                        "node_pool": {"capacity_per_game": tree.capacity, "peak_used_last_step": engine.max_nodes_used},
                        "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},

@@ -76,17 +76,21 @@ def test_bf16_graph_evaluator_within_1e2_of_fp32(n):
         assert set(np.where(N[g] >= 0)[0].tolist()) == set(acts)
 
 
-def test_selfplay_batch_is_consistent():
+@pytest.mark.parametrize("tail_tiers", [(), (24, 6, 2)])
+def test_selfplay_batch_is_consistent(tail_tiers):
     """A small self-play batch: every sample's pi is a distribution over legal moves of its state, consecutive
-    states follow by a legal move in pi's support, z is the final disc-difference sign seen from the mover."""
+    states follow by a legal move in pi's support, z is the final disc-difference sign seen from the mover.
+    With tail tiers the last live games are moved to smaller tree batches (TreeBatch.adopt) on the way."""
     from alphazero_b200 import boardops as bo
     from alphazero_b200.games.othello import OthelloNet
     from alphazero_b200.selfplay import SelfPlayEngine
     n, G, n_sim = 6, 48, 24
     torch.manual_seed(1)
     net = OthelloNet(n=n)
-    eng = SelfPlayEngine(net, G, n=n, n_sim=n_sim, seed=3)
-    batch = eng.play().cpu()
+    eng = SelfPlayEngine(net, G, n=n, n_sim=n_sim, seed=3, tail_tiers=tail_tiers)
+    for _ in range(3 if tail_tiers else 1):     # from the second use on a tier's searches replay a CUDA graph
+        batch = eng.play().cpu()
+    assert (len(eng.trees()) > 1) == bool(tail_tiers)
     assert eng.total_sims == eng.total_moves * n_sim
     assert len(batch) == eng.total_moves
     own, opp = bo.bits_to_numpy(batch.own), bo.bits_to_numpy(batch.opp)
