@@ -41,9 +41,20 @@ class SampleBatch:
         return int(self.own.numel())
 
     def cpu(self) -> "SampleBatch":
-        return SampleBatch(self.own.cpu(), self.opp.cpu(), self.pi.cpu(), self.z.cpu(), self.episode_idx.cpu(),
-                           self.move_idx.cpu(), self.n, self.rows,
-                           None if self.transformation is None else self.transformation.cpu(), self.game)
+        """Host copy.  Device tensors go through pinned staging buffers (torch's caching host allocator keeps them for
+        the next batch) as asynchronous copies followed by one synchronisation."""
+        if not self.own.is_cuda:
+            return self
+
+        def host(x):
+            if x is None:
+                return None
+            return torch.empty(x.shape, dtype=x.dtype, pin_memory=True).copy_(x, non_blocking=True)
+
+        out = SampleBatch(host(self.own), host(self.opp), host(self.pi), host(self.z), host(self.episode_idx),
+                          host(self.move_idx), self.n, self.rows, host(self.transformation), self.game)
+        torch.cuda.current_stream(self.own.device).synchronize()
+        return out
 
     @property
     def n_rows(self) -> int:
@@ -139,7 +150,7 @@ class SelfPlayEngine:
         # Tail of a batch: games of one batch end within a few plies of each other, and the last plies would run the
         # full-size leaf batch through the network for a handful of live games (Othello 8x8, 4096 games: 1481 / 285 /
         # 29 / 8 / 1 / 1 games live after plies 60..65).  `tail_tiers` = sizes of smaller TreeBatches (own pools,
-        # evaluator and search graph, built on first use) the live games are moved to once they fit:
+        # evaluator and search graph) the live games are moved to once they fit:
         # "auto" = G/2, G/8, G/64 for G >= 1024, nothing below; () switches it off.  A caller-supplied evaluator is
         # bound to the main tree, so it switches it off too.
         if tail_tiers == "auto":
@@ -161,6 +172,8 @@ class SelfPlayEngine:
         self.total_moves = 0
         self.plies_played = 0
         self.max_nodes_used = 0      # high-water mark of any game's node pool half over the last play()
+        for size in self.tail_tiers:      # built (pools, evaluator, search graph) up front: nothing is set up inside play()
+            self._tier(size)
         self.search_events = None    # set to [] to record (start event, end event, steps, batch size) of every search of play()
 
     def set_network(self, nn) -> None:
@@ -178,7 +191,9 @@ class SelfPlayEngine:
                              device=a["device"], seed=a["seed"] + 0x9E3779B9 * size, tie_random=a["tie_random"],
                              dirichlet_alpha=a["dirichlet_alpha"], dirichlet_epsilon=a["dirichlet_epsilon"],
                              enc_dtype=a["dtype"], max_depth=self.tree.max_depth, graph_first_use=True)
-            self._tiers[size] = (tree, make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"]))
+            ev = make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"])
+            tree.search(self.n_sim, ev, extra_steps=0, check=False)      # captures the tier's search graph now
+            self._tiers[size] = (tree, ev)
         return self._tiers[size]
 
     def trees(self):

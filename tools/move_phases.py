@@ -8,8 +8,14 @@ from alphazero_b200.games.othello import OthelloNet
 
 G = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 n_sim = int(sys.argv[2]) if len(sys.argv) > 2 else 200
+game = sys.argv[3] if len(sys.argv) > 3 else "othello"
 torch.manual_seed(0)
-eng = SelfPlayEngine(OthelloNet(n=8), G, n=8, n_sim=n_sim, seed=1)
+if game == "connect4":
+    from alphazero_b200.games.connect4 import Connect4Net
+    from alphazero_b200.gamespec import Connect4Spec
+    eng = SelfPlayEngine(Connect4Net(board_width=7, board_height=6), G, n=Connect4Spec(7, 6), n_sim=n_sim, seed=1, tail_tiers=())
+else:
+    eng = SelfPlayEngine(OthelloNet(n=8), G, n=8, n_sim=n_sim, seed=1, tail_tiers=())
 for _ in range(2):
     eng.play()
 tree, spec = eng.tree, eng.spec
