@@ -256,6 +256,7 @@ def run_ours(args):
         sims = moves = games = 0
         last = None
         for _ in range(steps):
+            last = None         # release the previous step's buffers (pinned host staging) before the next step asks
             last = fn()
             sims += engine.total_sims; moves += engine.total_moves; games += G
         e1.record()
