@@ -50,10 +50,9 @@ AZ_HD uint64_t az_shift_dyn(uint64_t x, int d) {
 }
 
 AZ_HD uint64_t az_board_mask(int n) {
-    uint64_t row = (n >= 8) ? 0xFFULL : ((1ULL << n) - 1ULL);
-    uint64_t m = 0;
-    for (int r = 0; r < n; ++r) m |= row << (8 * r);
-    return m;
+    if (n >= 8) return ~0ULL;
+    const uint64_t row = (1ULL << n) - 1ULL;                       // n low columns of a canvas row ...
+    return (row * 0x0101010101010101ULL) & ((1ULL << (8 * n)) - 1ULL);   // ... in each of the n low rows
 }
 
 // Dumb7fill along one direction: opponent discs contiguous to `gen` (excluding gen).  A line holds <= 6 of them.

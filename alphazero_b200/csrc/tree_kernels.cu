@@ -99,14 +99,16 @@ __device__ __forceinline__ az_u32x4 az_draw4(uint64_t seed, uint32_t g, uint32_t
 }
 
 // Writes the network encoding of a side-relative position: +1 own, -1 opp, 0 empty, row-major n x n.
-__device__ __forceinline__ void az_encode_leaf(const az_tree& t, const az_dims& d, int g, int lane, uint64_t own,
-                                               uint64_t opp) {
-    const int cells = d.rows * d.cols;
+// Out of line with scalar arguments: only the generic (torch module) evaluator asks for it, the fused network path reads
+// the leaf bitboards, and its runtime divisions would otherwise sit inside the tree step's instruction stream.
+__device__ __noinline__ void az_encode_leaf(void* enc, int enc_dtype, int rows, int cols, int g, int lane, uint64_t own,
+                                            uint64_t opp) {
+    const int cells = rows * cols;
     for (int k = lane; k < cells; k += 32) {
-        int bit = (k / d.cols) * 8 + (k % d.cols);
+        int bit = (k / cols) * 8 + (k % cols);
         float v = (float)((int)((own >> bit) & 1ULL) - (int)((opp >> bit) & 1ULL));
-        if (t.enc_dtype == 0) reinterpret_cast<float*>(t.enc)[(size_t)g * cells + k] = v;
-        else reinterpret_cast<__nv_bfloat16*>(t.enc)[(size_t)g * cells + k] = __float2bfloat16(v);
+        if (enc_dtype == 0) reinterpret_cast<float*>(enc)[(size_t)g * cells + k] = v;
+        else reinterpret_cast<__nv_bfloat16*>(enc)[(size_t)g * cells + k] = __float2bfloat16(v);
     }
 }
 
@@ -200,6 +202,7 @@ __device__ __forceinline__ void az_backup(const az_tree& t, az_node* nodes, int 
     if (fabs(outcome) < 1e-4) reward = 0.0;
     else reward = ((double)player_to_play * outcome > 0.0) ? -fabs(outcome) : fabs(outcome);
     const uint32_t* path = t.path + (size_t)g * t.max_depth;
+#pragma unroll 1
     for (int j = lane; j < len; j += 32) {
         az_node* nd = &nodes[j < 32 ? path_lane : path[j]];
         uint4* q = reinterpret_cast<uint4*>(nd);
@@ -230,7 +233,7 @@ struct LeafRegs {
 
 // First round: everything that only depends on g.  With az_tree.logits the evaluator's raw bf16 row is turned into
 // probabilities / value here (net_heads.cuh: the arithmetic of az_net_heads).
-template <int GAME>
+template <int GAME, int MODE>
 __device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, const az_dims& d, int g, int lane) {
     LeafRegs r;
     r.kind = t.leaf_kind[g];
@@ -242,7 +245,7 @@ __device__ __forceinline__ LeafRegs az_load_leaf(const az_tree& t, const az_dims
     r.alloc.base = t.n_alloc[g];
     r.path_lane = lane < t.max_depth ? t.path[(size_t)g * t.max_depth + lane] : 0u;
     r.alloc.row[0] = r.alloc.row[1] = r.alloc.row[2] = 0.f;
-    if (t.mode == AZ_MODE_NEURAL) {
+    if (MODE == AZ_MODE_NEURAL) {
         const int A = az_rules<GAME>::action_size(d);
         if (t.logits) {
             const __nv_bfloat16* row = reinterpret_cast<const __nv_bfloat16*>(t.logits) + (size_t)g * t.logits_ld;
@@ -298,6 +301,16 @@ __device__ __forceinline__ void az_finish(const az_tree& t, const az_dims& d, az
 
 // ------------------------------------------------------------------------------------------------ select
 
+// fair_max's uniform pick among tied lanes (utils.py:28-34).  Out of line: ties are rare (a few unvisited children with
+// equal priors), and the Philox rounds would otherwise sit in the middle of the selection loop's instruction stream.
+__device__ __noinline__ int az_tie_pick(uint64_t seed, uint32_t g, uint32_t event, uint32_t ties) {
+    az_u32x4 r = az_draw4(seed, g, event, 0u, 0x54494555u);
+    int pick = (int)az_bounded(r.x, (uint32_t)__popc(ties));
+    uint32_t m = ties;
+    for (int i = 0; i < pick; ++i) m &= m - 1;
+    return __ffs(m) - 1;
+}
+
 // Warp arg-max of `score` over the lanes with valid == true.  Ties: lowest child index (parity mode) or uniform
 // among the tied children (fair_max, utils.py:28-34).  `idx` is the child index held by the lane.
 // Returns the winning child index (same value in every lane) and, through src_lane, the lane that holds it.
@@ -322,11 +335,7 @@ __device__ __forceinline__ int az_warp_argmax(double score, int idx, bool valid,
         const uint32_t who = __ballot_sync(AZ_FULL, tied && (uint32_t)idx == key);
         win_lane = __ffs(who) - 1;
     } else {
-        az_u32x4 r = az_draw4(seed, g, event, 0u, 0x54494555u);
-        int pick = (int)az_bounded(r.x, (uint32_t)__popc(ties));
-        uint32_t m = ties;
-        for (int i = 0; i < pick; ++i) m &= m - 1;
-        win_lane = __ffs(m) - 1;
+        win_lane = az_tie_pick(seed, g, event, ties);
     }
     (void)lane;
     *src_lane = win_lane;
@@ -335,7 +344,7 @@ __device__ __forceinline__ int az_warp_argmax(double score, int idx, bool valid,
 
 // Dirichlet noise on the priors of the root's children (mcts.py:234-240): P = (1-eps) P + eps * Dir(alpha)_j with
 // Gamma(alpha) draws by Marsaglia-Tsang (alpha < 1 boosted by U^(1/alpha)), lane j <-> child j.
-__device__ __forceinline__ double az_gamma_draw(double alpha, uint64_t seed, uint32_t g, uint32_t event, uint32_t j) {
+__device__ __noinline__ double az_gamma_draw(double alpha, uint64_t seed, uint32_t g, uint32_t event, uint32_t j) {
     uint32_t attempt = 0;
     az_u32x4 r = az_draw4(seed, g, event, j, 0x47414D30u);
     double boost = 1.0;
@@ -357,17 +366,18 @@ __device__ __forceinline__ double az_gamma_draw(double alpha, uint64_t seed, uin
     }
 }
 
-__device__ __forceinline__ void az_root_noise(const az_tree& t, az_node* nodes, int g, int lane, const NodeRec& root,
-                                              uint32_t event) {
-    const int k = root.n_children();
+// Out of line (once per move per game; its float64 pow / log / cospi would triple the selection loop's code), with
+// scalar arguments only so that the kernel's parameter struct never has to be materialised in local memory.
+__device__ __noinline__ void az_root_noise(az_node* nodes, uint32_t first_child, int k, float alpha, float eps_f,
+                                           uint64_t seed, int g, int lane, uint32_t event) {
     double g0 = 0.0, g1 = 0.0;
-    if (lane < k) g0 = az_gamma_draw((double)t.dirichlet_alpha, t.seed, (uint32_t)g, event, (uint32_t)lane);
-    if (lane + 32 < k) g1 = az_gamma_draw((double)t.dirichlet_alpha, t.seed, (uint32_t)g, event, (uint32_t)lane + 32u);
+    if (lane < k) g0 = az_gamma_draw((double)alpha, seed, (uint32_t)g, event, (uint32_t)lane);
+    if (lane + 32 < k) g1 = az_gamma_draw((double)alpha, seed, (uint32_t)g, event, (uint32_t)lane + 32u);
     const double sum = az_warp_sum(g0 + g1);
-    const double eps = (double)t.dirichlet_eps;
+    const double eps = (double)eps_f;
     if (sum > 0.0) {
         for (int j = lane; j < k; j += 32) {
-            float* P = &nodes[root.first_child + j].P;
+            float* P = &nodes[first_child + j].P;
             double noise = (j < 32 ? g0 : g1) / sum;
             *P = (float)((1.0 - eps) * (double)(*P) + eps * noise);
         }
@@ -382,6 +392,7 @@ __device__ __forceinline__ void az_root_noise(const az_tree& t, az_node* nodes, 
 // Picks the child of `cur` that maximises PUCT (neural, mcts.py:44-46) or UCT (rollout, mcts.py:38-42).
 // Returns the child's pool index and its record (broadcast to all lanes).
 // `pre` = record of child `lane` (valid when lane < k), loaded by the caller ahead of time.
+template <int MODE>
 __device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_node* nodes, int g, int lane,
                                                   const NodeRec& cur, uint32_t event, NodeRec* child_out,
                                                   const NodeRec& pre) {
@@ -389,15 +400,16 @@ __device__ __forceinline__ uint32_t az_pick_child(const az_tree& t, const az_nod
     const double parentN = (double)cur.N;
     // sqrt / log of the parent's visit count are shared by all children
     const double sqrtN = __dsqrt_rn(parentN);
-    const double logN = (t.mode == AZ_MODE_ROLLOUT && cur.N > 0u) ? log(parentN) : 0.0;
+    const double logN = (MODE == AZ_MODE_ROLLOUT && cur.N > 0u) ? log(parentN) : 0.0;
     NodeRec mine;
     mine.Q = 0.0; mine.P = 0.f; mine.N = 0u; mine.first_child = 0u; mine.meta = 0u;
     double best_score = -INFINITY;
     int best_j = -1;
+#pragma unroll 1
     for (int j = lane; j < k; j += 32) {
         const NodeRec c = j < 32 ? pre : az_load_node(&nodes[cur.first_child + j]);
         double s;
-        if (t.mode == AZ_MODE_NEURAL) {
+        if (MODE == AZ_MODE_NEURAL) {
             // Q + c_puct * P * sqrt(N_parent) / (1 + N), c_puct = 1.0, evaluated left to right in float64
             s = __dadd_rn(c.Q, __ddiv_rn(__dmul_rn((double)c.P, sqrtN), (double)(1u + c.N)));
         } else {
@@ -430,7 +442,7 @@ __device__ __forceinline__ RootRegs az_load_root(const az_tree& t, int g) {
     return r;
 }
 
-template <int GAME>
+template <int GAME, int MODE>
 __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane,
                                           const RootRegs& root) {
     using W = az_warp_rules<GAME>;
@@ -444,13 +456,14 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
     int len = 1;
     if (lane == 0) path[0] = 0u;
 
-    if (t.mode == AZ_MODE_NEURAL && !(cur.flags() & AZ_NODE_EVAL)) {
+    if (MODE == AZ_MODE_NEURAL && !(cur.flags() & AZ_NODE_EVAL)) {
         kind = AZ_LEAF_PRIME;                                   // mcts.py:231-233
         len = 0;
     } else {
-        if (t.mode == AZ_MODE_NEURAL && t.dirichlet_alpha > 0.f && t.dirichlet_eps > 0.f &&
+        if (MODE == AZ_MODE_NEURAL && t.dirichlet_alpha > 0.f && t.dirichlet_eps > 0.f &&
             (cur.flags() & AZ_NODE_EXPANDED) && !(cur.flags() & AZ_NODE_NOISED)) {
-            az_root_noise(t, nodes, g, lane, cur, event);       // mcts.py:235-240
+            az_root_noise(nodes, cur.first_child, cur.n_children(), t.dirichlet_alpha, t.dirichlet_eps, t.seed, g, lane,
+                          event);                               // mcts.py:235-240
             event += 1u;
         }
         NodeRec pre;                 // child `lane` of cur, loaded one level ahead (while the move is applied)
@@ -462,10 +475,10 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
                 bool terminal;
                 W::legal(own, opp, d, lane, &terminal);
                 if (terminal) {                                 // mcts.py:146-147
-                    kind = t.mode == AZ_MODE_NEURAL ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_ROLLOUT;
+                    kind = MODE == AZ_MODE_NEURAL ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_ROLLOUT;
                     break;
                 }
-                if (t.mode == AZ_MODE_NEURAL) {
+                if (MODE == AZ_MODE_NEURAL) {
                     if (!(cur.flags() & AZ_NODE_EVAL)) { kind = AZ_LEAF_NN; break; }   // pool-overflow fallback
                     if (lane == 0) {
                         uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[cur_idx]);
@@ -491,7 +504,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             }
             if (!pre_ok && lane < cur.n_children()) pre = az_load_node(&nodes[cur.first_child + lane]);
             NodeRec child;
-            uint32_t child_idx = az_pick_child(t, nodes, g, lane, cur, event, &child, pre);
+            uint32_t child_idx = az_pick_child<MODE>(t, nodes, g, lane, cur, event, &child, pre);
             event += 1u;
             // the chosen child's own children block (if it has one) is fetched now, under the move application
             pre_ok = child.first_child != 0u;
@@ -500,7 +513,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             player = -player;
             if (len >= t.max_depth) {
                 if (lane == 0) t.status[g] |= AZ_STATUS_DEPTH;
-                kind = t.mode == AZ_MODE_NEURAL ? AZ_LEAF_NN : AZ_LEAF_ROLLOUT;
+                kind = MODE == AZ_MODE_NEURAL ? AZ_LEAF_NN : AZ_LEAF_ROLLOUT;
                 break;
             }
             if (lane == 0) path[len] = child_idx;
@@ -508,7 +521,7 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
             cur = child;
             cur_idx = child_idx;
             if (cur.N == 0u) {                                  // mcts.py:143-144: first visit = the leaf
-                if (t.mode == AZ_MODE_NEURAL) {
+                if (MODE == AZ_MODE_NEURAL) {
                     bool terminal;
                     W::legal(own, opp, d, lane, &terminal);
                     kind = terminal ? az_terminal_kind<GAME>(own, opp, player, d) : AZ_LEAF_NN;
@@ -527,13 +540,16 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
         t.path_len[g] = (uint32_t)len;
         t.rng_ctr[g] = event;
     }
-    if (t.mode == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t, d, g, lane, own, opp);
+    if (MODE == AZ_MODE_NEURAL && t.enc) az_encode_leaf(t.enc, t.enc_dtype, d.rows, d.cols, g, lane, own, opp);
 }
 
 #ifndef AZ_TREE_MIN_CTAS
 #define AZ_TREE_MIN_CTAS 7    // resident CTAs per SM the register budget is sized for: 1024 CTAs / 148 SMs = one wave at 7
 #endif
-template <int GAME>
+// MODE (AZ_MODE_NEURAL / AZ_MODE_ROLLOUT) is a template parameter so that each instantiation only carries its own mode's
+// code: the kernel is bound by instruction fetch and dependent-issue latency, not by memory (ncu: `no_instructions` is the
+// top warp stall), so everything that is not on the per-simulation path is compiled out or kept out of line.
+template <int GAME, int MODE>
 __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
     // launched with az_launch_pdl: every warp waits for the evaluator's outputs (probs / value) before anything else --
     // also the warps of finished games, so that this grid never completes before its predecessor has -- and then lets
@@ -549,7 +565,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tre
     const uint8_t half = t.half[g];
     const uint32_t sims_before = t.sims_done[g];
     LeafRegs lf;
-    if (do_finish) lf = az_load_leaf<GAME>(t, d, g, lane);
+    if (do_finish) lf = az_load_leaf<GAME, MODE>(t, d, g, lane);
     RootRegs root;
     if (do_select) root = az_load_root(t, g);
     if (!active) return;
@@ -560,7 +576,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tre
         az_finish<GAME>(t, d, nodes, g, lane, lf);
         backed_up = lf.kind != AZ_LEAF_IDLE && lf.kind != AZ_LEAF_PRIME;
     }
-    if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME>(t, d, nodes, g, lane, root);
+    if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME, MODE>(t, d, nodes, g, lane, root);
 }
 
 // ------------------------------------------------------------------------------------------------ misc kernels
@@ -861,12 +877,15 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
     if (n_sim < 0) return AZ_ERR_ARG;
     const dim3 grid(az_warp_grid(t->G)), block(AZ_WARPS_PER_CTA * 32);
     cudaError_t e;
+#define AZ_STEP(GAME, MODE) az_launch_pdl(k_tree_step<GAME, MODE>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select)
+    const bool neural = t->mode == AZ_MODE_NEURAL;
     if (t->game == AZ_GAME_OTHELLO)
-        e = az_launch_pdl(k_tree_step<AZ_GAME_OTHELLO>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+        e = neural ? AZ_STEP(AZ_GAME_OTHELLO, AZ_MODE_NEURAL) : AZ_STEP(AZ_GAME_OTHELLO, AZ_MODE_ROLLOUT);
     else if (t->game == AZ_GAME_CONNECT4)
-        e = az_launch_pdl(k_tree_step<AZ_GAME_CONNECT4>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+        e = neural ? AZ_STEP(AZ_GAME_CONNECT4, AZ_MODE_NEURAL) : AZ_STEP(AZ_GAME_CONNECT4, AZ_MODE_ROLLOUT);
     else
-        e = az_launch_pdl(k_tree_step<AZ_GAME_TICTACTOE>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select);
+        e = neural ? AZ_STEP(AZ_GAME_TICTACTOE, AZ_MODE_NEURAL) : AZ_STEP(AZ_GAME_TICTACTOE, AZ_MODE_ROLLOUT);
+#undef AZ_STEP
     if (e != cudaSuccess) return az_set_cuda_error(e, "k_tree_step");
     AZ_CHECK_LAUNCH("k_tree_step");
     return AZ_OK;
