@@ -193,11 +193,12 @@ __device__ __forceinline__ az_dirlane az_dirlane_of(int lane) {
     return d;
 }
 
-__device__ __forceinline__ uint64_t az_or_reduce8(uint64_t x) {
-    x |= __shfl_xor_sync(0xffffffffu, x, 1);
-    x |= __shfl_xor_sync(0xffffffffu, x, 2);
-    x |= __shfl_xor_sync(0xffffffffu, x, 4);
-    return x;
+// OR of x over the lanes with `mine` set, delivered to every lane: two `redux.sync` (low / high word) instead of three
+// dependent 64-bit shuffle steps plus a broadcast.
+__device__ __forceinline__ uint64_t az_or_lanes(uint64_t x, bool mine) {
+    const uint32_t lo = __reduce_or_sync(0xffffffffu, mine ? (uint32_t)x : 0u);
+    const uint32_t hi = __reduce_or_sync(0xffffffffu, mine ? (uint32_t)(x >> 32) : 0u);
+    return ((uint64_t)hi << 32) | lo;
 }
 
 // Discs flipped when the side owning `own` plays the single-bit square `mv` (same value in every lane).
@@ -209,9 +210,7 @@ __device__ __forceinline__ uint64_t az_flips_warp(uint64_t mv, uint64_t own, uin
     for (int i = 0; i < 5; ++i) x |= (x << d.s) & d.keep & p;
     x = ((x << d.s) & d.keep & o) ? x : 0ULL;
     if (d.rev) x = __brevll(x);
-    if (lane & 8) x = 0ULL;                     // one position only: lanes 8..15 would duplicate lanes 0..7
-    x = az_or_reduce8(x);
-    return __shfl_sync(0xffffffffu, x, 0);
+    return az_or_lanes(x, lane < 8);            // one position only: lanes 8.. would duplicate lanes 0..7
 }
 
 // Placement squares of the side owning `own` (result in every lane) and, through other_out, of the other side.
@@ -227,9 +226,9 @@ __device__ __forceinline__ uint64_t az_legal_warp(uint64_t own, uint64_t opp, ui
     for (int i = 0; i < 5; ++i) x |= (x << d.s) & d.keep & p;
     x = (x << d.s) & d.keep & empty;
     if (d.rev) x = __brevll(x);
-    x = az_or_reduce8(x);                       // lanes 0..7 hold legal(own, opp), lanes 8..15 legal(opp, own)
-    if (other_out) *other_out = __shfl_sync(0xffffffffu, x, 8);
-    return __shfl_sync(0xffffffffu, x, 0);
+    // lanes 0..7 hold the directions of legal(own, opp), lanes 8..15 those of legal(opp, own)
+    if (other_out) *other_out = az_or_lanes(x, (lane & 24) == 8);
+    return az_or_lanes(x, lane < 8);
 }
 
 // Plays action `a` for the side to move and swaps sides; warp-cooperative twin of az_apply.

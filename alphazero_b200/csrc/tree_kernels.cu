@@ -314,30 +314,32 @@ __device__ __noinline__ int az_tie_pick(uint64_t seed, uint32_t g, uint32_t even
 // Warp arg-max of `score` over the lanes with valid == true.  Ties: lowest child index (parity mode) or uniform
 // among the tied children (fair_max, utils.py:28-34).  `idx` is the child index held by the lane.
 // Returns the winning child index (same value in every lane) and, through src_lane, the lane that holds it.
+//
+// The maximum is taken with two `redux.sync` on an order-preserving 64-bit integer image of the double (high word, then
+// low word among the lanes that hold the high-word maximum) instead of five dependent 64-bit shuffle steps: the
+// selection loop is a chain of dependent warp collectives, so their count is what a simulation costs.  A lane's `idx`
+// is `lane` or `lane + 32`, so the lowest tied child index is the lowest tied lane with idx < 32, else the lowest tied lane.
 __device__ __forceinline__ int az_warp_argmax(double score, int idx, bool valid, bool tie_random, uint64_t seed,
                                               uint32_t g, uint32_t event, int* src_lane) {
-    const int lane = threadIdx.x & 31;
-    double best = valid ? score : -INFINITY;
-    // NaN never occurs: Q, P finite; +inf only for unvisited children in UCT mode.
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        double o = __shfl_xor_sync(AZ_FULL, best, off);
-        best = o > best ? o : best;
-    }
-    const bool tied = valid && (score == best);
+    // NaN never occurs: Q, P finite; +inf only for unvisited children in UCT mode.  -0.0 is folded into +0.0 so that
+    // equal doubles have equal images (score == best in the reference's comparison).
+    uint64_t b = (uint64_t)__double_as_longlong(score);
+    if (b == 0x8000000000000000ULL) b = 0ULL;
+    b ^= (b >> 63) ? ~0ULL : 0x8000000000000000ULL;          // unsigned order == double order
+    if (!valid) b = 0ULL;                                      // below the image of every double, -inf included
+    const uint32_t hi = (uint32_t)(b >> 32), lo = (uint32_t)b;
+    const uint32_t max_hi = __reduce_max_sync(AZ_FULL, hi);
+    const bool cand = hi == max_hi;
+    const uint32_t max_lo = __reduce_max_sync(AZ_FULL, cand ? lo : 0u);
+    const bool tied = valid && cand && lo == max_lo;
     const uint32_t ties = __ballot_sync(AZ_FULL, tied);
     int win_lane;
     if (!tie_random || __popc(ties) == 1) {
-        // lowest child index among the tied lanes; lane order == child order within one 32-chunk
-        uint32_t key = tied ? (uint32_t)idx : 0xffffffffu;
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) key = min(key, __shfl_xor_sync(AZ_FULL, key, off));
-        const uint32_t who = __ballot_sync(AZ_FULL, tied && (uint32_t)idx == key);
-        win_lane = __ffs(who) - 1;
+        const uint32_t first_half = __ballot_sync(AZ_FULL, tied && idx < 32);
+        win_lane = __ffs(first_half ? first_half : ties) - 1;
     } else {
         win_lane = az_tie_pick(seed, g, event, ties);
     }
-    (void)lane;
     *src_lane = win_lane;
     return __shfl_sync(AZ_FULL, idx, win_lane);
 }
