@@ -185,10 +185,12 @@ struct az_dirlane {
 };
 
 __device__ __forceinline__ az_dirlane az_dirlane_of(int lane) {
-    const int k = lane & 3;
+    const uint32_t k = (uint32_t)lane & 3u;
     az_dirlane d;
-    d.s = k == 0 ? 1u : (k == 1 ? 8u : (k == 2 ? 9u : 7u));
-    d.keep = k == 1 ? ~0ULL : (k == 3 ? AZ_NOT_COL7 : AZ_NOT_COL0);
+    d.s = (0x7981u >> (4u * k)) & 15u;                          // 1, 8, 9, 7
+    // column guard, the same byte pattern in both words: all cells (S), not column 7 (SW), not column 0 (E, SE)
+    const uint32_t w = k == 1u ? 0xFFFFFFFFu : (k == 3u ? (uint32_t)AZ_NOT_COL7 : (uint32_t)AZ_NOT_COL0);
+    d.keep = ((uint64_t)w << 32) | w;
     d.rev = (lane & 4) != 0;
     return d;
 }
