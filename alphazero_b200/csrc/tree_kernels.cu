@@ -171,8 +171,10 @@ __device__ __forceinline__ uint32_t az_alloc_children(const az_tree& t, const az
         if (sum < 1e-6f) {
             p0 = p1 = (float)(1.0 / (double)k);
         } else {
-            p0 = __fdiv_rn(p0, sum);
-            p1 = __fdiv_rn(p1, sum);
+            // only lanes that hold a child divide: a zero numerator (idle lanes; every lane's second slot when k <= 32)
+            // would send the whole warp through the division's slow path, twice per simulation
+            if (has0) p0 = __fdiv_rn(p0, sum);
+            if (has1) p1 = __fdiv_rn(p1, sum);
         }
     }
     if (has0) az_store_node(&nodes[base + lane], 0.0, p0, 0u, 0u, az_make_meta(0, a0, 0u));
