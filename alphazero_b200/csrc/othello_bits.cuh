@@ -172,7 +172,7 @@ AZ_HD int az_nth_set_bit(uint64_t m, int k) {
 #ifdef __CUDACC__
 // ------------------------------------------------------------------------------------------------ warp-cooperative forms
 // The tree kernels give one warp to one game, so every lane would repeat the same 8-direction ray computation.
-// These variants give one DIRECTION to a lane instead and OR the eight results with warp shuffles: ~1/5 of the
+// These variants give one DIRECTION to a lane instead and OR the eight results with `redux.sync`: ~1/5 of the
 // instructions of az_flips / az_legal_mask.  All lanes must be converged and hold the same (own, opp).
 //
 // Lanes 0..3 walk E, S, SE, SW with left shifts by 1, 8, 9, 7; lanes 4..7 walk the opposite directions W, N, NW, NE
