@@ -135,7 +135,7 @@ class SelfPlayEngine:
                  dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
                  temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
                  tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
-                 network_path: str = "auto", tail_tiers="auto"):
+                 network_path: str = "auto", tail_tiers="auto", evaluator_factory=None):
         # `n`: Othello board size or a GameSpec (gamespec.Connect4Spec(7, 6) for BASELINE config 5)
         self.spec = spec = as_spec(n)
         self.G, self.n, self.n_sim = G, spec.n, n_sim
@@ -143,8 +143,13 @@ class SelfPlayEngine:
         self.tree = TreeBatch(G, n=spec, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
                               tie_random=tie_random, dirichlet_alpha=dirichlet_alpha,
                               dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
+        # `evaluator`: a ready evaluator bound to the main tree; `evaluator_factory(tree) -> evaluator`: builds one per
+        # tree batch (main and tail tiers), e.g. lambda t: HashEvaluator(salt, tree=t); default: the network's own
+        self._evaluator_factory = evaluator_factory
         if evaluator is not None:
             self.evaluator = evaluator
+        elif evaluator_factory is not None:
+            self.evaluator = evaluator_factory(self.tree)
         else:
             self.evaluator = make_evaluator(nn, self.tree, dtype=dtype, path=network_path)
         # Tail of a batch: games of one batch end within a few plies of each other, and the last plies would run the
@@ -178,10 +183,10 @@ class SelfPlayEngine:
 
     def set_network(self, nn) -> None:
         """trainer.update_network (trainer.py:383-387): refresh the device snapshot + CUDA graph."""
-        self.evaluator.refresh(nn)
         self._tier_args["nn"] = nn
-        for _, ev in self._tiers.values():
-            ev.refresh(nn)
+        for _, ev in self.trees():
+            if hasattr(ev, "refresh"):
+                ev.refresh(nn)
 
     def _tier(self, size: int):
         """(TreeBatch, evaluator) of `size` slots for the tail of a batch, built on first use."""
@@ -191,7 +196,10 @@ class SelfPlayEngine:
                              device=a["device"], seed=a["seed"] + 0x9E3779B9 * size, tie_random=a["tie_random"],
                              dirichlet_alpha=a["dirichlet_alpha"], dirichlet_epsilon=a["dirichlet_epsilon"],
                              enc_dtype=a["dtype"], max_depth=self.tree.max_depth, graph_first_use=True)
-            ev = make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"])
+            if self._evaluator_factory is not None:
+                ev = self._evaluator_factory(tree)
+            else:
+                ev = make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"])
             tree.search(self.n_sim, ev, extra_steps=0, check=False)      # captures the tier's search graph now
             self._tiers[size] = (tree, ev)
         return self._tiers[size]

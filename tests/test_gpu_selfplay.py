@@ -143,3 +143,31 @@ def test_sample_batch_states_match_reference_layout():
     first = s[0]
     want = np.zeros((6, 6)); want[2, 2] = want[3, 3] = 1; want[2, 3] = want[3, 2] = -1
     assert (first == want).all()
+
+
+def test_tail_tiers_do_not_change_the_games():
+    """Deterministic setting (hash evaluator, temperature 0, no Dirichlet noise, lowest-index tie-break): moving the
+    last live games to smaller tree batches (TreeBatch.adopt: root, kept search tree, counters) must leave every
+    sample -- state, visit-count policy, outcome -- identical to the run that keeps them in the full batch."""
+    from alphazero_b200 import boardops as bo
+    from alphazero_b200.evaluators import HashEvaluator
+    from alphazero_b200.selfplay import SelfPlayEngine
+    n, n_sim = 6, 40
+    black, white, player = _random_positions(n, 96, 5)
+    G = len(black)
+    own, opp = np.where(player > 0, black, white), np.where(player > 0, white, black)
+    d_own, d_opp, d_player = bo.bits_from_numpy(own), bo.bits_from_numpy(opp), torch.from_numpy(player).cuda()
+    batches = []
+    for tiers in ((), (G // 2, G // 6, 4)):
+        eng = SelfPlayEngine(None, G, n=n, n_sim=n_sim, dirichlet_alpha=None, dirichlet_epsilon=None,
+                             temp_scheduler_type="constant", temp_max_step=0, temp_min_step=0, seed=11,
+                             tie_random=False, tail_tiers=tiers,
+                             evaluator_factory=lambda t: HashEvaluator(salt=77, tree=t))
+        for _ in range(2):      # second batch: searches replay CUDA graphs
+            b = eng.play(d_own, d_opp, d_player).cpu()
+        assert (len(eng.trees()) > 1) == bool(tiers)
+        batches.append(b)
+    a, b = batches
+    assert len(a) == len(b) and len(a) > G
+    for name in ("own", "opp", "pi", "z", "episode_idx", "move_idx"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
