@@ -14,11 +14,10 @@ Evaluators: alphazero_b200.evaluators.{NetEvaluator, HashEvaluator}; rollout mod
 import ctypes
 import time
 
-import numpy as np
 import torch
 
 from . import _lib
-from .boardops import PASS, _ptr, _stream, to_i64
+from .boardops import _ptr, _stream, to_i64
 from .gamespec import as_spec
 
 NODE_BYTES = 32

@@ -264,7 +264,6 @@ def run_ours(args):
         wall = time.time() - t0
         clocks = sampler.stop()
         ms = max(e0.elapsed_time(e1), 0.0)
-        ms = max(ms, 0.0)
         stats = torch.tensor([ms, wall * 1000.0], dtype=torch.float64, device=dev)
         tot = torch.tensor([sims, moves, games], dtype=torch.float64, device=dev)
         if world > 1:
