@@ -128,6 +128,25 @@ class SampleBatch:
         return out
 
 
+def default_tail_tiers(G: int) -> tuple:
+    """Sizes of the tail tiers of a G-game batch: G/2, G/8, G/64 from 1024 games on, none below."""
+    return tuple(sorted(G // d for d in (2, 8, 64))) if G >= 1024 else ()
+
+
+def normalise_tail_tiers(tail_tiers, G: int) -> tuple:
+    """"auto" -> default_tail_tiers(G); else the distinct sizes in (0, G), ascending."""
+    if isinstance(tail_tiers, str):
+        if tail_tiers != "auto":
+            raise ValueError(f"tail_tiers must be 'auto' or a sequence of sizes, not {tail_tiers!r}")
+        return default_tail_tiers(G)
+    return tuple(sorted({int(x) for x in (tail_tiers or ()) if 0 < int(x) < G}))
+
+
+def pick_tail_tier(n_live: int, current_size: int, tiers: tuple):
+    """The smallest tier that holds `n_live` games and is smaller than the batch they are in, or None (stay)."""
+    return next((x for x in tiers if n_live <= x < current_size), None)
+
+
 class SelfPlayEngine:
     """G concurrent AlphaZero self-play games on one GPU."""
 
@@ -158,9 +177,7 @@ class SelfPlayEngine:
         # evaluator and search graph) the live games are moved to once they fit:
         # "auto" = G/2, G/8, G/64 for G >= 1024, nothing below; () switches it off.  A caller-supplied evaluator is
         # bound to the main tree, so it switches it off too.
-        if tail_tiers == "auto":
-            tail_tiers = tuple(G // d for d in (2, 8, 64)) if G >= 1024 else ()
-        self.tail_tiers = tuple(sorted({int(x) for x in (tail_tiers or ()) if 0 < int(x) < G})) if evaluator is None else ()
+        self.tail_tiers = normalise_tail_tiers(tail_tiers, G) if evaluator is None else ()
         self._tiers = {}             # size -> (TreeBatch, evaluator)
         self._tier_args = dict(nn=nn, dtype=dtype, network_path=network_path, seed=seed, tie_random=tie_random,
                                dirichlet_alpha=dirichlet_alpha, dirichlet_epsilon=dirichlet_epsilon, device=device)
@@ -266,7 +283,7 @@ class SelfPlayEngine:
             n_live, n_nodes = torch.stack([live.sum(), (tree.n_alloc * live).max().to(torch.int64)]).tolist()
             if n_live == 0:
                 break
-            size = next((x for x in self.tail_tiers if n_live <= x < tree.G), None)
+            size = pick_tail_tier(n_live, tree.G, self.tail_tiers)
             if size is not None:
                 sel = torch.nonzero(live).flatten()
                 sub, evaluator = self._tier(size)
