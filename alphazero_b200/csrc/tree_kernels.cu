@@ -72,10 +72,11 @@ __device__ __forceinline__ uint32_t az_make_meta(int n_children, int move, uint3
     return (uint32_t)n_children | ((uint32_t)move << 8) | (flags << 16);
 }
 
+// The selection only follows the winner's links (N, child block, move / flags): its Q and P are not broadcast.
 __device__ __forceinline__ NodeRec az_bcast_node(const NodeRec& r, int src) {
     NodeRec o;
-    o.Q = __shfl_sync(AZ_FULL, r.Q, src);
-    o.P = __shfl_sync(AZ_FULL, r.P, src);
+    o.Q = 0.0;
+    o.P = 0.f;
     o.N = __shfl_sync(AZ_FULL, r.N, src);
     o.first_child = __shfl_sync(AZ_FULL, r.first_child, src);
     o.meta = __shfl_sync(AZ_FULL, r.meta, src);
@@ -335,15 +336,16 @@ __device__ __forceinline__ int az_warp_argmax(double score, int idx, bool valid,
     const uint32_t max_lo = __reduce_max_sync(AZ_FULL, cand ? lo : 0u);
     const bool tied = valid && cand && lo == max_lo;
     const uint32_t ties = __ballot_sync(AZ_FULL, tied);
+    const uint32_t first_half = __ballot_sync(AZ_FULL, tied && idx < 32);
     int win_lane;
     if (!tie_random || __popc(ties) == 1) {
-        const uint32_t first_half = __ballot_sync(AZ_FULL, tied && idx < 32);
         win_lane = __ffs(first_half ? first_half : ties) - 1;
     } else {
         win_lane = az_tie_pick(seed, g, event, ties);
     }
     *src_lane = win_lane;
-    return __shfl_sync(AZ_FULL, idx, win_lane);
+    // the winner's idx is its lane, or lane + 32 when it is not among the first-half ties: no shuffle needed
+    return win_lane + (((first_half >> win_lane) & 1u) ? 0 : 32);
 }
 
 // Dirichlet noise on the priors of the root's children (mcts.py:234-240): P = (1-eps) P + eps * Dir(alpha)_j with
