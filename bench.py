@@ -113,21 +113,24 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
 
 
-def ncu_traffic(kernel_substr):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, from the committed ncu --set full
-    capture (profiles/r1_ncu_full_summary.json, same command at n_sim=8); None when the capture is absent."""
-    path = os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")
-    if not os.path.isfile(path):
-        return None
-    vals = []
-    for k in json.load(open(path)):
-        if kernel_substr in k["kernel"]:
-            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-            tot = 0.0
-            for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                tot += (k[m]["value"] or 0.0) * scale.get(k[m]["unit"], 1.0)
-            vals.append(tot)
-    return sum(vals) / len(vals) if vals else None
+def ncu_traffic(kernel_substr, captures=("r1_ncu_full_summary.json",)):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, from the first of the committed
+    `ncu --set full` summaries under profiles/ that holds the kernel; None when there is none."""
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for name in captures:
+        path = os.path.join(ROOT, "profiles", name)
+        if not os.path.isfile(path):
+            continue
+        vals = []
+        for k in json.load(open(path)):
+            if kernel_substr in k["kernel"]:
+                tot = 0.0
+                for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tot += (k[m]["value"] or 0.0) * scale.get(k[m]["unit"], 1.0)
+                vals.append(tot)
+        if vals:
+            return sum(vals) / len(vals)
+    return None
 
 
 def cpu_baseline(args, seconds):
@@ -353,7 +356,9 @@ def run_ours(args):
                      "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": tree_gbs / peaks["hbm_gbs"],
                      "ms_per_launch": tree_ms, "mean_depth": mean_depth, "bytes_per_sim": bytes_per_sim,
                      "share_of_step": tree_ms / (eval_ms + tree_ms), "ms_per_launch_eager": eager_tree_ms,
-                     "traffic": ncu_traffic("k_tree_step")}
+                     # mid-game tree steps (plies ~40, n_sim 200: tools/gpu_ncu_tree.sh) when that capture is committed,
+                     # else the shallow trees of the n_sim = 8 capture
+                     "traffic": ncu_traffic("k_tree_step", ("r1_ncu_tree_midgame.json", "r1_ncu_full_summary.json"))}
 
     if rank == 0:
         value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
