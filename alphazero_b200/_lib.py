@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "sample_kernels.cu", "peak_kernels.cu", "mma_probe.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "fcstack_kernels.cu", "sample_kernels.cu", "player_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
@@ -80,9 +80,13 @@ SIGNATURES = {
     "az_tree_choose": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_tree_advance": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p]),
     "az_eval_hash": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_u64, c_void_p, c_void_p, c_void_p]),
+    "az_greedy_move": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_u64, ctypes.c_uint32, c_int,
+                                c_void_p, c_void_p, c_void_p]),
     "az_net_wblob_bytes": (c_int, []),
     "az_net_trunk_boards_per_group": (c_int, [c_int, c_i64]),
-    "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
+    "az_net_fcstack_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "az_net_fcstack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "az_connect4_image_bits": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_heads": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_headgemm_blob_bytes": (c_i64, [c_int, c_int]),
@@ -91,8 +95,6 @@ SIGNATURES = {
     "az_augment_twins": (c_int, [c_int]),
     "az_augment_plan": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p]),
     "az_augment_apply": (c_int, [c_void_p] * 6 + [c_i64, c_int, c_int, c_int, c_int] + [c_void_p] * 9),
-    "az_peak_int32": (c_int, [c_int, c_int, c_void_p, c_i64, ctypes.POINTER(ctypes.c_int64), c_void_p]),
-    "az_peak_mma": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "az_samples_batch": (c_int, [c_void_p] * 5 + [c_i64, c_i64, c_int, c_int, c_int] + [c_void_p] * 5),
 }
 

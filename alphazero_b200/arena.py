@@ -2,8 +2,8 @@
 reference's "parallel" mode -- all games of a match as ONE device batch instead of a multiprocessing.Pool.
 
 Batched mode supports the players whose move rule runs on the device: MCTSPlayer / AlphaZeroPlayer (TreeBatch search,
-greedy on visit counts with random tie-break, tree reuse through both players' moves) and RandomPlayer (uniform legal
-move).  Other players fall back to nothing: a ValueError says so."""
+greedy on visit counts with random tie-break, tree reuse through both players' moves), RandomPlayer (uniform legal
+move) and GreedyPlayer (az_greedy_move).  Other players (HumanPlayer) fall back to nothing: a ValueError says so."""
 from collections import defaultdict
 from time import time
 
@@ -15,7 +15,7 @@ from .base import Board, Player
 from .engine import TreeBatch
 from .fused_net import make_evaluator
 from .gamespec import spec_of
-from .players import AlphaZeroPlayer, MCTSPlayer, RandomPlayer
+from .players import AlphaZeroPlayer, GreedyPlayer, MCTSPlayer, RandomPlayer
 
 
 def _empty_stats() -> dict:
@@ -30,6 +30,8 @@ class _BatchedSide:
         self.player = player
         self.tree = None
         self.evaluator = None
+        self.greedy = isinstance(player, GreedyPlayer)
+        self.seed, self.n_calls = seed, 0
         self.gen = torch.Generator(device="cuda")
         self.gen.manual_seed(seed)
         if isinstance(player, AlphaZeroPlayer):
@@ -42,9 +44,9 @@ class _BatchedSide:
         elif isinstance(player, MCTSPlayer):
             self.n_sim = player.n_sim
             self.tree = TreeBatch(G, n=spec, mode="rollout", n_sim_hint=self.n_sim, seed=seed, tie_random=True)
-        elif not isinstance(player, RandomPlayer):
+        elif not isinstance(player, (RandomPlayer, GreedyPlayer)):
             raise ValueError(f"{player} has no batched device implementation (supported: MCTSPlayer, "
-                             "AlphaZeroPlayer, RandomPlayer); use play_games instead")
+                             "AlphaZeroPlayer, RandomPlayer, GreedyPlayer); use play_games instead")
         if self.tree is not None and self.n_sim is None:
             raise ValueError("batched arena needs n_sim players (compute_time is wall-clock bound per game)")
 
@@ -56,6 +58,9 @@ class _BatchedSide:
             self.tree.search(self.n_sim, self.evaluator, check=False)
             action, _ = self.tree.choose(None)        # temp = 0: MCTSPlayer.get_move default (players.py:161)
             return torch.where(mask, action, torch.full_like(action, 255))
+        if self.greedy:        # one-ply look-ahead on get_score with a random tie-break (players.py:98-123)
+            self.n_calls += 1
+            return spec.greedy_moves(own, opp, mask=mask, seed=self.seed, ctr=self.n_calls, tie_random=True)
         bits, no_move_action = spec.legal_action_bits(spec.legal(own, opp))                         # [G, 64]
         has = bits.sum(dim=1) > 0
         bits[~has, 0] = 1.0                                # dummy support for rows without a move (Othello: pass)
@@ -177,8 +182,7 @@ class Arena:
                 break
         for s in sides:
             if s.tree is not None:
-                s.tree.status.bitwise_and_(~4)   # inactive games never advance; illegal-move bits cannot be set here
-                s.tree.check_status()
+                s.tree.check_status()            # overflow / depth / a move the tree's position does not have
         _, score, winner = spec.terminal_score(own, opp, player)
         score, winner, p2s = score.abs().cpu().numpy(), winner.cpu().numpy(), p2_starts.cpu().numpy()
         if verbose:

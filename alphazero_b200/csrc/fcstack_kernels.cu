@@ -1,0 +1,422 @@
+// The fully connected stack of the policy-value networks -- fc1 + BN + ReLU -> fc2 + BN + ReLU -> fc_probs || fc_value
+// (alphazero/games/othello.py:352-362 layers, :374-382 forward; connect4.py:381-390, :403-411) -- as ONE tcgen05
+// kernel for sm_100a.  Replaces the three library GEMMs the first version of the fused evaluator launched.
+//
+// Work split.  A thread-block cluster of RT x NS CTAs owns RT row tiles of 128 positions; CTA (r, c) computes, for row
+// tile r, the c-th slice of the output columns of every layer (fc1: N1/NS columns, fc2: N2/NS, heads: a padded share
+// of the A + 1 outputs).  With 4096 positions, RT = 2 and NS = 4 that is 16 clusters = 128 CTAs, one per SM.
+//
+// Operands.  Everything the tensor core reads is staged in shared memory in the K-major no-swizzle layout
+// ([8-wide K plane][row][8] bf16: 16 bytes per row per plane), and every stage is ONE contiguous block of global
+// memory in exactly that layout, so a stage is filled by plain bulk async copies (cp.async.bulk, no tensor maps):
+//   * activations ("packed A"): [row tile][K chunk][K plane][128 rows][8]; the conv trunk writes its features in this
+//     layout, and the epilogues of fc1 / fc2 write h1 / h2 in it (global scratch that never leaves the L2);
+//   * weights ("packed B", built once on the host): [column slice c][K chunk][K plane][N/NS rows][8].
+// The A block of a stage is needed by the NS CTAs of a row tile and the B block by the RT CTAs of a column slice: each
+// CTA issues 1/NS of the A block and 1/RT of the B block with .multicast::cluster to the whole group, so every byte
+// leaves the L2 once per cluster.  A stage's `full` barrier collects the bytes from all issuers; its `empty` barrier
+// collects one tcgen05.commit (multicast) from every CTA the issuer sends to.
+//
+// Layer chaining.  fc1's accumulator (128 x N1/NS fp32) sits in TMEM columns [0, 256), fc2's in [256, 384), the heads'
+// in [384, 512): no accumulator is reused, so the MMA warp never waits for an epilogue.  The epilogue warps turn a
+// finished accumulator into bf16 blocks of the next layer's K-chunk width (bias + ReLU, BatchNorm folded on the
+// host), store them as packed A blocks and signal a per-block `ready` barrier in all NS CTAs of the row tile
+// (remote mbarrier arrive); the producer of the next layer waits for the block it is about to fetch, and fetches the
+// blocks in the order they are produced.  The heads' epilogue adds the bias and writes the bf16 logits row that the
+// tree step (az_tree.logits) or az_net_heads reads.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../../include/az_b200.h"
+#include "common.cuh"
+#include "umma.cuh"
+
+#define FS_STAGES 4
+#define FS_A_BYTES 16384                      // one A stage: 64 (K) x 128 rows bf16
+#define FS_B_BYTES 32768                      // one B stage: 64 (K) x 256 columns bf16
+#define FS_STAGE_BYTES (FS_A_BYTES + FS_B_BYTES)
+#define FS_EPI_WARPS 8                        // warps 0-7: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = block parity)
+#define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 8: bulk copies (one lane)
+#define FS_MMA_WARP (FS_EPI_WARPS + 1)        // warp 9: tcgen05.mma issue (one elected lane), TMEM allocation
+#define FS_THREADS ((FS_EPI_WARPS + 2) * 32)
+#define FS_MAX_CHUNKS 16                      // K chunks per layer
+#define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
+#define FB_FULL 0
+#define FB_EMPTY (FB_FULL + FS_STAGES)
+#define FB_ACC (FB_EMPTY + FS_STAGES)
+#define FB_READY (FB_ACC + 3)                 // [2][FS_MAX_CHUNKS]: block kc of h1 / h2 of this row tile is in global memory
+#define FB_COUNT (FB_READY + 2 * FS_MAX_CHUNKS)
+#define FS_SM_BIAS (FS_STAGES * FS_STAGE_BYTES)
+#define FS_SM_BARS (FS_SM_BIAS + FS_BIAS_FLOATS * 4)
+#define FS_SM_TMEM_PTR (FS_SM_BARS + 8 * 48)
+#define FS_SM_TOTAL (FS_SM_TMEM_PTR + 16)
+static_assert(FB_COUNT <= 48, "barrier area");
+static_assert(FS_SM_TOTAL <= 232448, "shared memory per CTA on sm_100");
+
+struct FcStackParams {
+    const uint8_t* x;          // layer-1 input, packed A: [tiles][K0/kch0][kch0/8][128][8] bf16
+    const uint8_t* wblob;      // packed B of the three layers, then their float32 biases (az_net_fcstack_plan)
+    uint8_t* h1;               // scratch, packed A: [tiles][K1/kch1][kch1/8][128][8]
+    uint8_t* h2;               // scratch, packed A: [tiles][K2/kch2][kch2/8][128][8]
+    __nv_bfloat16* logits;     // [G][ld]
+    long long G;
+    int ld, n_out;             // row pitch of logits; real outputs (action_size + 1)
+    int K[3], Nc[3], kch[3];   // per layer: K, output columns per CTA, K chunk (16 / 32 / 64)
+    int RT, NS, hpc;           // cluster shape; real head outputs per column slice
+    uint32_t w_off[3], b_off[3];
+};
+
+__device__ __forceinline__ void fs_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// mbarrier waits of this kernel: a wait that lasts longer than ~2 s of SM clocks is a protocol bug (a peer CTA that
+// never sends / never releases) -- trap, so that the launch fails with an error instead of hanging the device.
+#define FS_WAIT_LIMIT (4000000000LL)
+__device__ __forceinline__ void fs_mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) return;
+        const long long t = clock64();
+        if (t0 == 0) t0 = t;
+        else if (t - t0 > FS_WAIT_LIMIT) __trap();
+    }
+}
+// the same with cluster-scope acquire: pairs with the remote release-arrive of another CTA's epilogue
+__device__ __forceinline__ void fs_mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) return;
+        const long long t = clock64();
+        if (t0 == 0) t0 = t;
+        else if (t - t0 > FS_WAIT_LIMIT) __trap();
+    }
+}
+
+// arrive (release, cluster scope) on the barrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void fs_mbar_arrive_remote(uint32_t bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
+        "}" ::"r"(bar), "r"(rank) : "memory");
+}
+
+__device__ __forceinline__ void fs_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+// global -> shared bulk copy completing on `bar`; with more than one destination the bytes (and the completion) go to
+// the same offsets in every CTA of `mask`
+__device__ __forceinline__ void fs_bulk_copy(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint32_t mask,
+                                             bool multicast) {
+    if (multicast)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+                     ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"((uint16_t)mask) : "memory");
+    else
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void fs_commit_multicast(uint32_t bar, uint32_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)mask) : "memory");
+}
+
+// wait for the tcgen05.ld's issued so far; the registers are read-write operands so that no use is scheduled before it
+__device__ __forceinline__ void fs_tmem_wait64(uint32_t (&v)[64]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+        : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+          "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+          "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
+          "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31]),
+          "+r"(v[32]), "+r"(v[33]), "+r"(v[34]), "+r"(v[35]), "+r"(v[36]), "+r"(v[37]), "+r"(v[38]), "+r"(v[39]),
+          "+r"(v[40]), "+r"(v[41]), "+r"(v[42]), "+r"(v[43]), "+r"(v[44]), "+r"(v[45]), "+r"(v[46]), "+r"(v[47]),
+          "+r"(v[48]), "+r"(v[49]), "+r"(v[50]), "+r"(v[51]), "+r"(v[52]), "+r"(v[53]), "+r"(v[54]), "+r"(v[55]),
+          "+r"(v[56]), "+r"(v[57]), "+r"(v[58]), "+r"(v[59]), "+r"(v[60]), "+r"(v[61]), "+r"(v[62]), "+r"(v[63])
+        :: "memory");
+}
+
+__device__ __forceinline__ void fs_tmem_ld16(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+
+__global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int RT = p.RT, NS = p.NS;
+    uint32_t rank, cluster_id;
+    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    asm("mov.u32 %0, %%clusterid.x;" : "=r"(cluster_id));
+    const int r = (int)rank / NS, c = (int)rank % NS;
+    const int m = (int)cluster_id * RT + r;                   // row tile of this CTA
+    const uint32_t a_mask = ((1u << NS) - 1u) << (r * NS);    // the CTAs of row tile r
+    uint32_t b_mask = 0u;                                     // the CTAs of column slice c
+    for (int rr = 0; rr < RT; ++rr) b_mask |= 1u << (rr * NS + c);
+    const uint32_t all_mask = a_mask | b_mask;
+    const bool mc_a = NS > 1, mc_b = RT > 1, mc_any = mc_a || mc_b;
+
+    const uint32_t bars = smem_u32(smem + FS_SM_BARS);
+    const uint32_t bar_full0 = bars + 8 * FB_FULL, bar_empty0 = bars + 8 * FB_EMPTY, bar_acc0 = bars + 8 * FB_ACC;
+    const uint32_t bar_ready0 = bars + 8 * FB_READY;
+    float* bias_s = reinterpret_cast<float*>(smem + FS_SM_BIAS);
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + FS_SM_TMEM_PTR);
+    const int bias_off[3] = {0, 256, 384};
+    const uint32_t col_off[3] = {0u, 256u, 384u};             // TMEM columns of the three accumulators
+
+    // ---- setup: barriers, biases of this column slice (weights: not produced by the preceding kernel), TMEM
+    if (tid == 0) {
+        for (int s = 0; s < FS_STAGES; ++s) { mbar_init(bar_full0 + 8 * s, 1); mbar_init(bar_empty0 + 8 * s, __popc(all_mask)); }
+        for (int L = 0; L < 3; ++L) mbar_init(bar_acc0 + 8 * L, 1);
+        for (int i = 0; i < 2 * FS_MAX_CHUNKS; ++i) mbar_init(bar_ready0 + 8 * i, 4);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+#pragma unroll
+    for (int L = 0; L < 3; ++L) {
+        const float* b = reinterpret_cast<const float*>(p.wblob + p.b_off[L]) + c * p.Nc[L];
+        for (int i = tid; i < p.Nc[L]; i += FS_THREADS) bias_s[bias_off[L] + i] = b[i];
+    }
+    if (warp == FS_MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    fs_cluster_sync();            // every CTA's barriers exist before any multicast copy / remote arrive targets them
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_ptr_smem;
+    az_pdl_wait();                // the layer-1 input is the preceding kernel's output
+    az_pdl_trigger();
+
+    if (warp == FS_PRODUCER_WARP) {
+        // ================================================================== producer: one lane issues every copy
+        if (lane == 0) {
+            uint32_t it = 0;
+#pragma unroll
+            for (int L = 0; L < 3; ++L) {
+                const int kch = p.kch[L], nch = p.K[L] / kch;
+                const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
+                const uint32_t a_part = a_bytes / (uint32_t)NS, b_part = b_bytes / (uint32_t)RT;
+                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + (size_t)c * a_part;
+                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + (size_t)r * b_part;
+                const int bps = nch / NS;                     // blocks the epilogue of one CTA produced (L > 0)
+                for (int q = 0; q < nch; ++q, ++it) {
+                    // L > 0: fetch in production order -- block j of every column slice, then block j + 1
+                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
+                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
+                    if (L > 0) {
+                        fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
+                        asm volatile("fence.proxy.async.global;" ::: "memory");
+                    }
+                    const uint32_t full = bar_full0 + 8 * s;
+                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
+                    fs_expect_tx(full, a_bytes + b_bytes);
+                    fs_bulk_copy(sa + (uint32_t)c * a_part, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
+                    fs_bulk_copy(sb + (uint32_t)r * b_part, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == FS_MMA_WARP) {
+        // ================================================================== MMA issue
+        uint32_t it = 0;
+#pragma unroll
+        for (int L = 0; L < 3; ++L) {
+            const int kch = p.kch[L], nch = p.K[L] / kch, ksteps = kch >> 4;
+            const uint32_t nc = (uint32_t)p.Nc[L];
+            const uint32_t idesc = umma_idesc_bf16_m128(nc);
+            const uint32_t d_tmem = tmem_base + col_off[L];
+            for (int q = 0; q < nch; ++q, ++it) {
+                const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                fs_mbar_wait(bar_full0 + 8 * s, ph);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (elect_one()) {
+                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint64_t ad = umma_desc(sa + (uint32_t)k * 4096u, 2048u, 128u);
+                        const uint64_t bd = umma_desc(sb + (uint32_t)k * 32u * nc, 16u * nc, 128u);
+                        umma_bf16(d_tmem, ad, bd, idesc, (q | k) ? 1u : 0u);
+                    }
+                    if (mc_any) fs_commit_multicast(bar_empty0 + 8 * s, all_mask);
+                    else umma_commit(bar_empty0 + 8 * s);
+                    if (q == nch - 1) umma_commit(bar_acc0 + 8 * L);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ================================================================== epilogue
+        const int quarter = warp & 3, half = warp >> 2;
+        const int row = quarter * 32 + lane;                  // TMEM lane = row of the tile
+        const long long grow = (long long)m * 128 + row;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        uint32_t v[64];
+#pragma unroll
+        for (int i = 0; i < 64; ++i) v[i] = 0u;
+#pragma unroll
+        for (int L = 0; L < 3; ++L) {
+            fs_mbar_wait(bar_acc0 + 8 * L, 0u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (L < 2) {
+                const int bw = p.kch[L + 1];                  // block width = the next layer's K chunk
+                const int nblk = p.Nc[L] / bw, nchn = p.K[L + 1] / bw;
+                uint8_t* hbase = (L == 0 ? p.h1 : p.h2) + (size_t)m * nchn * ((size_t)bw * 256) + (size_t)row * 16;
+                for (int j = half; j < nblk; j += 2) {
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq)
+                        if (qq * 16 < bw) fs_tmem_ld16(t_lane + col_off[L] + (uint32_t)(j * bw + qq * 16), &v[qq * 16]);
+                    fs_tmem_wait64(v);
+                    const int kcn = c * nblk + j;             // this block's K chunk in the next layer
+                    uint8_t* dst = hbase + (size_t)kcn * ((size_t)bw * 256);
+                    const float* bs = bias_s + bias_off[L] + j * bw;
+#pragma unroll
+                    for (int pl = 0; pl < 8; ++pl) {
+                        if (pl * 8 < bw) {
+                            const float4 b0 = *reinterpret_cast<const float4*>(bs + pl * 8);
+                            const float4 b1 = *reinterpret_cast<const float4*>(bs + pl * 8 + 4);
+                            uint4 o;
+                            o.x = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 0]) + b0.x, __uint_as_float(v[pl * 8 + 1]) + b0.y);
+                            o.y = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 2]) + b0.z, __uint_as_float(v[pl * 8 + 3]) + b0.w);
+                            o.z = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 4]) + b1.x, __uint_as_float(v[pl * 8 + 5]) + b1.y);
+                            o.w = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 6]) + b1.z, __uint_as_float(v[pl * 8 + 7]) + b1.w);
+                            *reinterpret_cast<uint4*>(dst + pl * 2048) = o;
+                        }
+                    }
+                    // generic-proxy stores -> bulk async copies of other CTAs: proxy fence + cluster-scope release
+                    asm volatile("fence.proxy.async.global;" ::: "memory");
+                    asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                    __syncwarp();
+                    if (lane < NS) fs_mbar_arrive_remote(bar_ready0 + 8 * (L * FS_MAX_CHUNKS + kcn), (uint32_t)(r * NS + lane));
+                }
+            } else if (half == 0) {
+                const int ncols = p.Nc[2];
+#pragma unroll
+                for (int qq = 0; qq < 2; ++qq)
+                    if (qq * 16 < ncols) fs_tmem_ld16(t_lane + col_off[2] + (uint32_t)(qq * 16), &v[qq * 16]);
+                fs_tmem_wait64(v);
+                if (grow < p.G) {
+                    __nv_bfloat16* out = p.logits + grow * p.ld + c * p.hpc;
+                    const float* bs = bias_s + bias_off[2];
+#pragma unroll
+                    for (int col = 0; col < 32; ++col)
+                        if (col < p.hpc && c * p.hpc + col < p.n_out)
+                            out[col] = __float2bfloat16_rn(__uint_as_float(v[col]) + bs[col]);
+                }
+            }
+        }
+    }
+
+    // ---- teardown: no CTA leaves while a peer may still signal its barriers or copy into its shared memory
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    fs_cluster_sync();
+    if (warp == FS_MMA_WARP)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+
+struct FcPlan {
+    int kch[3], Nc[3], K[3];
+    int hpc, n3c;
+    uint32_t w_off[3], b_off[3];
+    int64_t blob_bytes;
+};
+
+static int fc_chunk(int k) { return k >= 64 ? 64 : k; }
+
+// Shapes of the three layers for a network K1 -> N1 -> N2 -> n_out with NS column slices; false when the kernel has
+// no mapping for them.
+static bool fc_plan(int K1, int N1, int N2, int n_out, int NS, FcPlan* pl) {
+    if (NS < 1 || NS > 8 || K1 < 16 || N1 < 16 || N2 < 16 || n_out < 1) return false;
+    if ((N1 % NS) || (N2 % NS)) return false;
+    pl->hpc = (n_out + NS - 1) / NS;
+    pl->n3c = ((pl->hpc + 15) / 16) * 16;
+    pl->K[0] = K1; pl->K[1] = N1; pl->K[2] = N2;
+    pl->Nc[0] = N1 / NS; pl->Nc[1] = N2 / NS; pl->Nc[2] = pl->n3c;
+    pl->kch[0] = fc_chunk(K1); pl->kch[1] = fc_chunk(pl->Nc[0]); pl->kch[2] = fc_chunk(pl->Nc[1]);
+    const int max_nc[3] = {256, 128, 32};
+    int64_t off = 0;
+    for (int L = 0; L < 3; ++L) {
+        const int kch = pl->kch[L];
+        if ((kch % 16) || (pl->K[L] % kch) || pl->K[L] / kch > FS_MAX_CHUNKS) return false;
+        if ((pl->Nc[L] % 16) || pl->Nc[L] > max_nc[L]) return false;
+        if (L > 0 && (pl->Nc[L - 1] % kch)) return false;        // whole blocks per producing CTA
+        if ((kch * 256 / NS) % 16) return false;                 // bulk-copy granularity of an A part
+        pl->w_off[L] = (uint32_t)off;
+        off += (int64_t)NS * pl->Nc[L] * pl->K[L] * 2;
+    }
+    for (int L = 0; L < 3; ++L) { pl->b_off[L] = (uint32_t)off; off += (int64_t)NS * pl->Nc[L] * 4; }
+    pl->blob_bytes = off;
+    return true;
+}
+
+// out[0..2] K chunk per layer, out[3..5] columns per CTA per layer, out[6] real head outputs per slice,
+// out[7..9] byte offsets of the packed weights, out[10..12] of the float32 biases, out[13] blob bytes
+extern "C" int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, int64_t* out) {
+    FcPlan pl;
+    if (!out || !fc_plan(K1, N1, N2, n_out, NS, &pl)) return AZ_ERR_ARG;
+    for (int L = 0; L < 3; ++L) {
+        out[L] = pl.kch[L]; out[3 + L] = pl.Nc[L]; out[7 + L] = pl.w_off[L]; out[10 + L] = pl.b_off[L];
+    }
+    out[6] = pl.hpc; out[13] = pl.blob_bytes;
+    return AZ_OK;
+}
+
+extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out,
+                              int64_t G, int K1, int N1, int N2, int RT, int NS, void* stream) {
+    FcPlan pl;
+    if (!fc_plan(K1, N1, N2, n_out, NS, &pl) || RT < 1 || RT * NS > 8 || ld < n_out || G < 0 ||
+        (G > 0 && (!x || !wblob || !h1 || !h2 || !logits)))
+        return AZ_ERR_ARG;
+    if (G == 0) return AZ_OK;
+    static bool attr_set = false;
+    if (!attr_set) {
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_fcstack, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SM_TOTAL));
+        attr_set = true;
+    }
+    FcStackParams p;
+    p.x = (const uint8_t*)x; p.wblob = (const uint8_t*)wblob; p.h1 = (uint8_t*)h1; p.h2 = (uint8_t*)h2;
+    p.logits = (__nv_bfloat16*)logits; p.G = G; p.ld = ld; p.n_out = n_out;
+    for (int L = 0; L < 3; ++L) {
+        p.K[L] = pl.K[L]; p.Nc[L] = pl.Nc[L]; p.kch[L] = pl.kch[L]; p.w_off[L] = pl.w_off[L]; p.b_off[L] = pl.b_off[L];
+    }
+    p.RT = RT; p.NS = NS; p.hpc = pl.hpc;
+    const int64_t tiles = (G + 127) / 128, clusters = (tiles + RT - 1) / RT;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(clusters * RT * NS)); cfg.blockDim = dim3(FS_THREADS);
+    cfg.dynamicSmemBytes = FS_SM_TOTAL; cfg.stream = (cudaStream_t)stream;
+    static const bool no_pdl = getenv("AZ_B200_NO_PDL") != nullptr;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)(RT * NS); attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = no_pdl ? 1 : 2;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_net_fcstack, p);
+    if (e != cudaSuccess) return az_set_cuda_error(e, "k_net_fcstack");
+    AZ_CHECK_LAUNCH("k_net_fcstack");
+    return AZ_OK;
+}

@@ -42,6 +42,8 @@ struct az_rules<AZ_GAME_OTHELLO> {
     static AZ_HDM void apply(uint64_t& own, uint64_t& opp, int a, const az_dims&) { az_apply(own, opp, a); }
     static AZ_HDM bool is_terminal(uint64_t own, uint64_t opp, const az_dims& d) { return az_is_terminal(own, opp, d.bmask); }
     static AZ_HDM int winner(uint64_t own, uint64_t opp, int player, const az_dims&) { return az_winner(own, opp, player); }
+    // get_score(): sum(player * grid) from the side to move's view (othello.py:133-135)
+    static AZ_HDM int score(uint64_t own, uint64_t opp) { return az_disc_diff(own, opp); }
     // index of a canvas action in the network's policy vector (r*n+c, pass last; othello.py:391, 408-409)
     static AZ_HDM int net_index(int a, const az_dims& d) { return a == AZ_PASS ? d.rows * d.cols : (a >> 3) * d.cols + (a & 7); }
 };
@@ -57,6 +59,7 @@ struct az_rules<AZ_GAME_CONNECT4> {
     static AZ_HDM void apply(uint64_t& own, uint64_t& opp, int a, const az_dims& d) { az_c4_apply(own, opp, a, d.bmask); }
     static AZ_HDM bool is_terminal(uint64_t own, uint64_t opp, const az_dims& d) { return az_c4_is_terminal(own, opp, d.bmask); }
     static AZ_HDM int winner(uint64_t own, uint64_t opp, int player, const az_dims&) { return az_c4_winner(own, opp, player); }
+    static AZ_HDM int score(uint64_t own, uint64_t opp) { return az_disc_diff(own, opp); }      // connect4.py:137-139
     static AZ_HDM int net_index(int a, const az_dims& d) { return a < d.cols ? a : 0; }
 };
 
@@ -71,6 +74,7 @@ struct az_rules<AZ_GAME_TICTACTOE> {
     static AZ_HDM void apply(uint64_t& own, uint64_t& opp, int a, const az_dims&) { az_ttt_apply(own, opp, a); }
     static AZ_HDM bool is_terminal(uint64_t own, uint64_t opp, const az_dims&) { return az_ttt_is_terminal(own, opp); }
     static AZ_HDM int winner(uint64_t own, uint64_t opp, int player, const az_dims&) { return az_ttt_winner(own, opp, player); }
+    static AZ_HDM int score(uint64_t own, uint64_t opp) { return az_ttt_score(own, opp); }       // tictactoe.py:127-133
     // tictactoe.py:325, 340: index 3*r + c
     static AZ_HDM int net_index(int a, const az_dims&) { return (a >> 3) * 3 + (a & 7); }
 };

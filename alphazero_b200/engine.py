@@ -12,6 +12,7 @@ game per step (the reference's sequential order per game), with the leaf evaluat
 Evaluators: alphazero_b200.evaluators.{NetEvaluator, HashEvaluator}; rollout mode needs none (az_tree_rollout).
 """
 import ctypes
+import itertools
 import time
 
 import torch
@@ -21,6 +22,15 @@ from .boardops import _ptr, _stream, to_i64
 from .gamespec import as_spec
 
 NODE_BYTES = 32
+_EVALUATOR_UIDS = itertools.count(1)      # process-wide: id() of a dropped evaluator can be handed out again
+
+
+def _evaluator_uid(evaluator) -> int:
+    uid = getattr(evaluator, "_az_uid", None)
+    if uid is None:
+        uid = next(_EVALUATOR_UIDS)
+        evaluator._az_uid = uid
+    return uid
 
 
 class TreeBatch:
@@ -77,7 +87,9 @@ class TreeBatch:
         self.graph_search = bool(graph_search)
         self.graph_first_use = bool(graph_first_use)   # capture at the first use (batches that exist to be reused)
         self.graph_step_launches = 0  # az_tree_step kernels replayed inside search graphs (not seen by _lib.LAUNCH_CALLS)
-        self._search_graphs = {}      # (n_sim, steps, id(evaluator), evaluator.version) -> CUDAGraph | None (seen once)
+        # (n_sim, steps, evaluator uid, evaluator.version, descriptor fields baked into the launches)
+        #   -> [CUDAGraph | None (seen once), evaluator (kept alive: the graph replays into its buffers)]
+        self._search_graphs = {}
         self._desc = _lib.AzTree()
         d = self._desc
         for name in ("nodes", "half", "n_alloc", "root_own", "root_opp", "root_player", "active", "sims_done",
@@ -219,24 +231,32 @@ class TreeBatch:
             enqueue = getattr(evaluator, "enqueue", None)
             if enqueue is None:
                 return None
-            key = (int(n_sim), int(steps), id(evaluator), getattr(evaluator, "version", 0))
+            ident = (_evaluator_uid(evaluator), getattr(evaluator, "version", 0))
         else:
-            enqueue = self.rollout_leaves
-            key = (int(n_sim), int(steps), 0, 0)
+            enqueue, evaluator = self.rollout_leaves, None
+            ident = (0, 0)
+        # az_tree is passed to the kernels BY VALUE, so everything in it that a setter can change after the capture
+        # (set_dirichlet, set_encoding, the logits binding of search) is part of the key: a replay never runs with
+        # stale settings, it is re-captured
+        d = self._desc
+        baked = (d.enc, d.logits, int(d.logits_ld), float(d.dirichlet_alpha), float(d.dirichlet_eps), int(d.tie_random),
+                 int(d.seed), int(d.mode))
+        key = (int(n_sim), int(steps)) + ident + (baked,)
         if key not in self._search_graphs:
-            for k in [k for k in self._search_graphs if k[2] == key[2] and k[3] != key[3]]:
-                del self._search_graphs[k]                      # graphs over a refreshed evaluator's old buffers
-            self._search_graphs[key] = None
+            for k in [k for k in self._search_graphs if k[:3] == key[:3] and k != key]:
+                del self._search_graphs[k]                      # graphs over old weights / old settings
+            self._search_graphs[key] = [None, evaluator]
             if not self.graph_first_use:
                 return None
-        if self._search_graphs[key] is None:
+        entry = self._search_graphs[key]
+        if entry[0] is None:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 for _ in range(steps):
                     enqueue()
                     self.step(n_sim, finish=True, select=True)
-            self._search_graphs[key] = g
-        return self._search_graphs[key]
+            entry[0] = g
+        return entry[0]
 
     def check_status(self) -> None:
         """Raises if any game hit a pool overflow / depth overflow / illegal move (synchronises)."""

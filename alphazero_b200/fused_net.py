@@ -11,10 +11,14 @@ only re-packs them for the kernels:
   * fc1 columns permuted from the reference's channel-major flatten (c*m*m + pos) to the trunk kernel's
     position-major feature order (pos*32 + c);
   * fc_probs and fc_value concatenated into one [n*n+2, 512] head.
-Per step:  az_net_trunk (tcgen05)  ->  fc1 + ReLU, fc2 + ReLU, heads (cuBLASLt GEMMs with fused bias/ReLU epilogues,
-plain library GEMMs)  ->  az_net_heads (softmax / tanh straight into tree.probs / tree.value), all in one CUDA graph.
+Per step (default, heads="stack"):  az_net_trunk (tcgen05, features in the packed operand layout)  ->  az_net_fcstack
+(fc1 + ReLU, fc2 + ReLU, heads as ONE tcgen05 cluster kernel, csrc/fcstack_kernels.cu)  ->  az_net_heads (softmax /
+tanh straight into tree.probs / tree.value; inside a whole-search graph the tree step does that itself): no library
+kernel on the path.  heads="library" keeps the first version (three cuBLASLt GEMMs) as a cross-check for the tests.
 Input is the leaf bitboards (tree.leaf_own / leaf_opp): the float encoding of the board is never materialised.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -62,6 +66,59 @@ def pack_trunk_weights(net) -> torch.Tensor:
     return torch.from_numpy(packed.copy())
 
 
+def fcstack_plan(K1: int, N1: int, N2: int, n_out: int, NS: int) -> dict:
+    """Layer shapes / blob offsets of az_net_fcstack for a K1 -> N1 -> N2 -> n_out stack cut into NS column slices
+    (the C side is the single source of truth: az_net_fcstack_plan); raises ValueError when there is no mapping."""
+    import ctypes
+    out = (ctypes.c_int64 * 14)()
+    if _lib.lib().az_net_fcstack_plan(K1, N1, N2, n_out, NS, out) != 0:
+        raise ValueError(f"az_net_fcstack has no mapping for {K1} -> {N1} -> {N2} -> {n_out} with {NS} column slices")
+    v = list(out)
+    return {"kch": v[0:3], "Nc": v[3:6], "hpc": v[6], "w_off": v[7:10], "b_off": v[10:13], "bytes": v[13],
+            "K": [K1, N1, N2], "NS": NS, "n_out": n_out}
+
+
+def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int):
+    """(uint8 blob, plan) for az_net_fcstack from the three layers' [N][K] weights / [N] biases (BatchNorm folded):
+    per layer [NS][K/kch][kch/8][N/NS][8] bf16 -- slice c of the output columns, K chunk, 8-wide K plane, column, K % 8
+    = the tcgen05 K-major no-swizzle B operand, one contiguous block per (slice, chunk) -- then the float32 biases.
+    The heads are spread over the slices hpc outputs each, zero padded to a multiple of 16 columns."""
+    n_out, N2 = wh.shape
+    plan = fcstack_plan(w1.shape[1], w1.shape[0], w2.shape[0], n_out, NS)
+    hpc, n3c = plan["hpc"], plan["Nc"][2]
+    wh_p = torch.zeros(NS * n3c, N2, dtype=torch.float64)
+    bh_p = torch.zeros(NS * n3c, dtype=torch.float64)
+    for c in range(NS):
+        lo, hi = c * hpc, min(n_out, (c + 1) * hpc)
+        if hi > lo:
+            wh_p[c * n3c:c * n3c + hi - lo] = wh[lo:hi].double().cpu()
+            bh_p[c * n3c:c * n3c + hi - lo] = bh[lo:hi].double().cpu()
+    blob = np.zeros(plan["bytes"], dtype=np.uint8)
+    for L, (w, b) in enumerate(((w1, b1), (w2, b2), (wh_p, bh_p))):
+        N, K = w.shape
+        kch, nc = plan["kch"][L], plan["Nc"][L]
+        assert N == NS * nc and K == plan["K"][L]
+        bits = _bf16_bits(w).reshape(NS, nc, K // kch, kch // 8, 8).transpose(0, 2, 3, 1, 4)
+        blob[plan["w_off"][L]:plan["w_off"][L] + N * K * 2] = np.ascontiguousarray(bits).reshape(-1).view(np.uint8)
+        blob[plan["b_off"][L]:plan["b_off"][L] + N * 4] = b.float().cpu().numpy().astype(np.float32).view(np.uint8)
+    return torch.from_numpy(blob), plan
+
+
+def pack_rows(x: torch.Tensor, kch: int = 64) -> torch.Tensor:
+    """Row-major [G][K] -> the packed A operand layout [ceil(G/128)][K/kch][kch/8][128][8] (rows zero padded)."""
+    G, K = x.shape
+    T = (G + 127) // 128
+    xp = torch.zeros(T * 128, K, dtype=x.dtype, device=x.device)
+    xp[:G] = x
+    return xp.view(T, 128, K // kch, kch // 8, 8).permute(0, 2, 3, 1, 4).contiguous()
+
+
+def unpack_rows(packed: torch.Tensor, G: int, K: int, kch: int = 64) -> torch.Tensor:
+    """Inverse of pack_rows: the first G rows as a row-major [G][K] tensor."""
+    T = packed.numel() // (128 * K)
+    return packed.reshape(T, K // kch, kch // 8, 128, 8).permute(0, 3, 1, 2, 4).reshape(T * 128, K)[:G]
+
+
 def _image_shape(nn):
     """(rows, cols) of the image the network's first convolution sees, or None if the fused trunk has no kernel for it."""
     from .games.connect4 import Connect4Net
@@ -88,16 +145,22 @@ class FusedNetEvaluator:
 
     own_kernels_per_call = 2   # k_net_trunk + k_net_heads (replayed inside the CUDA graph)
 
-    def __init__(self, nn, tree, use_cuda_graph: bool = True, heads: str = "library", heads_in_tree: bool = True):
-        """heads_in_tree: inside a whole-search graph (TreeBatch.search -> enqueue()) the softmax / tanh of the heads is
+    def __init__(self, nn, tree, use_cuda_graph: bool = True, heads: str = "stack", heads_in_tree: bool = True,
+                 stack_shape=None):
+        """heads: "stack" (default) = az_net_fcstack, the hand-written fc1 -> fc2 -> heads kernel; "library" = the
+        three cuBLASLt GEMMs of the first version (kept as a cross-check); "fused" = library fc1 / fc2 + az_net_headgemm.
+        stack_shape: (RT, NS) cluster shape of az_net_fcstack, default by batch size (env AZ_B200_FCSTACK="RT,NS").
+        heads_in_tree: inside a whole-search graph (TreeBatch.search -> enqueue()) the softmax / tanh of the heads is
         left to the tree step, which reads the bf16 logits row itself (az_tree.logits, same arithmetic and bits as
         az_net_heads); a plain call still runs az_net_heads so that tree.probs / tree.value are always valid."""
-        if heads not in ("fused", "library"):
-            raise ValueError("heads must be 'fused' (az_net_headgemm) or 'library' (cuBLASLt GEMM + az_net_heads)")
+        if heads not in ("stack", "fused", "library"):
+            raise ValueError("heads must be 'stack' (az_net_fcstack), 'library' (cuBLASLt GEMMs + az_net_heads) or "
+                             "'fused' (library fc1 / fc2 + az_net_headgemm)")
         self.tree = tree
         self.use_cuda_graph = use_cuda_graph
         self.heads = heads
-        self.heads_in_tree = bool(heads_in_tree) and heads == "library"
+        self.stack_shape = stack_shape
+        self.heads_in_tree = bool(heads_in_tree) and heads != "fused"
         self.own_launches = 0
         self.graph = None
         self.n_calls = 0
@@ -114,7 +177,8 @@ class FusedNetEvaluator:
             raise ValueError(f"the fused trunk has no kernel for {nn}")
         self.rows, self.cols = shape
         self.connect4 = t.spec.game == "connect4"
-        self.own_kernels_per_call = 3 if self.connect4 else 2     # (+ az_connect4_image_bits)
+        # k_net_trunk + k_net_heads (+ k_net_fcstack) (+ az_connect4_image_bits)
+        self.own_kernels_per_call = 2 + (1 if self.heads == "stack" else 0) + (1 if self.connect4 else 0)
         if nn.action_size != t.A or (not self.connect4 and nn.n != t.n) or \
                 (self.connect4 and (nn.width, nn.height) != (t.spec.cols, t.spec.rows)):
             raise ValueError(f"network {nn} does not match the tree's game {t.spec}")
@@ -145,10 +209,22 @@ class FusedNetEvaluator:
         assert blob.nbytes == int(_lib.lib().az_net_headgemm_blob_bytes(h2, self.NH))
         self.head_blob = torch.from_numpy(blob.copy()).to(dev)
         self.h2_features = h2
-        self.features = torch.zeros(G, m * 32, dtype=torch.bfloat16, device=dev)
-        self.h1 = torch.empty(G, h1, dtype=torch.bfloat16, device=dev)
-        self.h2 = torch.empty(G, h2, dtype=torch.bfloat16, device=dev)
-        self.logits = torch.empty(G, self.ld, dtype=torch.bfloat16, device=dev)
+        self.K1, self.N1, self.N2 = m * 32, h1, h2
+        if self.heads == "stack":
+            self.RT, self.NS = self._stack_shape(G, h1)
+            blob, self.plan = pack_fcstack(w1, b1, w2, b2, wh[:A + 1], bh[:A + 1], self.NS)
+            self.stack_blob = blob.to(dev)
+            tiles = -(-((G + 127) // 128) // self.RT) * self.RT          # row tiles, a whole number of clusters
+            self.tiles = tiles
+            self.features = torch.zeros(tiles * 128 * m * 32, dtype=torch.bfloat16, device=dev)      # packed layout
+            self.h1 = torch.zeros(tiles * 128 * h1, dtype=torch.bfloat16, device=dev)
+            self.h2 = torch.zeros(tiles * 128 * h2, dtype=torch.bfloat16, device=dev)
+            self.logits = torch.zeros(G, self.ld, dtype=torch.bfloat16, device=dev)
+        else:
+            self.features = torch.zeros(G, m * 32, dtype=torch.bfloat16, device=dev)
+            self.h1 = torch.empty(G, h1, dtype=torch.bfloat16, device=dev)
+            self.h2 = torch.empty(G, h2, dtype=torch.bfloat16, device=dev)
+            self.logits = torch.empty(G, self.ld, dtype=torch.bfloat16, device=dev)
         # (pointer, row pitch) TreeBatch.search puts into az_tree.logits for this evaluator, or None
         self.logits_binding = (self.logits.data_ptr(), self.ld) if self.heads_in_tree else None
         if self.connect4:
@@ -157,6 +233,25 @@ class FusedNetEvaluator:
         self.graph = None
         if self.use_cuda_graph:
             self._capture()
+
+    def _stack_shape(self, G: int, N1: int):
+        """(RT, NS) of the az_net_fcstack clusters: NS column slices so that a slice of fc1 fits one accumulator
+        (N1/NS <= 256), RT = 2 row tiles per cluster (the weights leave the L2 once per two tiles) when there are
+        at least two."""
+        shape = self.stack_shape
+        if shape is None and os.environ.get("AZ_B200_FCSTACK"):
+            shape = tuple(int(v) for v in os.environ["AZ_B200_FCSTACK"].split(","))
+        if shape is not None:
+            return int(shape[0]), int(shape[1])
+        NS = max(1, N1 // 256)
+        RT = 2 if (G + 127) // 128 >= 2 and NS * 2 <= 8 else 1
+        return RT, NS
+
+    def features_rowmajor(self) -> torch.Tensor:
+        """bf16 [G][(rows-4)(cols-4)*32] view / copy of the trunk's output whatever layout it was written in."""
+        if self.heads == "stack":
+            return unpack_rows(self.features, self.tree.G, self.K1)
+        return self.features
 
     def trunk(self, debug=None, debug_layer: int = 0) -> None:
         t = self.tree
@@ -167,19 +262,25 @@ class FusedNetEvaluator:
                        "az_connect4_image_bits")
             own, opp = self.img_own, self.img_opp
         _lib.check(_lib.lib().az_net_trunk(_ptr(own), _ptr(opp), self.rows, self.cols, t.G, _ptr(self.wblob),
-                                           _ptr(self.features), _ptr(debug), int(debug_layer), _stream()), "az_net_trunk")
+                                           _ptr(self.features), 1 if self.heads == "stack" else 0, _ptr(debug),
+                                           int(debug_layer), _stream()), "az_net_trunk")
 
     def _forward(self, output_transform: bool = True) -> None:
         t = self.tree
         self.trunk()
-        with torch.no_grad():
-            torch._addmm_activation(self.b1, self.features, self.w1t, out=self.h1)      # fused bias + ReLU epilogue
-            torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
-            if self.heads == "library":
-                torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
+        if self.heads == "stack":
+            _lib.check(_lib.lib().az_net_fcstack(_ptr(self.features), _ptr(self.stack_blob), _ptr(self.h1), _ptr(self.h2),
+                                                 _ptr(self.logits), self.ld, self.A + 1, t.G, self.K1, self.N1, self.N2,
+                                                 self.RT, self.NS, _stream()), "az_net_fcstack")
+        else:
+            with torch.no_grad():
+                torch._addmm_activation(self.b1, self.features, self.w1t, out=self.h1)      # fused bias + ReLU epilogue
+                torch._addmm_activation(self.b2, self.h1, self.w2t, out=self.h2)
+                if self.heads == "library":
+                    torch.addmm(self.bh, self.h2, self.wht, out=self.logits)
         if not output_transform:
             return
-        if self.heads == "library":
+        if self.heads != "fused":
             _lib.check(_lib.lib().az_net_heads(_ptr(self.logits), self.ld, self.A, t.G, _ptr(t.probs), _ptr(t.value),
                                                _stream()), "az_net_heads")
         else:       # fc_probs / fc_value + softmax / tanh in one tcgen05 kernel

@@ -47,6 +47,18 @@ class GameSpec:
         return (torch.empty(G, dtype=torch.uint8, device=own.device), torch.empty(G, dtype=torch.int8, device=own.device),
                 torch.empty(G, dtype=torch.int8, device=own.device))
 
+    def greedy_moves(self, own, opp, mask=None, seed: int = 0, ctr: int = 0, tie_random: bool = True, want_ties: bool = False):
+        """GreedyPlayer.get_move for every position (players.py:98-123, az_greedy_move): uint8 actions (255 where
+        mask is 0); with want_ties also the uint64 sets of the maximising actions."""
+        G = own.numel()
+        action = torch.empty(G, dtype=torch.uint8, device=own.device)
+        ties = torch.empty(G, dtype=torch.int64, device=own.device) if want_ties else None
+        m = None if mask is None else mask.to(torch.uint8).contiguous()
+        _lib.check(_lib.lib().az_greedy_move(self.game_id, _ptr(own), _ptr(opp), _ptr(m), self.n, self.height, G,
+                                             _to_u64(seed), int(ctr) & 0xFFFFFFFF, 1 if tie_random else 0, _ptr(action),
+                                             _ptr(ties), _stream()), "az_greedy_move")
+        return (action, ties) if want_ties else action
+
     def __eq__(self, other):
         return type(self) is type(other) and (self.n, self.height) == (other.n, other.height)
 

@@ -270,7 +270,8 @@ class AlphaZeroTrainer:
         opponent_player = PLAYERS_REGISTER[cfg.eval_opponent](**kwargs)
         arena = Arena(player1=eval_player, player2=opponent_player, board=BOARDS_REGISTER[self.game](config=cfg))
         self.print(f"\nAlphaZeroPlayer evaluation against {opponent_player} ({cfg.eval_episodes} episodes)")
-        batched = cfg.eval_opponent in ("mcts", "random") and cfg.simulations is not None and cfg.eval_episodes % 2 == 0
+        batched = cfg.eval_opponent in ("mcts", "random", "greedy") and cfg.simulations is not None and \
+            cfg.eval_episodes % 2 == 0
         if batched:
             stats = arena.play_games_in_parallel(n_rounds=cfg.eval_episodes, n_process=2, return_stats=True)
         else:

@@ -243,6 +243,18 @@ int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream);
 int az_eval_hash(const uint64_t* own, const uint64_t* opp, int action_size, int64_t G, uint64_t salt, float* probs,
                  float* value, void* stream);
 
+/* ---------------------------------------------------------------- search-free players ------------------ */
+
+/* GreedyPlayer.get_move for G positions (alphazero/players.py:98-123): every legal move is played on a copy, its value
+ * is -get_score() of the resulting board (the score of the side that just moved), the best value wins; ties are broken
+ * uniformly at random (utils.fair_max, utils.py:28-34) with Philox4x32-10 keyed by (seed; game index, ctr) when
+ * tie_random != 0, else the lowest action index wins.  game: AZ_GAME_*; n / height as in az_tree (Othello: board size;
+ * Connect4: width, height).  mask (optional): games with mask[g] == 0 get action 255.  action: uint8 [G] on the
+ * canvas action space (Othello pass = 64 when there is no placement).  ties (optional): uint64 [G], the set of
+ * maximising actions (0 for a pass / masked game). */
+int az_greedy_move(int game, const uint64_t* own, const uint64_t* opp, const uint8_t* mask, int n, int height, int64_t G,
+                   uint64_t seed, uint32_t ctr, int tie_random, uint8_t* action, uint64_t* ties, void* stream);
+
 /* ---------------------------------------------------------------- fused network kernels ---------------- */
 
 /* Bytes of the packed trunk weights expected by az_net_trunk (built by alphazero_b200/fused_net.py). */
@@ -254,12 +266,14 @@ int az_net_wblob_bytes(void);
  * player*grid, base.py:363, is formed on the fly).  Othello: the image is the board, (rows, cols) = (8, 8) or (6, 6).
  * Connect4 7x6: Connect4Net views the (height, width) grid as a (width, height) image, (rows, cols) = (7, 6); make
  * the bitboards with az_connect4_image_bits.
- * features: bf16 [G][(rows-4)*(cols-4) * 32], position-major / channel-minor (fc1's columns are permuted to match).
+ * features: bf16 [G][(rows-4)*(cols-4) * 32], position-major / channel-minor (fc1's columns are permuted to match);
+ * with features_packed != 0 the same values in the packed operand layout az_net_fcstack reads:
+ * [ceil(G/128)][K/64][8][128][8] bf16, element (g, k) at tile g/128, chunk k/64, plane (k%64)/8, row g%128, k%8.
  * tcgen05 implicit GEMM, activations resident in shared memory.
  * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>
  * (az_net_trunk_boards_per_group gives boards_per_group). */
 int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob,
-                 void* features, void* debug, int debug_layer, void* stream);
+                 void* features, int features_packed, void* debug, int debug_layer, void* stream);
 
 /* Boards per group az_net_trunk uses for G images of `rows` rows on the current device (> 0; the layout of its
  * optional debug dump depends on it: group = g / boards, row = (g % boards) * (rows+1)*8 + (1+i)*8 + j). */
@@ -286,6 +300,25 @@ int az_net_heads(const void* logits, int ld, int action_size, int64_t G, float* 
 int64_t az_net_headgemm_blob_bytes(int K, int NH);
 int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action_size, int64_t G, float* probs,
                     float* value, void* stream);
+
+/* The fully connected stack fc1 + BN + ReLU -> fc2 + BN + ReLU -> fc_probs || fc_value of OthelloNet / Connect4Net
+ * (othello.py:352-362, 374-382; connect4.py:381-390, 403-411; eval-mode BatchNorm1d folded, dropout off) as ONE
+ * tcgen05 kernel over thread-block clusters of RT x NS CTAs (RT row tiles of 128 positions x NS column slices,
+ * RT*NS <= 8; operands by multicast bulk async copies, h1 / h2 exchanged through `h1` / `h2` scratch that stays in
+ * the L2).  Replaces the three library GEMMs of the first fused evaluator.
+ *   x       bf16 packed operand layout [T][K1/64][8][128][8] (what az_net_trunk writes with features_packed = 1),
+ *           T = ceil(G/128) rounded up to a multiple of RT
+ *   wblob   az_net_fcstack_plan(...)[13] bytes: per layer the weights [NS][K/kch][kch/8][N/NS][8] bf16
+ *           (blob[c][kc][p][n][j] = W[c*N/NS + n][kc*kch + 8p + j]; heads: slice c holds outputs c*hpc .. c*hpc+hpc-1,
+ *           zero padded to a multiple of 16 rows), then float32 biases in the same column order
+ *   h1, h2  scratch, T*128*N1*2 and T*128*N2*2 bytes
+ *   logits  bf16 [G][ld], columns 0 .. n_out-1 written (n_out = action_size + 1: policy logits, then the value logit)
+ * az_net_fcstack_plan fills out[14]: K chunk per layer [0..2], columns per CTA per layer [3..5], hpc [6], byte offsets
+ * of the weights [7..9] and biases [10..12], blob bytes [13]; AZ_ERR_ARG when the kernel has no mapping for the shape
+ * (needs N1/NS <= 256, N2/NS <= 128, ceil(n_out/NS) <= 32, K1 % 64 == 0 or K1 in {16, 32}). */
+int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, int64_t* out);
+int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out, int64_t G,
+                   int K1, int N1, int N2, int RT, int NS, void* stream);
 
 /* ---------------------------------------------------------------- TicTacToe ----------------------------- */
 /* 3 x 3 board on the same canvas (bit r*8+c, r, c < 3); an action is the canvas cell, there is no pass; the policy
@@ -356,22 +389,6 @@ int az_augment_apply(const uint64_t* own, const uint64_t* opp, const float* pi, 
 int az_samples_batch(const uint64_t* own, const uint64_t* opp, const float* pi, const int8_t* z,
                      const int64_t* index, int64_t S, int64_t B, int rows, int cols, int action_size, float* input,
                      float* pi_out, float* z_out, int32_t* bad_index, void* stream);
-
-/* ---------------------------------------------------------------- measurement only --------------------- */
-
-/* Integer-ALU issue-rate micro-benchmark (the roofline denominator of the board kernels):
- * launches 148*8 CTAs of 256 threads, each thread running `iters` x 32 instructions of one kind in 8 independent
- * chains.  kind 0 LOP3, 1 SHF, 2 IADD3, 3 shift-mask-or (the movegen step, 2 instructions).  out: >= 148*8*256
- * uint32 (sink).  *ops_per_thread (host, optional) = instructions each thread executed in the timed loop. */
-int az_peak_int32(int kind, int iters, uint32_t* out, int64_t out_len, int64_t* ops_per_thread, void* stream);
-
-/* tcgen05.mma issue-rate probe (the evidence behind the trunk's N = 96 design): every SM issues
- * `reps` x `k_steps` MMAs of shape m x n x 16 (bf16 from shared memory, K-major no-swizzle, fp32 in TMEM), the
- * k_steps of a rep accumulating into one of `regions` (1 or 2) accumulators; cycles[sm] (device, 148 int64) = SM
- * clocks from the first issue to the completion of the last.
- * flags: 1 = every MMA accumulates (no zero-initialising MMA), 2 = tcgen05.commit after every chain, 4 = three warps
- * keep reading 96 accumulator columns with tcgen05.ld meanwhile. */
-int az_peak_mma(int m, int n, int k_steps, int reps, int regions, int flags, int64_t* cycles, void* stream);
 
 #ifdef __cplusplus
 }

@@ -57,6 +57,7 @@ def lib():
         L.orc_mct_new_tictactoe.argtypes = [i32, i32, u64, u64, vp, vp]
         L.orc_mct_new_connect4.restype = vp
         L.orc_mct_new_connect4.argtypes = [i32, i32, i32, i32, u64, u64, vp, vp]
+        L.orc_greedy_moves.argtypes = [i32, vp, vp, vp, i32, i32, i64, vp, vp]
         _lib = L
     return _lib
 
@@ -105,6 +106,16 @@ def playouts(black, white, player, n, per_root, seed, first_id=0):
     lib().orc_othello_playouts(P(black), P(white), P(player), n, len(black), per_root, seed, first_id,
                                P(fb), P(fw), P(win), P(pl))
     return fb, fw, win, pl
+
+
+def greedy_moves(game, black, white, player, n, h=None):
+    """GreedyPlayer.get_move for every position: (lowest-index best action uint8 [G], set of best actions uint64 [G]);
+    game 0 Othello (n), 1 Connect4 (n = width, h = height), 2 TicTacToe."""
+    G = len(black)
+    best, ties = np.zeros(G, np.uint8), np.zeros(G, np.uint64)
+    lib().orc_greedy_moves(game, P(np.ascontiguousarray(black, np.uint64)), P(np.ascontiguousarray(white, np.uint64)),
+                           P(np.ascontiguousarray(player, np.int8)), n, n if h is None else h, G, P(best), P(ties))
+    return best, ties
 
 
 def hash_eval(own, opp, action_size, salt):

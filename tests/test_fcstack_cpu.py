@@ -1,0 +1,70 @@
+"""CPU: the host side of az_net_fcstack -- plan, weight packing, operand packing -- against a NumPy walk-through of the
+kernel's own address arithmetic (tests/fcstack_emulator.py) and the plain matrix products it must equal."""
+import numpy as np
+import pytest
+import torch
+
+from fcstack_emulator import emulate
+
+
+def _stack(K1, N1, N2, n_out, seed):
+    g = torch.Generator().manual_seed(seed)
+    w1 = torch.randn(N1, K1, generator=g, dtype=torch.float64) / K1 ** 0.5
+    w2 = torch.randn(N2, N1, generator=g, dtype=torch.float64) / N1 ** 0.5
+    wh = torch.randn(n_out, N2, generator=g, dtype=torch.float64) / N2 ** 0.5
+    b1, b2, bh = (torch.randn(n, generator=g, dtype=torch.float64) * 0.1 for n in (N1, N2, n_out))
+    return w1, b1, w2, b2, wh, bh
+
+
+def _bf(x):
+    return x.float().to(torch.bfloat16).float()
+
+
+@pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
+    (512, 1024, 512, 66, 2, 4, 300),     # OthelloNet 8x8: three row tiles -> two clusters, the last one half empty
+    (128, 1024, 512, 38, 1, 4, 128),     # OthelloNet 6x6
+    (128, 1024, 512, 38, 1, 8, 70),      # eight column slices
+    (192, 64, 32, 8, 1, 1, 200),         # Connect4Net: no cluster
+    (192, 64, 32, 8, 2, 1, 500),         # Connect4Net, the weights multicast over two row tiles
+])
+def test_packing_matches_the_kernels_addressing(K1, N1, N2, n_out, RT, NS, G):
+    from alphazero_b200.fused_net import pack_fcstack, pack_rows
+    w1, b1, w2, b2, wh, bh = _stack(K1, N1, N2, n_out, seed=K1 + NS)
+    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+    assert blob.numel() == plan["bytes"]
+    x = _bf(torch.randn(G, K1, generator=torch.Generator().manual_seed(1)))
+    tiles = -(-((G + 127) // 128) // RT) * RT
+    xp = torch.zeros(tiles * 128, K1)
+    xp[:G] = x
+    packed = pack_rows(xp.to(torch.bfloat16), plan["kch"][0]).reshape(-1).view(torch.uint8).numpy()
+    ld = ((n_out + 7) // 8) * 8
+    got = emulate(packed, blob.numpy(), plan, G, ld, RT, NS)
+    h1 = _bf(torch.relu(x.double() @ _bf(w1).double().t() + b1.float().double()))
+    h2 = _bf(torch.relu(h1.double() @ _bf(w2).double().t() + b2.float().double()))
+    want = _bf(h2.double() @ _bf(wh).double().t() + bh.float().double()).numpy()
+    assert np.isnan(got[:, n_out:]).all()            # the pad columns of a logits row are never written
+    assert np.isfinite(got[:, :n_out]).all()
+    # fp32 accumulation order differs from the float64 product: allow a bf16 ulp of the logits
+    assert np.abs(got[:, :n_out] - want).max() <= 2.0 ** -7 * max(1.0, np.abs(want).max())
+
+
+def test_plan_refuses_shapes_without_a_mapping():
+    from alphazero_b200.fused_net import fcstack_plan
+    with pytest.raises(ValueError):
+        fcstack_plan(512, 1024, 512, 66, 2)          # a slice of fc1 would not fit its 256 accumulator columns
+    with pytest.raises(ValueError):
+        fcstack_plan(500, 1024, 512, 66, 4)          # K1 not a whole number of chunks
+    p = fcstack_plan(512, 1024, 512, 66, 4)
+    assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 17
+    assert p["bytes"] == (1024 * 512 + 512 * 1024 + 128 * 512) * 2 + (1024 + 512 + 128) * 4
+
+
+def test_pack_rows_round_trip():
+    from alphazero_b200.fused_net import pack_rows, unpack_rows
+    x = torch.arange(300 * 128, dtype=torch.float32).reshape(300, 128).to(torch.bfloat16)
+    p = pack_rows(x)
+    assert p.shape == (3, 2, 8, 128, 8)
+    assert torch.equal(unpack_rows(p, 300, 128), x)
+    # element (g, k) sits at tile g/128, chunk k/64, plane (k%64)/8, row g%128, k%8 -- the trunk's store address
+    g, k = 133, 77
+    assert p[g // 128, k // 64, (k % 64) // 8, g % 128, k % 8] == x[g, k]

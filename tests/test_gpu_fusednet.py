@@ -70,7 +70,7 @@ def test_trunk_layers_match_fp32(n):
     ev.trunk()
     torch.cuda.synchronize()
     m = n - 4
-    feat = ev.features.float().cpu().reshape(G, m * m, 32).permute(0, 2, 1).reshape(G, 32, m, m)
+    feat = ev.features_rowmajor().float().cpu().reshape(G, m * m, 32).permute(0, 2, 1).reshape(G, 32, m, m)
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
@@ -131,7 +131,7 @@ def test_fused_heads_kernel_matches_library_heads(n, G):
     b = torch.randint(0, 2**62, (G,), device="cuda") & bmask & ~a
     tree.leaf_own.copy_(a); tree.leaf_opp.copy_(b)
     outs = {}
-    for heads in ("library", "fused"):
+    for heads in ("library", "fused", "stack"):
         ev = FusedNetEvaluator(net, tree, heads=heads)
         tree.probs.zero_(); tree.value.zero_()
         ev()
@@ -140,11 +140,66 @@ def test_fused_heads_kernel_matches_library_heads(n, G):
     assert (outs["fused"][0].sum(1) - 1).abs().max() < 1e-5
     assert (outs["fused"][0] - outs["library"][0]).abs().max() < 3e-3
     assert (outs["fused"][1] - outs["library"][1]).abs().max() < 5e-3
+    # the hand-written fc stack against the three library GEMMs: both round h1 / h2 / logits to bf16
+    assert (outs["stack"][0] - outs["library"][0]).abs().max() < 3e-3
+    assert (outs["stack"][1] - outs["library"][1]).abs().max() < 8e-3
     # against the module itself in fp32: the north star's 1e-2
     net32 = net.to("cuda"); net32.device = torch.device("cuda")
     from alphazero_b200.gamespec import OthelloSpec
     p32, v32 = net32.predict(OthelloSpec(n).encode(a, b))
     assert (outs["fused"][0] - p32).abs().max() < 1e-2 and (outs["fused"][1] - v32.reshape(-1)).abs().max() < 1e-2
+    assert (outs["stack"][0] - p32).abs().max() < 1e-2 and (outs["stack"][1] - v32.reshape(-1)).abs().max() < 1e-2
+
+
+@pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
+    (512, 1024, 512, 66, 2, 4, 4096),    # OthelloNet 8x8 at the bench's batch: 16 clusters of 8
+    (512, 1024, 512, 66, 2, 4, 300),     # ragged: three row tiles, the second cluster half empty
+    (512, 1024, 512, 66, 1, 4, 129),
+    (512, 1024, 512, 66, 1, 8, 1000),
+    (128, 1024, 512, 38, 2, 4, 700),     # OthelloNet 6x6
+    (192, 64, 32, 8, 1, 1, 2048),        # Connect4Net: one CTA per row tile, 32-wide last chunk
+    (192, 64, 32, 8, 2, 1, 333),
+])
+def test_fcstack_raw_shapes(K1, N1, N2, n_out, RT, NS, G):
+    """az_net_fcstack through the C ABI on random operands against float64 torch (h1 / h2 rounded to bf16 as the
+    kernel's epilogues do): every cluster shape the evaluators use, ragged last tiles, pad columns untouched."""
+    from alphazero_b200 import _lib
+    from alphazero_b200.fused_net import pack_fcstack, pack_rows
+    torch.manual_seed(K1 + G)
+    w1 = torch.randn(N1, K1, dtype=torch.float64) / K1 ** 0.5
+    w2 = torch.randn(N2, N1, dtype=torch.float64) / N1 ** 0.5
+    wh = torch.randn(n_out, N2, dtype=torch.float64) / N2 ** 0.5
+    b1, b2, bh = (torch.randn(n, dtype=torch.float64) * 0.1 for n in (N1, N2, n_out))
+    x = torch.randn(G, K1).to(torch.bfloat16)
+    bf = lambda t: t.float().to(torch.bfloat16)
+    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+    blob = blob.cuda()
+    tiles = -(-((G + 127) // 128) // RT) * RT
+    xp = torch.zeros(tiles * 128, K1, dtype=torch.bfloat16)
+    xp[:G] = x
+    xp = pack_rows(xp, plan["kch"][0]).cuda()
+    s1 = torch.zeros(tiles * 128 * N1, dtype=torch.bfloat16, device="cuda")
+    s2 = torch.zeros(tiles * 128 * N2, dtype=torch.bfloat16, device="cuda")
+    ld = ((n_out + 7) // 8) * 8
+    logits = torch.full((G, ld), -77.0, dtype=torch.bfloat16, device="cuda")
+    for _ in range(2):                   # twice: the scratch buffers are reused
+        _lib.check(_lib.lib().az_net_fcstack(xp.data_ptr(), blob.data_ptr(), s1.data_ptr(), s2.data_ptr(),
+                                             logits.data_ptr(), ld, n_out, G, K1, N1, N2, RT, NS,
+                                             torch.cuda.current_stream().cuda_stream), "az_net_fcstack")
+    torch.cuda.synchronize()
+    xd = x.cuda()
+    h1 = bf(torch.relu(xd.double() @ bf(w1).cuda().double().t() + b1.float().double().cuda()))
+    h2 = bf(torch.relu(h1.double() @ bf(w2).cuda().double().t() + b2.float().double().cuda()))
+    want = h2.double() @ bf(wh).cuda().double().t() + bh.float().double().cuda()
+    got = logits[:, :n_out].double()
+    # one bf16 ulp of the logits (+ the rare h1 / h2 element that rounds the other way under fp32 accumulation)
+    assert (got - want).abs().max().item() <= 2.0 ** -7 * max(1.0, want.abs().max().item())
+    assert (logits[:, n_out:] == -77.0).all()
+    # argument checks: shapes without a mapping are refused, not mis-launched
+    assert _lib.lib().az_net_fcstack(xp.data_ptr(), blob.data_ptr(), s1.data_ptr(), s2.data_ptr(), logits.data_ptr(),
+                                     ld, n_out, G, K1, N1, N2, 4, 4, 0) != 0
+    assert _lib.lib().az_net_fcstack(xp.data_ptr(), blob.data_ptr(), s1.data_ptr(), s2.data_ptr(), logits.data_ptr(),
+                                     n_out - 1, n_out, G, K1, N1, N2, RT, NS, 0) != 0
 
 
 @pytest.mark.parametrize("K,A,G", [(32, 65, 200), (64, 7, 129), (512, 37, 1000), (256, 95, 64)])
@@ -207,9 +262,9 @@ def test_tree_step_reading_logits_gives_identical_search(game):
             rec.append((N.clone(), Q.clone(), P.clone(), rn.clone(), action.clone()))
             tree.advance(action)
             tree.check_status()
-        assert any(g is not None for g in tree._search_graphs.values())      # moves 1.. replayed the search graph
+        assert any(e[0] is not None for e in tree._search_graphs.values())      # moves 1.. replayed the search graph
         # first search from the host loop (trunk + az_net_heads per step), three from the graph
-        per_call = 3 if game == "connect4" else 2                          # (+ az_connect4_image_bits)
+        per_call = 4 if game == "connect4" else 3   # trunk, fcstack, heads (+ az_connect4_image_bits)
         assert ev.own_launches == (n_sim + 1) * per_call + 3 * (n_sim + 1) * (per_call - (1 if in_tree else 0))
         stats[in_tree] = rec
     for a, b in zip(stats[False], stats[True]):

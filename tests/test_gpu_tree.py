@@ -135,7 +135,7 @@ def test_visit_counts_identical_to_oracle(n, n_sim, G, graph):
         term, _, _ = orc.terminal(black, white, player, n)
         alive = alive & (term == 0)
         tree.active.copy_(torch.from_numpy(alive.astype(np.uint8)).cuda())
-    assert any(g is not None for g in tree._search_graphs.values()) == graph
+    assert any(e[0] is not None for e in tree._search_graphs.values()) == graph
     assert ev.n_calls == 4 * (n_sim + 1)
 
 
@@ -174,3 +174,40 @@ def test_temperature_sampling_distribution():
         mean_pi += want
     freq /= G; mean_pi /= G
     assert np.abs(freq - mean_pi).max() < 0.03
+
+
+def test_search_graph_follows_dirichlet_settings_and_evaluator_swaps():
+    """The whole-search CUDA graph bakes az_tree in by value: changing the Dirichlet settings or swapping the evaluator
+    between searches must re-capture, never replay a stale graph (the reference reads mct.dirichlet_* and mct.nn live,
+    mcts.py:78-83, 234-240)."""
+    from alphazero_b200.evaluators import HashEvaluator
+    G, n_sim = 64, 40
+
+    def root_priors(tree, ev):
+        tree.reset_roots()
+        tree.search(n_sim, ev)
+        return tree.root_stats()[2].clone()
+
+    tree = _mk_tree(G, 8, n_sim_hint=n_sim, seed=3)
+    ev = HashEvaluator(5, tree)
+    plain = root_priors(tree, ev)
+    assert torch.equal(root_priors(tree, ev), plain)            # second use: captured and replayed
+    assert any(e[0] is not None for e in tree._search_graphs.values())
+    tree.set_dirichlet(0.3, 0.25)
+    noisy = root_priors(tree, ev)
+    legal = plain > 0
+    assert (noisy[legal] != plain[legal]).any()                  # the noise is ON in the third search
+    assert torch.allclose(noisy.sum(1), torch.ones(G, device="cuda"), atol=1e-5)
+    root_priors(tree, ev)                                        # captured with the noise on
+    tree.set_dirichlet(None, None)
+    assert torch.equal(root_priors(tree, ev), plain)            # and OFF again
+    # a new evaluator object (different hash salt): its graph must not be confused with the dropped one's
+    fresh = _mk_tree(G, 8, n_sim_hint=n_sim, seed=3)
+    want = root_priors(fresh, HashEvaluator(6, fresh))
+    del ev
+    for _ in range(3):
+        ev2 = HashEvaluator(6, tree)
+        got = root_priors(tree, ev2)
+        assert torch.equal(root_priors(tree, ev2), got)
+        assert torch.equal(got, want)
+        del ev2

@@ -97,6 +97,8 @@ def ncu_pass():
 def main():
     torch.cuda.init()
     L = _lib.lib()
+    from tools.probes import build as _probes      # measurement-only kernels live outside the product library
+    PL = _probes.lib()
     if "--ncu" in sys.argv:
         return ncu_pass()
     out = {"device": torch.cuda.get_device_name(0)}
@@ -112,7 +114,7 @@ def main():
     peaks = {}
     for kind, name in enumerate(("lop3", "shf", "iadd3", "shift_mask_or")):
         ops = ctypes.c_int64(0)
-        call = lambda: _lib.check(L.az_peak_int32(kind, 4096, sink.data_ptr(), sink.numel(), ctypes.byref(ops),
+        call = lambda: _lib.check(PL.az_peak_int32(kind, 4096, sink.data_ptr(), sink.numel(), ctypes.byref(ops),
                                                   torch.cuda.current_stream().cuda_stream), "az_peak_int32")
         t = timed(call, iters=10)
         peaks[name] = {"warp_inst_per_s": sink.numel() / 32 * ops.value / t, "ms": t * 1e3}

@@ -1,0 +1,104 @@
+"""az_net_fcstack on random operands: checks it against float64 torch and times it inside a CUDA graph, for several
+cluster shapes, next to the three cuBLASLt GEMMs it replaces.
+
+    python tools/fcstack_probe.py [G] [iters]
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from alphazero_b200 import _lib
+from alphazero_b200.fused_net import pack_fcstack, pack_rows
+
+G = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+iters = int(sys.argv[2]) if len(sys.argv) > 2 else 400
+dev = "cuda"
+
+
+def time_graph(fn, reps=20):
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        fn()
+    torch.cuda.current_stream().wait_stream(side)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = max(1, iters // reps)
+    e0.record()
+    for _ in range(n):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return 1000 * e0.elapsed_time(e1) / (n * reps)
+
+
+def run(K1, N1, N2, n_out, shapes, G):
+    torch.manual_seed(K1 + n_out)
+    w1 = torch.randn(N1, K1, dtype=torch.float64) / K1 ** 0.5
+    w2 = torch.randn(N2, N1, dtype=torch.float64) / N1 ** 0.5
+    wh = torch.randn(n_out, N2, dtype=torch.float64) / N2 ** 0.5
+    b1, b2, bh = (torch.randn(n, dtype=torch.float64) * 0.1 for n in (N1, N2, n_out))
+    x = torch.randn(G, K1).to(torch.bfloat16)
+    bf = lambda t: t.float().to(torch.bfloat16)
+    xd = x.to(dev)
+    # reference: float64 products of the bf16-rounded operands, bf16 rounding of h1 / h2 like the kernel's epilogues
+    h1 = bf(torch.relu(xd.double() @ bf(w1).to(dev).double().t() + b1.float().double().to(dev)))
+    h2 = bf(torch.relu(h1.double() @ bf(w2).to(dev).double().t() + b2.float().double().to(dev)))
+    want = h2.double() @ bf(wh).to(dev).double().t() + bh.float().double().to(dev)
+    ld = ((n_out + 7) // 8) * 8
+    stream = torch.cuda.current_stream().cuda_stream
+    print(f"--- {K1} -> {N1} -> {N2} -> {n_out}, G = {G}")
+    for RT, NS in shapes:
+        blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+        blob = blob.to(dev)
+        tiles = -(-((G + 127) // 128) // RT) * RT
+        xp = torch.zeros(tiles * 128, K1, dtype=torch.bfloat16)
+        xp[:G] = x
+        xp = pack_rows(xp, plan["kch"][0]).to(dev)
+        s1 = torch.zeros(tiles * 128 * N1, dtype=torch.bfloat16, device=dev)
+        s2 = torch.zeros(tiles * 128 * N2, dtype=torch.bfloat16, device=dev)
+        logits = torch.full((G, ld), -77.0, dtype=torch.bfloat16, device=dev)
+
+        def call():
+            _lib.check(_lib.lib().az_net_fcstack(xp.data_ptr(), blob.data_ptr(), s1.data_ptr(), s2.data_ptr(),
+                                                 logits.data_ptr(), ld, n_out, G, K1, N1, N2, RT, NS, stream), "az_net_fcstack")
+        call()
+        torch.cuda.synchronize()
+        err = (logits[:, :n_out].double() - want).abs().max().item()
+        pad_ok = bool((logits[:, n_out:] == -77.0).all().item())
+        scale = want.abs().max().item()
+        us = time_graph(call)
+        flops = 2.0 * G * (K1 * N1 + N1 * N2 + N2 * n_out)
+        print(f"RT={RT} NS={NS}: max |err| {err:.4f} (logit scale {scale:.2f}, bf16 ulp {scale * 2 ** -8:.4f}) pad untouched {pad_ok}"
+              f" | {us:7.2f} us in a graph = {flops / us / 1e6:7.1f} TFLOP/s")
+    # the library path it replaces
+    w1t, w2t, wht = (bf(w).t().contiguous().to(dev) for w in (w1, w2, torch.cat([wh, torch.zeros(ld - n_out, N2, dtype=torch.float64)])))
+    bb1, bb2, bbh = bf(b1).to(dev), bf(b2).to(dev), bf(torch.cat([bh, torch.zeros(ld - n_out, dtype=torch.float64)])).to(dev)
+    o1 = torch.empty(G, N1, dtype=torch.bfloat16, device=dev); o2 = torch.empty(G, N2, dtype=torch.bfloat16, device=dev)
+    o3 = torch.empty(G, ld, dtype=torch.bfloat16, device=dev)
+
+    def lib3():
+        torch._addmm_activation(bb1, xd, w1t, out=o1)
+        torch._addmm_activation(bb2, o1, w2t, out=o2)
+        torch.addmm(bbh, o2, wht, out=o3)
+    with torch.no_grad():
+        us = time_graph(lib3)
+    print(f"cuBLASLt fc1 + fc2 + heads: {us:7.2f} us in a graph")
+
+
+if __name__ == "__main__":
+    which = os.environ.get("FCSTACK_PROBE", "all")
+    if which in ("all", "othello8"):
+        run(512, 1024, 512, 66, [(2, 4), (1, 4), (1, 8)], G)
+    if which in ("all", "small"):
+        run(512, 1024, 512, 66, [(2, 4), (1, 4)], 300)
+        run(128, 1024, 512, 38, [(2, 4), (1, 8)], 1000)
+        run(192, 64, 32, 8, [(1, 1), (2, 1)], 2048)

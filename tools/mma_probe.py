@@ -4,7 +4,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from alphazero_b200 import _lib
 
-L = _lib.lib()
+from tools.probes import build as _probes
+L = _probes.lib()
 cyc = torch.zeros(148, dtype=torch.int64, device="cuda")
 
 

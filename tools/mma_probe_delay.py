@@ -2,7 +2,8 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from alphazero_b200 import _lib
-L = _lib.lib()
+from tools.probes import build as _probes
+L = _probes.lib()
 cyc = torch.zeros(148, dtype=torch.int64, device="cuda")
 def run(m, n, ks, regions, flags):
     reps = 768 // ks

@@ -6,7 +6,8 @@
 #include <stdint.h>
 
 #include "../../include/az_b200.h"
-#include "common.cuh"
+#include "../../alphazero_b200/csrc/common.cuh"
+#include "az_probes.h"
 
 namespace probe {
 

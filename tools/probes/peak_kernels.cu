@@ -7,7 +7,8 @@
 #include <stdint.h>
 
 #include "../../include/az_b200.h"
-#include "common.cuh"
+#include "../../alphazero_b200/csrc/common.cuh"
+#include "az_probes.h"
 
 template <int KIND>
 __global__ void __launch_bounds__(256) k_peak_int32(uint32_t* __restrict__ out, int iters, uint32_t b, uint32_t c) {
