@@ -35,6 +35,7 @@ class AzTree(ctypes.Structure):
         ("mode", ctypes.c_int32), ("tie_random", ctypes.c_int32), ("enc_dtype", ctypes.c_int32),
         ("dirichlet_alpha", ctypes.c_float), ("dirichlet_eps", ctypes.c_float), ("game", ctypes.c_int32),
         ("height", ctypes.c_int32), ("logits_ld", ctypes.c_int32), ("logits", c_void_p),
+        ("n_leaves", ctypes.c_int32), ("reserved", ctypes.c_int32),
     ]
 
 

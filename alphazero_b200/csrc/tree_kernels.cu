@@ -35,6 +35,8 @@ struct NodeRec {
     uint32_t N;
     uint32_t first_child;
     uint32_t meta;  // n_children | move << 8 | flags << 16
+    uint32_t vloss; // descents in flight through this node (throughput mode; always 0 in parity mode)
+    float W;        // float32 sum of the backed-up rewards (throughput mode)
     __device__ __forceinline__ int n_children() const { return (int)(meta & 0xffu); }
     __device__ __forceinline__ int move() const { return (int)((meta >> 8) & 0xffu); }
     __device__ __forceinline__ uint32_t flags() const { return (meta >> 16) & 0xffu; }
@@ -49,6 +51,8 @@ __device__ __forceinline__ NodeRec az_load_node(const az_node* p) {
     r.N = a.w;
     r.first_child = b.x;
     r.meta = b.y;
+    r.vloss = b.z;
+    r.W = __uint_as_float(b.w);
     return r;
 }
 
@@ -585,6 +589,216 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tre
     if (do_select && sims_before + (backed_up ? 1u : 0u) < (uint32_t)n_sim) az_select<GAME, MODE>(t, d, nodes, g, lane, root);
 }
 
+// ------------------------------------------------------------------------------------------------ throughput mode
+//
+// L = az_tree.n_leaves > 1 leaves in flight per game and step (an EXTENSION: the reference evaluates one leaf at a time,
+// mcts.py:254-269; with L = 1 this kernel is the reference's order and bit-identical to k_tree_step).  One warp still
+// owns a game and makes its L descents one after the other -- descent l must see the virtual losses of descents < l,
+// so they are a dependent chain anyway -- which keeps the search deterministic; what the mode buys is a leaf batch of
+// G*L positions for the network.  Per node two more words (the spare 8 bytes of az_node):
+//   vloss  descents in flight through the node: added along the path when a descent ends, removed by its backup.  A child
+//          with v > 0 is scored as if it had v more visits that all lost: Q' = (W - v)/(N + v), N' = N + v; its parent's
+//          visit count in the exploration term likewise.  A child with v == 0 is scored with the reference's float64
+//          running mean exactly as in parity mode;
+//   W      float32 sum of the rewards backed up through the node (the Q of the virtual-loss formula above).
+// vloss, N and W are updated with atomics (red.global): today one warp owns a game, so they are uncontended, but the
+// counters stay correct if the descents of a game are ever spread over warps.
+// Leaf slot of (game g, descent l) in every per-leaf array: l*G + g, so the evaluator sees one flat batch of G*L rows.
+// Two descents of one step can meet at the same not-yet-evaluated node (forced lines: a single child): the later one is
+// dropped (no virtual loss was added yet, nothing to undo) and the game simply backs up fewer leaves that step; the host
+// runs steps until every game has its n_sim simulations.
+
+__device__ __forceinline__ void az_backup_multi(const az_tree& t, az_node* nodes, int lane, int player_to_play,
+                                                double outcome, int len, const uint32_t* path) {
+    double reward;
+    if (fabs(outcome) < 1e-4) reward = 0.0;
+    else reward = ((double)player_to_play * outcome > 0.0) ? -fabs(outcome) : fabs(outcome);
+#pragma unroll 1
+    for (int j = lane; j < len; j += 32) {
+        az_node* nd = &nodes[path[j]];
+        const uint4 a = reinterpret_cast<const uint4*>(nd)[0];
+        const double Q = __hiloint2double((int)a.y, (int)a.x);
+        const uint32_t N = a.w;
+        const double r = ((len - 1 - j) & 1) ? -reward : reward;
+        nd->Q = __ddiv_rn(__dadd_rn(__dmul_rn((double)N, Q), r), (double)(N + 1u));      // mcts.py:220
+        atomicAdd(&nd->N, 1u);
+        atomicAdd(&nd->W, (float)r);
+        atomicSub(&nd->vloss, 1u);
+    }
+    __syncwarp();
+}
+
+// One descent (mcts.py:226-248 up to the evaluation) under the virtual losses of the descents already in flight.
+// Returns 1 when a leaf was written to slot `s`, 0 when the descent was dropped; *only_one is set when no further descent
+// may start this step (the root itself is being evaluated).
+template <int GAME>
+__device__ __forceinline__ int az_select_multi(const az_tree& t, const az_dims& d, az_node* nodes, int g, int lane, int s,
+                                               const RootRegs& root, uint32_t& event, bool* only_one) {
+    using W = az_warp_rules<GAME>;
+    uint64_t own = root.own, opp = root.opp;
+    int player = root.player;
+    uint32_t* path = t.path + (size_t)s * t.max_depth;
+    NodeRec cur = az_load_node(&nodes[0]);
+    uint32_t cur_idx = 0u;
+    int kind = AZ_LEAF_IDLE;
+    int len = 1;
+    if (lane == 0) path[0] = 0u;
+    *only_one = false;
+    if (!(cur.flags() & AZ_NODE_EVAL)) {
+        kind = AZ_LEAF_PRIME;                                   // mcts.py:231-233
+        len = 0;
+        *only_one = true;
+    } else {
+        if (t.dirichlet_alpha > 0.f && t.dirichlet_eps > 0.f && (cur.flags() & AZ_NODE_EXPANDED) &&
+            !(cur.flags() & AZ_NODE_NOISED)) {
+            az_root_noise(nodes, cur.first_child, cur.n_children(), t.dirichlet_alpha, t.dirichlet_eps, t.seed, g, lane,
+                          event);                               // mcts.py:235-240
+            event += 1u;
+        }
+        while (true) {
+            if (!(cur.flags() & AZ_NODE_EXPANDED)) {
+                bool terminal;
+                W::legal(own, opp, d, lane, &terminal);
+                if (terminal) { kind = az_terminal_kind<GAME>(own, opp, player, d); break; }     // mcts.py:146-147
+                if (!(cur.flags() & AZ_NODE_EVAL)) { kind = cur.vloss ? AZ_LEAF_IDLE : AZ_LEAF_NN; break; }   // overflow fallback
+                if (lane == 0) {
+                    uint32_t* w = reinterpret_cast<uint32_t*>(&nodes[cur_idx]);
+                    w[5] |= (AZ_NODE_EXPANDED << 16);           // mcts.py:155-160
+                }
+            }
+            // PUCT over the children, lane j <-> child j (and j + 32)
+            const int k = cur.n_children();
+            const double sqrtN = __dsqrt_rn((double)(cur.N + cur.vloss));
+            NodeRec mine;
+            mine.Q = 0.0; mine.P = 0.f; mine.N = 0u; mine.first_child = 0u; mine.meta = 0u; mine.vloss = 0u; mine.W = 0.f;
+            double best_score = -INFINITY;
+            int best_j = -1;
+#pragma unroll 1
+            for (int j = lane; j < k; j += 32) {
+                const NodeRec c = az_load_node(&nodes[cur.first_child + j]);
+                double sc;
+                if (c.vloss == 0u) {
+                    sc = __dadd_rn(c.Q, __ddiv_rn(__dmul_rn((double)c.P, sqrtN), (double)(1u + c.N)));     // mcts.py:44-46
+                } else {
+                    const double n_eff = (double)(c.N + c.vloss);
+                    const double q_eff = __ddiv_rn((double)c.W - (double)c.vloss, n_eff);
+                    sc = __dadd_rn(q_eff, __ddiv_rn(__dmul_rn((double)c.P, sqrtN), 1.0 + n_eff));
+                }
+                if (best_j < 0 || sc > best_score) { best_score = sc; best_j = j; mine = c; }
+            }
+            int src;
+            const int win = az_warp_argmax(best_score, best_j, best_j >= 0, t.tie_random != 0, t.seed, (uint32_t)g, event, &src);
+            event += 1u;
+            NodeRec child = az_bcast_node(mine, src);
+            child.vloss = __shfl_sync(AZ_FULL, mine.vloss, src);
+            const uint32_t child_idx = cur.first_child + (uint32_t)win;
+            W::apply(own, opp, child.move(), d, lane);
+            player = -player;
+            if (len >= t.max_depth) {
+                if (lane == 0) t.status[g] |= AZ_STATUS_DEPTH;
+                kind = AZ_LEAF_NN;
+                break;
+            }
+            if (lane == 0) path[len] = child_idx;
+            ++len;
+            cur = child;
+            cur_idx = child_idx;
+            if (cur.N == 0u) {                                  // mcts.py:143-144: first visit = the leaf
+                bool terminal;
+                W::legal(own, opp, d, lane, &terminal);
+                if (terminal) kind = az_terminal_kind<GAME>(own, opp, player, d);
+                else kind = cur.vloss ? AZ_LEAF_IDLE : AZ_LEAF_NN;     // already being evaluated this step: drop
+                break;
+            }
+        }
+    }
+    if (kind == AZ_LEAF_IDLE) return 0;
+    __syncwarp();                                               // path[] written by lane 0 is read by all lanes
+    if (kind != AZ_LEAF_PRIME)
+        for (int j = lane; j < len; j += 32) atomicAdd(&nodes[path[j]].vloss, 1u);
+    if (lane == 0) {
+        t.leaf_node[s] = cur_idx;
+        t.leaf_kind[s] = (uint8_t)kind;
+        t.leaf_own[s] = own;
+        t.leaf_opp[s] = opp;
+        t.leaf_player[s] = (int8_t)player;
+        t.path_len[s] = (uint32_t)len;
+    }
+    if (t.enc) az_encode_leaf(t.enc, t.enc_dtype, d.rows, d.cols, s, lane, own, opp);
+    __syncwarp();
+    return 1;
+}
+
+template <int GAME>
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_step_multi(az_tree t, int n_sim, int do_finish, int do_select) {
+    az_pdl_wait();
+    az_pdl_trigger();
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    const az_dims d = az_rules<GAME>::dims(t.n, t.height);
+    const int L = t.n_leaves, A = az_rules<GAME>::action_size(d);
+    az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
+    uint32_t sims = t.sims_done[g];
+    if (do_finish) {
+#pragma unroll 1
+        for (int l = 0; l < L; ++l) {
+            const int s = l * t.G + g;
+            const int kind = t.leaf_kind[s];
+            if (kind == AZ_LEAF_IDLE) continue;
+            const uint32_t leaf = t.leaf_node[s];
+            const int leaf_player = t.leaf_player[s];
+            const int len = (int)t.path_len[s];
+            float value = 0.f;
+            if (kind == AZ_LEAF_NN || kind == AZ_LEAF_PRIME) {
+                AllocPre pre;
+                pre.base = t.n_alloc[g];
+                pre.meta = reinterpret_cast<const uint32_t*>(&nodes[leaf])[5];
+                pre.row[0] = pre.row[1] = pre.row[2] = 0.f;
+                if (t.logits) {
+                    const __nv_bfloat16* row = reinterpret_cast<const __nv_bfloat16*>(t.logits) + (size_t)s * t.logits_ld;
+                    float x[3];
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) x[i] = (lane + 32 * i) < A ? __bfloat162float(row[lane + 32 * i]) : 0.f;
+                    const __nv_bfloat16 v = row[A];
+                    az_heads_softmax(x, lane, A, pre.row);
+                    value = az_heads_value(v);
+                } else {
+                    const float* pr = t.probs + (size_t)s * A;
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) if (lane + 32 * i < A) pre.row[i] = pr[lane + 32 * i];
+                    value = t.value[s];
+                }
+                int k;
+                az_alloc_children<GAME>(t, d, nodes, g, lane, leaf, t.leaf_own[s], t.leaf_opp[s], true, 0u, &k, &pre);
+            }
+            if (kind != AZ_LEAF_PRIME) {
+                double outcome;
+                if (kind == AZ_LEAF_NN) outcome = (double)((float)leaf_player * value);        // base.py:366
+                else outcome = kind == AZ_LEAF_DRAW ? 0.0 : (kind == AZ_LEAF_BLACK ? 1.0 : -1.0);
+                az_backup_multi(t, nodes, lane, leaf_player, outcome, len, t.path + (size_t)s * t.max_depth);
+                sims += 1u;
+            }
+            if (lane == 0) t.leaf_kind[s] = AZ_LEAF_IDLE;
+            __syncwarp();
+        }
+        if (lane == 0) t.sims_done[g] = sims;
+    }
+    if (do_select) {
+        const RootRegs root = az_load_root(t, g);
+        uint32_t event = root.event;
+        uint32_t in_flight = 0u;
+#pragma unroll 1
+        for (int l = 0; l < L; ++l) {
+            if (sims + in_flight >= (uint32_t)n_sim) break;
+            bool only_one;
+            in_flight += (uint32_t)az_select_multi<GAME>(t, d, nodes, g, lane, l * t.G + g, root, event, &only_one);
+            if (only_one) break;
+        }
+        if (lane == 0) t.rng_ctr[g] = event;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ misc kernels
 
 __global__ void __launch_bounds__(256) k_tree_reset(az_tree t, const uint8_t* __restrict__ mask) {
@@ -593,7 +807,7 @@ __global__ void __launch_bounds__(256) k_tree_reset(az_tree t, const uint8_t* __
     az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
     az_store_node(&nodes[0], 0.0, 0.f, 0u, 0u, az_make_meta(0, 0xff, 0u));
     t.n_alloc[g] = 1u;
-    t.leaf_kind[g] = AZ_LEAF_IDLE;
+    for (int l = 0; l < max(1, t.n_leaves); ++l) t.leaf_kind[l * t.G + g] = AZ_LEAF_IDLE;
     t.sims_done[g] = 0u;
     t.status[g] = 0u;
     t.path_len[g] = 0u;
@@ -852,6 +1066,7 @@ static int az_check_tree(const az_tree* t) {
     if (t->mode != AZ_MODE_ROLLOUT && t->mode != AZ_MODE_NEURAL) return AZ_ERR_ARG;
     if (t->mode == AZ_MODE_NEURAL && (!t->probs || !t->value)) return AZ_ERR_ARG;
     if (t->mode == AZ_MODE_ROLLOUT && !t->value) return AZ_ERR_ARG;
+    if (t->n_leaves < 0 || t->n_leaves > 8 || (t->n_leaves > 1 && t->mode != AZ_MODE_NEURAL)) return AZ_ERR_ARG;
     if (t->logits) {                                            // raw network rows: A policy logits + the value logit
         const int A = t->game == AZ_GAME_OTHELLO ? t->n * t->n + 1 : (t->game == AZ_GAME_CONNECT4 ? t->n : 9);
         if (t->mode != AZ_MODE_NEURAL || t->logits_ld < A + 1) return AZ_ERR_ARG;
@@ -885,6 +1100,15 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
     cudaError_t e;
 #define AZ_STEP(GAME, MODE) az_launch_pdl(k_tree_step<GAME, MODE>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select)
     const bool neural = t->mode == AZ_MODE_NEURAL;
+    if (t->n_leaves >= 1 && neural) {          // throughput mode (n_leaves = 0: the parity kernel)
+#define AZ_STEP_MULTI(GAME) az_launch_pdl(k_tree_step_multi<GAME>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select)
+        e = t->game == AZ_GAME_OTHELLO ? AZ_STEP_MULTI(AZ_GAME_OTHELLO)
+            : (t->game == AZ_GAME_CONNECT4 ? AZ_STEP_MULTI(AZ_GAME_CONNECT4) : AZ_STEP_MULTI(AZ_GAME_TICTACTOE));
+#undef AZ_STEP_MULTI
+        if (e != cudaSuccess) return az_set_cuda_error(e, "k_tree_step_multi");
+        AZ_CHECK_LAUNCH("k_tree_step_multi");
+        return AZ_OK;
+    }
     if (t->game == AZ_GAME_OTHELLO)
         e = neural ? AZ_STEP(AZ_GAME_OTHELLO, AZ_MODE_NEURAL) : AZ_STEP(AZ_GAME_OTHELLO, AZ_MODE_ROLLOUT);
     else if (t->game == AZ_GAME_CONNECT4)

@@ -105,6 +105,11 @@ class TreeBatch:
         self.set_dirichlet(dirichlet_alpha, dirichlet_epsilon)
         self.reset_roots()
 
+    def __getstate__(self):
+        raise TypeError("TreeBatch owns device memory (node pools, CUDA graphs) and cannot be pickled; send the "
+                        "position (root_own / root_opp / root_player) and build a TreeBatch in the receiving process. "
+                        "MCT / MCTSPlayer / AlphaZeroPlayer pickle without their device tree (mcts.MCT.__getstate__).")
+
     # ------------------------------------------------------------------ configuration
     def set_encoding(self, on: bool) -> None:
         """Switches the float network encoding written by the select kernel on/off (evaluators that read the leaf

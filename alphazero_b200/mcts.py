@@ -74,6 +74,30 @@ class MCT:
         self._pending = []      # change_root calls made before the first search (no device tree yet)
         self._n = None
         self._spec = None
+        self._nn_stamp = None   # weights fingerprint the evaluator's bf16 snapshot was taken at
+
+    # ---- pickling (the reference ships players / MCTs into a multiprocessing.Pool, arena.py:211-234) -------
+    def __getstate__(self) -> dict:
+        """The device tree (node pools, CUDA graphs) does not travel: a pickled MCT keeps its configuration and its
+        network and starts from a fresh root on the other side, like a player after reset() (players.py:151-152).
+        Arena workers reset their players before every game (arena.py:56-58), so nothing is lost there."""
+        state = dict(self.__dict__)
+        state["_tree"] = state["_evaluator"] = state["_nn_stamp"] = None
+        state["_pending"] = []
+        return state
+
+    def __setstate__(self, state: dict) -> None:
+        self.__dict__.update(state)
+
+    @staticmethod
+    def _weights_stamp(nn):
+        """Changes whenever a parameter / buffer of `nn` is written in place (load_state_dict, optimizer.step()): the
+        reference evaluates the live module (base.py:357-367), so the snapshot must follow it."""
+        if nn is None:
+            return None
+        if not hasattr(nn, "parameters"):      # a test double that supplies its own evaluator
+            return (id(nn), 0)
+        return (id(nn), sum(int(t._version) for t in list(nn.parameters()) + list(nn.buffers())))
 
     # ---- attributes the reference's callers set directly (players.py:213-215, trainer.py:387) -------------
     @property
@@ -86,6 +110,7 @@ class MCT:
             raise ValueError(f"Trying to set a neural network for the MCT but the evaluation method is {self.eval_method}")
         self._nn = nn
         self._evaluator = None          # re-snapshot the weights / re-capture the CUDA graph on the next search
+        self._nn_stamp = None
 
     @property
     def dirichlet_alpha(self):
@@ -135,6 +160,11 @@ class MCT:
             else:
                 t.set_encoding(True)
                 self._evaluator = make_evaluator(self._nn, t)     # switches the encoding off when it reads bitboards
+            self._nn_stamp = self._weights_stamp(self._nn)
+        elif self.eval_method == TreeEval.NEURAL and self._nn_stamp != self._weights_stamp(self._nn):
+            if hasattr(self._evaluator, "refresh"):               # weights changed in place since the snapshot
+                self._evaluator.refresh(self._nn)
+            self._nn_stamp = self._weights_stamp(self._nn)
 
     def _adopt(self, old: "MCT") -> None:
         """Re-uses the device pools / CUDA graph of a discarded MCT of the same kind (player.reset() builds a new MCT
@@ -144,7 +174,7 @@ class MCT:
         self._tree, self._n, self._spec = old._tree, old._n, old._spec
         self._tree.set_dirichlet(self._dirichlet_alpha, self._dirichlet_epsilon)
         if old._nn is self._nn:
-            self._evaluator = old._evaluator
+            self._evaluator, self._nn_stamp = old._evaluator, old._nn_stamp     # (_ensure_tree refreshes a stale one)
         self._tree.reset_trees()
         self._tree.root_own.fill_(-1)      # no position yet: the first search uploads the board
 

@@ -142,7 +142,8 @@ typedef struct az_node {
     uint8_t move;         /* action that led here (Othello: 0..63, 64 = pass; Connect4: column) */
     uint8_t flags;        /* AZ_NODE_* */
     uint8_t reserved0;
-    uint32_t reserved1[2];
+    uint32_t vloss;       /* throughput mode (az_tree.n_leaves >= 1): descents in flight through this node */
+    float W;              /* throughput mode: float32 sum of the backed-up rewards */
 } az_node;
 
 #define AZ_NODE_EVAL 1u     /* children allocated with priors (reference: node._children_probs is not None) */
@@ -204,6 +205,11 @@ typedef struct az_tree {
                               logit at A).  When not NULL az_tree_step takes priors = softmax(logits[0 .. A)) and
                               value = tanh(logits[A]) -- the arithmetic of az_net_heads, same bits -- from here and
                               ignores probs / value: the evaluator then needs no output-transform launch. */
+    int32_t n_leaves;      /* 0: parity mode, the reference's one leaf per game per step (mcts.py:254-269).
+                              L >= 1: throughput mode (neural only) -- up to L leaves in flight per game and step under
+                              virtual loss; every per-leaf array (leaf_*, path, path_len, enc, probs, value, logits) then
+                              has G*L entries, slot l*G + g = descent l of game g.  L = 1 is bit-identical to parity. */
+    int32_t reserved;
 } az_tree;
 
 /* Fresh trees (reference: MCT() / player.reset()) for the games with mask[g] != 0 (mask NULL = all):

@@ -203,3 +203,45 @@ def test_trainer_self_play_samples_and_augmentation():
     tr.update_network(OthelloNet(n=6))       # network swap refreshes the device snapshot
     tr.self_play(1, seed=5)
     assert len(tr.memory) > 0
+
+
+def test_players_pickle_without_their_device_tree():
+    """The reference ships boards / players into a multiprocessing.Pool (arena.py:211-234): GPU-backed players must
+    pickle (the device tree stays behind, the copy starts from a fresh root) and a TreeBatch must refuse loudly."""
+    import pickle
+    from alphazero_b200.engine import TreeBatch
+    from alphazero_b200.games.othello import OthelloBoard, OthelloNet
+    from alphazero_b200.players import AlphaZeroPlayer, MCTSPlayer
+    board = OthelloBoard(n=6)
+    torch.manual_seed(0)
+    for player in (MCTSPlayer(n_sim=20), AlphaZeroPlayer(n_sim=20, nn=OthelloNet(n=6))):
+        move, _, counts, _ = player.get_move(board)
+        assert player.mct._tree is not None and sum(counts.values()) == 20
+        twin = pickle.loads(pickle.dumps(player))
+        assert twin.mct._tree is None and twin.n_sim == 20
+        move2, _, counts2, _ = twin.get_move(board)
+        assert move2 in board.get_moves() and sum(counts2.values()) == 20
+    b2 = pickle.loads(pickle.dumps(board))
+    assert (b2.grid == board.grid).all() and b2.player == board.player
+    with pytest.raises(TypeError, match="cannot be pickled"):
+        pickle.dumps(TreeBatch(2, n=6, mode="rollout", capacity=64))
+
+
+def test_mct_follows_in_place_weight_updates():
+    """The reference MCT evaluates the live module (base.py:357-367): load_state_dict / optimizer steps on the same
+    object must reach the evaluator's bf16 snapshot without going through the nn setter."""
+    from alphazero_b200.games.othello import OthelloBoard, OthelloNet
+    from alphazero_b200.players import AlphaZeroPlayer
+    torch.manual_seed(1)
+    net, other = OthelloNet(n=6), OthelloNet(n=6)
+    with torch.no_grad():
+        other.fc_probs.weight.mul_(6.0)
+    board = OthelloBoard(n=6)
+    player = AlphaZeroPlayer(n_sim=4, nn=net)
+    _, _, _, prior_a = player.get_move(board)
+    player.reset()
+    net.load_state_dict(other.state_dict())               # same object, new weights
+    _, _, _, prior_b = player.get_move(board)
+    fresh = AlphaZeroPlayer(n_sim=4, nn=other)
+    _, _, _, prior_c = fresh.get_move(board)
+    assert prior_b == prior_c and prior_a != prior_b

@@ -54,7 +54,6 @@ def run(K1, N1, N2, n_out, shapes, G):
     h2 = bf(torch.relu(h1.double() @ bf(w2).to(dev).double().t() + b2.float().double().to(dev)))
     want = h2.double() @ bf(wh).to(dev).double().t() + bh.float().double().to(dev)
     ld = ((n_out + 7) // 8) * 8
-    stream = torch.cuda.current_stream().cuda_stream
     print(f"--- {K1} -> {N1} -> {N2} -> {n_out}, G = {G}")
     for RT, NS in shapes:
         blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
@@ -69,7 +68,8 @@ def run(K1, N1, N2, n_out, shapes, G):
 
         def call():
             _lib.check(_lib.lib().az_net_fcstack(xp.data_ptr(), blob.data_ptr(), s1.data_ptr(), s2.data_ptr(),
-                                                 logits.data_ptr(), ld, n_out, G, K1, N1, N2, RT, NS, stream), "az_net_fcstack")
+                                                 logits.data_ptr(), ld, n_out, G, K1, N1, N2, RT, NS,
+                                                 torch.cuda.current_stream().cuda_stream), "az_net_fcstack")
         call()
         torch.cuda.synchronize()
         err = (logits[:, :n_out].double() - want).abs().max().item()

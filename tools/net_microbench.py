@@ -14,7 +14,8 @@ torch.manual_seed(0)
 net = OthelloNet(n=8)
 tree = TreeBatch(G, n=8, mode="neural", capacity=64)
 tree.leaf_own.random_(0, 2**62); tree.leaf_opp.copy_(~tree.leaf_own & torch.randint(0, 2**62, (G,), device="cuda"))
-ev = FusedOthelloEvaluator(net, tree)
+ev = FusedOthelloEvaluator(net, tree, heads="library")      # the first version: trunk + three cuBLASLt GEMMs
+ev_stack = FusedOthelloEvaluator(net, tree)                 # the product: trunk + az_net_fcstack
 
 
 def timeit(fn, name):
@@ -63,6 +64,19 @@ timeit_graph(lambda: torch._addmm_activation(ev.b2, ev.h1, ev.w2t, out=ev.h2), "
 timeit_graph(lambda: torch.addmm(ev.bh, ev.h2, ev.wht, out=ev.logits), "heads gemm (cuBLASLt)")
 timeit_graph(lambda: _lib.check(_lib.lib().az_net_heads(ev.logits.data_ptr(), ev.ld, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads softmax/tanh")
 timeit_graph(lambda: _lib.check(_lib.lib().az_net_headgemm(ev.h2.data_ptr(), ev.h2_features, ev.head_blob.data_ptr(), ev.NH, ev.A, G, tree.probs.data_ptr(), tree.value.data_ptr(), torch.cuda.current_stream().cuda_stream)), "heads fused (tcgen05)")
+def _fcstack():
+    e = ev_stack
+    _lib.check(_lib.lib().az_net_fcstack(e.features.data_ptr(), e.stack_blob.data_ptr(), e.h1.data_ptr(), e.h2.data_ptr(),
+                                         e.logits.data_ptr(), e.ld, e.A + 1, G, e.K1, e.N1, e.N2, e.RT, e.NS,
+                                         torch.cuda.current_stream().cuda_stream), "az_net_fcstack")
+
+
+timeit_graph(_fcstack, f"fc1+fc2+heads az_net_fcstack RT={ev_stack.RT} NS={ev_stack.NS}")
+timeit_graph(ev_stack.trunk, "trunk, packed features")
+timeit_graph(ev.trunk, "trunk, row-major features")
+timeit_graph(ev_stack.enqueue, "trunk + fcstack (what the search graph holds)")
+timeit_graph(ev.enqueue, "trunk + 3 cuBLASLt GEMMs (first version)")
+timeit(ev_stack, "whole forward (graph, stack)")
 timeit(ev, f"whole forward (graph, {ev.heads})")
 ev_fused = FusedOthelloEvaluator(net, tree, heads="fused")
 timeit(ev_fused, "whole forward (graph, fused)")
@@ -72,7 +86,7 @@ timeit(lambda: tree.step(200, True, True), "tree step (idle leaves)")
 dbg = torch.zeros(148 * 16, dtype=torch.int64, device="cuda")
 for _ in range(3):      # back to back, like the search loop: the last launch is reported
     _lib.check(_lib.lib().az_net_trunk(tree.leaf_own.data_ptr(), tree.leaf_opp.data_ptr(), 8, 8, G, ev.wblob.data_ptr(),
-                                       ev.features.data_ptr(), dbg.data_ptr(), 100, torch.cuda.current_stream().cuda_stream), "trunk timing")
+                                       ev.features.data_ptr(), 0, dbg.data_ptr(), 100, torch.cuda.current_stream().cuda_stream), "trunk timing")
 torch.cuda.synchronize()
 d = dbg.reshape(148, 16).double()
 names = ["mma: wait ready", "mma: wait empty", "mma: issue+commit", "mma: loop total", "mma: wait im2col", "epi team0: wait full",
