@@ -39,8 +39,9 @@ class _BatchedSide:
             self.n_sim = player.n_sim
             self.tree = TreeBatch(G, n=spec, mode="neural", n_sim_hint=self.n_sim, seed=seed, tie_random=True,
                                   dirichlet_alpha=player.mct.dirichlet_alpha,
-                                  dirichlet_epsilon=player.mct.dirichlet_epsilon, enc_dtype=torch.bfloat16)
-            self.evaluator = make_evaluator(nn, self.tree)
+                                  dirichlet_epsilon=player.mct.dirichlet_epsilon, enc_dtype=torch.bfloat16,
+                                  leaves=getattr(player, "leaves", None))
+            self.evaluator = make_evaluator(nn, self.tree.leaf_view)
         elif isinstance(player, MCTSPlayer):
             self.n_sim = player.n_sim
             self.tree = TreeBatch(G, n=spec, mode="rollout", n_sim_hint=self.n_sim, seed=seed, tie_random=True)

@@ -40,7 +40,10 @@
 #define FS_EPI_WARPS 8                        // warps 0-7: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = block parity)
 #define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 8: bulk copies (one lane)
 #define FS_MMA_WARP (FS_EPI_WARPS + 1)        // warp 9: tcgen05.mma issue (one elected lane), TMEM allocation
-#define FS_THREADS ((FS_EPI_WARPS + 2) * 32)
+#define FS_LOADER_WARP0 (FS_EPI_WARPS + 2)     // warps 10-13: cp.async loaders (the LSU path beside the bulk-copy unit)
+#define FS_LOADER_WARPS 4
+#define FS_LOADERS (FS_LOADER_WARPS * 32)
+#define FS_THREADS ((FS_EPI_WARPS + 2 + FS_LOADER_WARPS) * 32)
 #define FS_MAX_CHUNKS 16                      // K chunks per layer
 #define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
 #define FB_FULL 0
@@ -65,6 +68,12 @@ struct FcStackParams {
     int ld, n_out;             // row pitch of logits; real outputs (action_size + 1)
     int K[3], Nc[3], kch[3];   // per layer: K, output columns per CTA, K chunk (16 / 32 / 64)
     int RT, NS, hpc;           // cluster shape; real head outputs per column slice
+    int mc_a, mc_b;            // 1: the A / B block of a stage is fetched once per cluster and multicast; 0: every CTA
+                               //    fetches its own copy (the bytes INTO an SM are the same either way)
+    int lsu_a, lsu_b_planes;   // stage bytes fetched by the loader warps with cp.async instead of the bulk-copy unit:
+                               //    the A block (0 / 1) and the last lsu_b_planes of the B block's K planes.  Measured:
+                               //    one SM's bulk-copy unit streams ~33 B/clk, far below what the MMAs consume; the LSU
+                               //    path runs beside it (profiles/r2_fcstack_experiments.txt)
     uint32_t w_off[3], b_off[3];
 };
 
@@ -174,8 +183,9 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const uint32_t a_mask = ((1u << NS) - 1u) << (r * NS);    // the CTAs of row tile r
     uint32_t b_mask = 0u;                                     // the CTAs of column slice c
     for (int rr = 0; rr < RT; ++rr) b_mask |= 1u << (rr * NS + c);
-    const uint32_t all_mask = a_mask | b_mask;
-    const bool mc_a = NS > 1, mc_b = RT > 1, mc_any = mc_a || mc_b;
+    const bool lsu_a = p.lsu_a != 0, use_lsu = lsu_a || p.lsu_b_planes > 0;
+    const bool mc_a = p.mc_a && NS > 1 && !lsu_a, mc_b = p.mc_b && RT > 1 && p.lsu_b_planes == 0, mc_any = mc_a || mc_b;
+    const uint32_t all_mask = (1u << rank) | (mc_a ? a_mask : 0u) | (mc_b ? b_mask : 0u);   // CTAs this one sends stage data to
 
     const uint32_t bars = smem_u32(smem + FS_SM_BARS);
     const uint32_t bar_full0 = bars + 8 * FB_FULL, bar_empty0 = bars + 8 * FB_EMPTY, bar_acc0 = bars + 8 * FB_ACC;
@@ -187,7 +197,10 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
 
     // ---- setup: barriers, biases of this column slice (weights: not produced by the preceding kernel), TMEM
     if (tid == 0) {
-        for (int s = 0; s < FS_STAGES; ++s) { mbar_init(bar_full0 + 8 * s, 1); mbar_init(bar_empty0 + 8 * s, __popc(all_mask)); }
+        for (int s = 0; s < FS_STAGES; ++s) {
+            mbar_init(bar_full0 + 8 * s, 1u + (use_lsu ? FS_LOADERS : 0u));
+            mbar_init(bar_empty0 + 8 * s, __popc(all_mask));
+        }
         for (int L = 0; L < 3; ++L) mbar_init(bar_acc0 + 8 * L, 1);
         for (int i = 0; i < 2 * FS_MAX_CHUNKS; ++i) mbar_init(bar_ready0 + 8 * i, 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -217,28 +230,72 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
             for (int L = 0; L < 3; ++L) {
                 const int kch = p.kch[L], nch = p.K[L] / kch;
                 const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
-                const uint32_t a_part = a_bytes / (uint32_t)NS, b_part = b_bytes / (uint32_t)RT;
-                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + (size_t)c * a_part;
-                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + (size_t)r * b_part;
+                // the loader warps take the A block (lsu_a) and the tail of the B block; this thread the rest
+                const uint32_t a_bulk = lsu_a ? 0u : a_bytes;
+                const uint32_t b_bulk = b_bytes - (uint32_t)min(p.lsu_b_planes, kch >> 3) * (uint32_t)p.Nc[L] * 16u;
+                // with multicast this CTA fetches part c of the A block / part r of the B block for its whole group
+                const uint32_t a_part = mc_a ? a_bulk / (uint32_t)NS : a_bulk, b_part = mc_b ? b_bulk / (uint32_t)RT : b_bulk;
+                const uint32_t a_skip = mc_a ? (uint32_t)c * a_part : 0u, b_skip = mc_b ? (uint32_t)r * b_part : 0u;
+                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + a_skip;
+                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + b_skip;
                 const int bps = nch / NS;                     // blocks the epilogue of one CTA produced (L > 0)
                 for (int q = 0; q < nch; ++q, ++it) {
                     // L > 0: fetch in production order -- block j of every column slice, then block j + 1
                     const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
                     const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
                     fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
-                    if (L > 0) {
+                    if (L > 0 && a_bulk) {
                         fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
                         asm volatile("fence.proxy.async.global;" ::: "memory");
                     }
                     const uint32_t full = bar_full0 + 8 * s;
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
-                    fs_expect_tx(full, a_bytes + b_bytes);
-                    fs_bulk_copy(sa + (uint32_t)c * a_part, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
-                    fs_bulk_copy(sb + (uint32_t)r * b_part, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
+                    if (a_bulk + b_bulk) fs_expect_tx(full, a_bulk + b_bulk);
+                    else mbar_arrive(full);
+                    if (a_bulk) fs_bulk_copy(sa + a_skip, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
+                    if (b_bulk) fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
                 }
             }
         }
         __syncwarp();
+    } else if (warp >= FS_LOADER_WARP0) {
+        // ================================================================== loaders: the LSU half of every stage
+        // 16 bytes per cp.async, consecutive threads -> consecutive 16-byte pieces (the blocks are contiguous in global
+        // memory and in the stage).  A thread's copies of a stage arrive on the stage's full barrier when they complete
+        // (cp.async.mbarrier.arrive), followed by the thread's own arrival.
+        if (use_lsu) {
+            const int lt = tid - FS_LOADER_WARP0 * 32;
+            uint32_t it = 0;
+#pragma unroll
+            for (int L = 0; L < 3; ++L) {
+                const int kch = p.kch[L], nch = p.K[L] / kch;
+                const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
+                const uint32_t b_lsu = (uint32_t)min(p.lsu_b_planes, kch >> 3) * (uint32_t)p.Nc[L] * 16u;
+                const uint32_t b_head = b_bytes - b_lsu;      // bytes of the B block the bulk copy brings
+                const uint32_t a_pieces = lsu_a ? a_bytes >> 4 : 0u, pieces = a_pieces + (b_lsu >> 4);
+                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes;
+                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + b_head;
+                const int bps = nch / NS;
+                for (int q = 0; q < nch; ++q, ++it) {
+                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
+                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
+                    if (L > 0 && lsu_a) fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
+                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES + b_head;
+                    const uint8_t* ga = a_src + (size_t)kc * a_bytes;
+                    const uint8_t* gb = b_src + (size_t)kc * b_bytes;
+                    for (uint32_t i = (uint32_t)lt; i < pieces; i += FS_LOADERS) {
+                        const bool is_a = i < a_pieces;
+                        const uint32_t off = (is_a ? i : i - a_pieces) << 4;
+                        const uint32_t dst = (is_a ? sa : sb) + off;
+                        const uint8_t* src = (is_a ? ga : gb) + off;
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+                    }
+                    asm volatile("cp.async.mbarrier.arrive.shared::cta.b64 [%0];" ::"r"(bar_full0 + 8 * s) : "memory");
+                    mbar_arrive(bar_full0 + 8 * s);
+                }
+            }
+        }
     } else if (warp == FS_MMA_WARP) {
         // ================================================================== MMA issue
         uint32_t it = 0;
@@ -251,6 +308,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
             for (int q = 0; q < nch; ++q, ++it) {
                 const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
                 fs_mbar_wait(bar_full0 + 8 * s, ph);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // cp.async (generic proxy) -> tcgen05.mma
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 if (elect_one()) {
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
@@ -404,6 +462,14 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
         p.K[L] = pl.K[L]; p.Nc[L] = pl.Nc[L]; p.kch[L] = pl.kch[L]; p.w_off[L] = pl.w_off[L]; p.b_off[L] = pl.b_off[L];
     }
     p.RT = RT; p.NS = NS; p.hpc = pl.hpc;
+    static const int mc_flags = getenv("AZ_B200_FCSTACK_MC") ? atoi(getenv("AZ_B200_FCSTACK_MC")) : 0;   // bit 0: A, bit 1: B
+    p.mc_a = mc_flags & 1; p.mc_b = (mc_flags >> 1) & 1;
+    static int lsu_a = -1, lsu_b = -1;
+    if (lsu_a < 0) {
+        lsu_a = 1; lsu_b = 4;                                 // default split, see FcStackParams
+        if (const char* e = getenv("AZ_B200_FCSTACK_LSU")) sscanf(e, "%d,%d", &lsu_a, &lsu_b);
+    }
+    p.lsu_a = lsu_a; p.lsu_b_planes = lsu_b < 0 ? 0 : (lsu_b > 8 ? 8 : lsu_b);
     const int64_t tiles = (G + 127) / 128, clusters = (tiles + RT - 1) / RT;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(clusters * RT * NS)); cfg.blockDim = dim3(FS_THREADS);

@@ -194,6 +194,9 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     // launched with az_launch_pdl: everything above (barriers, TMEM, the weight copy in flight) may run beside the tail
     // of the tree step that selects this launch's leaves; nothing below may
     az_pdl_wait();
+    // the fc stack that follows (az_net_fcstack, also launched with az_launch_pdl) may start its prologue on every SM a
+    // CTA of this grid has left; it waits for the whole grid before it reads the features
+    az_pdl_trigger();
     const long long t_setup = timing ? clock64() : 0;
 
     if (warp >= MMA_WARP + NET_MMA_WARPS) {

@@ -33,11 +33,30 @@ def _evaluator_uid(evaluator) -> int:
     return uid
 
 
+class LeafView:
+    """What an evaluator sees of a throughput-mode TreeBatch: the flat batch of G * leaves leaf slots (slot l*G + g =
+    descent l of game g) with the attributes evaluators read from a tree."""
+
+    def __init__(self, tree: "TreeBatch"):
+        self.tree = tree
+        self.G = tree.n_slots
+        self.spec, self.n, self.A, self.device = tree.spec, tree.n, tree.A, tree.device
+        for name in ("leaf_own", "leaf_opp", "leaf_player", "leaf_kind", "enc", "probs", "value"):
+            setattr(self, name, getattr(tree, name))
+
+    def set_encoding(self, on: bool) -> None:
+        self.tree.set_encoding(on)
+
+
 class TreeBatch:
     def __init__(self, G: int, n=8, mode: str = "neural", capacity: int = None, n_sim_hint: int = 200,
                  device="cuda", seed: int = 0, tie_random: bool = True, dirichlet_alpha: float = None,
                  dirichlet_epsilon: float = None, enc_dtype=torch.float32, max_depth: int = 128,
-                 graph_search: bool = True, graph_first_use: bool = False):
+                 graph_search: bool = True, graph_first_use: bool = False, leaves: int = None):
+        """leaves: None = parity mode, the reference's one leaf per game per simulation step (mcts.py:254-269).
+        An integer L >= 1 = throughput mode (neural only; an extension, include/az_b200.h az_tree.n_leaves): up to L
+        leaves of a game in flight per step under virtual loss, the evaluator sees G*L leaf slots (`leaf_view`).
+        L = 1 is bit-identical to parity mode."""
         if not torch.cuda.is_available():
             raise RuntimeError("TreeBatch needs a CUDA device (alphazero_b200 has no CPU path)")
         if mode not in ("neural", "rollout"):
@@ -47,6 +66,10 @@ class TreeBatch:
         self.G, self.n, self.mode = int(G), self.spec.n, mode
         self.A = self.spec.action_size
         self.device = torch.device(device)
+        if leaves is not None and (mode != "neural" or not 1 <= int(leaves) <= 8):
+            raise ValueError("leaves (throughput mode) needs mode='neural' and 1 <= leaves <= 8")
+        self.leaves = None if leaves is None else int(leaves)
+        self.n_slots = self.G * (self.leaves or 1)       # leaf slots the evaluator sees
         if capacity is None:
             # per search at most (n_sim + 1) child blocks are added and the re-rooted subtree is kept.  Measured on
             # Othello 8x8 self-play (n_sim = 200, tools/pool_use.py): the fullest of 4096 games peaks at 5.4-7.6 k nodes,
@@ -68,17 +91,18 @@ class TreeBatch:
         self.sims_done = z(G, dtype=torch.int32)
         self.rng_ctr = z(G, dtype=torch.int32)
         self.status = z(G, dtype=torch.int32)
-        self.leaf_node = z(G, dtype=torch.int32)
-        self.leaf_kind = z(G, dtype=torch.uint8)
-        self.leaf_own = z(G, dtype=torch.int64)
-        self.leaf_opp = z(G, dtype=torch.int64)
-        self.leaf_player = z(G, dtype=torch.int8)
-        self.path = z(G * self.max_depth, dtype=torch.int32)
-        self.path_len = z(G, dtype=torch.int32)
+        S = self.n_slots
+        self.leaf_node = z(S, dtype=torch.int32)
+        self.leaf_kind = z(S, dtype=torch.uint8)
+        self.leaf_own = z(S, dtype=torch.int64)
+        self.leaf_opp = z(S, dtype=torch.int64)
+        self.leaf_player = z(S, dtype=torch.int8)
+        self.path = z(S * self.max_depth, dtype=torch.int32)
+        self.path_len = z(S, dtype=torch.int32)
         self.enc_dtype = enc_dtype
-        self.enc = z(G, self.spec.rows, self.spec.cols, dtype=enc_dtype)
-        self.probs = z(G, self.A, dtype=torch.float32)
-        self.value = z(G, dtype=torch.float32)
+        self.enc = z(S, self.spec.rows, self.spec.cols, dtype=enc_dtype)
+        self.probs = z(S, self.A, dtype=torch.float32)
+        self.value = z(S, dtype=torch.float32)
         self.n_rollouts = 0
         self.simulation_time = 0.0
         self.profile = None   # set to {"eval": [], "tree": []} to record (start, end) CUDA events per call
@@ -102,6 +126,8 @@ class TreeBatch:
         d.mode = _lib.MODE_NEURAL if mode == "neural" else _lib.MODE_ROLLOUT
         d.tie_random = 1 if tie_random else 0
         d.enc_dtype = {torch.float32: 0, torch.bfloat16: 1}[enc_dtype]
+        d.n_leaves = self.leaves or 0
+        self.leaf_view = LeafView(self) if (self.leaves or 1) > 1 else self    # what evaluators are built over
         self.set_dirichlet(dirichlet_alpha, dirichlet_epsilon)
         self.reset_roots()
 
@@ -150,9 +176,9 @@ class TreeBatch:
         (the live half of the node pool, its first `n_nodes` records -- default the whole half), random counter and
         sticky status.  Slots k.. are switched off.  Used by SelfPlayEngine to carry the last live games of a batch
         over to a smaller batch (smaller leaf batches for the network) when most games have ended."""
-        if (src.spec.game_id, src.n, src.spec.height, src.capacity, src.mode) != \
-                (self.spec.game_id, self.n, self.spec.height, self.capacity, self.mode):
-            raise ValueError("adopt: the two tree batches differ in game, pool capacity or mode")
+        if (src.spec.game_id, src.n, src.spec.height, src.capacity, src.mode, src.leaves) != \
+                (self.spec.game_id, self.n, self.spec.height, self.capacity, self.mode, self.leaves):
+            raise ValueError("adopt: the two tree batches differ in game, pool capacity, mode or leaves in flight")
         k = int(sel.numel())
         if k > self.G:
             raise ValueError(f"adopt: {k} games do not fit {self.G} slots")
@@ -194,6 +220,14 @@ class TreeBatch:
         self.sims_done.zero_()
         self.step(n_sim, finish=False, select=True)
         steps = n_sim + (extra_steps if self.mode == "neural" else 0)
+        L = self.leaves or 1
+        if L > 1:
+            # throughput mode: L simulations per step when no descent is dropped, plus a margin for dropped descents
+            # (two descents of one step meeting at the same unevaluated node); whatever is still missing after the
+            # planned steps is made up one step at a time below
+            per = -(-n_sim // L)
+            steps = per + (extra_steps if self.mode == "neural" else 0) + max(2, per // 8)
+        self.last_search_steps = steps
         prof = self.profile
         graph = self._search_graph(n_sim, steps, evaluator) if (self.graph_search and prof is None) else None
         if graph is not None:
@@ -209,7 +243,7 @@ class TreeBatch:
                 e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
                 e0.record()
             if self.mode == "neural":
-                evaluator(self)
+                evaluator(self.leaf_view)
             else:
                 self.rollout_leaves()
             if prof is not None:
@@ -221,6 +255,12 @@ class TreeBatch:
                 prof["tree"].append((e1, e2))
                 prof["depth_sum"] += self.path_len[self.active.bool()].sum()
                 prof["depth_cnt"] += self.active.sum()
+        if L > 1:
+            self.extra_steps_last_search = 0
+            while bool(((self.sims_done < n_sim) & self.active.bool()).any().item()):
+                evaluator(self.leaf_view)
+                self.step(n_sim, finish=True, select=True)
+                self.extra_steps_last_search += 1
         self.n_rollouts = int(n_sim)
         if check:
             self.check_status()

@@ -60,7 +60,10 @@ class MCT:
     TIE_RANDOM = True    # fair_max semantics; tests set False for the deterministic lowest-action-index tie-break
 
     def __init__(self, eval_method: str = None, nn: PolicyValueNetwork = None, dirichlet_alpha: float = None,
-                 dirichlet_epsilon: float = None) -> None:
+                 dirichlet_epsilon: float = None, leaves: int = None) -> None:
+        """`leaves` (an extension, not in the reference): None = the reference's one leaf per simulation; L >= 1 =
+        throughput mode with up to L leaves in flight per step under virtual loss (engine.TreeBatch)."""
+        self.leaves = leaves
         self.n_rollouts = 0
         self.simulation_time = 0
         self.eval_method = TreeEval.to_dict()["rollout" if eval_method is None else eval_method]
@@ -139,7 +142,8 @@ class MCT:
             mode = "neural" if self.eval_method == TreeEval.NEURAL else "rollout"
             self._tree = TreeBatch(1, n=spec, mode=mode, capacity=self.CAPACITY, seed=int(np.random.randint(1 << 31)),
                                    tie_random=self.TIE_RANDOM, dirichlet_alpha=self._dirichlet_alpha,
-                                   dirichlet_epsilon=self._dirichlet_epsilon, enc_dtype=torch.bfloat16)
+                                   dirichlet_epsilon=self._dirichlet_epsilon, enc_dtype=torch.bfloat16,
+                                   leaves=self.leaves if mode == "neural" else None)
             self._spec, self._n = spec, spec.n
             self._evaluator = None
             self._pending = []
@@ -156,10 +160,10 @@ class MCT:
             if self._nn is None:
                 raise ValueError("MCT in neural mode needs a network before search")
             if hasattr(self._nn, "make_batched_evaluator"):      # evaluator supplied by the network object itself
-                self._evaluator = self._nn.make_batched_evaluator(t)
+                self._evaluator = self._nn.make_batched_evaluator(t.leaf_view)
             else:
                 t.set_encoding(True)
-                self._evaluator = make_evaluator(self._nn, t)     # switches the encoding off when it reads bitboards
+                self._evaluator = make_evaluator(self._nn, t.leaf_view)   # switches the encoding off when it reads bitboards
             self._nn_stamp = self._weights_stamp(self._nn)
         elif self.eval_method == TreeEval.NEURAL and self._nn_stamp != self._weights_stamp(self._nn):
             if hasattr(self._evaluator, "refresh"):               # weights changed in place since the snapshot
@@ -169,7 +173,7 @@ class MCT:
     def _adopt(self, old: "MCT") -> None:
         """Re-uses the device pools / CUDA graph of a discarded MCT of the same kind (player.reset() builds a new MCT
         per game, players.py:151-152, 228-234); the tree itself starts fresh."""
-        if old is None or old._tree is None or old.eval_method != self.eval_method:
+        if old is None or old._tree is None or old.eval_method != self.eval_method or old.leaves != self.leaves:
             return
         self._tree, self._n, self._spec = old._tree, old._n, old._spec
         self._tree.set_dirichlet(self._dirichlet_alpha, self._dirichlet_epsilon)

@@ -88,9 +88,12 @@ class AlphaZeroPlayer(MCTSPlayer):
     """MCTS with network leaf evaluation and optional Dirichlet root noise (players.py:198-234)."""
 
     def __init__(self, n_sim: int = None, compute_time: float = None, nn: PolicyValueNetwork = None,
-                 dirichlet_alpha: float = None, dirichlet_epsilon: float = None, verbose: bool = False) -> None:
+                 dirichlet_alpha: float = None, dirichlet_epsilon: float = None, verbose: bool = False,
+                 leaves: int = None) -> None:
+        """`leaves` is an extension (throughput mode, see mcts.MCT); None keeps the reference's search order."""
         super().__init__(n_sim=n_sim, compute_time=compute_time, verbose=verbose)
-        self.mct = MCT(eval_method="neural", nn=nn)
+        self.leaves = leaves
+        self.mct = MCT(eval_method="neural", nn=nn, leaves=leaves)
         self.mct.dirichlet_alpha = dirichlet_alpha
         self.mct.dirichlet_epsilon = dirichlet_epsilon
 
@@ -98,12 +101,12 @@ class AlphaZeroPlayer(MCTSPlayer):
         return AlphaZeroPlayer(n_sim=self.n_sim, compute_time=self.compute_time,
                                nn=self.mct.nn.clone() if self.mct.nn is not None else None,
                                dirichlet_alpha=self.mct.dirichlet_alpha, dirichlet_epsilon=self.mct.dirichlet_epsilon,
-                               verbose=self.verbose)
+                               verbose=self.verbose, leaves=self.leaves)
 
     def reset(self) -> None:
         old = self.mct
         self.mct = MCT(eval_method="neural", nn=old.nn, dirichlet_alpha=old.dirichlet_alpha,
-                       dirichlet_epsilon=old.dirichlet_epsilon)
+                       dirichlet_epsilon=old.dirichlet_epsilon, leaves=self.leaves)
         self.mct._adopt(old)
 
 

@@ -154,23 +154,24 @@ class SelfPlayEngine:
                  dirichlet_epsilon: float = 0.25, temp_scheduler_type: str = "linear", temp_max_step: int = 4,
                  temp_min_step: int = 4, seed: int = 0, dtype=torch.bfloat16, capacity: int = None,
                  tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
-                 network_path: str = "auto", tail_tiers="auto", evaluator_factory=None):
+                 network_path: str = "auto", tail_tiers="auto", evaluator_factory=None, leaves: int = None):
         # `n`: Othello board size or a GameSpec (gamespec.Connect4Spec(7, 6) for BASELINE config 5)
         self.spec = spec = as_spec(n)
         self.G, self.n, self.n_sim = G, spec.n, n_sim
         self.max_plies = max_plies
         self.tree = TreeBatch(G, n=spec, mode="neural", capacity=capacity, n_sim_hint=n_sim, device=device, seed=seed,
                               tie_random=tie_random, dirichlet_alpha=dirichlet_alpha,
-                              dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype)
+                              dirichlet_epsilon=dirichlet_epsilon, enc_dtype=dtype, leaves=leaves)
+        self.leaves = leaves
         # `evaluator`: a ready evaluator bound to the main tree; `evaluator_factory(tree) -> evaluator`: builds one per
         # tree batch (main and tail tiers), e.g. lambda t: HashEvaluator(salt, tree=t); default: the network's own
         self._evaluator_factory = evaluator_factory
         if evaluator is not None:
             self.evaluator = evaluator
         elif evaluator_factory is not None:
-            self.evaluator = evaluator_factory(self.tree)
+            self.evaluator = evaluator_factory(self.tree.leaf_view)
         else:
-            self.evaluator = make_evaluator(nn, self.tree, dtype=dtype, path=network_path)
+            self.evaluator = make_evaluator(nn, self.tree.leaf_view, dtype=dtype, path=network_path)
         # Tail of a batch: games of one batch end within a few plies of each other, and the last plies would run the
         # full-size leaf batch through the network for a handful of live games (Othello 8x8, 4096 games: 1481 / 285 /
         # 29 / 8 / 1 / 1 games live after plies 60..65).  `tail_tiers` = sizes of smaller TreeBatches (own pools,
@@ -212,11 +213,12 @@ class SelfPlayEngine:
             tree = TreeBatch(size, n=self.spec, mode="neural", capacity=self.tree.capacity, n_sim_hint=self.n_sim,
                              device=a["device"], seed=a["seed"] + 0x9E3779B9 * size, tie_random=a["tie_random"],
                              dirichlet_alpha=a["dirichlet_alpha"], dirichlet_epsilon=a["dirichlet_epsilon"],
-                             enc_dtype=a["dtype"], max_depth=self.tree.max_depth, graph_first_use=True)
+                             enc_dtype=a["dtype"], max_depth=self.tree.max_depth, graph_first_use=True,
+                             leaves=self.leaves)
             if self._evaluator_factory is not None:
-                ev = self._evaluator_factory(tree)
+                ev = self._evaluator_factory(tree.leaf_view)
             else:
-                ev = make_evaluator(a["nn"], tree, dtype=a["dtype"], path=a["network_path"])
+                ev = make_evaluator(a["nn"], tree.leaf_view, dtype=a["dtype"], path=a["network_path"])
             tree.search(self.n_sim, ev, extra_steps=0, check=False)      # captures the tier's search graph now
             self._tiers[size] = (tree, ev)
         return self._tiers[size]
@@ -261,7 +263,7 @@ class SelfPlayEngine:
             tree.search(self.n_sim, evaluator, extra_steps=1 if t == 0 else 0, check=False)
             if self.search_events is not None:
                 e1.record()
-                self.search_events.append((e0, e1, self.n_sim + (1 if t == 0 else 0), tree.G))
+                self.search_events.append((e0, e1, tree.last_search_steps, tree.G))
             sims += (tree.sims_done.to(torch.int64) * live).sum()
             peak = torch.maximum(peak, tree.n_alloc[:k].max())
             temp_t = torch.full((tree.G,), float(self.temp[t]), dtype=torch.float32, device=tree.device)

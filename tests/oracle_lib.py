@@ -57,6 +57,7 @@ def lib():
         L.orc_mct_new_tictactoe.argtypes = [i32, i32, u64, u64, vp, vp]
         L.orc_mct_new_connect4.restype = vp
         L.orc_mct_new_connect4.argtypes = [i32, i32, i32, i32, u64, u64, vp, vp]
+        L.orc_mct_set_leaves.argtypes = [vp, i32]
         L.orc_greedy_moves.argtypes = [i32, vp, vp, vp, i32, i32, i64, vp, vp]
         _lib = L
     return _lib
@@ -201,7 +202,7 @@ class OracleMCT:
     """Sequential pointer-tree MCT of the oracle (restates alphazero/mcts.py).  `n` = Othello board size, or
     (width, height) with game="connect4"."""
 
-    def __init__(self, n, mode="neural", tie_random=False, salt=0, seed=0, dirichlet=None, game="othello"):
+    def __init__(self, n, mode="neural", tie_random=False, salt=0, seed=0, dirichlet=None, game="othello", leaves=None):
         if game == "tictactoe":
             self.h = lib().orc_mct_new_tictactoe(1 if mode == "neural" else 0, int(tie_random), salt, seed, None, None)
         elif game == "connect4":
@@ -211,6 +212,8 @@ class OracleMCT:
             self.h = lib().orc_mct_new(n, 1 if mode == "neural" else 0, int(tie_random), salt, seed, None, None)
         if dirichlet:
             lib().orc_mct_set_dirichlet(self.h, dirichlet[0], dirichlet[1])
+        if leaves:      # throughput mode (extension): up to `leaves` leaves in flight per step under virtual loss
+            lib().orc_mct_set_leaves(self.h, int(leaves))
 
     def search(self, black, white, player, n_sim):
         lib().orc_mct_search(self.h, int(black), int(white), int(player), int(n_sim))

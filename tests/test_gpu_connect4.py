@@ -534,7 +534,7 @@ def test_fused_connect4_net_matches_reference_outputs(golden_dir):
     with torch.no_grad():
         a = F.relu(net.bn1(net.conv1(x))); a = F.relu(net.bn2(net.conv2(a)))
         a = F.relu(net.bn3(net.conv3(a))); a4 = F.relu(net.bn4(net.conv4(a)))     # [G, 32, 3, 2]
-    feat = ev.features.float().cpu().reshape(G, 6, 32).permute(0, 2, 1).reshape(G, 32, 3, 2)
+    feat = ev.features_rowmajor().float().cpu().reshape(G, 6, 32).permute(0, 2, 1).reshape(G, 32, 3, 2)
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
     # a batch larger than one round of CTAs, with a partially filled last group
     G2 = 4099

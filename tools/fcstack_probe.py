@@ -98,6 +98,8 @@ if __name__ == "__main__":
     which = os.environ.get("FCSTACK_PROBE", "all")
     if which in ("all", "othello8"):
         run(512, 1024, 512, 66, [(2, 4), (1, 4), (1, 8)], G)
+    if which == "othello8_14":
+        run(512, 1024, 512, 66, [(1, 4)], G)
     if which in ("all", "small"):
         run(512, 1024, 512, 66, [(2, 4), (1, 4)], 300)
         run(128, 1024, 512, 38, [(2, 4), (1, 8)], 1000)
