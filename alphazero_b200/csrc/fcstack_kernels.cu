@@ -75,6 +75,7 @@ struct FcStackParams {
                                //    one SM's bulk-copy unit streams ~33 B/clk, far below what the MMAs consume; the LSU
                                //    path runs beside it (profiles/r2_fcstack_experiments.txt)
     uint32_t w_off[3], b_off[3];
+    long long* debug;          // optional [n_ctas][32] cycle stamps (az_net_fcstack_debug), see tools/fcstack_probe.py
 };
 
 __device__ __forceinline__ void fs_cluster_sync() {
@@ -175,6 +176,8 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int RT = p.RT, NS = p.NS;
+    long long* dbg = p.debug ? p.debug + (size_t)blockIdx.x * 32 : nullptr;
+    const long long t_entry = dbg ? clock64() : 0;
     uint32_t rank, cluster_id;
     asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     asm("mov.u32 %0, %%clusterid.x;" : "=r"(cluster_id));
@@ -221,11 +224,13 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const uint32_t tmem_base = *tmem_ptr_smem;
     az_pdl_wait();                // the layer-1 input is the preceding kernel's output
     az_pdl_trigger();
+    if (dbg && tid == 0) dbg[1] = clock64() - t_entry;
 
     if (warp == FS_PRODUCER_WARP) {
         // ================================================================== producer: one lane issues every copy
         if (lane == 0) {
             uint32_t it = 0;
+            long long w_empty = 0, w_ready = 0;
 #pragma unroll
             for (int L = 0; L < 3; ++L) {
                 const int kch = p.kch[L], nch = p.K[L] / kch;
@@ -243,11 +248,14 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     // L > 0: fetch in production order -- block j of every column slice, then block j + 1
                     const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
                     const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                    const long long c0 = dbg ? clock64() : 0;
                     fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
+                    const long long c1 = dbg ? clock64() : 0;
                     if (L > 0 && a_bulk) {
                         fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
                         asm volatile("fence.proxy.async.global;" ::: "memory");
                     }
+                    if (dbg) { w_empty += c1 - c0; w_ready += clock64() - c1; if (q == 0) dbg[26 + L] = c0 - t_entry; }
                     const uint32_t full = bar_full0 + 8 * s;
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
                     if (a_bulk + b_bulk) fs_expect_tx(full, a_bulk + b_bulk);
@@ -256,6 +264,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     if (b_bulk) fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
                 }
             }
+            if (dbg) { dbg[20] = w_empty; dbg[21] = w_ready; }
         }
         __syncwarp();
     } else if (warp >= FS_LOADER_WARP0) {
@@ -299,6 +308,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     } else if (warp == FS_MMA_WARP) {
         // ================================================================== MMA issue
         uint32_t it = 0;
+        long long w_full = 0, t_issue = 0;
 #pragma unroll
         for (int L = 0; L < 3; ++L) {
             const int kch = p.kch[L], nch = p.K[L] / kch, ksteps = kch >> 4;
@@ -307,9 +317,12 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
             const uint32_t d_tmem = tmem_base + col_off[L];
             for (int q = 0; q < nch; ++q, ++it) {
                 const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                const long long c0 = dbg ? clock64() : 0;
                 fs_mbar_wait(bar_full0 + 8 * s, ph);
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // cp.async (generic proxy) -> tcgen05.mma
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const long long c1 = dbg ? clock64() : 0;
+                if (dbg && lane == 0) { w_full += c1 - c0; if (q == 0) dbg[2 + L * 6] = c1 - t_entry; }
                 if (elect_one()) {
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
                     for (int k = 0; k < ksteps; ++k) {
@@ -322,8 +335,10 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     if (q == nch - 1) umma_commit(bar_acc0 + 8 * L);
                 }
                 __syncwarp();
+                if (dbg && lane == 0) { const long long c2 = clock64(); t_issue += c2 - c1; if (q == nch - 1) dbg[3 + L * 6] = c2 - t_entry; }
             }
         }
+        if (dbg && lane == 0) { dbg[22] = w_full; dbg[23] = t_issue; }
     } else {
         // ================================================================== epilogue
         const int quarter = warp & 3, half = warp >> 2;
@@ -337,6 +352,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
         for (int L = 0; L < 3; ++L) {
             fs_mbar_wait(bar_acc0 + 8 * L, 0u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (dbg && tid == 0) dbg[4 + L * 6] = clock64() - t_entry;
             if (L < 2) {
                 const int bw = p.kch[L + 1];                  // block width = the next layer's K chunk
                 const int nblk = p.Nc[L] / bw, nchn = p.K[L + 1] / bw;
@@ -383,6 +399,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                             out[col] = __float2bfloat16_rn(__uint_as_float(v[col]) + bs[col]);
                 }
             }
+            if (dbg && tid == 0) dbg[5 + L * 6] = clock64() - t_entry;
         }
     }
 
@@ -390,6 +407,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     fs_cluster_sync();
+    if (dbg && tid == 0) dbg[24] = clock64() - t_entry;
     if (warp == FS_MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
 }
@@ -443,6 +461,10 @@ extern "C" int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, in
     return AZ_OK;
 }
 
+static long long* g_fcstack_debug = nullptr;
+// Measurement hook: launches after this call write per-CTA cycle stamps to buf ([grid][32] int64, device); NULL = off.
+extern "C" int az_net_fcstack_debug(void* buf) { g_fcstack_debug = (long long*)buf; return AZ_OK; }
+
 extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out,
                               int64_t G, int K1, int N1, int N2, int RT, int NS, void* stream) {
     FcPlan pl;
@@ -461,7 +483,7 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
     for (int L = 0; L < 3; ++L) {
         p.K[L] = pl.K[L]; p.Nc[L] = pl.Nc[L]; p.kch[L] = pl.kch[L]; p.w_off[L] = pl.w_off[L]; p.b_off[L] = pl.b_off[L];
     }
-    p.RT = RT; p.NS = NS; p.hpc = pl.hpc;
+    p.RT = RT; p.NS = NS; p.hpc = pl.hpc; p.debug = g_fcstack_debug;
     static const int mc_flags = getenv("AZ_B200_FCSTACK_MC") ? atoi(getenv("AZ_B200_FCSTACK_MC")) : 0;   // bit 0: A, bit 1: B
     p.mc_a = mc_flags & 1; p.mc_b = (mc_flags >> 1) & 1;
     static int lsu_a = -1, lsu_b = -1;

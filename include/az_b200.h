@@ -323,6 +323,9 @@ int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action
  * of the weights [7..9] and biases [10..12], blob bytes [13]; AZ_ERR_ARG when the kernel has no mapping for the shape
  * (needs N1/NS <= 256, N2/NS <= 128, ceil(n_out/NS) <= 32, K1 % 64 == 0 or K1 in {16, 32}). */
 int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, int64_t* out);
+/* Measurement hook: while buf != NULL every az_net_fcstack launch writes per-CTA SM-clock stamps of its pipeline phases
+ * to buf ([grid][32] int64, device memory; layout in csrc/fcstack_kernels.cu / tools/fcstack_probe.py). */
+int az_net_fcstack_debug(void* buf);
 int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out, int64_t G,
                    int K1, int N1, int N2, int RT, int NS, void* stream);
 

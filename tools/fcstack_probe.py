@@ -75,6 +75,24 @@ def run(K1, N1, N2, n_out, shapes, G):
         err = (logits[:, :n_out].double() - want).abs().max().item()
         pad_ok = bool((logits[:, n_out:] == -77.0).all().item())
         scale = want.abs().max().item()
+        if os.environ.get("FCSTACK_STAMPS"):
+            n_ctas = tiles * NS
+            dbg = torch.zeros(n_ctas * 32, dtype=torch.int64, device=dev)
+            _lib.lib().az_net_fcstack_debug(dbg.data_ptr())
+            for _ in range(3):
+                call()
+            torch.cuda.synchronize()
+            _lib.lib().az_net_fcstack_debug(None)
+            d = dbg.reshape(n_ctas, 32).double()
+            names = {1: "setup done (cluster sync, pdl wait)", 26: "producer: first wait L1", 2: "L1 first stage full",
+                     3: "L1 last MMA issued", 4: "L1 accumulator complete (epilogue wakes)", 5: "L1 epilogue done",
+                     27: "producer: first wait L2", 8: "L2 first stage full", 9: "L2 last MMA issued", 10: "L2 accumulator complete",
+                     11: "L2 epilogue done", 28: "producer: first wait L3", 14: "L3 first stage full", 15: "L3 last MMA issued",
+                     16: "L3 accumulator complete", 17: "L3 epilogue done", 24: "exit (after teardown cluster sync)",
+                     20: "producer: total wait empty", 21: "producer: total wait ready", 22: "mma: total wait full",
+                     23: "mma: total issue"}
+            for i, nm in names.items():
+                print(f"    {nm:44s} median {d[:, i].median().item():8.0f}  min {d[:, i].min().item():8.0f}  max {d[:, i].max().item():8.0f} cycles")
         us = time_graph(call)
         flops = 2.0 * G * (K1 * N1 + N1 * N2 + N2 * n_out)
         print(f"RT={RT} NS={NS}: max |err| {err:.4f} (logit scale {scale:.2f}, bf16 ulp {scale * 2 ** -8:.4f}) pad untouched {pad_ok}"
