@@ -37,13 +37,10 @@
 #define FS_A_BYTES 16384                      // one A stage: 64 (K) x 128 rows bf16
 #define FS_B_BYTES 32768                      // one B stage: 64 (K) x 256 columns bf16
 #define FS_STAGE_BYTES (FS_A_BYTES + FS_B_BYTES)
-#define FS_EPI_WARPS 8                        // warps 0-7: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = block parity)
-#define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 8: bulk copies (one lane)
-#define FS_MMA_WARP (FS_EPI_WARPS + 1)        // warp 9: tcgen05.mma issue (one elected lane), TMEM allocation
-#define FS_LOADER_WARP0 (FS_EPI_WARPS + 2)     // warps 10-13: cp.async loaders (the LSU path beside the bulk-copy unit)
-#define FS_LOADER_WARPS 4
-#define FS_LOADERS (FS_LOADER_WARPS * 32)
-#define FS_THREADS ((FS_EPI_WARPS + 2 + FS_LOADER_WARPS) * 32)
+#define FS_EPI_WARPS 16                       // warps 0-15: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = output block)
+#define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 16: bulk copies (one lane)
+#define FS_MMA_WARP (FS_EPI_WARPS + 1)        // warp 17: tcgen05.mma issue (one elected lane), TMEM allocation
+#define FS_THREADS ((FS_EPI_WARPS + 2) * 32)
 #define FS_MAX_CHUNKS 16                      // K chunks per layer
 #define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
 #define FB_FULL 0
@@ -70,10 +67,6 @@ struct FcStackParams {
     int RT, NS, hpc;           // cluster shape; real head outputs per column slice
     int mc_a, mc_b;            // 1: the A / B block of a stage is fetched once per cluster and multicast; 0: every CTA
                                //    fetches its own copy (the bytes INTO an SM are the same either way)
-    int lsu_a, lsu_b_planes;   // stage bytes fetched by the loader warps with cp.async instead of the bulk-copy unit:
-                               //    the A block (0 / 1) and the last lsu_b_planes of the B block's K planes.  Measured:
-                               //    one SM's bulk-copy unit streams ~33 B/clk, far below what the MMAs consume; the LSU
-                               //    path runs beside it (profiles/r2_fcstack_experiments.txt)
     uint32_t w_off[3], b_off[3];
     long long* debug;          // optional [n_ctas][32] cycle stamps (az_net_fcstack_debug), see tools/fcstack_probe.py
 };
@@ -186,8 +179,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const uint32_t a_mask = ((1u << NS) - 1u) << (r * NS);    // the CTAs of row tile r
     uint32_t b_mask = 0u;                                     // the CTAs of column slice c
     for (int rr = 0; rr < RT; ++rr) b_mask |= 1u << (rr * NS + c);
-    const bool lsu_a = p.lsu_a != 0, use_lsu = lsu_a || p.lsu_b_planes > 0;
-    const bool mc_a = p.mc_a && NS > 1 && !lsu_a, mc_b = p.mc_b && RT > 1 && p.lsu_b_planes == 0, mc_any = mc_a || mc_b;
+    const bool mc_a = p.mc_a && NS > 1, mc_b = p.mc_b && RT > 1, mc_any = mc_a || mc_b;
     const uint32_t all_mask = (1u << rank) | (mc_a ? a_mask : 0u) | (mc_b ? b_mask : 0u);   // CTAs this one sends stage data to
 
     const uint32_t bars = smem_u32(smem + FS_SM_BARS);
@@ -199,19 +191,13 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const uint32_t col_off[3] = {0u, 256u, 384u};             // TMEM columns of the three accumulators
 
     // ---- setup: barriers, biases of this column slice (weights: not produced by the preceding kernel), TMEM
-    if (tid == 0) {
-        for (int s = 0; s < FS_STAGES; ++s) {
-            mbar_init(bar_full0 + 8 * s, 1u + (use_lsu ? FS_LOADERS : 0u));
-            mbar_init(bar_empty0 + 8 * s, __popc(all_mask));
-        }
-        for (int L = 0; L < 3; ++L) mbar_init(bar_acc0 + 8 * L, 1);
-        for (int i = 0; i < 2 * FS_MAX_CHUNKS; ++i) mbar_init(bar_ready0 + 8 * i, 4);
+    if (tid < FB_COUNT) {      // one barrier per thread
+        uint32_t count = 1u;                                                      // acc[L]: one tcgen05.commit
+        if (tid < FB_EMPTY) count = 1u;                                           // full[s]: the producer's expect_tx
+        else if (tid < FB_ACC) count = (uint32_t)__popc(all_mask);                // empty[s]: one commit per receiving CTA
+        else if (tid >= FB_READY) count = 4u;                                     // ready[block]: the four quarter warps
+        mbar_init(bars + 8 * tid, count);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-#pragma unroll
-    for (int L = 0; L < 3; ++L) {
-        const float* b = reinterpret_cast<const float*>(p.wblob + p.b_off[L]) + c * p.Nc[L];
-        for (int i = tid; i < p.Nc[L]; i += FS_THREADS) bias_s[bias_off[L] + i] = b[i];
     }
     if (warp == FS_MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(512));
@@ -235,11 +221,8 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
             for (int L = 0; L < 3; ++L) {
                 const int kch = p.kch[L], nch = p.K[L] / kch;
                 const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
-                // the loader warps take the A block (lsu_a) and the tail of the B block; this thread the rest
-                const uint32_t a_bulk = lsu_a ? 0u : a_bytes;
-                const uint32_t b_bulk = b_bytes - (uint32_t)min(p.lsu_b_planes, kch >> 3) * (uint32_t)p.Nc[L] * 16u;
                 // with multicast this CTA fetches part c of the A block / part r of the B block for its whole group
-                const uint32_t a_part = mc_a ? a_bulk / (uint32_t)NS : a_bulk, b_part = mc_b ? b_bulk / (uint32_t)RT : b_bulk;
+                const uint32_t a_part = mc_a ? a_bytes / (uint32_t)NS : a_bytes, b_part = mc_b ? b_bytes / (uint32_t)RT : b_bytes;
                 const uint32_t a_skip = mc_a ? (uint32_t)c * a_part : 0u, b_skip = mc_b ? (uint32_t)r * b_part : 0u;
                 const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + a_skip;
                 const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + b_skip;
@@ -251,60 +234,23 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     const long long c0 = dbg ? clock64() : 0;
                     fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
                     const long long c1 = dbg ? clock64() : 0;
-                    if (L > 0 && a_bulk) {
-                        fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
-                        asm volatile("fence.proxy.async.global;" ::: "memory");
-                    }
-                    if (dbg) { w_empty += c1 - c0; w_ready += clock64() - c1; if (q == 0) dbg[26 + L] = c0 - t_entry; }
                     const uint32_t full = bar_full0 + 8 * s;
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
-                    if (a_bulk + b_bulk) fs_expect_tx(full, a_bulk + b_bulk);
-                    else mbar_arrive(full);
-                    if (a_bulk) fs_bulk_copy(sa + a_skip, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
-                    if (b_bulk) fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
+                    fs_expect_tx(full, a_bytes + b_bytes);
+                    // the weights do not depend on the previous layer: they are on their way while the block is awaited
+                    fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
+                    // The writers made their stores visible at cluster scope before the (release) arrive that completes
+                    // this barrier, and the copy below reads the L2, so observing the barrier is enough: a cluster-scope
+                    // acquire + proxy fence here cost ~540 cycles per stage and made this thread the bottleneck of
+                    // layers 2 and 3 (profiles/r2_fcstack_experiments.txt).
+                    if (L > 0) fs_mbar_wait(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
+                    if (dbg) { w_empty += c1 - c0; w_ready += clock64() - c1; if (q == 0) dbg[26 + L] = c0 - t_entry; }
+                    fs_bulk_copy(sa + a_skip, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
                 }
             }
             if (dbg) { dbg[20] = w_empty; dbg[21] = w_ready; }
         }
         __syncwarp();
-    } else if (warp >= FS_LOADER_WARP0) {
-        // ================================================================== loaders: the LSU half of every stage
-        // 16 bytes per cp.async, consecutive threads -> consecutive 16-byte pieces (the blocks are contiguous in global
-        // memory and in the stage).  A thread's copies of a stage arrive on the stage's full barrier when they complete
-        // (cp.async.mbarrier.arrive), followed by the thread's own arrival.
-        if (use_lsu) {
-            const int lt = tid - FS_LOADER_WARP0 * 32;
-            uint32_t it = 0;
-#pragma unroll
-            for (int L = 0; L < 3; ++L) {
-                const int kch = p.kch[L], nch = p.K[L] / kch;
-                const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
-                const uint32_t b_lsu = (uint32_t)min(p.lsu_b_planes, kch >> 3) * (uint32_t)p.Nc[L] * 16u;
-                const uint32_t b_head = b_bytes - b_lsu;      // bytes of the B block the bulk copy brings
-                const uint32_t a_pieces = lsu_a ? a_bytes >> 4 : 0u, pieces = a_pieces + (b_lsu >> 4);
-                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes;
-                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + b_head;
-                const int bps = nch / NS;
-                for (int q = 0; q < nch; ++q, ++it) {
-                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
-                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
-                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
-                    if (L > 0 && lsu_a) fs_mbar_wait_cluster(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
-                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES + b_head;
-                    const uint8_t* ga = a_src + (size_t)kc * a_bytes;
-                    const uint8_t* gb = b_src + (size_t)kc * b_bytes;
-                    for (uint32_t i = (uint32_t)lt; i < pieces; i += FS_LOADERS) {
-                        const bool is_a = i < a_pieces;
-                        const uint32_t off = (is_a ? i : i - a_pieces) << 4;
-                        const uint32_t dst = (is_a ? sa : sb) + off;
-                        const uint8_t* src = (is_a ? ga : gb) + off;
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-                    }
-                    asm volatile("cp.async.mbarrier.arrive.shared::cta.b64 [%0];" ::"r"(bar_full0 + 8 * s) : "memory");
-                    mbar_arrive(bar_full0 + 8 * s);
-                }
-            }
-        }
     } else if (warp == FS_MMA_WARP) {
         // ================================================================== MMA issue
         uint32_t it = 0;
@@ -341,10 +287,20 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
         if (dbg && lane == 0) { dbg[22] = w_full; dbg[23] = t_issue; }
     } else {
         // ================================================================== epilogue
-        const int quarter = warp & 3, half = warp >> 2;
+        const int quarter = warp & 3, blk = warp >> 2;        // blk: which 64-wide output block of a layer this warp converts
         const int row = quarter * 32 + lane;                  // TMEM lane = row of the tile
-        const long long grow = (long long)m * 128 + row;
         const uint32_t t_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        {   // biases of this column slice -> shared memory, while the first layer's operands stream in
+            const int n0 = p.Nc[0], n1 = p.Nc[1], n2 = p.Nc[2];
+            for (int i = tid; i < n0 + n1 + n2; i += FS_EPI_WARPS * 32) {
+                const int L = i < n0 ? 0 : (i < n0 + n1 ? 1 : 2);
+                const int j = i - (L == 0 ? 0 : (L == 1 ? n0 : n0 + n1));
+                const int nc = L == 0 ? n0 : (L == 1 ? n1 : n2);
+                const uint32_t off = L == 0 ? p.b_off[0] : (L == 1 ? p.b_off[1] : p.b_off[2]);
+                bias_s[(L == 0 ? 0 : (L == 1 ? 256 : 384)) + j] = reinterpret_cast<const float*>(p.wblob + off)[c * nc + j];
+            }
+            asm volatile("bar.sync 1, %0;" ::"r"(FS_EPI_WARPS * 32) : "memory");
+        }
         uint32_t v[64];
 #pragma unroll
         for (int i = 0; i < 64; ++i) v[i] = 0u;
@@ -357,11 +313,12 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                 const int bw = p.kch[L + 1];                  // block width = the next layer's K chunk
                 const int nblk = p.Nc[L] / bw, nchn = p.K[L + 1] / bw;
                 uint8_t* hbase = (L == 0 ? p.h1 : p.h2) + (size_t)m * nchn * ((size_t)bw * 256) + (size_t)row * 16;
-                for (int j = half; j < nblk; j += 2) {
+                for (int j = blk; j < nblk; j += FS_EPI_WARPS / 4) {
 #pragma unroll
                     for (int qq = 0; qq < 4; ++qq)
                         if (qq * 16 < bw) fs_tmem_ld16(t_lane + col_off[L] + (uint32_t)(j * bw + qq * 16), &v[qq * 16]);
                     fs_tmem_wait64(v);
+                    if (dbg && tid == 0) dbg[29 + L] = clock64() - t_entry;
                     const int kcn = c * nblk + j;             // this block's K chunk in the next layer
                     uint8_t* dst = hbase + (size_t)kcn * ((size_t)bw * 256);
                     const float* bs = bias_s + bias_off[L] + j * bw;
@@ -378,25 +335,45 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                             *reinterpret_cast<uint4*>(dst + pl * 2048) = o;
                         }
                     }
-                    // generic-proxy stores -> bulk async copies of other CTAs: proxy fence + cluster-scope release
+                    if (dbg && tid == 0) dbg[6 + L * 6] = clock64() - t_entry;
+                    // The block is read by bulk copies (async proxy) of all CTAs of the row tile: every storing lane's
+                    // proxy fence, then the release of the remote arrive -- cumulative over the warp's stores through
+                    // __syncwarp -- publishes it.  (A fence.acq_rel.cluster per lane on top of that cost ~1400 cycles per
+                    // block and is redundant.)
                     asm volatile("fence.proxy.async.global;" ::: "memory");
-                    asm volatile("fence.acq_rel.cluster;" ::: "memory");
                     __syncwarp();
                     if (lane < NS) fs_mbar_arrive_remote(bar_ready0 + 8 * (L * FS_MAX_CHUNKS + kcn), (uint32_t)(r * NS + lane));
+                    if (dbg && tid == 0) dbg[7 + L * 6] = clock64() - t_entry;
                 }
-            } else if (half == 0) {
-                const int ncols = p.Nc[2];
+            } else if (blk == 0) {
+                // heads: bias, bf16, then through shared memory so that the global stores are row-contiguous 4-byte words
+                // (lane = row stores of 2 bytes at a 144-byte pitch cost one L1 wavefront per lane: 3 800 cycles measured)
+                const int ncols = p.Nc[2], hpc = p.hpc, pw = hpc >> 1;      // hpc is even (fc_plan)
 #pragma unroll
                 for (int qq = 0; qq < 2; ++qq)
                     if (qq * 16 < ncols) fs_tmem_ld16(t_lane + col_off[2] + (uint32_t)(qq * 16), &v[qq * 16]);
                 fs_tmem_wait64(v);
-                if (grow < p.G) {
-                    __nv_bfloat16* out = p.logits + grow * p.ld + c * p.hpc;
-                    const float* bs = bias_s + bias_off[2];
+                if (dbg && tid == 0) dbg[31] = clock64() - t_entry;
+                uint32_t* stage = reinterpret_cast<uint32_t*>(smem);         // stage 0 is free: every MMA has completed
+                const float* bs = bias_s + bias_off[2];
 #pragma unroll
-                    for (int col = 0; col < 32; ++col)
-                        if (col < p.hpc && c * p.hpc + col < p.n_out)
-                            out[col] = __float2bfloat16_rn(__uint_as_float(v[col]) + bs[col]);
+                for (int k = 0; k < 16; ++k)
+                    if (k < pw) {
+                        __nv_bfloat162 two = __floats2bfloat162_rn(__uint_as_float(v[2 * k]) + bs[2 * k],
+                                                                   __uint_as_float(v[2 * k + 1]) + bs[2 * k + 1]);
+                        stage[row * 17 + k] = *reinterpret_cast<uint32_t*>(&two);   // odd pitch: no bank conflicts
+                    }
+                asm volatile("bar.sync 2, 128;" ::: "memory");
+                const long long row0 = (long long)m * 128;
+                for (int idx = tid; idx < 128 * pw; idx += 128) {
+                    const int rr = idx / pw, k = idx - rr * pw;
+                    const int h = c * hpc + 2 * k;
+                    if (row0 + rr < p.G && h < p.n_out) {
+                        __nv_bfloat16* out = p.logits + (row0 + rr) * p.ld + h;
+                        const uint32_t w = stage[rr * 17 + k];
+                        if (h + 1 < p.n_out) *reinterpret_cast<uint32_t*>(out) = w;
+                        else *out = __ushort_as_bfloat16((unsigned short)(w & 0xffffu));
+                    }
                 }
             }
             if (dbg && tid == 0) dbg[5 + L * 6] = clock64() - t_entry;
@@ -428,7 +405,7 @@ static int fc_chunk(int k) { return k >= 64 ? 64 : k; }
 static bool fc_plan(int K1, int N1, int N2, int n_out, int NS, FcPlan* pl) {
     if (NS < 1 || NS > 8 || K1 < 16 || N1 < 16 || N2 < 16 || n_out < 1) return false;
     if ((N1 % NS) || (N2 % NS)) return false;
-    pl->hpc = (n_out + NS - 1) / NS;
+    pl->hpc = (((n_out + NS - 1) / NS) + 1) & ~1;      // even: the heads' epilogue stores bf16 pairs
     pl->n3c = ((pl->hpc + 15) / 16) * 16;
     pl->K[0] = K1; pl->K[1] = N1; pl->K[2] = N2;
     pl->Nc[0] = N1 / NS; pl->Nc[1] = N2 / NS; pl->Nc[2] = pl->n3c;
@@ -486,12 +463,6 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
     p.RT = RT; p.NS = NS; p.hpc = pl.hpc; p.debug = g_fcstack_debug;
     static const int mc_flags = getenv("AZ_B200_FCSTACK_MC") ? atoi(getenv("AZ_B200_FCSTACK_MC")) : 0;   // bit 0: A, bit 1: B
     p.mc_a = mc_flags & 1; p.mc_b = (mc_flags >> 1) & 1;
-    static int lsu_a = -1, lsu_b = -1;
-    if (lsu_a < 0) {
-        lsu_a = 1; lsu_b = 4;                                 // default split, see FcStackParams
-        if (const char* e = getenv("AZ_B200_FCSTACK_LSU")) sscanf(e, "%d,%d", &lsu_a, &lsu_b);
-    }
-    p.lsu_a = lsu_a; p.lsu_b_planes = lsu_b < 0 ? 0 : (lsu_b > 8 ? 8 : lsu_b);
     const int64_t tiles = (G + 127) / 128, clusters = (tiles + RT - 1) / RT;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(clusters * RT * NS)); cfg.blockDim = dim3(FS_THREADS);

@@ -55,7 +55,7 @@ def test_plan_refuses_shapes_without_a_mapping():
     with pytest.raises(ValueError):
         fcstack_plan(500, 1024, 512, 66, 4)          # K1 not a whole number of chunks
     p = fcstack_plan(512, 1024, 512, 66, 4)
-    assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 17
+    assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 18      # even: bf16 pairs
     assert p["bytes"] == (1024 * 512 + 512 * 1024 + 128 * 512) * 2 + (1024 + 512 + 128) * 4
 
 

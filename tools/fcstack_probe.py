@@ -89,6 +89,9 @@ def run(K1, N1, N2, n_out, shapes, G):
                      27: "producer: first wait L2", 8: "L2 first stage full", 9: "L2 last MMA issued", 10: "L2 accumulator complete",
                      11: "L2 epilogue done", 28: "producer: first wait L3", 14: "L3 first stage full", 15: "L3 last MMA issued",
                      16: "L3 accumulator complete", 17: "L3 epilogue done", 24: "exit (after teardown cluster sync)",
+                     29: "L1 epilogue: first block in registers", 6: "L1 epilogue: first block stored", 7: "L1 epilogue: first block signalled",
+                     30: "L2 epilogue: first block in registers", 12: "L2 epilogue: first block stored", 13: "L2 epilogue: first block signalled",
+                     31: "L3 epilogue: accumulator in registers",
                      20: "producer: total wait empty", 21: "producer: total wait ready", 22: "mma: total wait full",
                      23: "mma: total issue"}
             for i, nm in names.items():
