@@ -80,6 +80,7 @@ SIGNATURES = {
     "az_tree_root_stats": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_tree_choose": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p, c_void_p, c_void_p]),
     "az_tree_advance": (c_int, [ctypes.POINTER(AzTree), c_void_p, c_void_p]),
+    "az_tree_move": (c_int, [ctypes.POINTER(AzTree), ctypes.c_float] + [c_void_p] * 9),
     "az_eval_hash": (c_int, [c_void_p, c_void_p, c_int, c_i64, c_u64, c_void_p, c_void_p, c_void_p]),
     "az_greedy_move": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_u64, ctypes.c_uint32, c_int,
                                 c_void_p, c_void_p, c_void_p]),

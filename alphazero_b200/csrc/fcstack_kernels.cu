@@ -38,9 +38,12 @@
 #define FS_B_BYTES 32768                      // one B stage: 64 (K) x 256 columns bf16
 #define FS_STAGE_BYTES (FS_A_BYTES + FS_B_BYTES)
 #define FS_EPI_WARPS 16                       // warps 0-15: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = output block)
-#define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 16: bulk copies (one lane)
-#define FS_MMA_WARP (FS_EPI_WARPS + 1)        // warp 17: tcgen05.mma issue (one elected lane), TMEM allocation
-#define FS_THREADS ((FS_EPI_WARPS + 2) * 32)
+#define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 16: bulk copies of the B (weight) blocks, one lane
+#define FS_PRODUCER_A_WARP (FS_EPI_WARPS + 1) // warp 17: bulk copies of the A (activation) blocks, one lane.  Issuing a
+                                              // bulk copy costs the issuing thread ~370 cycles (measured): one thread for
+                                              // both copies of a stage made the producer the bottleneck of every layer
+#define FS_MMA_WARP (FS_EPI_WARPS + 2)        // warp 18: tcgen05.mma issue (one elected lane), TMEM allocation
+#define FS_THREADS ((FS_EPI_WARPS + 3) * 32)
 #define FS_MAX_CHUNKS 16                      // K chunks per layer
 #define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
 #define FB_FULL 0
@@ -236,19 +239,38 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     const long long c1 = dbg ? clock64() : 0;
                     const uint32_t full = bar_full0 + 8 * s;
                     const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
-                    fs_expect_tx(full, a_bytes + b_bytes);
-                    // the weights do not depend on the previous layer: they are on their way while the block is awaited
+                    fs_expect_tx(full, a_bytes + b_bytes);      // the A bytes come from the other producer warp
                     fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
-                    // The writers made their stores visible at cluster scope before the (release) arrive that completes
-                    // this barrier, and the copy below reads the L2, so observing the barrier is enough: a cluster-scope
-                    // acquire + proxy fence here cost ~540 cycles per stage and made this thread the bottleneck of
-                    // layers 2 and 3 (profiles/r2_fcstack_experiments.txt).
-                    if (L > 0) fs_mbar_wait(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
                     if (dbg) { w_empty += c1 - c0; w_ready += clock64() - c1; if (q == 0) dbg[26 + L] = c0 - t_entry; }
-                    fs_bulk_copy(sa + a_skip, a_src + (size_t)kc * a_bytes, a_part, full, a_mask, mc_a);
                 }
             }
             if (dbg) { dbg[20] = w_empty; dbg[21] = w_ready; }
+        }
+        __syncwarp();
+    } else if (warp == FS_PRODUCER_A_WARP) {
+        // ================================================================== producer of the activation blocks
+        if (lane == 0) {
+            uint32_t it = 0;
+#pragma unroll
+            for (int L = 0; L < 3; ++L) {
+                const int kch = p.kch[L], nch = p.K[L] / kch;
+                const uint32_t a_bytes = (uint32_t)kch * 256u;
+                const uint32_t a_part = mc_a ? a_bytes / (uint32_t)NS : a_bytes;
+                const uint32_t a_skip = mc_a ? (uint32_t)c * a_part : 0u;
+                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + a_skip;
+                const int bps = nch / NS;
+                for (int q = 0; q < nch; ++q, ++it) {
+                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
+                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
+                    // The writers made their stores visible at cluster scope before the (release) arrive that completes
+                    // this barrier, and the copy below reads the L2, so observing the barrier is enough: a cluster-scope
+                    // acquire + proxy fence here cost ~540 cycles per stage (profiles/r2_fcstack_experiments.txt).
+                    if (L > 0) fs_mbar_wait(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
+                    fs_bulk_copy(smem_u32(smem + s * FS_STAGE_BYTES) + a_skip, a_src + (size_t)kc * a_bytes, a_part,
+                                 bar_full0 + 8 * s, a_mask, mc_a);
+                }
+            }
         }
         __syncwarp();
     } else if (warp == FS_MMA_WARP) {
@@ -265,7 +287,6 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                 const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
                 const long long c0 = dbg ? clock64() : 0;
                 fs_mbar_wait(bar_full0 + 8 * s, ph);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // cp.async (generic proxy) -> tcgen05.mma
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const long long c1 = dbg ? clock64() : 0;
                 if (dbg && lane == 0) { w_full += c1 - c0; if (q == 0) dbg[2 + L * 6] = c1 - t_entry; }

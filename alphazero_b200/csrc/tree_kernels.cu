@@ -855,31 +855,23 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_root_stats(az_tr
     }
 }
 
-// get_action_probs (mcts.py:95-116) + the categorical draw of MCTSPlayer.get_move (players.py:184-189).
+// get_action_probs (mcts.py:95-116) + the categorical draw of MCTSPlayer.get_move (players.py:184-189) for game g by
+// its warp: returns the chosen move (same value in every lane) and writes the policy row pi_row[0 .. A) (may be NULL).
 template <int GAME>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t, const float* __restrict__ temp,
-                                                                     uint8_t* __restrict__ action,
-                                                                     float* __restrict__ pi) {
+__device__ __forceinline__ int az_choose_warp(const az_tree& t, const az_dims& d, int g, int lane, float T,
+                                              float* __restrict__ pi_row) {
     using R = az_rules<GAME>;
-    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (g >= t.G || !t.active[g]) return;
-    const az_dims d = R::dims(t.n, t.height);
     const int A = R::action_size(d);
     const az_node* nodes = t.nodes + ((size_t)g * 2 + t.half[g]) * (size_t)t.capacity;
-    if (pi) for (int a = lane; a < A; a += 32) pi[(size_t)g * A + a] = 0.f;
+    if (pi_row) for (int a = lane; a < A; a += 32) pi_row[a] = 0.f;
     __syncwarp();
     NodeRec root = az_load_node(&nodes[0]);
     const uint32_t event = t.rng_ctr[g];
     if (!(root.flags() & AZ_NODE_EXPANDED)) {                   // mcts.py:101-102: {pass_move: 1.}
-        if (lane == 0) {
-            action[g] = AZ_PASS;
-            if (pi) pi[(size_t)g * A + A - 1] = 1.f;
-        }
-        return;
+        if (lane == 0 && pi_row) pi_row[A - 1] = 1.f;
+        return AZ_PASS;
     }
     const int k = root.n_children();
-    const float T = temp ? temp[g] : 0.f;
     // lane j holds child j (and j+32 in the 33-children corner case)
     uint32_t n0 = 0, n1 = 0;
     int m0 = AZ_PASS, m1 = AZ_PASS;
@@ -893,7 +885,7 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
         az_warp_argmax((double)(second ? n1 : n0), second ? lane + 32 : lane, lane < k, t.tie_random != 0, t.seed,
                        (uint32_t)g, event, &src);
         chosen_move = __shfl_sync(AZ_FULL, second ? m1 : m0, src);
-        if (lane == 0 && pi) pi[(size_t)g * A + R::net_index(chosen_move, d)] = 1.f;
+        if (lane == 0 && pi_row) pi_row[R::net_index(chosen_move, d)] = 1.f;
     } else {
         const double inv = 1.0 / (double)T;
         double w0 = lane < k ? pow((double)n0, inv) : 0.0;
@@ -901,9 +893,9 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
         if (T == 1.f) { w0 = lane < k ? (double)n0 : 0.0; w1 = lane + 32 < k ? (double)n1 : 0.0; }
         const double sum = az_warp_sum(w0 + w1);
         const double p0 = w0 / sum, p1 = w1 / sum;
-        if (pi) {
-            if (lane < k) pi[(size_t)g * A + R::net_index(m0, d)] = (float)p0;
-            if (lane + 32 < k) pi[(size_t)g * A + R::net_index(m1, d)] = (float)p1;
+        if (pi_row) {
+            if (lane < k) pi_row[R::net_index(m0, d)] = (float)p0;
+            if (lane + 32 < k) pi_row[R::net_index(m1, d)] = (float)p1;
         }
         // inverse-CDF draw in child order: inclusive prefix sum of p0 over lanes, then the 33rd child
         double c = p0;
@@ -925,10 +917,22 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
                                                                        : __shfl_sync(AZ_FULL, m0, last);
         }
     }
-    if (lane == 0) {
-        action[g] = (uint8_t)chosen_move;
-        t.rng_ctr[g] = event + 1u;
-    }
+    if (lane == 0) t.rng_ctr[g] = event + 1u;
+    return chosen_move;
+}
+
+template <int GAME>
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t, const float* __restrict__ temp,
+                                                                     uint8_t* __restrict__ action,
+                                                                     float* __restrict__ pi) {
+    using R = az_rules<GAME>;
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    const az_dims d = R::dims(t.n, t.height);
+    const int chosen = az_choose_warp<GAME>(t, d, g, lane, temp ? temp[g] : 0.f,
+                                            pi ? pi + (size_t)g * R::action_size(d) : nullptr);
+    if (lane == 0) action[g] = (uint8_t)chosen;
 }
 
 // ------------------------------------------------------------------------------------------------ advance
@@ -938,20 +942,18 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_choose(az_tree t
 // node, an exclusive warp scan of their child counts assigns the destination blocks, then the child blocks are
 // copied with coalesced 32-byte-per-lane loads/stores), so the root is always node 0 and a game's tree stays
 // dense no matter how long the game lasts.
+// Body of az_tree_advance for game g by its warp; returns false (status bit set, game untouched) for an illegal move,
+// else the new root position and the size of the re-rooted tree.
 template <int GAME>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree t, const uint8_t* __restrict__ action) {
+__device__ __forceinline__ bool az_advance_warp(const az_tree& t, const az_dims& d, int g, int lane, int a,
+                                                uint64_t* new_own, uint64_t* new_opp, int* new_player,
+                                                uint32_t* new_nodes) {
     using R = az_rules<GAME>;
-    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
-    if (g >= t.G || !t.active[g]) return;
-    const int a = action[g];
-    if (a == 255) return;
-    const az_dims d = R::dims(t.n, t.height);
     uint64_t own = t.root_own[g], opp = t.root_opp[g];
     const bool ok = R::is_legal(az_warp_rules<GAME>::legal(own, opp, d, lane, nullptr), a);
     if (!ok) {
         if (lane == 0) t.status[g] |= AZ_STATUS_ILLEGAL;
-        return;
+        return false;
     }
     const int h = t.half[g];
     const az_node* src = t.nodes + ((size_t)g * 2 + h) * (size_t)t.capacity;
@@ -1011,13 +1013,86 @@ __global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree 
         }
     }
     az_warp_rules<GAME>::apply(own, opp, a, d, lane);
+    const int player = -(int)t.root_player[g];
+    __syncwarp();
     if (lane == 0) {
         t.root_own[g] = own;
         t.root_opp[g] = opp;
-        t.root_player[g] = (int8_t)(-t.root_player[g]);
+        t.root_player[g] = (int8_t)player;
         t.half[g] = (uint8_t)(1 - h);
         t.n_alloc[g] = n_dst;
         t.leaf_kind[g] = AZ_LEAF_IDLE;
+    }
+    *new_own = own; *new_opp = opp; *new_player = player; *new_nodes = n_dst;
+    return true;
+}
+
+template <int GAME>
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_advance(az_tree t, const uint8_t* __restrict__ action) {
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G || !t.active[g]) return;
+    const int a = action[g];
+    if (a == 255) return;
+    const az_dims d = az_rules<GAME>::dims(t.n, t.height);
+    uint64_t own, opp;
+    int player;
+    uint32_t n_nodes;
+    az_advance_warp<GAME>(t, d, g, lane, a, &own, &opp, &player, &n_nodes);
+}
+
+// One ply of batched self-play for every active game, by the game's warp (SelfPlayEngine.play): record the position
+// in the history (trainer.py:241-246), choose the move and the policy target (mcts.py:95-116, players.py:184-189),
+// play it and re-root (mcts.py:118-125), test the new position (othello.py:212-229) and retire finished games.
+// Replaces az_tree_choose + az_tree_advance + az_*_terminal_score + a dozen elementwise launches per ply.
+//   slot_game  game id of every slot (NULL = identity): the history / winner arrays are indexed by game id
+//   h_*        history row of this ply, [n_games]; h_pi [n_games][A]
+//   counters   int64[8] of this ply, zeroed by the caller: [0] games still live after the ply, [1] largest tree (nodes)
+//              among them, [2] simulations of the searches just consumed, [3] moves played, [4] largest tree before
+//              the move (pool high-water mark)
+template <int GAME>
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_move(az_tree t, float temp, const int32_t* __restrict__ slot_game,
+                                                                   uint64_t* __restrict__ h_own, uint64_t* __restrict__ h_opp,
+                                                                   int8_t* __restrict__ h_player, uint8_t* __restrict__ h_live,
+                                                                   float* __restrict__ h_pi, int8_t* __restrict__ winner,
+                                                                   unsigned long long* __restrict__ counters) {
+    using R = az_rules<GAME>;
+    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= t.G) return;
+    const bool live = t.active[g] != 0;
+    if (!live) {
+        if (!slot_game && lane == 0) h_live[g] = 0;
+        return;
+    }
+    const int gid = slot_game ? slot_game[g] : g;
+    const az_dims d = R::dims(t.n, t.height);
+    const int A = R::action_size(d);
+    if (lane == 0) {
+        h_own[gid] = t.root_own[g];
+        h_opp[gid] = t.root_opp[g];
+        h_player[gid] = t.root_player[g];
+        h_live[gid] = 1;
+        atomicAdd(&counters[2], (unsigned long long)t.sims_done[g]);
+        atomicAdd(&counters[3], 1ULL);
+        atomicMax(&counters[4], (unsigned long long)t.n_alloc[g]);
+    }
+    const int a = az_choose_warp<GAME>(t, d, g, lane, temp, h_pi + (size_t)gid * A);
+    __syncwarp();
+    uint64_t own, opp;
+    int player;
+    uint32_t n_nodes;
+    if (!az_advance_warp<GAME>(t, d, g, lane, a, &own, &opp, &player, &n_nodes)) return;
+    bool terminal;
+    az_warp_rules<GAME>::legal(own, opp, d, lane, &terminal);
+    if (lane == 0) {
+        if (terminal) {
+            winner[gid] = (int8_t)R::winner(own, opp, player, d);
+            t.active[g] = 0;
+        } else {
+            atomicAdd(&counters[0], 1ULL);
+            atomicMax(&counters[1], (unsigned long long)n_nodes);
+        }
     }
 }
 
@@ -1153,6 +1228,18 @@ extern "C" int az_tree_advance(const az_tree* t, const uint8_t* action, void* st
     if (!action) return AZ_ERR_ARG;
     AZ_LAUNCH_GAME(t->game, k_tree_advance, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, action);
     AZ_CHECK_LAUNCH("k_tree_advance");
+    return AZ_OK;
+}
+
+extern "C" int az_tree_move(const az_tree* t, float temp, const int32_t* slot_game, uint64_t* h_own, uint64_t* h_opp,
+                            int8_t* h_player, uint8_t* h_live, float* h_pi, int8_t* winner, int64_t* counters,
+                            void* stream) {
+    int rc = az_check_tree(t);
+    if (rc) return rc;
+    if (!h_own || !h_opp || !h_player || !h_live || !h_pi || !winner || !counters || temp < 0.f) return AZ_ERR_ARG;
+    AZ_LAUNCH_GAME(t->game, k_tree_move, az_warp_grid(t->G), AZ_WARPS_PER_CTA * 32, (cudaStream_t)stream, *t, temp,
+                   slot_game, h_own, h_opp, h_player, h_live, h_pi, winner, (unsigned long long*)counters);
+    AZ_CHECK_LAUNCH("k_tree_move");
     return AZ_OK;
 }
 

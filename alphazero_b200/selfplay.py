@@ -191,6 +191,10 @@ class SelfPlayEngine:
         self.h_live = torch.zeros(T, G, dtype=torch.bool, device=dev)
         self.h_pi = torch.zeros(T, G, A, dtype=torch.float32, device=dev)
         self.winner = torch.zeros(G, dtype=torch.int8, device=dev)
+        # per-ply counters written by az_tree_move: live games after the ply, largest re-rooted tree, simulations, moves,
+        # largest tree before the move; mirrored to pinned host memory one small async copy per ply
+        self._counters = torch.zeros(T, 8, dtype=torch.int64, device=dev)
+        self._host_counters = torch.zeros(T, 8, dtype=torch.int64).pin_memory()
         self.total_sims = 0
         self.total_moves = 0
         self.plies_played = 0
@@ -229,8 +233,15 @@ class SelfPlayEngine:
 
     def play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
              start_player: torch.Tensor = None) -> SampleBatch:
-        """Plays G games to the end and returns their samples (device tensors)."""
+        """Plays G games to the end and returns their samples (device tensors).
+
+        Per ply: one search (a CUDA graph replay) and ONE kernel for everything else (az_tree_move: history record,
+        move choice + policy target, re-rooting, terminal test, retiring finished games, counters).  The host only
+        needs to know how many games are still live -- to stop and to move the survivors to a smaller batch (tail
+        tiers); while nearly all games of a large batch are running it reads that number one ply late from pinned
+        memory, so the ply loop never waits for the device."""
         tree, G, spec = self.tree, self.G, self.spec
+        L = _lib.lib()
         if start_own is None:
             tree.reset_roots()
         else:
@@ -240,22 +251,17 @@ class SelfPlayEngine:
         live = term == 0
         self.winner.copy_(win)
         tree.active.copy_(live.to(torch.uint8))
-        sims = torch.zeros((), dtype=torch.int64, device=tree.device)
-        peak = torch.zeros((), dtype=torch.int32, device=tree.device)
+        self.h_live.zero_()          # a tail tier only writes the rows of its own (live) games
+        self._counters.zero_()
+        h_live8 = self.h_live.view(torch.uint8)
         t = 0
-        # `tree` / `evaluator` = the batch the live games are in (the main one, later a tail tier); `idx` = game id of
-        # each of its first k slots (None = identity)
-        evaluator, idx, k = self.evaluator, None, G
+        # `tree` / `evaluator` = the batch the live games are in (the main one, later a tail tier); `slot_game` = game id
+        # of each of its slots (None = identity)
+        evaluator, idx, slot_game = self.evaluator, None, None
         used = [tree]
-        n_live = G
-        while t < self.max_plies:
-            if idx is None:
-                self.h_own[t].copy_(tree.root_own); self.h_opp[t].copy_(tree.root_opp)
-                self.h_player[t].copy_(tree.root_player); self.h_live[t].copy_(live)
-            else:
-                self.h_own[t].index_copy_(0, idx, tree.root_own[:k]); self.h_opp[t].index_copy_(0, idx, tree.root_opp[:k])
-                self.h_player[t].index_copy_(0, idx, tree.root_player[:k])
-                self.h_live[t].zero_(); self.h_live[t].index_copy_(0, idx, live[:k])
+        n_live = known = int(live.sum().item())
+        events = []
+        while t < self.max_plies and n_live > 0:
             # fresh roots only exist on the first move: afterwards the played child always carries visits
             if self.search_events is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -264,45 +270,48 @@ class SelfPlayEngine:
             if self.search_events is not None:
                 e1.record()
                 self.search_events.append((e0, e1, tree.last_search_steps, tree.G))
-            sims += (tree.sims_done.to(torch.int64) * live).sum()
-            peak = torch.maximum(peak, tree.n_alloc[:k].max())
-            temp_t = torch.full((tree.G,), float(self.temp[t]), dtype=torch.float32, device=tree.device)
-            action, pi = tree.choose(temp_t)
-            if idx is None:
-                self.h_pi[t].copy_(pi)
-            else:
-                self.h_pi[t].index_copy_(0, idx, pi[:k])
-            tree.advance(action)
-            term, _, win = spec.terminal_score(tree.root_own, tree.root_opp, tree.root_player)
-            newly = live & (term == 1)
-            if idx is None:
-                self.winner = torch.where(newly, win, self.winner)
-            else:
-                self.winner.index_copy_(0, idx, torch.where(newly[:k], win[:k], self.winner[idx]))
-            live = live & (term == 0)
-            tree.active.copy_(live.to(torch.uint8))
+            _lib.check(L.az_tree_move(tree.desc, float(self.temp[t]), _ptr(slot_game), _ptr(self.h_own[t]), _ptr(self.h_opp[t]),
+                                      _ptr(self.h_player[t]), _ptr(h_live8[t]), _ptr(self.h_pi[t]), _ptr(self.winner),
+                                      _ptr(self._counters[t]), _stream()), "az_tree_move")
+            self._host_counters[t].copy_(self._counters[t], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            events.append(ev)
             t += 1
-            n_live, n_nodes = torch.stack([live.sum(), (tree.n_alloc * live).max().to(torch.int64)]).tolist()
+            # exact count (wait for this ply's counters) in small batches, in the tail tiers and once games have begun
+            # to end; one ply late -- no stall -- while more than 90 % of a large batch is still running
+            lag = 1 if (tree is self.tree and G >= 1024 and known > 0.9 * G) else 0
+            look = t - 1 - lag
+            if look < 0:
+                continue
+            events[look].synchronize()
+            known, n_nodes = int(self._host_counters[look, 0]), int(self._host_counters[look, 1])
+            if lag:
+                continue
+            n_live = known
             if n_live == 0:
                 break
             size = pick_tail_tier(n_live, tree.G, self.tail_tiers)
             if size is not None:
-                sel = torch.nonzero(live).flatten()
+                sel = torch.nonzero(tree.active).flatten()
                 sub, evaluator = self._tier(size)
                 sub.adopt(tree, sel, n_nodes)
                 idx = sel if idx is None else idx[sel]
-                tree, k = sub, n_live
+                slot_game = torch.zeros(sub.G, dtype=torch.int32, device=tree.device)
+                slot_game[:n_live] = idx.to(torch.int32)
+                tree = sub
                 used.append(tree)
-                live = tree.active.bool()
+        torch.cuda.current_stream().synchronize()
         for tr in used:
             tr.check_status()
-        if n_live > 0:
+        cnt = self._host_counters[:t]
+        if int(cnt[t - 1, 0]) > 0 if t > 0 else n_live > 0:
             raise RuntimeError(f"self-play did not finish within max_plies={self.max_plies}")
-        self.plies_played = t
-        self.total_sims = int(sims.item())
-        self.max_nodes_used = int(peak.item())
+        self.plies_played = int((cnt[:, 3] > 0).sum())
+        self.total_sims = int(cnt[:, 2].sum())
+        self.total_moves = int(cnt[:, 3].sum())
+        self.max_nodes_used = int(cnt[:, 4].max()) if t > 0 else 0
         mask = self.h_live[:t]                                   # [t, G]
-        self.total_moves = int(mask.sum().item())
         move_idx, episode_idx = torch.nonzero(mask.t(), as_tuple=True)[::-1]   # ordered by episode, then move
         own = self.h_own[:t].t()[mask.t()]
         opp = self.h_opp[:t].t()[mask.t()]

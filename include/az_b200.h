@@ -244,6 +244,20 @@ int az_tree_choose(const az_tree* t, const float* temp, uint8_t* action, float* 
  * AZ_STATUS_ILLEGAL and leave the game untouched. */
 int az_tree_advance(const az_tree* t, const uint8_t* action, void* stream);
 
+/* One ply of batched self-play for every active game (AlphaZeroTrainer.self_play's inner loop, trainer.py:236-262, for
+ * all games at once): records the position and the policy target of the ply, chooses the move like az_tree_choose with
+ * temperature `temp` for all games (schedulers.py), plays it and re-roots like az_tree_advance, and retires the games
+ * that are over (active[g] = 0, winner[game] = absolute id of the winner, othello.py:221-229).
+ *   slot_game  int32 [G] game id of every slot of this tree batch, or NULL (slot = game); the arrays below are indexed
+ *              by game id
+ *   h_own, h_opp, h_player, h_live   this ply's row of the history: root position before the move, 1 in h_live
+ *              (identity mapping: 0 for inactive slots; with slot_game the caller pre-zeroes the row)
+ *   h_pi       this ply's policy targets, [games][action_size] in network order
+ *   counters   int64 [8], caller-zeroed: [0] live games after the ply, [1] the largest re-rooted tree among them
+ *              (nodes), [2] sum of sims_done of the moved games, [3] moves played, [4] the largest tree before the move */
+int az_tree_move(const az_tree* t, float temp, const int32_t* slot_game, uint64_t* h_own, uint64_t* h_opp,
+                 int8_t* h_player, uint8_t* h_live, float* h_pi, int8_t* winner, int64_t* counters, void* stream);
+
 /* Deterministic hash evaluator (test double for PolicyValueNetwork.evaluate, see tests/hash_eval.py):
  * probs[g][a] = q/4096 for a < action_size, value[g] in {-256..255}/256 from (own, opp, salt). */
 int az_eval_hash(const uint64_t* own, const uint64_t* opp, int action_size, int64_t G, uint64_t salt, float* probs,
