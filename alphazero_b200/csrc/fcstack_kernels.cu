@@ -21,9 +21,14 @@
 // in [384, 512): no accumulator is reused, so the MMA warp never waits for an epilogue.  The epilogue warps turn a
 // finished accumulator into bf16 blocks of the next layer's K-chunk width (bias + ReLU, BatchNorm folded on the
 // host), store them as packed A blocks and signal a per-block `ready` barrier in all NS CTAs of the row tile
-// (remote mbarrier arrive); the producer of the next layer waits for the block it is about to fetch, and fetches the
-// blocks in the order they are produced.  The heads' epilogue adds the bias and writes the bf16 logits row that the
-// tree step (az_tree.logits) or az_net_heads reads.
+// (remote mbarrier arrive); the producer of the next layer waits for the blocks it is about to fetch.  The heads'
+// epilogue adds the bias and writes the bf16 logits row that the tree step (az_tree.logits) or az_net_heads reads.
+//
+// Warp roles (19 warps): 0-15 epilogue (warp % 4 = TMEM lane quarter, warp / 4 = which 64-column block of the layer's
+// output), 16 / 17 producers of the weight / activation blocks (one lane each: a bulk copy costs its issuing thread ~370
+// cycles), 18 MMA issue.  What the cycle stamps of az_net_fcstack_debug showed, and what was tried and dropped
+// (multicast, a cp.async loader path beside the bulk-copy unit, cluster-scope acquires in the producer), is in
+// profiles/r2_fcstack_experiments.txt.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -33,10 +38,17 @@
 #include "common.cuh"
 #include "umma.cuh"
 
+// Operand ring: 192 KB cut into 4 slots of 48 KB for fc1 (A: 64 K x 128 rows = 16 KB, B: 64 K x 256 columns = 32 KB) and
+// into 3 slots of 64 KB for fc2 / the heads, whose stages hold TWO 64-wide K chunks (A 32 KB + B up to 32 KB): half as
+// many stage hand-overs (barrier waits, commits, bulk-copy issues -- ~370 cycles per copy for the issuing thread) per
+// tcgen05.mma.  The two sets have their own barriers; fc2's first fill waits until fc1's last MMA has completed.
 #define FS_STAGES 4
-#define FS_A_BYTES 16384                      // one A stage: 64 (K) x 128 rows bf16
-#define FS_B_BYTES 32768                      // one B stage: 64 (K) x 256 columns bf16
+#define FS_A_BYTES 16384
+#define FS_B_BYTES 32768
 #define FS_STAGE_BYTES (FS_A_BYTES + FS_B_BYTES)
+#define FS_STAGES2 3
+#define FS_A2_BYTES 32768
+#define FS_STAGE2_BYTES 65536
 #define FS_EPI_WARPS 16                       // warps 0-15: epilogue (warp % 4 = TMEM lane quarter, warp / 4 = output block)
 #define FS_PRODUCER_WARP FS_EPI_WARPS         // warp 16: bulk copies of the B (weight) blocks, one lane
 #define FS_PRODUCER_A_WARP (FS_EPI_WARPS + 1) // warp 17: bulk copies of the A (activation) blocks, one lane.  Issuing a
@@ -48,14 +60,17 @@
 #define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
 #define FB_FULL 0
 #define FB_EMPTY (FB_FULL + FS_STAGES)
-#define FB_ACC (FB_EMPTY + FS_STAGES)
+#define FB_FULL2 (FB_EMPTY + FS_STAGES)
+#define FB_EMPTY2 (FB_FULL2 + FS_STAGES2)
+#define FB_ACC (FB_EMPTY2 + FS_STAGES2)
 #define FB_READY (FB_ACC + 3)                 // [2][FS_MAX_CHUNKS]: block kc of h1 / h2 of this row tile is in global memory
 #define FB_COUNT (FB_READY + 2 * FS_MAX_CHUNKS)
 #define FS_SM_BIAS (FS_STAGES * FS_STAGE_BYTES)
 #define FS_SM_BARS (FS_SM_BIAS + FS_BIAS_FLOATS * 4)
-#define FS_SM_TMEM_PTR (FS_SM_BARS + 8 * 48)
+#define FS_SM_TMEM_PTR (FS_SM_BARS + 8 * 56)
 #define FS_SM_TOTAL (FS_SM_TMEM_PTR + 16)
-static_assert(FB_COUNT <= 48, "barrier area");
+static_assert(FB_COUNT <= 56, "barrier area");
+static_assert(FS_STAGES2 * FS_STAGE2_BYTES <= FS_STAGES * FS_STAGE_BYTES, "both slot sets share the ring");
 static_assert(FS_SM_TOTAL <= 232448, "shared memory per CTA on sm_100");
 
 struct FcStackParams {
@@ -168,6 +183,27 @@ __device__ __forceinline__ void fs_tmem_ld16(uint32_t taddr, uint32_t* r) {
         : "r"(taddr) : "memory");
 }
 
+// Stage geometry of layer L, the same in every role: K chunks per stage, stage-iterations, slot size / count, offset of
+// the B block inside a slot and the first full barrier of the layer's slot set (its empty barriers follow).
+struct FsGeom {
+    int chunks, iters, slots;
+    uint32_t slot_bytes, b_off, bar_full, bar_empty;
+};
+__device__ __forceinline__ FsGeom fs_geom(const FcStackParams& p, int L, uint32_t bars) {
+    FsGeom g;
+    const int nch = p.K[L] / p.kch[L];
+    if (L == 0) {
+        g.chunks = 1; g.slots = FS_STAGES; g.slot_bytes = FS_STAGE_BYTES; g.b_off = FS_A_BYTES;
+        g.bar_full = bars + 8 * FB_FULL; g.bar_empty = bars + 8 * FB_EMPTY;
+    } else {
+        g.chunks = (p.kch[L] == 64 && (nch & 1) == 0) ? 2 : 1;
+        g.slots = FS_STAGES2; g.slot_bytes = FS_STAGE2_BYTES; g.b_off = FS_A2_BYTES;
+        g.bar_full = bars + 8 * FB_FULL2; g.bar_empty = bars + 8 * FB_EMPTY2;
+    }
+    g.iters = nch / g.chunks;
+    return g;
+}
+
 __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -186,7 +222,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const uint32_t all_mask = (1u << rank) | (mc_a ? a_mask : 0u) | (mc_b ? b_mask : 0u);   // CTAs this one sends stage data to
 
     const uint32_t bars = smem_u32(smem + FS_SM_BARS);
-    const uint32_t bar_full0 = bars + 8 * FB_FULL, bar_empty0 = bars + 8 * FB_EMPTY, bar_acc0 = bars + 8 * FB_ACC;
+    const uint32_t bar_acc0 = bars + 8 * FB_ACC;
     const uint32_t bar_ready0 = bars + 8 * FB_READY;
     float* bias_s = reinterpret_cast<float*>(smem + FS_SM_BIAS);
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + FS_SM_TMEM_PTR);
@@ -196,7 +232,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     // ---- setup: barriers, biases of this column slice (weights: not produced by the preceding kernel), TMEM
     if (tid < FB_COUNT) {      // one barrier per thread
         uint32_t count = 1u;                                                      // acc[L]: one tcgen05.commit
-        if (tid < FB_EMPTY) count = 1u;                                           // full[s]: the producer's expect_tx
+        if (tid < FB_EMPTY || (tid >= FB_FULL2 && tid < FB_EMPTY2)) count = 1u;   // full[s]: the producer's expect_tx
         else if (tid < FB_ACC) count = (uint32_t)__popc(all_mask);                // empty[s]: one commit per receiving CTA
         else if (tid >= FB_READY) count = 4u;                                     // ready[block]: the four quarter warps
         mbar_init(bars + 8 * tid, count);
@@ -216,31 +252,28 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     if (dbg && tid == 0) dbg[1] = clock64() - t_entry;
 
     if (warp == FS_PRODUCER_WARP) {
-        // ================================================================== producer: one lane issues every copy
+        // ================================================================== producer of the weight blocks (one lane)
         if (lane == 0) {
             uint32_t it = 0;
             long long w_empty = 0, w_ready = 0;
 #pragma unroll
             for (int L = 0; L < 3; ++L) {
-                const int kch = p.kch[L], nch = p.K[L] / kch;
-                const uint32_t a_bytes = (uint32_t)kch * 256u, b_bytes = (uint32_t)kch * (uint32_t)p.Nc[L] * 2u;
-                // with multicast this CTA fetches part c of the A block / part r of the B block for its whole group
-                const uint32_t a_part = mc_a ? a_bytes / (uint32_t)NS : a_bytes, b_part = mc_b ? b_bytes / (uint32_t)RT : b_bytes;
-                const uint32_t a_skip = mc_a ? (uint32_t)c * a_part : 0u, b_skip = mc_b ? (uint32_t)r * b_part : 0u;
-                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + a_skip;
-                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * nch * b_bytes + b_skip;
-                const int bps = nch / NS;                     // blocks the epilogue of one CTA produced (L > 0)
-                for (int q = 0; q < nch; ++q, ++it) {
-                    // L > 0: fetch in production order -- block j of every column slice, then block j + 1
-                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
-                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+                const FsGeom g = fs_geom(p, L, bars);
+                if (L == 1) { it = 0; fs_mbar_wait(bar_acc0, 0u); }      // the 64 KB slots overlay fc1's: fc1 must be done
+                const uint32_t a_bytes = (uint32_t)(g.chunks * p.kch[L]) * 256u;
+                const uint32_t b_bytes = (uint32_t)(g.chunks * p.kch[L]) * (uint32_t)p.Nc[L] * 2u;
+                // with multicast this CTA fetches part r of the B block for its whole column group
+                const uint32_t b_part = mc_b ? b_bytes / (uint32_t)RT : b_bytes, b_skip = mc_b ? (uint32_t)r * b_part : 0u;
+                const uint8_t* b_src = p.wblob + p.w_off[L] + (size_t)c * g.iters * b_bytes + b_skip;
+                for (int q = 0; q < g.iters; ++q, ++it) {
+                    const uint32_t s = it % (uint32_t)g.slots, ph = (it / (uint32_t)g.slots) & 1u;
                     const long long c0 = dbg ? clock64() : 0;
-                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
+                    fs_mbar_wait(g.bar_empty + 8 * s, ph ^ 1u);
                     const long long c1 = dbg ? clock64() : 0;
-                    const uint32_t full = bar_full0 + 8 * s;
-                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
+                    const uint32_t full = g.bar_full + 8 * s;
                     fs_expect_tx(full, a_bytes + b_bytes);      // the A bytes come from the other producer warp
-                    fs_bulk_copy(sb + b_skip, b_src + (size_t)kc * b_bytes, b_part, full, b_mask, mc_b);
+                    fs_bulk_copy(smem_u32(smem) + s * g.slot_bytes + g.b_off + b_skip, b_src + (size_t)q * b_bytes, b_part,
+                                 full, b_mask, mc_b);
                     if (dbg) { w_empty += c1 - c0; w_ready += clock64() - c1; if (q == 0) dbg[26 + L] = c0 - t_entry; }
                 }
             }
@@ -248,27 +281,28 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
         }
         __syncwarp();
     } else if (warp == FS_PRODUCER_A_WARP) {
-        // ================================================================== producer of the activation blocks
+        // ================================================================== producer of the activation blocks (one lane)
         if (lane == 0) {
             uint32_t it = 0;
 #pragma unroll
             for (int L = 0; L < 3; ++L) {
-                const int kch = p.kch[L], nch = p.K[L] / kch;
-                const uint32_t a_bytes = (uint32_t)kch * 256u;
-                const uint32_t a_part = mc_a ? a_bytes / (uint32_t)NS : a_bytes;
-                const uint32_t a_skip = mc_a ? (uint32_t)c * a_part : 0u;
-                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * nch * a_bytes + a_skip;
-                const int bps = nch / NS;
-                for (int q = 0; q < nch; ++q, ++it) {
-                    const int kc = L == 0 ? q : (q % NS) * bps + q / NS;
-                    const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
-                    fs_mbar_wait(bar_empty0 + 8 * s, ph ^ 1u);
-                    // The writers made their stores visible at cluster scope before the (release) arrive that completes
-                    // this barrier, and the copy below reads the L2, so observing the barrier is enough: a cluster-scope
+                const FsGeom g = fs_geom(p, L, bars);
+                if (L == 1) { it = 0; fs_mbar_wait(bar_acc0, 0u); }
+                const uint32_t a_bytes = (uint32_t)(g.chunks * p.kch[L]) * 256u;
+                const uint32_t a_part = mc_a ? a_bytes / (uint32_t)NS : a_bytes, a_skip = mc_a ? (uint32_t)c * a_part : 0u;
+                const uint8_t* a_src = (L == 0 ? p.x : (L == 1 ? p.h1 : p.h2)) + (size_t)m * g.iters * a_bytes + a_skip;
+                for (int q = 0; q < g.iters; ++q, ++it) {
+                    const uint32_t s = it % (uint32_t)g.slots, ph = (it / (uint32_t)g.slots) & 1u;
+                    fs_mbar_wait(g.bar_empty + 8 * s, ph ^ 1u);
+                    // h1 / h2 blocks in ascending K order (all blocks of column slice 0, then slice 1, ...).  The writers
+                    // made their stores visible at cluster scope before the (release) arrive that completes a block's
+                    // barrier, and the copy below reads the L2, so observing the barrier is enough: a cluster-scope
                     // acquire + proxy fence here cost ~540 cycles per stage (profiles/r2_fcstack_experiments.txt).
-                    if (L > 0) fs_mbar_wait(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + kc), 0u);
-                    fs_bulk_copy(smem_u32(smem + s * FS_STAGE_BYTES) + a_skip, a_src + (size_t)kc * a_bytes, a_part,
-                                 bar_full0 + 8 * s, a_mask, mc_a);
+                    if (L > 0)
+                        for (int i = 0; i < g.chunks; ++i)
+                            fs_mbar_wait(bar_ready0 + 8 * ((L - 1) * FS_MAX_CHUNKS + q * g.chunks + i), 0u);
+                    fs_bulk_copy(smem_u32(smem) + s * g.slot_bytes + a_skip, a_src + (size_t)q * a_bytes, a_part,
+                                 g.bar_full + 8 * s, a_mask, mc_a);
                 }
             }
         }
@@ -279,30 +313,32 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
         long long w_full = 0, t_issue = 0;
 #pragma unroll
         for (int L = 0; L < 3; ++L) {
-            const int kch = p.kch[L], nch = p.K[L] / kch, ksteps = kch >> 4;
+            const FsGeom g = fs_geom(p, L, bars);
+            if (L == 1) it = 0;
+            const int ksteps = g.chunks * (p.kch[L] >> 4);
             const uint32_t nc = (uint32_t)p.Nc[L];
             const uint32_t idesc = umma_idesc_bf16_m128(nc);
             const uint32_t d_tmem = tmem_base + col_off[L];
-            for (int q = 0; q < nch; ++q, ++it) {
-                const uint32_t s = it % FS_STAGES, ph = (it / FS_STAGES) & 1u;
+            for (int q = 0; q < g.iters; ++q, ++it) {
+                const uint32_t s = it % (uint32_t)g.slots, ph = (it / (uint32_t)g.slots) & 1u;
                 const long long c0 = dbg ? clock64() : 0;
-                fs_mbar_wait(bar_full0 + 8 * s, ph);
+                fs_mbar_wait(g.bar_full + 8 * s, ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const long long c1 = dbg ? clock64() : 0;
                 if (dbg && lane == 0) { w_full += c1 - c0; if (q == 0) dbg[2 + L * 6] = c1 - t_entry; }
                 if (elect_one()) {
-                    const uint32_t sa = smem_u32(smem + s * FS_STAGE_BYTES), sb = sa + FS_A_BYTES;
+                    const uint32_t sa = smem_u32(smem) + s * g.slot_bytes, sb = sa + g.b_off;
                     for (int k = 0; k < ksteps; ++k) {
                         const uint64_t ad = umma_desc(sa + (uint32_t)k * 4096u, 2048u, 128u);
                         const uint64_t bd = umma_desc(sb + (uint32_t)k * 32u * nc, 16u * nc, 128u);
                         umma_bf16(d_tmem, ad, bd, idesc, (q | k) ? 1u : 0u);
                     }
-                    if (mc_any) fs_commit_multicast(bar_empty0 + 8 * s, all_mask);
-                    else umma_commit(bar_empty0 + 8 * s);
-                    if (q == nch - 1) umma_commit(bar_acc0 + 8 * L);
+                    if (mc_any) fs_commit_multicast(g.bar_empty + 8 * s, all_mask);
+                    else umma_commit(g.bar_empty + 8 * s);
+                    if (q == g.iters - 1) umma_commit(bar_acc0 + 8 * L);
                 }
                 __syncwarp();
-                if (dbg && lane == 0) { const long long c2 = clock64(); t_issue += c2 - c1; if (q == nch - 1) dbg[3 + L * 6] = c2 - t_entry; }
+                if (dbg && lane == 0) { const long long c2 = clock64(); t_issue += c2 - c1; if (q == g.iters - 1) dbg[3 + L * 6] = c2 - t_entry; }
             }
         }
         if (dbg && lane == 0) { dbg[22] = w_full; dbg[23] = t_issue; }

@@ -12,6 +12,7 @@ import torch
 
 from . import _lib
 from . import boardops as bo
+from .boardops import _ptr, _stream
 from .engine import TreeBatch
 from .fused_net import make_evaluator
 from .gamespec import as_spec

@@ -45,7 +45,11 @@ def parse_args():
     ap.add_argument("--game", default="othello", choices=["othello", "connect4"],
                     help="othello: BASELINE config 3/4 (the headline); connect4: config 5 (7x6, Connect4Net)")
     ap.add_argument("--net", default="fused", choices=["fused", "torch"],
-                    help="fused: hand-written tcgen05 trunk + fused heads; torch: the module's own bf16 forward")
+                    help="fused: hand-written tcgen05 trunk + fc stack; torch: the module's own bf16 forward")
+    ap.add_argument("--leaves", type=int, default=4,
+                    help="also measure throughput mode with this many leaves in flight per game (0 = skip); the headline "
+                         "stays the reference's order, one leaf per game per step")
+    ap.add_argument("--no-extras", action="store_true", help="skip the extra.* measurements (configs 2, 4, 5, strong scaling)")
     return ap.parse_args()
 
 
@@ -248,9 +252,10 @@ def run_ours(args):
                 getattr(ev, "n_calls", 0) * getattr(ev, "own_kernels_per_call", 0)
         return c
 
-    def timed(fn, steps):
-        sampler = ClockSampler(local_rank)
-        sampler.start()
+    def timed(fn, steps, sample=True):
+        sampler = ClockSampler(local_rank) if sample else None
+        if sampler:
+            sampler.start()
         barrier()
         launches0 = counted_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -265,7 +270,7 @@ def run_ours(args):
         e1.record()
         barrier()
         wall = time.time() - t0
-        clocks = sampler.stop()
+        clocks = sampler.stop() if sampler else None
         ms = max(e0.elapsed_time(e1), 0.0)
         stats = torch.tensor([ms, wall * 1000.0], dtype=torch.float64, device=dev)
         tot = torch.tensor([sims, moves, games], dtype=torch.float64, device=dev)
@@ -278,9 +283,22 @@ def run_ours(args):
                 # and the tree steps / evaluator kernels replayed inside whole-search graphs
                 "launches": counted_launches() - launches0}
 
-    dev_run = timed(step_device, args.steps)
     step_e2e()          # warm-up of the end-to-end path (pinned staging buffers of the device->host read)
-    e2e_run = timed(step_e2e, args.steps)
+    # device-resident and end-to-end steps alternate, so that the two numbers see the same clocks and the same box
+    dev_run = e2e_run = None
+    sampler = ClockSampler(local_rank)      # one clock record over the whole timed region (both kinds of step)
+    sampler.start()
+    for _ in range(args.steps):
+        a = timed(step_device, 1, sample=False)
+        b = timed(step_e2e, 1, sample=False)
+        if dev_run is None:
+            dev_run, e2e_run = a, b
+        else:
+            for acc, x in ((dev_run, a), (e2e_run, b)):
+                for key in ("ms", "wall_ms", "sims", "moves", "games", "launches"):
+                    acc[key] += x[key]
+                acc["last"] = x["last"]
+    dev_run["clocks"] = e2e_run["clocks"] = sampler.stop()
     # the e2e region includes host-side packing, so its clock is the wall clock between the two barriers
     e2e_ms = max(e2e_run["ms"], e2e_run["wall_ms"])
     batch, host = e2e_run["last"]

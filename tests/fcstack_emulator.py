@@ -54,7 +54,7 @@ def emulate(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int,
             bps = nch // NS
             acc = {(r, c): np.zeros((128, Nc[L]), np.float32) for r in range(RT) for c in range(NS)}
             for q in range(nch):
-                kc = q if L == 0 else (q % NS) * bps + q // NS
+                kc = q          # ascending K: all blocks of column slice 0, then slice 1, ...
                 # every CTA's stage after all issuers' (multicast) parts have landed
                 stage_a = {r: np.zeros(a_bytes, np.uint8) for r in range(RT)}
                 stage_b = {c: np.zeros(b_bytes, np.uint8) for c in range(NS)}
