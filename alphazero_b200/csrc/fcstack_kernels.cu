@@ -210,6 +210,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     const int RT = p.RT, NS = p.NS;
     long long* dbg = p.debug ? p.debug + (size_t)blockIdx.x * 32 : nullptr;
     const long long t_entry = dbg ? clock64() : 0;
+    if (dbg && tid == 0) { unsigned long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt)); dbg[25] = (long long)gt; }
     uint32_t rank, cluster_id;
     asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     asm("mov.u32 %0, %%clusterid.x;" : "=r"(cluster_id));
@@ -441,7 +442,10 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     fs_cluster_sync();
-    if (dbg && tid == 0) dbg[24] = clock64() - t_entry;
+    if (dbg && tid == 0) {
+        dbg[24] = clock64() - t_entry;
+        unsigned long long gt; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt)); dbg[19] = (long long)gt;
+    }
     if (warp == FS_MMA_WARP)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
 }

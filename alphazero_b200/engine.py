@@ -72,10 +72,11 @@ class TreeBatch:
         self.n_slots = self.G * (self.leaves or 1)       # leaf slots the evaluator sees
         if capacity is None:
             # per search at most (n_sim + 1) child blocks are added and the re-rooted subtree is kept.  Measured on
-            # Othello 8x8 self-play (n_sim = 200, tools/pool_use.py): the fullest of 4096 games peaks at 5.4-7.6 k nodes,
-            # but over several hundred thousand games 48 * (n_sim + 1) = 9.6 k was exceeded once -- so the default is
-            # 4x that (10 GB for 4096 games, of 180 GB).  Overflow is detected (status bit) and raised, never silent.
-            capacity = max(1024, 192 * (n_sim_hint + 1))
+            # Othello 8x8 self-play (n_sim = 200, tools/pool_use.py): the fullest of 4096 games peaks at 5.4-7.6 k nodes
+            # and over several hundred thousand games 48 * (n_sim + 1) = 9.6 k was exceeded once -- the default is twice
+            # that (5 GB for 4096 games).  Overflow is detected (status bit) and raised, never silent; SelfPlayEngine
+            # answers it by doubling the pools and replaying the batch.
+            capacity = max(1024, 96 * (n_sim_hint + 1))
         self.capacity = int(capacity)
         self.max_depth = int(max_depth)
         dev = self.device

@@ -236,15 +236,16 @@ class FusedNetEvaluator:
 
     def _stack_shape(self, G: int, N1: int):
         """(RT, NS) of the az_net_fcstack clusters: NS column slices so that a slice of fc1 fits one accumulator
-        (N1/NS <= 256), RT = 2 row tiles per cluster (the weights leave the L2 once per two tiles) when there are
-        at least two."""
+        (N1/NS <= 256), one row tile per cluster.  Clusters of 4 all fit the GPU at once (32 of them at 4096 positions);
+        clusters of 8 (RT = 2, the weights multicast over two row tiles) do not -- the 16th waits for a second wave,
+        which doubles the kernel's latency (measured: 37 us against 19.5 us, profiles/r2_fcstack_experiments.txt)."""
         shape = self.stack_shape
         if shape is None and os.environ.get("AZ_B200_FCSTACK"):
             shape = tuple(int(v) for v in os.environ["AZ_B200_FCSTACK"].split(","))
         if shape is not None:
             return int(shape[0]), int(shape[1])
         NS = max(1, N1 // 256)
-        RT = 2 if (G + 127) // 128 >= 2 and NS * 2 <= 8 else 1
+        RT = 1
         return RT, NS
 
     def features_rowmajor(self) -> torch.Tensor:

@@ -157,6 +157,12 @@ class SelfPlayEngine:
                  tie_random: bool = True, device="cuda", max_plies: int = 128, evaluator=None,
                  network_path: str = "auto", tail_tiers="auto", evaluator_factory=None, leaves: int = None):
         # `n`: Othello board size or a GameSpec (gamespec.Connect4Spec(7, 6) for BASELINE config 5)
+        self._ctor = dict(nn=nn, G=G, n=n, n_sim=n_sim, dirichlet_alpha=dirichlet_alpha, dirichlet_epsilon=dirichlet_epsilon,
+                          temp_scheduler_type=temp_scheduler_type, temp_max_step=temp_max_step, temp_min_step=temp_min_step,
+                          seed=seed, dtype=dtype, capacity=capacity, tie_random=tie_random, device=device,
+                          max_plies=max_plies, evaluator=evaluator, network_path=network_path, tail_tiers=tail_tiers,
+                          evaluator_factory=evaluator_factory, leaves=leaves)
+        self.pool_grows = getattr(self, "pool_grows", 0)
         self.spec = spec = as_spec(n)
         self.G, self.n, self.n_sim = G, spec.n, n_sim
         self.max_plies = max_plies
@@ -234,7 +240,28 @@ class SelfPlayEngine:
 
     def play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
              start_player: torch.Tensor = None) -> SampleBatch:
-        """Plays G games to the end and returns their samples (device tensors).
+        """Plays G games to the end and returns their samples (device tensors).  A node pool that turns out too small
+        (the default is sized from measurements, not from the worst case) is answered by doubling every pool and
+        replaying the batch -- never by dropping simulations."""
+        while True:
+            try:
+                return self._play(start_own, start_opp, start_player)
+            except RuntimeError as e:
+                if "node pool overflow" not in str(e) or self._ctor["evaluator"] is not None or self.pool_grows >= 4:
+                    raise
+                grows, events, nn = self.pool_grows + 1, self.search_events, self._tier_args["nn"]
+                kw = dict(self._ctor, capacity=2 * self.tree.capacity, nn=nn)
+                for tr, _ in self.trees():
+                    tr.nodes = None                      # release the old pools before the larger ones are allocated
+                self._tiers.clear()
+                torch.cuda.empty_cache()
+                self.pool_grows = grows
+                self.__init__(**kw)
+                self.search_events = events
+
+    def _play(self, start_own: torch.Tensor = None, start_opp: torch.Tensor = None,
+              start_player: torch.Tensor = None) -> SampleBatch:
+        """One attempt of play().
 
         Per ply: one search (a CUDA graph replay) and ONE kernel for everything else (az_tree_move: history record,
         move choice + policy target, re-rooting, terminal test, retiring finished games, counters).  The host only

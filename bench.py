@@ -333,6 +333,7 @@ def run_ours(args):
     engine.search_events = None
     step_ms = full_ms / max(1, search_steps)
     eval_ms, tree_ms, timing = eager_eval_ms, eager_tree_ms, "eager calls between CUDA events"
+    kernel_ms = None
     if hasattr(engine.evaluator, "enqueue") and tree.graph_search:
         K = 64
         net_graph = torch.cuda.CUDAGraph()
@@ -349,17 +350,43 @@ def run_ours(args):
         torch.cuda.synchronize()
         eval_ms = g0.elapsed_time(g1) / (8 * K)
         tree_ms = max(step_ms - eval_ms, 1e-6)
+        ev = engine.evaluator
+        if getattr(ev, "heads", None) == "stack":      # the two hand-written kernels of the forward, each alone in a graph
+            def in_graph(fn, reps=32):
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr):
+                    for _ in range(reps):
+                        fn()
+                gr.replay(); torch.cuda.synchronize()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                for _ in range(8):
+                    gr.replay()
+                a1.record(); torch.cuda.synchronize()
+                return a0.elapsed_time(a1) / (8 * reps)
+            L = _lib.lib()
+            stream = lambda: torch.cuda.current_stream().cuda_stream
+            kernel_ms = {"k_net_trunk": in_graph(ev.trunk),
+                         "k_net_fcstack": in_graph(lambda: _lib.check(L.az_net_fcstack(
+                             ev.features.data_ptr(), ev.stack_blob.data_ptr(), ev.h1.data_ptr(), ev.h2.data_ptr(),
+                             ev.logits.data_ptr(), ev.ld, ev.A + 1, ev.tree.G, ev.K1, ev.N1, ev.N2, ev.RT, ev.NS, stream()),
+                             "az_net_fcstack"))}
         timing = ("inside CUDA graphs: forward = 64 forwards back to back in one graph; tree step = "
                   "(search time / simulation steps) - forward")
         del net_graph
     tflops = G * flop_per_eval / (eval_ms * 1e-3) / 1e12
     roofline = {
-        "bound": "tensor", "kernel": f"policy-value network forward over the leaf batch (bf16, CUDA graph, path={args.net})",
+        "bound": "tensor",
+        "kernel": "policy-value network forward over the leaf batch = k_net_trunk (conv1-4, tcgen05) + k_net_fcstack "
+                  "(fc1, fc2, heads, tcgen05 cluster kernel), both hand-written, bf16, inside the whole-search CUDA graph"
+                  if args.net == "fused" else "the torch module's own bf16 forward (library kernels)",
+        "library_share": 0.0 if args.net == "fused" else 1.0,
+        "kernel_ms_alone_in_graph": kernel_ms,
         "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": tflops / peaks["bf16_tflops_sustained"], "peak_source": peaks["source"] + " (sustained: timed inside a long step)",
-        "traffic": ncu_traffic("k_net_trunk") if args.net == "fused" else None,
-        "traffic_note": "DRAM bytes per k_net_trunk launch (ncu --set full, profiles/r1_ncu_full_summary.txt); "
-                        "activations never leave shared memory, features stay in L2 for the fc GEMMs",
+        "traffic": ncu_traffic("k_net_trunk", ("r2_ncu_full_summary.json", "r1_ncu_full_summary.json")) if args.net == "fused" else None,
+        "traffic_note": "DRAM bytes per k_net_trunk launch (ncu --set full summary under profiles/); activations never "
+                        "leave shared memory, features / h1 / h2 stay in the L2 for the fc stack",
         "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
         "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
         "search_share_of_batch": search_ms / (dev_run["ms"] / args.steps),
@@ -378,6 +405,92 @@ def run_ours(args):
                      # else the shallow trees of the n_sim = 8 capture
                      "traffic": ncu_traffic("k_tree_step", ("r1_ncu_tree_midgame.json", "r1_ncu_full_summary.json"))}
 
+    capacity_used, peak_used, tiers_used, pool_gb = tree.capacity, engine.max_nodes_used, list(engine.tail_tiers), tree.nodes.numel() / 1e9
+    extra = {}
+    if not args.no_extras:
+        # free the headline engine's pools before the other configurations allocate theirs
+        del prof, tree
+        ev = batch = host = None
+        dev_run["last"] = e2e_run["last"] = None
+        engine = None
+        torch.cuda.empty_cache()
+
+        def side_run(label, game="othello", games=G, sims=n_sim, leaves=None, warm=1):
+            """One more configuration, one timed batch: value = simulations of all ranks / max-over-ranks device time."""
+            try:
+                torch.manual_seed(0)
+                if game == "connect4":
+                    from alphazero_b200.games.connect4 import Connect4Net
+                    from alphazero_b200.gamespec import Connect4Spec
+                    sp, nt = Connect4Spec(7, 6), Connect4Net(board_width=7, board_height=6)
+                else:
+                    from alphazero_b200.gamespec import OthelloSpec
+                    sp, nt = OthelloSpec(8), OthelloNet(n=8)
+                eng = SelfPlayEngine(nt, games, n=sp, n_sim=sims, dirichlet_alpha=0.03, dirichlet_epsilon=0.25,
+                                     temp_scheduler_type="linear", temp_max_step=4, temp_min_step=4,
+                                     seed=0x5EED + 7919 * rank, dtype=torch.bfloat16, device=dev, network_path=args.net,
+                                     leaves=leaves)
+
+                def one():
+                    b = eng.play()
+                    if world > 1:
+                        from alphazero_b200.distributed import gather_samples
+                        b = gather_samples(b, episode_offset=rank * games)
+                    return b
+                for _ in range(warm):
+                    one()
+                barrier()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                one()
+                a1.record()
+                barrier()
+                st = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device=dev)
+                tot = torch.tensor([eng.total_sims, eng.total_moves], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(st, op=dist.ReduceOp.MAX)
+                    dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+                out = {"value": float(tot[0]) / (float(st[0]) * 1e-3), "unit": UNIT, "ms_per_step": float(st[0]),
+                       "games_per_gpu": games, "games_total": games * world, "n_sim": sims, "game": game,
+                       "leaves_in_flight_per_game": leaves or 1, "pool_grows": eng.pool_grows}
+                del eng
+                torch.cuda.empty_cache()
+                return out
+            except Exception as e:          # an extra must not take the headline line down with it
+                return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+        if args.game == "othello":
+            if args.leaves and args.leaves > 1:
+                extra["throughput_mode"] = side_run("throughput", leaves=args.leaves)
+                extra["throughput_mode"]["note"] = ("same workload, up to %d leaves of a game in flight per step under virtual "
+                                                    "loss (an extension: the headline keeps the reference's order)" % args.leaves)
+            if G == 4096 and n_sim == 200:
+                total = 32768
+                if total % world == 0:
+                    extra["strong_scaling"] = side_run("strong", games=total // world)
+                    extra["strong_scaling"]["note"] = "SURVEY 8(d) config 4 strong scaling: 32 768 games in total at every N"
+                if world == 8:
+                    extra["config4"] = side_run("config4", sims=400)
+                    extra["config5"] = side_run("config5", game="connect4", games=2048)
+            if world == 1:
+                try:        # BASELINE config 2: board kernels alone
+                    b9 = {}
+                    for name, fn in (("perft9", lambda: bo.perft(8, 9)),
+                                     ("playouts_1M", lambda: bo.playouts(
+                                         torch.tensor([bo.to_i64(spec.start_position()[0])], dtype=torch.int64, device=dev),
+                                         torch.tensor([bo.to_i64(spec.start_position()[1])], dtype=torch.int64, device=dev),
+                                         torch.ones(1, dtype=torch.int8, device=dev), 8, 1_000_000, 0x5EED))):
+                        fn(); torch.cuda.synchronize()
+                        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        a0.record(); res = fn(); a1.record(); torch.cuda.synchronize()
+                        b9[name + "_ms"] = a0.elapsed_time(a1)
+                        if name == "perft9":
+                            b9["perft9_leaves"] = int(res)
+                    b9["playouts_per_s"] = 1e6 / (b9["playouts_1M_ms"] * 1e-3)
+                    extra["config2"] = b9
+                except Exception as e:
+                    extra["config2"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
         value = dev_run["sims"] / (dev_run["ms"] * 1e-3)
         e2e_value = e2e_run["sims"] / (e2e_ms * 1e-3)
@@ -389,9 +502,9 @@ def run_ours(args):
             "config": {"workload": workload, "board": f"{spec.cols}x{spec.rows}", "games_per_gpu": G, "n_sim": n_sim,
                        "net": net_name + " random-init seed 0", "dirichlet": [0.03, 0.25], "temperature": "linear 4/4",
                        "leaves_in_flight_per_game": 1, "network_path": args.net, "tree_reuse": True,
-                       "tail_tiers": list(engine.tail_tiers),
-                       "l2": "working set (node pools %.1f GB) larger than L2, no flush" % (tree.nodes.numel() / 1e9),
-                       "node_pool": {"capacity_per_game": tree.capacity, "peak_used_last_step": engine.max_nodes_used},
+                       "tail_tiers": tiers_used,
+                       "l2": "working set (node pools %.1f GB) larger than L2, no flush" % pool_gb,
+                       "node_pool": {"capacity_per_game": capacity_used, "peak_used_last_step": peak_used},
                        "parallelism": f"games sharded over {world} GPU(s), sample all-gather at the end" if world > 1 else "1 GPU"},
             "games_per_hour": dev_run["games"] / (dev_run["ms"] * 1e-3) * 3600.0,
             "moves_per_step": dev_run["moves"] / args.steps,
@@ -401,7 +514,16 @@ def run_ours(args):
             "gpu_launches": dev_run["launches"],
             "roofline": roofline,
             "roofline_tree": tree_roofline,
+            "extra": extra,
         }
+        ref_path = os.path.join(ROOT, "profiles", "r2_python_reference_cpu.json")
+        if os.path.isfile(ref_path):
+            r = json.load(open(ref_path))
+            line["cpu_baseline_python_reference"] = {
+                "value": r["neural_all_cores_sims_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "reference",
+                "one_process": r["neural_1_process_sims_per_s"], "config1_games_per_hour": r["config1_games_per_hour_all_cores"],
+                "sample": "the UNMODIFIED Python reference, MCT('neural').search(n_sim=200), timed in the build container "
+                          "(oracle/time_reference.py): it cannot travel to the GPU box, so it is quoted, not re-timed"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, args.cpu_seconds)
         print(json.dumps(line), flush=True)

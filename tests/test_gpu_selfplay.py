@@ -171,3 +171,17 @@ def test_tail_tiers_do_not_change_the_games():
     assert len(a) == len(b) and len(a) > G
     for name in ("own", "opp", "pi", "z", "episode_idx", "move_idx"):
         assert torch.equal(getattr(a, name), getattr(b, name)), name
+
+
+def test_pool_overflow_grows_the_pools_and_replays_the_batch():
+    """A node pool that is too small must never cost simulations: the engine doubles every pool and replays."""
+    from alphazero_b200.evaluators import HashEvaluator
+    from alphazero_b200.selfplay import SelfPlayEngine
+    eng = SelfPlayEngine(None, 24, n=6, n_sim=40, seed=2, capacity=128, evaluator_factory=lambda t: HashEvaluator(5, t))
+    batch = eng.play()
+    assert eng.pool_grows >= 1 and eng.tree.capacity >= 256
+    assert eng.total_sims == eng.total_moves * 40 and len(batch) == eng.total_moves
+    ref = SelfPlayEngine(None, 24, n=6, n_sim=40, seed=2, evaluator_factory=lambda t: HashEvaluator(5, t))
+    want = ref.play()
+    assert ref.pool_grows == 0 and len(want) == len(batch)
+    assert torch.equal(want.own, batch.own) and torch.equal(want.pi, batch.pi) and torch.equal(want.z, batch.z)

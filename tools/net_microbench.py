@@ -72,6 +72,20 @@ def _fcstack():
 
 
 timeit_graph(_fcstack, f"fc1+fc2+heads az_net_fcstack RT={ev_stack.RT} NS={ev_stack.NS}")
+# absolute CTA start / end times (globaltimer) of the fc stack when it runs right after the trunk, as in the search graph
+_n_ctas = ev_stack.tiles * ev_stack.NS
+_dbg = torch.zeros(_n_ctas * 32, dtype=torch.int64, device="cuda")
+_lib.lib().az_net_fcstack_debug(_dbg.data_ptr())
+for _ in range(3):
+    ev_stack.enqueue()
+torch.cuda.synchronize()
+_lib.lib().az_net_fcstack_debug(None)
+_d = _dbg.reshape(_n_ctas, 32).double()
+_t0 = _d[:, 25].min()
+_starts, _ends = (_d[:, 25] - _t0) / 1e3, (_d[:, 19] - _t0) / 1e3
+print(f"fcstack after trunk: CTA entry 0 .. {_starts.max().item():.2f} us (median {_starts.median().item():.2f}), "
+      f"CTA exit {_ends.min().item():.2f} .. {_ends.max().item():.2f} us; entries later than 5 us: {int((_starts > 5).sum())} of {_n_ctas}")
+print("   entry histogram (us):", torch.histc(_starts.float(), bins=10, min=0, max=max(1.0, _starts.max().item())).int().tolist())
 timeit_graph(ev_stack.trunk, "trunk, packed features")
 timeit_graph(ev.trunk, "trunk, row-major features")
 timeit_graph(ev_stack.enqueue, "trunk + fcstack (what the search graph holds)")
