@@ -372,7 +372,9 @@ def make_evaluator(nn, tree, dtype=torch.bfloat16, path: str = "auto"):
     if path != "torch":
         for cls in (FusedNetEvaluator, TicTacToeNetEvaluator):
             if cls.supports(nn):
-                ev = cls(nn, tree)
+                # AZ_B200_HEADS=library: the first version's three cuBLASLt GEMMs instead of az_net_fcstack (A/B measurements)
+                kw = {"heads": os.environ["AZ_B200_HEADS"]} if cls is FusedNetEvaluator and os.environ.get("AZ_B200_HEADS") else {}
+                ev = cls(nn, tree, **kw)
                 tree.set_encoding(False)
                 return ev
         if path == "fused":
