@@ -17,7 +17,10 @@ METRICS = [
     "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.sum.pct_of_peak_sustained_elapsed",
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
     "l1tex__data_pipe_lsu_wavefronts_mem_shared_op_ld.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared_op_st.sum",
-    "smsp__inst_executed_op_shared_ld.sum", "smsp__inst_executed_op_shared_st.sum", "launch__registers_per_thread", "launch__grid_size",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_st.sum",
+    "smsp__sass_inst_executed_op_shared_ld.sum", "smsp__sass_inst_executed_op_shared_st.sum",
+    "memory_l1_wavefronts_shared", "memory_l1_wavefronts_shared_ideal", "derived__memory_l1_wavefronts_shared_excessive",
+    "launch__registers_per_thread", "launch__grid_size",
     "launch__block_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
     "smsp__inst_executed.sum", "smsp__inst_executed_pipe_alu.sum", "smsp__inst_executed_pipe_fmaheavy.sum",
     "smsp__inst_executed_pipe_fmalite.sum", "smsp__inst_executed_pipe_fma.sum", "smsp__inst_executed_pipe_lsu.sum",
