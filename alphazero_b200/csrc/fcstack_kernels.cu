@@ -54,8 +54,12 @@
 #define FS_PRODUCER_A_WARP (FS_EPI_WARPS + 1) // warp 17: bulk copies of the A (activation) blocks, one lane.  Issuing a
                                               // bulk copy costs the issuing thread ~370 cycles (measured): one thread for
                                               // both copies of a stage made the producer the bottleneck of every layer
-#define FS_MMA_WARP (FS_EPI_WARPS + 2)        // warp 18: tcgen05.mma issue (one elected lane), TMEM allocation
-#define FS_THREADS ((FS_EPI_WARPS + 3) * 32)
+#define FS_MMA_WARP (FS_EPI_WARPS + 2)        // warps 18, 19: tcgen05.mma issue (one elected lane each); 18 allocates TMEM.
+                                              // One thread issues a tcgen05.mma every ~97 cycles (measured), which made
+                                              // the issue the longest single item of a CTA: the two warps take alternate
+                                              // stages and accumulate into their OWN accumulator (the epilogue adds the two)
+#define FS_MMA_WARPS 2
+#define FS_THREADS ((FS_EPI_WARPS + 2 + FS_MMA_WARPS) * 32)
 #define FS_MAX_CHUNKS 16                      // K chunks per layer
 #define FS_BIAS_FLOATS 512                    // 256 + 128 + 128
 #define FB_FULL 0
@@ -63,7 +67,8 @@
 #define FB_FULL2 (FB_EMPTY + FS_STAGES)
 #define FB_EMPTY2 (FB_FULL2 + FS_STAGES2)
 #define FB_ACC (FB_EMPTY2 + FS_STAGES2)
-#define FB_READY (FB_ACC + 3)                 // [2][FS_MAX_CHUNKS]: block kc of h1 / h2 of this row tile is in global memory
+#define FB_TFREE (FB_ACC + 3)                 // fc1's accumulators have been read: fc2's may overwrite their TMEM columns
+#define FB_READY (FB_TFREE + 1)               // [2][FS_MAX_CHUNKS]: block kc of h1 / h2 of this row tile is in global memory
 #define FB_COUNT (FB_READY + 2 * FS_MAX_CHUNKS)
 #define FS_SM_BIAS (FS_STAGES * FS_STAGE_BYTES)
 #define FS_SM_BARS (FS_SM_BIAS + FS_BIAS_FLOATS * 4)
@@ -228,11 +233,20 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     float* bias_s = reinterpret_cast<float*>(smem + FS_SM_BIAS);
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + FS_SM_TMEM_PTR);
     const int bias_off[3] = {0, 256, 384};
-    const uint32_t col_off[3] = {0u, 256u, 384u};             // TMEM columns of the three accumulators
+    // TMEM columns of the two accumulators (one per MMA warp) of the three layers: fc1 fills all 512 columns, fc2 reuses
+    // [0, 256) once fc1's epilogue has read them (FB_TFREE), the heads sit beside fc2's
+    const uint32_t col_off[3][2] = {{0u, 256u}, {0u, 128u}, {256u, 288u}};
+    const uint32_t bar_tfree = bars + 8 * FB_TFREE;
 
     // ---- setup: barriers, biases of this column slice (weights: not produced by the preceding kernel), TMEM
     if (tid < FB_COUNT) {      // one barrier per thread
-        uint32_t count = 1u;                                                      // acc[L]: one tcgen05.commit
+        uint32_t count = 1u;
+        if (tid >= FB_ACC && tid < FB_ACC + 3) {                                  // acc[L]: one commit per MMA warp with work
+            const int L = tid - FB_ACC, nch = p.K[L] / p.kch[L];
+            const int iters = (L > 0 && p.kch[L] == 64 && (nch & 1) == 0) ? nch / 2 : nch;
+            count = iters >= 2 ? 2u : 1u;
+        }
+        if (tid == FB_TFREE) count = FS_EPI_WARPS;
         if (tid < FB_EMPTY || (tid >= FB_FULL2 && tid < FB_EMPTY2)) count = 1u;   // full[s]: the producer's expect_tx
         else if (tid < FB_ACC) count = (uint32_t)__popc(all_mask);                // empty[s]: one commit per receiving CTA
         else if (tid >= FB_READY) count = 4u;                                     // ready[block]: the four quarter warps
@@ -308,41 +322,48 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
             }
         }
         __syncwarp();
-    } else if (warp == FS_MMA_WARP) {
-        // ================================================================== MMA issue
-        uint32_t it = 0;
+    } else if (warp >= FS_MMA_WARP) {
+        // ================================================================== MMA issue: warp w takes the stages q with q % 2 == w
+        const int w = warp - FS_MMA_WARP;
+        uint32_t it0 = 0;
         long long w_full = 0, t_issue = 0;
 #pragma unroll
         for (int L = 0; L < 3; ++L) {
             const FsGeom g = fs_geom(p, L, bars);
-            if (L == 1) it = 0;
+            if (L == 1) {
+                it0 = 0;
+                fs_mbar_wait(bar_tfree, 0u);                  // fc1's accumulators have been read out of [0, 256)
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            }
             const int ksteps = g.chunks * (p.kch[L] >> 4);
             const uint32_t nc = (uint32_t)p.Nc[L];
             const uint32_t idesc = umma_idesc_bf16_m128(nc);
-            const uint32_t d_tmem = tmem_base + col_off[L];
-            for (int q = 0; q < g.iters; ++q, ++it) {
+            const uint32_t d_tmem = tmem_base + (w ? col_off[L][1] : col_off[L][0]);
+            for (int q = w; q < g.iters; q += FS_MMA_WARPS) {
+                const uint32_t it = it0 + (uint32_t)q;
                 const uint32_t s = it % (uint32_t)g.slots, ph = (it / (uint32_t)g.slots) & 1u;
                 const long long c0 = dbg ? clock64() : 0;
                 fs_mbar_wait(g.bar_full + 8 * s, ph);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const long long c1 = dbg ? clock64() : 0;
-                if (dbg && lane == 0) { w_full += c1 - c0; if (q == 0) dbg[2 + L * 6] = c1 - t_entry; }
+                if (dbg && lane == 0 && w == 0) { w_full += c1 - c0; if (q == 0) dbg[2 + L * 6] = c1 - t_entry; }
                 if (elect_one()) {
                     const uint32_t sa = smem_u32(smem) + s * g.slot_bytes, sb = sa + g.b_off;
                     for (int k = 0; k < ksteps; ++k) {
                         const uint64_t ad = umma_desc(sa + (uint32_t)k * 4096u, 2048u, 128u);
                         const uint64_t bd = umma_desc(sb + (uint32_t)k * 32u * nc, 16u * nc, 128u);
-                        umma_bf16(d_tmem, ad, bd, idesc, (q | k) ? 1u : 0u);
+                        umma_bf16(d_tmem, ad, bd, idesc, (q >= FS_MMA_WARPS || k) ? 1u : 0u);
                     }
                     if (mc_any) fs_commit_multicast(g.bar_empty + 8 * s, all_mask);
                     else umma_commit(g.bar_empty + 8 * s);
-                    if (q == g.iters - 1) umma_commit(bar_acc0 + 8 * L);
+                    if (q + FS_MMA_WARPS >= g.iters) umma_commit(bar_acc0 + 8 * L);     // this warp's last stage of the layer
                 }
                 __syncwarp();
-                if (dbg && lane == 0) { const long long c2 = clock64(); t_issue += c2 - c1; if (q == g.iters - 1) dbg[3 + L * 6] = c2 - t_entry; }
+                if (dbg && lane == 0 && w == 0) { const long long c2 = clock64(); t_issue += c2 - c1; if (q + FS_MMA_WARPS >= g.iters) dbg[3 + L * 6] = c2 - t_entry; }
             }
+            it0 += (uint32_t)g.iters;
         }
-        if (dbg && lane == 0) { dbg[22] = w_full; dbg[23] = t_issue; }
+        if (dbg && lane == 0 && w == 0) { dbg[22] = w_full; dbg[23] = t_issue; }
     } else {
         // ================================================================== epilogue
         const int quarter = warp & 3, blk = warp >> 2;        // blk: which 64-wide output block of a layer this warp converts
@@ -371,26 +392,38 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                 const int bw = p.kch[L + 1];                  // block width = the next layer's K chunk
                 const int nblk = p.Nc[L] / bw, nchn = p.K[L + 1] / bw;
                 uint8_t* hbase = (L == 0 ? p.h1 : p.h2) + (size_t)m * nchn * ((size_t)bw * 256) + (size_t)row * 16;
+                const bool two = fs_geom(p, L, bars).iters >= 2;        // both MMA warps accumulated: add their halves
                 for (int j = blk; j < nblk; j += FS_EPI_WARPS / 4) {
-#pragma unroll
-                    for (int qq = 0; qq < 4; ++qq)
-                        if (qq * 16 < bw) fs_tmem_ld16(t_lane + col_off[L] + (uint32_t)(j * bw + qq * 16), &v[qq * 16]);
-                    fs_tmem_wait64(v);
-                    if (dbg && tid == 0) dbg[29 + L] = clock64() - t_entry;
                     const int kcn = c * nblk + j;             // this block's K chunk in the next layer
                     uint8_t* dst = hbase + (size_t)kcn * ((size_t)bw * 256);
-                    const float* bs = bias_s + bias_off[L] + j * bw;
 #pragma unroll
-                    for (int pl = 0; pl < 8; ++pl) {
-                        if (pl * 8 < bw) {
-                            const float4 b0 = *reinterpret_cast<const float4*>(bs + pl * 8);
-                            const float4 b1 = *reinterpret_cast<const float4*>(bs + pl * 8 + 4);
-                            uint4 o;
-                            o.x = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 0]) + b0.x, __uint_as_float(v[pl * 8 + 1]) + b0.y);
-                            o.y = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 2]) + b0.z, __uint_as_float(v[pl * 8 + 3]) + b0.w);
-                            o.z = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 4]) + b1.x, __uint_as_float(v[pl * 8 + 5]) + b1.y);
-                            o.w = pack_relu_bf16x2(__uint_as_float(v[pl * 8 + 6]) + b1.z, __uint_as_float(v[pl * 8 + 7]) + b1.w);
-                            *reinterpret_cast<uint4*>(dst + pl * 2048) = o;
+                    for (int hb = 0; hb < 2; ++hb) {          // 32 columns at a time: 32 + 32 accumulator registers
+                        if (hb * 32 < bw) {
+                            const uint32_t col = (uint32_t)(j * bw + hb * 32);
+                            fs_tmem_ld16(t_lane + col_off[L][0] + col, &v[0]);
+                            fs_tmem_ld16(t_lane + col_off[L][0] + col + 16u, &v[16]);
+                            if (two) {
+                                fs_tmem_ld16(t_lane + col_off[L][1] + col, &v[32]);
+                                fs_tmem_ld16(t_lane + col_off[L][1] + col + 16u, &v[48]);
+                            }
+                            fs_tmem_wait64(v);
+                            if (dbg && tid == 0 && hb == 0) dbg[29 + L] = clock64() - t_entry;
+                            const float* bs = bias_s + bias_off[L] + j * bw + hb * 32;
+#pragma unroll
+                            for (int pl = 0; pl < 4; ++pl) {
+                                const float4 b0 = *reinterpret_cast<const float4*>(bs + pl * 8);
+                                const float4 b1 = *reinterpret_cast<const float4*>(bs + pl * 8 + 4);
+                                float x[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e)
+                                    x[e] = __uint_as_float(v[pl * 8 + e]) + (two ? __uint_as_float(v[32 + pl * 8 + e]) : 0.f);
+                                uint4 o;
+                                o.x = pack_relu_bf16x2(x[0] + b0.x, x[1] + b0.y);
+                                o.y = pack_relu_bf16x2(x[2] + b0.z, x[3] + b0.w);
+                                o.z = pack_relu_bf16x2(x[4] + b1.x, x[5] + b1.y);
+                                o.w = pack_relu_bf16x2(x[6] + b1.z, x[7] + b1.w);
+                                *reinterpret_cast<uint4*>(dst + (hb * 4 + pl) * 2048) = o;
+                            }
                         }
                     }
                     if (dbg && tid == 0) dbg[6 + L * 6] = clock64() - t_entry;
@@ -403,14 +436,28 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                     if (lane < NS) fs_mbar_arrive_remote(bar_ready0 + 8 * (L * FS_MAX_CHUNKS + kcn), (uint32_t)(r * NS + lane));
                     if (dbg && tid == 0) dbg[7 + L * 6] = clock64() - t_entry;
                 }
+                if (L == 0) {     // this warp no longer reads fc1's accumulators
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tfree);
+                }
             } else if (blk == 0) {
                 // heads: bias, bf16, then through shared memory so that the global stores are row-contiguous 4-byte words
                 // (lane = row stores of 2 bytes at a 144-byte pitch cost one L1 wavefront per lane: 3 800 cycles measured)
                 const int ncols = p.Nc[2], hpc = p.hpc, pw = hpc >> 1;      // hpc is even (fc_plan)
 #pragma unroll
+                const bool two = fs_geom(p, 2, bars).iters >= 2;
+#pragma unroll
                 for (int qq = 0; qq < 2; ++qq)
-                    if (qq * 16 < ncols) fs_tmem_ld16(t_lane + col_off[2] + (uint32_t)(qq * 16), &v[qq * 16]);
+                    if (qq * 16 < ncols) {
+                        fs_tmem_ld16(t_lane + col_off[2][0] + (uint32_t)(qq * 16), &v[qq * 16]);
+                        if (two) fs_tmem_ld16(t_lane + col_off[2][1] + (uint32_t)(qq * 16), &v[32 + qq * 16]);
+                    }
                 fs_tmem_wait64(v);
+                if (two) {
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(v[32 + e]));
+                }
                 if (dbg && tid == 0) dbg[31] = clock64() - t_entry;
                 uint32_t* stage = reinterpret_cast<uint32_t*>(smem);         // stage 0 is free: every MMA has completed
                 const float* bs = bias_s + bias_off[2];

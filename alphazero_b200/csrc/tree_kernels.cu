@@ -730,7 +730,7 @@ __device__ __forceinline__ int az_select_multi(const az_tree& t, const az_dims& 
 }
 
 template <int GAME>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32) k_tree_step_multi(az_tree t, int n_sim, int do_finish, int do_select) {
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step_multi(az_tree t, int n_sim, int do_finish, int do_select) {
     az_pdl_wait();
     az_pdl_trigger();
     const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);

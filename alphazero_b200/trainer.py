@@ -83,6 +83,33 @@ def samples_from_batch(batch: SampleBatch) -> list:
             for i in range(len(b))]
 
 
+def batch_from_samples(samples: list, game: str, device="cuda") -> SampleBatch:
+    """The reference's list[Sample] (normalised: player == 1, trainer.py:74-78) -> a SampleBatch on `device`: what
+    `trainer.memory = [...]` turns the caller's samples into, so that optimize_network trains on THEM."""
+    if len(samples) == 0:
+        raise ValueError("an empty memory cannot be turned into a SampleBatch")
+    rows, cols = samples[0].state.shape
+    own, opp = np.zeros(len(samples), np.uint64), np.zeros(len(samples), np.uint64)
+    for i, sm in enumerate(samples):
+        st = np.asarray(sm.state) * (sm.player if sm.player is not None else 1)
+        for r in range(rows):
+            for c in range(cols):
+                if st[r, c] > 0:
+                    own[i] |= np.uint64(1) << np.uint64(r * 8 + c)
+                elif st[r, c] < 0:
+                    opp[i] |= np.uint64(1) << np.uint64(r * 8 + c)
+    tags = list(SampleBatch.TRANSFORMATIONS)
+    tr = None
+    if any(sm.transformation is not None for sm in samples):
+        tr = torch.tensor([tags.index(sm.transformation) if sm.transformation in tags else 0 for sm in samples], dtype=torch.uint8)
+    t = lambda a, dt: torch.from_numpy(np.asarray(a)).to(dt).to(device)
+    z = [(sm.outcome or 0) * (sm.player if sm.player is not None else 1) for sm in samples]
+    return SampleBatch(t(own.view(np.int64), torch.int64), t(opp.view(np.int64), torch.int64),
+                       t(np.stack([np.asarray(sm.pi, np.float32) for sm in samples]), torch.float32), t(z, torch.int8),
+                       t([sm.episode_idx or 0 for sm in samples], torch.int32), t([sm.move_idx or 0 for sm in samples], torch.int32),
+                       cols, rows, None if tr is None else tr.to(device), game)
+
+
 class AlphaZeroTrainer:
     """Self-play producer with the reference trainer's attributes (trainer.py:121-138)."""
 
@@ -122,8 +149,14 @@ class AlphaZeroTrainer:
 
     @memory.setter
     def memory(self, value) -> None:
+        """Assigning a list of Samples (as callers of the reference's trainer.memory can) replaces the training data:
+        the device batch is rebuilt from the list, never left pointing at stale self-play samples."""
         self._memory = value
-        self.memory_batch = None if value is None else self.memory_batch
+        if value is None or len(value) == 0:
+            self.memory_batch = None
+        else:
+            dev = "cuda" if torch.cuda.is_available() else "cpu"
+            self.memory_batch = batch_from_samples(list(value), self.game, device=dev)
 
     def print(self, log: str):
         if self.verbose:
