@@ -98,6 +98,7 @@ SIGNATURES = {
     "az_augment_twins": (c_int, [c_int]),
     "az_augment_plan": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p]),
     "az_augment_apply": (c_int, [c_void_p] * 6 + [c_i64, c_int, c_int, c_int, c_int] + [c_void_p] * 9),
+    "az_samples_pack": (c_int, [c_void_p] * 7 + [c_int, c_i64, c_int] + [c_void_p] * 7),
     "az_samples_batch": (c_int, [c_void_p] * 5 + [c_i64, c_i64, c_int, c_int, c_int] + [c_void_p] * 5),
 }
 

@@ -287,3 +287,51 @@ extern "C" int az_samples_batch(const uint64_t* own, const uint64_t* opp, const 
     AZ_CHECK_LAUNCH("k_samples_batch");
     return AZ_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ history -> samples
+
+// The self-play history [T][G] (one row per ply, written by az_tree_move) as the training memory the reference builds
+// (trainer.py:241-265): samples ordered by episode, then move; z = winner * player (Sample.normalize, trainer.py:74-78).
+// A game is live for a prefix of the plies, so sample (g, t) sits at offset[g] + t.  One warp per (ply, game) entry:
+// 17 B of position, A floats of pi (lane j moves entries j, j + 32, j + 64), 10 B of indices.
+__global__ void __launch_bounds__(AZ_SAMPLE_WARPS * 32) k_samples_pack(
+        const uint64_t* __restrict__ h_own, const uint64_t* __restrict__ h_opp, const int8_t* __restrict__ h_player,
+        const uint8_t* __restrict__ h_live, const float* __restrict__ h_pi, const int8_t* __restrict__ winner,
+        const int64_t* __restrict__ offset, int T, int64_t G, int A, uint64_t* __restrict__ own, uint64_t* __restrict__ opp,
+        float* __restrict__ pi, int8_t* __restrict__ z, int32_t* __restrict__ episode, int32_t* __restrict__ move) {
+    const int64_t e = (int64_t)blockIdx.x * AZ_SAMPLE_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (e >= (int64_t)T * G) return;
+    if (!h_live[e]) return;
+    const int64_t t = e / G, g = e - t * G;
+    const int64_t i = offset[g] + t;
+    const float* src = h_pi + e * A;
+    float* dst = pi + i * A;
+    for (int a = lane; a < A; a += 32) dst[a] = src[a];
+    if (lane == 0) {
+        const int8_t pl = h_player[e];
+        own[i] = h_own[e];
+        opp[i] = h_opp[e];
+        z[i] = (int8_t)(winner[g] * pl);
+        episode[i] = (int32_t)g;
+        move[i] = (int32_t)t;
+    }
+}
+
+extern "C" int az_samples_pack(const uint64_t* h_own, const uint64_t* h_opp, const int8_t* h_player, const uint8_t* h_live,
+                               const float* h_pi, const int8_t* winner, const int64_t* offset, int T, int64_t G,
+                               int action_size, uint64_t* own, uint64_t* opp, float* pi, int8_t* z, int32_t* episode_idx,
+                               int32_t* move_idx, void* stream) {
+    if (T < 0 || G < 0 || action_size < 1 || action_size > AZ_CANVAS_ACTIONS) return AZ_ERR_ARG;
+    if (T == 0 || G == 0) return AZ_OK;
+    if (!h_own || !h_opp || !h_player || !h_live || !h_pi || !winner || !offset || !own || !opp || !pi || !z ||
+        !episode_idx || !move_idx)
+        return AZ_ERR_ARG;
+    const int64_t entries = (int64_t)T * G;
+    const unsigned grid = (unsigned)((entries + AZ_SAMPLE_WARPS - 1) / AZ_SAMPLE_WARPS);
+    k_samples_pack<<<grid, AZ_SAMPLE_WARPS * 32, 0, (cudaStream_t)stream>>>(h_own, h_opp, h_player, h_live, h_pi, winner,
+                                                                           offset, T, G, action_size, own, opp, pi, z,
+                                                                           episode_idx, move_idx);
+    AZ_CHECK_LAUNCH("k_samples_pack");
+    return AZ_OK;
+}

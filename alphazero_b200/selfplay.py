@@ -339,7 +339,27 @@ class SelfPlayEngine:
         self.total_sims = int(cnt[:, 2].sum())
         self.total_moves = int(cnt[:, 3].sum())
         self.max_nodes_used = int(cnt[:, 4].max()) if t > 0 else 0
+        self.plies_recorded = t
+        return self._samples(t, self.total_moves)
+
+    def _samples(self, t: int, total: int, fused: bool = True) -> SampleBatch:
+        """The history of the first t plies as a SampleBatch ordered by episode, then move (trainer.py:241-265).
+        fused: one az_samples_pack launch; else the same through torch indexing (kept as the test's cross-check)."""
+        spec, G, dev = self.spec, self.G, self.tree.device
         mask = self.h_live[:t]                                   # [t, G]
+        if fused:
+            A = spec.action_size
+            lengths = mask.sum(dim=0, dtype=torch.int64)
+            offset = torch.cumsum(lengths, 0) - lengths
+            own = torch.empty(total, dtype=torch.int64, device=dev); opp = torch.empty_like(own)
+            pi = torch.empty(total, A, dtype=torch.float32, device=dev)
+            z = torch.empty(total, dtype=torch.int8, device=dev)
+            ep = torch.empty(total, dtype=torch.int32, device=dev); mv = torch.empty_like(ep)
+            _lib.check(_lib.lib().az_samples_pack(_ptr(self.h_own), _ptr(self.h_opp), _ptr(self.h_player),
+                                                  _ptr(self.h_live.view(torch.uint8)), _ptr(self.h_pi), _ptr(self.winner),
+                                                  _ptr(offset), t, G, A, _ptr(own), _ptr(opp), _ptr(pi), _ptr(z), _ptr(ep),
+                                                  _ptr(mv), _stream()), "az_samples_pack")
+            return SampleBatch(own, opp, pi, z, ep, mv, spec.cols, spec.rows, None, spec.game)
         move_idx, episode_idx = torch.nonzero(mask.t(), as_tuple=True)[::-1]   # ordered by episode, then move
         own = self.h_own[:t].t()[mask.t()]
         opp = self.h_opp[:t].t()[mask.t()]

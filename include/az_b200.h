@@ -406,6 +406,15 @@ int az_augment_apply(const uint64_t* own, const uint64_t* opp, const float* pi, 
                      int action_size, const void* scratch, uint64_t* out_own, uint64_t* out_opp, float* out_pi,
                      int8_t* out_z, int32_t* out_episode, int32_t* out_move, uint8_t* out_transf, void* stream);
 
+/* The self-play history of G games over T plies (rows written by az_tree_move: position before the move, policy target,
+ * live flag) as the training memory of AlphaZeroTrainer.self_play (trainer.py:241-265): sample (game g, ply t) at index
+ * offset[g] + t -- offset = exclusive prefix sum of the games' lengths, so the samples are ordered by episode, then
+ * move -- with z = winner[g] * player (Sample.normalize, trainer.py:74-78), episode_idx = g, move_idx = t. */
+int az_samples_pack(const uint64_t* h_own, const uint64_t* h_opp, const int8_t* h_player, const uint8_t* h_live,
+                    const float* h_pi, const int8_t* winner, const int64_t* offset, int T, int64_t G, int action_size,
+                    uint64_t* own, uint64_t* opp, float* pi, int8_t* z, int32_t* episode_idx, int32_t* move_idx,
+                    void* stream);
+
 /* One mini-batch of AlphaZeroTrainer._batch_generator (trainer.py:288-322): for b < B, input[b] = the float32
  * rows x cols grid of sample index[b] (own = +1, opp = -1), pi_out[b] = its pi, z_out[b][0] = its outcome.
  * An index outside [0, S) sets *bad_index (device int32, caller-zeroed) to 1 and leaves row b untouched. */

@@ -185,3 +185,21 @@ def test_pool_overflow_grows_the_pools_and_replays_the_batch():
     want = ref.play()
     assert ref.pool_grows == 0 and len(want) == len(batch)
     assert torch.equal(want.own, batch.own) and torch.equal(want.pi, batch.pi) and torch.equal(want.z, batch.z)
+
+
+@pytest.mark.parametrize("game", ["othello6", "connect4"])
+def test_samples_pack_kernel_matches_torch_indexing(game):
+    """az_samples_pack (history rows -> samples ordered by episode, move) against the same through torch indexing."""
+    from alphazero_b200.evaluators import HashEvaluator
+    from alphazero_b200.gamespec import Connect4Spec, OthelloSpec
+    from alphazero_b200.selfplay import SelfPlayEngine
+    spec = Connect4Spec(7, 6) if game == "connect4" else OthelloSpec(6)
+    eng = SelfPlayEngine(None, 200, n=spec, n_sim=12, seed=7, evaluator_factory=lambda t: HashEvaluator(9, t))
+    got = eng.play()
+    want = eng._samples(eng.plies_recorded, eng.total_moves, fused=False)
+    assert len(got) == len(want) == eng.total_moves > 0
+    for name in ("own", "opp", "pi", "z", "episode_idx", "move_idx"):
+        assert torch.equal(getattr(got, name), getattr(want, name)), name
+    # ordered by episode, then move; every game contributes a prefix of plies
+    ep, mv = got.episode_idx.cpu().numpy(), got.move_idx.cpu().numpy()
+    assert (np.diff(ep) >= 0).all() and ((np.diff(mv) == 1) | (np.diff(ep) == 1)).all()

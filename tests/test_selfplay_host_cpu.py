@@ -49,3 +49,28 @@ def test_sample_batch_cpu_is_identity_on_host_tensors():
     b = SampleBatch(torch.zeros(3, dtype=torch.int64), torch.zeros(3, dtype=torch.int64), torch.zeros(3, 37), z,
                     torch.zeros(3, dtype=torch.int32), torch.zeros(3, dtype=torch.int32), 6)
     assert b.cpu() is b and len(b) == 3
+
+
+def test_trainer_memory_setter_rebuilds_the_batch():
+    """trainer.memory = [...] (the reference lets callers assign it, trainer.py:219) must train on THOSE samples: the
+    device batch is rebuilt from the list and round-trips."""
+    import numpy as np
+    from alphazero_b200.trainer import AlphaZeroTrainer, Sample, batch_from_samples, samples_from_batch
+    rng = np.random.RandomState(0)
+    samples = []
+    for i in range(20):
+        st = rng.choice([0.0, 1.0, -1.0], size=(6, 6))
+        pi = rng.rand(37); pi /= pi.sum()
+        player = 1 if i % 2 == 0 else -1
+        samples.append(Sample(st * player, pi, player, outcome=int(rng.choice([-1, 0, 1])), episode_idx=i // 5, move_idx=i % 5))
+    batch = batch_from_samples(samples, "othello", device="cpu")
+    back = samples_from_batch(batch)
+    for a, b in zip(samples, back):
+        assert np.array_equal(a.state * a.player, b.state) and np.allclose(a.pi, b.pi, atol=1e-7)
+        assert b.outcome == a.outcome * a.player and (b.episode_idx, b.move_idx) == (a.episode_idx, a.move_idx)
+    tr = AlphaZeroTrainer()
+    tr.game = "othello"
+    tr.memory = samples
+    assert tr.memory_batch is not None and len(tr.memory_batch) == 20 and tr.memory is samples
+    tr.memory = None
+    assert tr.memory_batch is None
