@@ -91,6 +91,7 @@ struct FcStackParams {
     int mc_a, mc_b;            // 1: the A / B block of a stage is fetched once per cluster and multicast; 0: every CTA
                                //    fetches its own copy (the bytes INTO an SM are the same either way)
     uint32_t w_off[3], b_off[3];
+    int late_trigger;          // 1: let the dependent kernel (the tree step) launch only when this grid has finished
     long long* debug;          // optional [n_ctas][32] cycle stamps (az_net_fcstack_debug), see tools/fcstack_probe.py
 };
 
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_ptr_smem;
     az_pdl_wait();                // the layer-1 input is the preceding kernel's output
-    az_pdl_trigger();
+    if (!p.late_trigger) az_pdl_trigger();
     if (dbg && tid == 0) dbg[1] = clock64() - t_entry;
 
     if (warp == FS_PRODUCER_WARP) {
@@ -569,6 +570,8 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
         p.K[L] = pl.K[L]; p.Nc[L] = pl.Nc[L]; p.kch[L] = pl.kch[L]; p.w_off[L] = pl.w_off[L]; p.b_off[L] = pl.b_off[L];
     }
     p.RT = RT; p.NS = NS; p.hpc = pl.hpc; p.debug = g_fcstack_debug;
+    static const int late_trigger = getenv("AZ_B200_FCSTACK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_FCSTACK_LATE_TRIGGER")) : 0;
+    p.late_trigger = late_trigger;
     static const int mc_flags = getenv("AZ_B200_FCSTACK_MC") ? atoi(getenv("AZ_B200_FCSTACK_MC")) : 0;   // bit 0: A, bit 1: B
     p.mc_a = mc_flags & 1; p.mc_b = (mc_flags >> 1) & 1;
     const int64_t tiles = (G + 127) / 128, clusters = (tiles + RT - 1) / RT;

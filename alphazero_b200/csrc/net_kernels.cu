@@ -97,6 +97,7 @@ struct NetTrunkParams {
     int boards_per_group;      // NB: NB * (n+1)*8 + 8 <= n_tiles * 128
     int n_tiles;               // 128-row tiles per group: 2 or 4
     int debug_layer;           // 0 = off, 1..3 = dump the output of conv1..conv3
+    int late_trigger;          // 1: no early programmatic launch of the kernel that follows (A/B measurements)
     int features_packed;       // 0: features[G][pos*32 + co]; 1: the packed A operand layout of az_net_fcstack
                                //    [G / 128][K / 64][8 K planes][128 rows][8] with K index = pos*32 + co
 };
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
     az_pdl_wait();
     // the fc stack that follows (az_net_fcstack, also launched with az_launch_pdl) may start its prologue on every SM a
     // CTA of this grid has left; it waits for the whole grid before it reads the features
-    az_pdl_trigger();
+    if (!p.late_trigger) az_pdl_trigger();
     const long long t_setup = timing ? clock64() : 0;
 
     if (warp >= MMA_WARP + NET_MMA_WARPS) {
@@ -717,6 +718,8 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
     net_group_shape(rows, G, n_sms, &p.boards_per_group, &p.n_tiles);
     p.debug_layer = debug ? debug_layer : 0;
     p.features_packed = features_packed ? 1 : 0;
+    static const int late_trigger = getenv("AZ_B200_TRUNK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_TRUNK_LATE_TRIGGER")) : 0;
+    p.late_trigger = late_trigger;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM
     cudaError_t e;
