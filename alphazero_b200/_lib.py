@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "fcstack_kernels.cu", "sample_kernels.cu", "player_kernels.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "fcstack_kernels.cu", "fcstack2_kernels.cu", "sample_kernels.cu", "player_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64
@@ -87,7 +87,7 @@ SIGNATURES = {
     "az_net_wblob_bytes": (c_int, []),
     "az_net_trunk_boards_per_group": (c_int, [c_int, c_i64]),
     "az_net_trunk": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p]),
-    "az_net_fcstack_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "az_net_fcstack_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "az_net_fcstack_debug": (c_int, [c_void_p]),
     "az_net_fcstack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "az_connect4_image_bits": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),

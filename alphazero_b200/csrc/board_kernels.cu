@@ -217,7 +217,7 @@ int az_set_cuda_error(cudaError_t e, const char* where) {
     return AZ_ERR_CUDA;
 }
 
-extern "C" int az_abi_version(void) { return 8; }
+extern "C" int az_abi_version(void) { return 9; }
 extern "C" const char* az_last_cuda_error(void) { return g_last_error; }
 
 extern "C" int az_othello_legal(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t* legal,

@@ -37,6 +37,7 @@
 #include "../../include/az_b200.h"
 #include "common.cuh"
 #include "umma.cuh"
+#include "fcstack_common.cuh"
 
 // Operand ring: 192 KB cut into 4 slots of 48 KB for fc1 (A: 64 K x 128 rows = 16 KB, B: 64 K x 256 columns = 32 KB) and
 // into 3 slots of 64 KB for fc2 / the heads, whose stages hold TWO 64-wide K chunks (A 32 KB + B up to 32 KB): half as
@@ -94,100 +95,6 @@ struct FcStackParams {
     int late_trigger;          // 1: let the dependent kernel (the tree step) launch only when this grid has finished
     long long* debug;          // optional [n_ctas][32] cycle stamps (az_net_fcstack_debug), see tools/fcstack_probe.py
 };
-
-__device__ __forceinline__ void fs_cluster_sync() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-
-// mbarrier waits of this kernel: a wait that lasts longer than ~2 s of SM clocks is a protocol bug (a peer CTA that
-// never sends / never releases) -- trap, so that the launch fails with an error instead of hanging the device.
-#define FS_WAIT_LIMIT (4000000000LL)
-__device__ __forceinline__ void fs_mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    long long t0 = 0;
-    for (;;) {
-        asm volatile(
-            "{\n\t"
-            ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t"
-            "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) return;
-        const long long t = clock64();
-        if (t0 == 0) t0 = t;
-        else if (t - t0 > FS_WAIT_LIMIT) __trap();
-    }
-}
-// the same with cluster-scope acquire: pairs with the remote release-arrive of another CTA's epilogue
-__device__ __forceinline__ void fs_mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    long long t0 = 0;
-    for (;;) {
-        asm volatile(
-            "{\n\t"
-            ".reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t"
-            "}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) return;
-        const long long t = clock64();
-        if (t0 == 0) t0 = t;
-        else if (t - t0 > FS_WAIT_LIMIT) __trap();
-    }
-}
-
-// arrive (release, cluster scope) on the barrier at the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ void fs_mbar_arrive_remote(uint32_t bar, uint32_t rank) {
-    asm volatile(
-        "{\n\t"
-        ".reg .b32 ra;\n\t"
-        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
-        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t"
-        "}" ::"r"(bar), "r"(rank) : "memory");
-}
-
-__device__ __forceinline__ void fs_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(bar), "r"(bytes) : "memory");
-}
-
-// global -> shared bulk copy completing on `bar`; with more than one destination the bytes (and the completion) go to
-// the same offsets in every CTA of `mask`
-__device__ __forceinline__ void fs_bulk_copy(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint32_t mask,
-                                             bool multicast) {
-    if (multicast)
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
-                     ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"((uint16_t)mask) : "memory");
-    else
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void fs_commit_multicast(uint32_t bar, uint32_t mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"((uint16_t)mask) : "memory");
-}
-
-// wait for the tcgen05.ld's issued so far; the registers are read-write operands so that no use is scheduled before it
-__device__ __forceinline__ void fs_tmem_wait64(uint32_t (&v)[64]) {
-    asm volatile("tcgen05.wait::ld.sync.aligned;"
-        : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
-          "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
-          "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
-          "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31]),
-          "+r"(v[32]), "+r"(v[33]), "+r"(v[34]), "+r"(v[35]), "+r"(v[36]), "+r"(v[37]), "+r"(v[38]), "+r"(v[39]),
-          "+r"(v[40]), "+r"(v[41]), "+r"(v[42]), "+r"(v[43]), "+r"(v[44]), "+r"(v[45]), "+r"(v[46]), "+r"(v[47]),
-          "+r"(v[48]), "+r"(v[49]), "+r"(v[50]), "+r"(v[51]), "+r"(v[52]), "+r"(v[53]), "+r"(v[54]), "+r"(v[55]),
-          "+r"(v[56]), "+r"(v[57]), "+r"(v[58]), "+r"(v[59]), "+r"(v[60]), "+r"(v[61]), "+r"(v[62]), "+r"(v[63])
-        :: "memory");
-}
-
-__device__ __forceinline__ void fs_tmem_ld16(uint32_t taddr, uint32_t* r) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr) : "memory");
-}
 
 // Stage geometry of layer L, the same in every role: K chunks per stage, stage-iterations, slot size / count, offset of
 // the B block inside a slot and the first full barrier of the layer's slot set (its empty barriers follow).
@@ -446,7 +353,6 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
                 // heads: bias, bf16, then through shared memory so that the global stores are row-contiguous 4-byte words
                 // (lane = row stores of 2 bytes at a 144-byte pitch cost one L1 wavefront per lane: 3 800 cycles measured)
                 const int ncols = p.Nc[2], hpc = p.hpc, pw = hpc >> 1;      // hpc is even (fc_plan)
-#pragma unroll
                 const bool two = fs_geom(p, 2, bars).iters >= 2;
 #pragma unroll
                 for (int qq = 0; qq < 2; ++qq)
@@ -500,20 +406,18 @@ __global__ void __launch_bounds__(FS_THREADS, 1) k_net_fcstack(FcStackParams p) 
 
 // ------------------------------------------------------------------------------------------------ C ABI
 
-struct FcPlan {
-    int kch[3], Nc[3], K[3];
-    int hpc, n3c;
-    uint32_t w_off[3], b_off[3];
-    int64_t blob_bytes;
-};
-
 static int fc_chunk(int k) { return k >= 64 ? 64 : k; }
 
 // Shapes of the three layers for a network K1 -> N1 -> N2 -> n_out with NS column slices; false when the kernel has
 // no mapping for them.
-static bool fc_plan(int K1, int N1, int N2, int n_out, int NS, FcPlan* pl) {
-    if (NS < 1 || NS > 8 || K1 < 16 || N1 < 16 || N2 < 16 || n_out < 1) return false;
+static bool fc_plan2(int K1, int N1, int N2, int n_out, FcPlan* pl);
+
+static bool fc_plan(int K1, int N1, int N2, int n_out, int RT, int NS, FcPlan* pl) {
+    if (NS < 1 || NS > 8 || RT < 1 || RT * NS > 8 || K1 < 16 || N1 < 16 || N2 < 16 || n_out < 1) return false;
     if ((N1 % NS) || (N2 % NS)) return false;
+    static const bool v1_only = getenv("AZ_B200_FCSTACK_V1") != nullptr;
+    if (RT == 1 && NS == 4 && !v1_only && fc_plan2(K1, N1, N2, n_out, pl)) return true;
+    pl->variant = 1;
     pl->hpc = (((n_out + NS - 1) / NS) + 1) & ~1;      // even: the heads' epilogue stores bf16 pairs
     pl->n3c = ((pl->hpc + 15) / 16) * 16;
     pl->K[0] = K1; pl->K[1] = N1; pl->K[2] = N2;
@@ -535,15 +439,40 @@ static bool fc_plan(int K1, int N1, int N2, int n_out, int NS, FcPlan* pl) {
     return true;
 }
 
+// Variant 2 (k_net_fcstack2): clusters of 4 column slices, fc1 in two passes of PW columns, the heads split over K.
+// Weights: fc1 [8 pass-slices][K1/64][8][PW][8], fc2 [4][N1/64][8][Nc2][8], heads [4 K slices][Nc2/8][n3][8]; biases
+// in natural order (the heads' zero padded to n3).
+static bool fc_plan2(int K1, int N1, int N2, int n_out, FcPlan* pl) {
+    const int NS = 4;
+    if ((K1 % 64) || K1 > 512 || (N1 % (2 * NS * 64)) || N1 / NS > 256 || (N2 % (NS * 32)) || N2 / NS > 128) return false;
+    const int n3 = ((n_out + 15) / 16) * 16;
+    if (n3 > 80) return false;
+    pl->variant = 2;
+    pl->K[0] = K1; pl->K[1] = N1; pl->K[2] = N2;
+    pl->Nc[0] = N1 / NS / 2; pl->Nc[1] = N2 / NS; pl->Nc[2] = n3;
+    pl->kch[0] = 64; pl->kch[1] = 64; pl->kch[2] = pl->Nc[1];
+    pl->hpc = n_out; pl->n3c = n3;
+    int64_t off = 0;
+    pl->w_off[0] = (uint32_t)off; off += (int64_t)N1 * K1 * 2;
+    pl->w_off[1] = (uint32_t)off; off += (int64_t)N2 * N1 * 2;
+    pl->w_off[2] = (uint32_t)off; off += (int64_t)n3 * N2 * 2;
+    pl->b_off[0] = (uint32_t)off; off += (int64_t)N1 * 4;
+    pl->b_off[1] = (uint32_t)off; off += (int64_t)N2 * 4;
+    pl->b_off[2] = (uint32_t)off; off += (int64_t)n3 * 4;
+    pl->blob_bytes = off;
+    return true;
+}
+
 // out[0..2] K chunk per layer, out[3..5] columns per CTA per layer, out[6] real head outputs per slice,
-// out[7..9] byte offsets of the packed weights, out[10..12] of the float32 biases, out[13] blob bytes
-extern "C" int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, int64_t* out) {
+// out[7..9] byte offsets of the packed weights, out[10..12] of the float32 biases, out[13] blob bytes, out[14] the
+// kernel variant the blob must be packed for (1: k_net_fcstack, 2: k_net_fcstack2 -- see FcPlan)
+extern "C" int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int RT, int NS, int64_t* out) {
     FcPlan pl;
-    if (!out || !fc_plan(K1, N1, N2, n_out, NS, &pl)) return AZ_ERR_ARG;
+    if (!out || !fc_plan(K1, N1, N2, n_out, RT, NS, &pl)) return AZ_ERR_ARG;
     for (int L = 0; L < 3; ++L) {
         out[L] = pl.kch[L]; out[3 + L] = pl.Nc[L]; out[7 + L] = pl.w_off[L]; out[10 + L] = pl.b_off[L];
     }
-    out[6] = pl.hpc; out[13] = pl.blob_bytes;
+    out[6] = pl.hpc; out[13] = pl.blob_bytes; out[14] = pl.variant;
     return AZ_OK;
 }
 
@@ -554,10 +483,16 @@ extern "C" int az_net_fcstack_debug(void* buf) { g_fcstack_debug = (long long*)b
 extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out,
                               int64_t G, int K1, int N1, int N2, int RT, int NS, void* stream) {
     FcPlan pl;
-    if (!fc_plan(K1, N1, N2, n_out, NS, &pl) || RT < 1 || RT * NS > 8 || ld < n_out || G < 0 ||
-        (G > 0 && (!x || !wblob || !h1 || !h2 || !logits)))
+    if (!fc_plan(K1, N1, N2, n_out, RT, NS, &pl) || ld < n_out || G < 0 ||
+        (G > 0 && (!x || !wblob || !h1 || !logits)))
         return AZ_ERR_ARG;
+    if (pl.variant == 1 && G > 0 && !h2) return AZ_ERR_ARG;
+    if (pl.variant == 2 && (ld & 1)) return AZ_ERR_ARG;      // the logits rows are stored as 4-byte words
     if (G == 0) return AZ_OK;
+    static const int late_trigger = getenv("AZ_B200_FCSTACK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_FCSTACK_LATE_TRIGGER")) : 0;
+    static const bool no_pdl = getenv("AZ_B200_NO_PDL") != nullptr;
+    if (pl.variant == 2)
+        return az_fcstack2_launch(pl, x, wblob, h1, logits, ld, n_out, G, g_fcstack_debug, late_trigger, !no_pdl, stream);
     static bool attr_set = false;
     if (!attr_set) {
         AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_fcstack, cudaFuncAttributeMaxDynamicSharedMemorySize, FS_SM_TOTAL));
@@ -570,7 +505,6 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
         p.K[L] = pl.K[L]; p.Nc[L] = pl.Nc[L]; p.kch[L] = pl.kch[L]; p.w_off[L] = pl.w_off[L]; p.b_off[L] = pl.b_off[L];
     }
     p.RT = RT; p.NS = NS; p.hpc = pl.hpc; p.debug = g_fcstack_debug;
-    static const int late_trigger = getenv("AZ_B200_FCSTACK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_FCSTACK_LATE_TRIGGER")) : 0;
     p.late_trigger = late_trigger;
     static const int mc_flags = getenv("AZ_B200_FCSTACK_MC") ? atoi(getenv("AZ_B200_FCSTACK_MC")) : 0;   // bit 0: A, bit 1: B
     p.mc_a = mc_flags & 1; p.mc_b = (mc_flags >> 1) & 1;
@@ -578,7 +512,6 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(clusters * RT * NS)); cfg.blockDim = dim3(FS_THREADS);
     cfg.dynamicSmemBytes = FS_SM_TOTAL; cfg.stream = (cudaStream_t)stream;
-    static const bool no_pdl = getenv("AZ_B200_NO_PDL") != nullptr;
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = (unsigned)(RT * NS); attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;

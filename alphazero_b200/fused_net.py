@@ -66,25 +66,54 @@ def pack_trunk_weights(net) -> torch.Tensor:
     return torch.from_numpy(packed.copy())
 
 
-def fcstack_plan(K1: int, N1: int, N2: int, n_out: int, NS: int) -> dict:
-    """Layer shapes / blob offsets of az_net_fcstack for a K1 -> N1 -> N2 -> n_out stack cut into NS column slices
-    (the C side is the single source of truth: az_net_fcstack_plan); raises ValueError when there is no mapping."""
+def fcstack_plan(K1: int, N1: int, N2: int, n_out: int, NS: int, RT: int = 1) -> dict:
+    """Layer shapes / blob offsets of az_net_fcstack for a K1 -> N1 -> N2 -> n_out stack on clusters of RT row tiles x NS
+    column slices (the C side is the single source of truth: az_net_fcstack_plan); raises ValueError when there is no
+    mapping.  "variant" names the kernel -- and with it the blob layout -- the C side will run for this shape."""
     import ctypes
-    out = (ctypes.c_int64 * 14)()
-    if _lib.lib().az_net_fcstack_plan(K1, N1, N2, n_out, NS, out) != 0:
-        raise ValueError(f"az_net_fcstack has no mapping for {K1} -> {N1} -> {N2} -> {n_out} with {NS} column slices")
+    out = (ctypes.c_int64 * 15)()
+    if _lib.lib().az_net_fcstack_plan(K1, N1, N2, n_out, RT, NS, out) != 0:
+        raise ValueError(f"az_net_fcstack has no mapping for {K1} -> {N1} -> {N2} -> {n_out} with {RT} x {NS} CTAs per cluster")
     v = list(out)
     return {"kch": v[0:3], "Nc": v[3:6], "hpc": v[6], "w_off": v[7:10], "b_off": v[10:13], "bytes": v[13],
-            "K": [K1, N1, N2], "NS": NS, "n_out": n_out}
+            "variant": v[14], "K": [K1, N1, N2], "NS": NS, "RT": RT, "n_out": n_out}
 
 
-def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int):
-    """(uint8 blob, plan) for az_net_fcstack from the three layers' [N][K] weights / [N] biases (BatchNorm folded):
-    per layer [NS][K/kch][kch/8][N/NS][8] bf16 -- slice c of the output columns, K chunk, 8-wide K plane, column, K % 8
-    = the tcgen05 K-major no-swizzle B operand, one contiguous block per (slice, chunk) -- then the float32 biases.
-    The heads are spread over the slices hpc outputs each, zero padded to a multiple of 16 columns."""
+def _kmajor(w, groups: int) -> np.ndarray:
+    """[N][K] weights -> bf16 bits [groups][K/64][8][N/groups][8]: per group of output columns and 64-wide K chunk the
+    tcgen05 K-major no-swizzle B operand (8-wide K plane, column, K % 8), one contiguous block per (group, chunk)."""
+    N, K = w.shape
+    return np.ascontiguousarray(_bf16_bits(w).reshape(groups, N // groups, K // 64, 8, 8).transpose(0, 2, 3, 1, 4))
+
+
+def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int, RT: int = 1):
+    """(uint8 blob, plan) for az_net_fcstack from the three layers' [N][K] weights / [N] biases (BatchNorm folded).
+    Variant 1: per layer [NS][K/kch][kch/8][N/NS][8] bf16 -- slice c of the output columns, K chunk, 8-wide K plane,
+    column, K % 8 = the tcgen05 K-major no-swizzle B operand, one contiguous block per (slice, chunk) -- then the float32
+    biases; the heads are spread over the slices hpc outputs each, zero padded to a multiple of 16 columns.
+    Variant 2 (include/az_b200.h): fc1 in 2 NS pass-slices, fc2 in NS slices, the heads in NS K slices of all (padded)
+    outputs; biases in natural order."""
     n_out, N2 = wh.shape
-    plan = fcstack_plan(w1.shape[1], w1.shape[0], w2.shape[0], n_out, NS)
+    plan = fcstack_plan(w1.shape[1], w1.shape[0], w2.shape[0], n_out, NS, RT)
+    blob = np.zeros(plan["bytes"], dtype=np.uint8)
+
+    def put(off, arr):
+        raw = np.ascontiguousarray(arr).reshape(-1).view(np.uint8)
+        blob[off:off + raw.size] = raw
+
+    if plan["variant"] == 2:
+        n3, nc2 = plan["Nc"][2], plan["Nc"][1]
+        wh_p = torch.zeros(n3, N2, dtype=torch.float64)
+        bh_p = torch.zeros(n3, dtype=torch.float64)
+        wh_p[:n_out] = wh.double().cpu()
+        bh_p[:n_out] = bh.double().cpu()
+        put(plan["w_off"][0], _kmajor(w1, 2 * NS))
+        put(plan["w_off"][1], _kmajor(w2, NS))
+        # heads: K slice c of every output: [NS][Nc2/8][n3][8]
+        put(plan["w_off"][2], _bf16_bits(wh_p).reshape(n3, NS, nc2 // 8, 8).transpose(1, 2, 0, 3))
+        for L, b in enumerate((b1, b2, bh_p)):
+            put(plan["b_off"][L], b.float().cpu().numpy().astype(np.float32))
+        return torch.from_numpy(blob), plan
     hpc, n3c = plan["hpc"], plan["Nc"][2]
     wh_p = torch.zeros(NS * n3c, N2, dtype=torch.float64)
     bh_p = torch.zeros(NS * n3c, dtype=torch.float64)
@@ -93,14 +122,12 @@ def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int):
         if hi > lo:
             wh_p[c * n3c:c * n3c + hi - lo] = wh[lo:hi].double().cpu()
             bh_p[c * n3c:c * n3c + hi - lo] = bh[lo:hi].double().cpu()
-    blob = np.zeros(plan["bytes"], dtype=np.uint8)
     for L, (w, b) in enumerate(((w1, b1), (w2, b2), (wh_p, bh_p))):
         N, K = w.shape
         kch, nc = plan["kch"][L], plan["Nc"][L]
         assert N == NS * nc and K == plan["K"][L]
-        bits = _bf16_bits(w).reshape(NS, nc, K // kch, kch // 8, 8).transpose(0, 2, 3, 1, 4)
-        blob[plan["w_off"][L]:plan["w_off"][L] + N * K * 2] = np.ascontiguousarray(bits).reshape(-1).view(np.uint8)
-        blob[plan["b_off"][L]:plan["b_off"][L] + N * 4] = b.float().cpu().numpy().astype(np.float32).view(np.uint8)
+        put(plan["w_off"][L], _bf16_bits(w).reshape(NS, nc, K // kch, kch // 8, 8).transpose(0, 2, 3, 1, 4))
+        put(plan["b_off"][L], b.float().cpu().numpy().astype(np.float32))
     return torch.from_numpy(blob), plan
 
 
@@ -212,7 +239,7 @@ class FusedNetEvaluator:
         self.K1, self.N1, self.N2 = m * 32, h1, h2
         if self.heads == "stack":
             self.RT, self.NS = self._stack_shape(G, h1)
-            blob, self.plan = pack_fcstack(w1, b1, w2, b2, wh[:A + 1], bh[:A + 1], self.NS)
+            blob, self.plan = pack_fcstack(w1, b1, w2, b2, wh[:A + 1], bh[:A + 1], self.NS, self.RT)
             self.stack_blob = blob.to(dev)
             tiles = -(-((G + 127) // 128) // self.RT) * self.RT          # row tiles, a whole number of clusters
             self.tiles = tiles

@@ -333,10 +333,16 @@ int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action
  *           zero padded to a multiple of 16 rows), then float32 biases in the same column order
  *   h1, h2  scratch, T*128*N1*2 and T*128*N2*2 bytes
  *   logits  bf16 [G][ld], columns 0 .. n_out-1 written (n_out = action_size + 1: policy logits, then the value logit)
- * az_net_fcstack_plan fills out[14]: K chunk per layer [0..2], columns per CTA per layer [3..5], hpc [6], byte offsets
- * of the weights [7..9] and biases [10..12], blob bytes [13]; AZ_ERR_ARG when the kernel has no mapping for the shape
- * (needs N1/NS <= 256, N2/NS <= 128, ceil(n_out/NS) <= 32, K1 % 64 == 0 or K1 in {16, 32}). */
-int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int NS, int64_t* out);
+ * az_net_fcstack_plan fills out[15]: K chunk per layer [0..2], columns per CTA per layer [3..5], hpc [6], byte offsets
+ * of the weights [7..9] and biases [10..12], blob bytes [13], kernel variant [14]; AZ_ERR_ARG when there is no mapping
+ * for the shape (needs N1/NS <= 256, N2/NS <= 128, ceil(n_out/NS) <= 32, K1 % 64 == 0 or K1 in {16, 32}).
+ * Variant 2 (k_net_fcstack2; chosen for RT = 1, NS = 4, K1 % 64 == 0, K1 <= 512, N1 % 512 == 0, N2 % 128 == 0,
+ * n_out <= 80 -- OthelloNet): fc1 in two passes of PW = N1/8 columns, so that the h1 exchange of pass 0 runs under the
+ * MMAs of pass 1; the heads split over K with the fp32 partial sums reduced through distributed shared memory, so
+ * that h2 never leaves the SM (`h2` unused).  Its blob: fc1 [8][K1/64][8][PW][8] (pass-slice 2c + h = columns
+ * (2c + h) PW ..), fc2 [4][N1/64][8][N2/4][8], heads [4][N2/32][n3][8] (K slice c, n3 = n_out rounded up to 16, zero
+ * padded), then the biases in natural column order; `ld` must be even. */
+int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int RT, int NS, int64_t* out);
 /* Measurement hook: while buf != NULL every az_net_fcstack launch writes per-CTA SM-clock stamps of its pipeline phases
  * to buf ([grid][32] int64, device memory; layout in csrc/fcstack_kernels.cu / tools/fcstack_probe.py). */
 int az_net_fcstack_debug(void* buf);

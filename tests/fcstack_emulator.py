@@ -95,3 +95,87 @@ def emulate(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int,
                                 ok = rows < G
                                 logits[rows[ok], hidx] = _bf16_round(y[ok, col])
     return logits
+
+
+def _kc2(q: int, c: int, bpp: int) -> int:
+    """f2_kc of csrc/fcstack2_kernels.cu: the K chunk of fc2's q-th chunk in CTA c."""
+    per = 4 * bpp
+    h, rem = divmod(q, per)
+    cs, j = ((rem // bpp) + c) & 3, rem % bpp
+    return cs * 2 * bpp + h * bpp + j
+
+
+def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int) -> np.ndarray:
+    """The same walk-through for k_net_fcstack2 (variant 2 of the plan): fc1 in two passes, h1 through global blocks
+    fetched stage by stage in the order f2_kc names, h2 in shared memory, the heads split over K and their four partial
+    sums added by the CTA that owns the row quarter."""
+    assert plan["variant"] == 2
+    K1, N1, N2 = plan["K"]
+    PW, Nc2, n3 = plan["Nc"]
+    n_out = plan["n_out"]
+    nkx, nch2, bpp = K1 // 64, N1 // 64, PW // 64
+    cps = 1 if nkx & 1 else 2
+    cps2 = 2 if PW == 128 else 1
+    n1p, n2 = nkx // cps, nch2 // cps2
+    a1, b1 = cps * 16384, cps * 64 * PW * 2
+    a2, b2, hb_bytes = cps2 * 16384, 64 * Nc2 * 2, Nc2 * n3 * 2
+    tiles = (G + 127) // 128
+    h1 = np.zeros(tiles * 128 * N1 * 2, np.uint8)
+    logits = np.full((G, ld), np.nan, dtype=np.float32)
+    bias1 = blob[plan["b_off"][0]:plan["b_off"][0] + N1 * 4].view(np.float32)
+    bias2 = blob[plan["b_off"][1]:plan["b_off"][1] + N2 * 4].view(np.float32)
+    bias3 = blob[plan["b_off"][2]:plan["b_off"][2] + n3 * 4].view(np.float32)
+    for m in range(tiles):
+        X = x_packed[m * nkx * 16384:(m + 1) * nkx * 16384]
+        for c in range(4):                                       # fc1: both passes of every CTA of the row tile
+            for h in range(2):
+                acc = np.zeros((128, PW), np.float32)
+                for q in range(n1p):
+                    src = plan["w_off"][0] + ((c * 2 + h) * n1p + q) * b1
+                    A = _read_operand(X[q * a1:(q + 1) * a1], 128, cps * 4, 2048)
+                    B = _read_operand(blob[src:src + b1], PW, cps * 4, 16 * PW)
+                    acc += A @ B.T
+                bits = _f32_to_bf16_bits(np.maximum(acc + bias1[c * 2 * PW + h * PW:c * 2 * PW + (h + 1) * PW][None, :], 0.0))
+                dst16 = h1.view(np.uint16)
+                for g in range(PW // 32):                        # warp (quarter, g): 32 columns = half a block
+                    j, hb = g >> 1, g & 1
+                    kc = c * 2 * bpp + h * bpp + j
+                    for pl in range(4):
+                        for row in range(128):
+                            off = ((m * nch2 + kc) * 16384 + row * 16 + (hb * 4 + pl) * 2048) // 2
+                            dst16[off:off + 8] = bits[row, g * 32 + pl * 8:g * 32 + pl * 8 + 8]
+        partial = np.zeros((4, 128, n3), np.float32)
+        for c in range(4):                                       # fc2 and this CTA's K slice of the heads
+            acc = np.zeros((128, Nc2), np.float32)
+            seen = []
+            for s in range(n2):
+                kc = _kc2(s * cps2, c, bpp)
+                seen += list(range(kc, kc + cps2))
+                a0 = (m * nch2 + kc) * 16384
+                srcb = plan["w_off"][1] + (c * nch2 + kc) * b2
+                A = _read_operand(h1[a0:a0 + a2], 128, cps2 * 4, 2048)
+                B = _read_operand(blob[srcb:srcb + cps2 * b2], Nc2, cps2 * 4, 16 * Nc2)
+                acc += A @ B.T
+            assert sorted(seen) == list(range(nch2))             # every K chunk exactly once
+            bits = _f32_to_bf16_bits(np.maximum(acc + bias2[c * Nc2:(c + 1) * Nc2][None, :], 0.0))
+            h2s = np.zeros(Nc2 * 256, np.uint8)
+            d16 = h2s.view(np.uint16)
+            for g in range(Nc2 // 32):
+                for pl in range(4):
+                    for row in range(128):
+                        off = ((g * 4 + pl) * 2048 + row * 16) // 2
+                        d16[off:off + 8] = bits[row, g * 32 + pl * 8:g * 32 + pl * 8 + 8]
+            srch = plan["w_off"][2] + c * hb_bytes
+            A = _read_operand(h2s, 128, Nc2 // 16, 2048)
+            B = _read_operand(blob[srch:srch + hb_bytes], n3, Nc2 // 16, 16 * n3)
+            partial[c] = A @ B.T
+        for owner in range(4):                                   # rows 32 owner .. : own registers + bias, then the peers in sender order
+            rows = slice(owner * 32, owner * 32 + 32)
+            total = partial[owner][rows] + bias3[None, :]
+            for si in range(3):
+                total = total + partial[(owner + si + 1) & 3][rows]
+            for rr in range(32):
+                r = m * 128 + owner * 32 + rr
+                if r < G:
+                    logits[r, :n_out] = _bf16_round(total[rr, :n_out])
+    return logits

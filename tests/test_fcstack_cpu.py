@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from fcstack_emulator import emulate
+from fcstack_emulator import emulate, emulate2
 
 
 def _stack(K1, N1, N2, n_out, seed):
@@ -22,7 +22,10 @@ def _bf(x):
 
 @pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
     (512, 1024, 512, 66, 2, 4, 300),     # OthelloNet 8x8: three row tiles -> two clusters, the last one half empty
-    (128, 1024, 512, 38, 1, 4, 128),     # OthelloNet 6x6
+    (512, 1024, 512, 66, 1, 4, 300),     # the evaluator's shape: k_net_fcstack2 (variant 2 of the plan)
+    (128, 1024, 512, 38, 1, 4, 128),     # OthelloNet 6x6 (variant 2)
+    (192, 512, 256, 80, 1, 4, 130),      # variant 2 with one block per pass, an odd number of input chunks, 64-column fc2 slices
+    (512, 1024, 512, 96, 1, 4, 100),     # too many outputs for variant 2's exchange buffer: the first kernel
     (128, 1024, 512, 38, 1, 8, 70),      # eight column slices
     (192, 64, 32, 8, 1, 1, 200),         # Connect4Net: no cluster
     (192, 64, 32, 8, 2, 1, 500),         # Connect4Net, the weights multicast over two row tiles
@@ -30,15 +33,19 @@ def _bf(x):
 def test_packing_matches_the_kernels_addressing(K1, N1, N2, n_out, RT, NS, G):
     from alphazero_b200.fused_net import pack_fcstack, pack_rows
     w1, b1, w2, b2, wh, bh = _stack(K1, N1, N2, n_out, seed=K1 + NS)
-    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS, RT)
     assert blob.numel() == plan["bytes"]
+    assert plan["variant"] == (2 if (RT, NS) == (1, 4) and n_out <= 80 else 1)
     x = _bf(torch.randn(G, K1, generator=torch.Generator().manual_seed(1)))
     tiles = -(-((G + 127) // 128) // RT) * RT
     xp = torch.zeros(tiles * 128, K1)
     xp[:G] = x
     packed = pack_rows(xp.to(torch.bfloat16), plan["kch"][0]).reshape(-1).view(torch.uint8).numpy()
     ld = ((n_out + 7) // 8) * 8
-    got = emulate(packed, blob.numpy(), plan, G, ld, RT, NS)
+    if plan["variant"] == 2:
+        got = emulate2(packed, blob.numpy(), plan, G, ld)
+    else:
+        got = emulate(packed, blob.numpy(), plan, G, ld, RT, NS)
     h1 = _bf(torch.relu(x.double() @ _bf(w1).double().t() + b1.float().double()))
     h2 = _bf(torch.relu(h1.double() @ _bf(w2).double().t() + b2.float().double()))
     want = _bf(h2.double() @ _bf(wh).double().t() + bh.float().double()).numpy()
@@ -54,9 +61,13 @@ def test_plan_refuses_shapes_without_a_mapping():
         fcstack_plan(512, 1024, 512, 66, 2)          # a slice of fc1 would not fit its 256 accumulator columns
     with pytest.raises(ValueError):
         fcstack_plan(500, 1024, 512, 66, 4)          # K1 not a whole number of chunks
-    p = fcstack_plan(512, 1024, 512, 66, 4)
+    p = fcstack_plan(512, 1024, 512, 66, 4, RT=2)
+    assert p["variant"] == 1
     assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 18      # even: bf16 pairs
     assert p["bytes"] == (1024 * 512 + 512 * 1024 + 128 * 512) * 2 + (1024 + 512 + 128) * 4
+    p = fcstack_plan(512, 1024, 512, 66, 4)
+    assert p["variant"] == 2 and p["Nc"] == [128, 128, 80]       # two passes of 128 columns, all heads padded to 80
+    assert p["bytes"] == (1024 * 512 + 512 * 1024 + 80 * 512) * 2 + (1024 + 512 + 80) * 4
 
 
 def test_pack_rows_round_trip():

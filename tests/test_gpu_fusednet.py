@@ -152,7 +152,11 @@ def test_fused_heads_kernel_matches_library_heads(n, G):
 
 
 @pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
-    (512, 1024, 512, 66, 2, 4, 4096),    # OthelloNet 8x8 at the bench's batch: 16 clusters of 8
+    (512, 1024, 512, 66, 1, 4, 4096),    # OthelloNet 8x8 at the bench's batch: 32 clusters of 4, k_net_fcstack2
+    (128, 1024, 512, 38, 1, 4, 700),     # OthelloNet 6x6 on k_net_fcstack2, ragged last tile
+    (192, 512, 256, 80, 1, 4, 333),      # k_net_fcstack2: odd number of input chunks, one block per pass, 64-column fc2 slices
+    (512, 1024, 512, 96, 1, 4, 200),     # more outputs than k_net_fcstack2's exchange buffer holds: the first kernel
+    (512, 1024, 512, 66, 2, 4, 4096),    # the first kernel, 16 clusters of 8
     (512, 1024, 512, 66, 2, 4, 300),     # ragged: three row tiles, the second cluster half empty
     (512, 1024, 512, 66, 1, 4, 129),
     (512, 1024, 512, 66, 1, 8, 1000),
@@ -172,7 +176,7 @@ def test_fcstack_raw_shapes(K1, N1, N2, n_out, RT, NS, G):
     b1, b2, bh = (torch.randn(n, dtype=torch.float64) * 0.1 for n in (N1, N2, n_out))
     x = torch.randn(G, K1).to(torch.bfloat16)
     bf = lambda t: t.float().to(torch.bfloat16)
-    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+    blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS, RT)
     blob = blob.cuda()
     tiles = -(-((G + 127) // 128) // RT) * RT
     xp = torch.zeros(tiles * 128, K1, dtype=torch.bfloat16)

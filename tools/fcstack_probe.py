@@ -56,7 +56,7 @@ def run(K1, N1, N2, n_out, shapes, G):
     ld = ((n_out + 7) // 8) * 8
     print(f"--- {K1} -> {N1} -> {N2} -> {n_out}, G = {G}")
     for RT, NS in shapes:
-        blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS)
+        blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS, RT)
         blob = blob.to(dev)
         tiles = -(-((G + 127) // 128) // RT) * RT
         xp = torch.zeros(tiles * 128, K1, dtype=torch.bfloat16)
@@ -94,11 +94,19 @@ def run(K1, N1, N2, n_out, shapes, G):
                      31: "L3 epilogue: accumulator in registers",
                      20: "producer: total wait empty", 21: "producer: total wait ready", 22: "mma: total wait full",
                      23: "mma: total issue"}
+            if plan["variant"] == 2:      # stamp slots of k_net_fcstack2 (csrc/fcstack2_kernels.cu)
+                names = {1: "setup done (cluster sync, pdl wait)", 2: "fc1 first stage full", 3: "fc1 pass 0 issued",
+                         4: "fc1 pass 1 issued", 5: "pass 0 accumulator seen by the epilogue", 6: "pass 0 blocks published",
+                         7: "pass 1 accumulator seen", 8: "pass 1 blocks published", 9: "fc2 first stage full",
+                         10: "fc2 middle stage full", 11: "fc2 last MMA issued", 12: "fc2 accumulator seen",
+                         13: "h2 in shared memory", 14: "heads: operands ready", 15: "heads issued",
+                         16: "heads accumulator seen", 17: "partial sums sent", 18: "after the cluster barrier",
+                         24: "exit (logits stored)"}
             for i, nm in names.items():
                 print(f"    {nm:44s} median {d[:, i].median().item():8.0f}  min {d[:, i].min().item():8.0f}  max {d[:, i].max().item():8.0f} cycles")
         us = time_graph(call)
         flops = 2.0 * G * (K1 * N1 + N1 * N2 + N2 * n_out)
-        print(f"RT={RT} NS={NS}: max |err| {err:.4f} (logit scale {scale:.2f}, bf16 ulp {scale * 2 ** -8:.4f}) pad untouched {pad_ok}"
+        print(f"RT={RT} NS={NS} variant {plan['variant']}: max |err| {err:.4f} (logit scale {scale:.2f}, bf16 ulp {scale * 2 ** -8:.4f}) pad untouched {pad_ok}"
               f" | {us:7.2f} us in a graph = {flops / us / 1e6:7.1f} TFLOP/s")
     # the library path it replaces
     w1t, w2t, wht = (bf(w).t().contiguous().to(dev) for w in (w1, w2, torch.cat([wh, torch.zeros(ld - n_out, N2, dtype=torch.float64)])))
@@ -121,6 +129,11 @@ if __name__ == "__main__":
         run(512, 1024, 512, 66, [(2, 4), (1, 4), (1, 8)], G)
     if which == "othello8_14":
         run(512, 1024, 512, 66, [(1, 4)], G)
+    if which == "v2":
+        run(512, 1024, 512, 66, [(1, 4)], G)
+        run(512, 1024, 512, 66, [(1, 4)], 300)
+        run(128, 1024, 512, 38, [(1, 4)], 1000)
+        run(192, 512, 256, 80, [(1, 4)], 333)
     if which in ("all", "small"):
         run(512, 1024, 512, 66, [(2, 4), (1, 4)], 300)
         run(128, 1024, 512, 38, [(2, 4), (1, 8)], 1000)
