@@ -90,6 +90,7 @@ SIGNATURES = {
     "az_net_fcstack_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "az_net_fcstack_debug": (c_int, [c_void_p]),
     "az_net_fcstack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "az_net_fcstack_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_i64, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "az_connect4_image_bits": (c_int, [c_void_p, c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_heads": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p]),
     "az_net_headgemm_blob_bytes": (c_i64, [c_int, c_int]),

@@ -218,6 +218,11 @@ int az_set_cuda_error(cudaError_t e, const char* where) {
 }
 
 extern "C" int az_abi_version(void) { return 9; }
+// a non-CUDA failure with a message for az_last_cuda_error (argument / capacity errors that deserve an explanation)
+int az_set_error_message(int code, const char* msg) {
+    snprintf(g_last_error, sizeof(g_last_error), "%s", msg);
+    return code;
+}
 extern "C" const char* az_last_cuda_error(void) { return g_last_error; }
 
 extern "C" int az_othello_legal(const uint64_t* own, const uint64_t* opp, int n, int64_t G, uint64_t* legal,

@@ -11,6 +11,7 @@
 
 // Records the CUDA error text for az_last_cuda_error() and returns AZ_ERR_CUDA.
 int az_set_cuda_error(cudaError_t e, const char* where);
+int az_set_error_message(int code, const char* msg);
 
 #define AZ_CUDA_TRY(expr)                                         \
     do {                                                          \

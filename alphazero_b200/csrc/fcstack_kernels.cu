@@ -32,6 +32,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "../../include/az_b200.h"
@@ -522,4 +523,53 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
     if (e != cudaSuccess) return az_set_cuda_error(e, "k_net_fcstack");
     AZ_CHECK_LAUNCH("k_net_fcstack");
     return AZ_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+
+// az_net_fcstack with the h1 / h2 scratch in a file-scope device array instead of caller-allocated buffers, for callers
+// that cannot allocate device memory (code under CUDA graph capture, serving loops, harnesses that forbid it).  No
+// counterpart in the reference.  The array is sized for
+// AZ_FCSTACK_STATIC_MAX_ROWS positions of OthelloNet's stack (N1 + N2 = 1536 columns per row): 6 MB that every
+// GPU which loads the library holds until the process exits.
+#define AZ_FCSTACK_STATIC_MAX_ROWS 2048
+#define AZ_FCSTACK_STATIC_BYTES ((size_t)AZ_FCSTACK_STATIC_MAX_ROWS * 1536 * 2)
+static __device__ __align__(256) uint8_t g_fcstack_static_scratch[AZ_FCSTACK_STATIC_BYTES];
+
+// In host code the array's name is only a handle: its device address comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+static int fcstack_static_scratch(uint8_t** out) {
+    static uint8_t* addr[64] = {};
+    int dev = 0;
+    AZ_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return az_set_error_message(AZ_ERR_ARG, "az_net_fcstack_static: device ordinal beyond 63");
+    if (!addr[dev]) {
+        void* ptr = nullptr;
+        AZ_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_fcstack_static_scratch));
+        addr[dev] = (uint8_t*)ptr;
+    }
+    *out = addr[dev];
+    return AZ_OK;
+}
+
+extern "C" int az_net_fcstack_static(const void* x, const void* wblob, void* logits, int ld, int n_out, int64_t G,
+                                     int K1, int N1, int N2, int RT, int NS, void* stream) {
+    if (G < 0 || RT < 1 || N1 < 1 || N2 < 1) return AZ_ERR_ARG;
+    const int64_t tiles = ((G + 127) / 128 + RT - 1) / RT * RT;              // whole clusters, like the caller's x
+    const int64_t h1_bytes = tiles * 128 * (int64_t)N1 * 2, h2_bytes = tiles * 128 * (int64_t)N2 * 2;
+    if (h1_bytes + h2_bytes > (int64_t)AZ_FCSTACK_STATIC_BYTES) {
+        char msg[320];
+        snprintf(msg, sizeof(msg),
+                 "az_net_fcstack_static: %lld positions of a %d -> %d -> %d stack need %lld bytes of scratch, the static array "
+                 "holds %lld (%d positions at N1 + N2 = 1536); use az_net_fcstack with caller-allocated h1 / h2",
+                 (long long)G, K1, N1, N2, (long long)(h1_bytes + h2_bytes), (long long)AZ_FCSTACK_STATIC_BYTES,
+                 AZ_FCSTACK_STATIC_MAX_ROWS);
+        return az_set_error_message(AZ_ERR_CAPACITY, msg);
+    }
+    if (G == 0) return AZ_OK;
+    uint8_t* scratch = nullptr;
+    const int rc = fcstack_static_scratch(&scratch);
+    if (rc != AZ_OK) return rc;
+    // nothing in the scratch has to start at zero: every block of h1 / h2 is written in this launch before it is read
+    return az_net_fcstack(x, wblob, scratch, scratch + h1_bytes, logits, ld, n_out, G, K1, N1, N2, RT, NS, stream);
 }

@@ -348,6 +348,16 @@ int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int RT, int NS, int64
 int az_net_fcstack_debug(void* buf);
 int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* logits, int ld, int n_out, int64_t G,
                    int K1, int N1, int N2, int RT, int NS, void* stream);
+/* az_net_fcstack for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and results as az_net_fcstack minus h1 / h2: the scratch is a static device array inside the library
+ * (6 MB = 2048 positions at N1 + N2 = 1536, held by every GPU that loads the library until the process exits); the
+ * call allocates and frees nothing.  Shapes whose h1 + h2 (ceil(G/128) rounded up to RT, x 128 x (N1 + N2) x 2 bytes)
+ * exceed the array return AZ_ERR_CAPACITY with the sizes in az_last_cuda_error().  All calls on a device share the
+ * array (it keeps the last call's contents; nothing in it has to start at zero): calls that overlap on the GPU --
+ * different streams, or graphs replayed concurrently -- race; serialise them or use az_net_fcstack. */
+int az_net_fcstack_static(const void* x, const void* wblob, void* logits, int ld, int n_out, int64_t G, int K1, int N1,
+                          int N2, int RT, int NS, void* stream);
 
 /* ---------------------------------------------------------------- TicTacToe ----------------------------- */
 /* 3 x 3 board on the same canvas (bit r*8+c, r, c < 3); an action is the canvas cell, there is no pass; the policy
