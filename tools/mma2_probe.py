@@ -1,0 +1,30 @@
+"""tcgen05.mma.cta_group::2 semantics probe (tools/probes/mma2_probe.cu): which half of B each CTA of the pair supplies
+and which rows of D each CTA's TMEM holds.
+
+    python tools/mma2_probe.py
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from tools.probes import build
+
+L = build.lib()
+torch.manual_seed(0)
+for N in (128, 256, 64):
+    A = torch.randn(256, 64).to(torch.bfloat16).cuda()
+    B = torch.randn(N, 64).to(torch.bfloat16).cuda()
+    want = (A.double() @ B.double().t()).float()
+    for swap in (0, 1):
+        D = torch.full((2, 128, N), float("nan"), device="cuda")
+        rc = L.az_probe_mma2(A.data_ptr(), B.data_ptr(), D.data_ptr(), N, swap, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        got = D.reshape(256, N)
+        err_direct = (got - want).abs().max().item()
+        # hypotheses: columns of the two halves swapped; rows of the two CTAs swapped
+        cs = torch.cat([want[:, N // 2:], want[:, :N // 2]], 1)
+        rs = torch.cat([want[128:], want[:128]], 0)
+        print(f"N={N} swap_b={swap} rc={rc}: |D - A B^T| max {err_direct:.4f} | vs column-halves swapped {(got - cs).abs().max().item():.4f}"
+              f" | vs row-halves swapped {(got - rs).abs().max().item():.4f} | nan {int(torch.isnan(got).sum())}")

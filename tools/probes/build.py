@@ -5,7 +5,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libaz_probes.so")
-SOURCES = ["peak_kernels.cu", "mma_probe.cu", "probe_common.cu"]
+SOURCES = ["peak_kernels.cu", "mma_probe.cu", "mma2_probe.cu", "probe_common.cu"]
 _lib = None
 
 
@@ -30,5 +30,7 @@ def lib() -> ctypes.CDLL:
         L.az_peak_int32.argtypes = [c_int, c_int, c_void_p, c_i64, ctypes.POINTER(ctypes.c_int64), c_void_p]
         L.az_peak_mma.restype = c_int
         L.az_peak_mma.argtypes = [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]
+        L.az_probe_mma2.restype = c_int
+        L.az_probe_mma2.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]
         _lib = L
     return _lib
