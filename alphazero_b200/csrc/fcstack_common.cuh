@@ -124,7 +124,8 @@ __device__ __forceinline__ void fs_st_cluster_v4(uint32_t addr, uint32_t a, uint
 
 // Shapes of the three layers (az_net_fcstack_plan).  variant 1: k_net_fcstack (any cluster shape); variant 2:
 // k_net_fcstack2 (clusters of 4 column slices, one row tile): Nc[0] is then the width of one of fc1's two passes and
-// Nc[2] the padded count of ALL head outputs (the heads are split over K, not over their outputs).
+// Nc[2] the padded count of ALL head outputs (the heads are split over K, not over their outputs); variant 3:
+// k_net_fcstack3 (the same schedule on CTA pairs, RT = 2: each CTA stages half of its column slice's weight columns).
 struct FcPlan {
     int variant;
     int kch[3], Nc[3], K[3];
@@ -135,3 +136,5 @@ struct FcPlan {
 
 int az_fcstack2_launch(const FcPlan& pl, const void* x, const void* wblob, void* h1, void* logits, int ld, int n_out,
                        int64_t G, long long* debug, int late_trigger, bool pdl, void* stream);
+int az_fcstack3_launch(const FcPlan& pl, const void* x, const void* wblob, void* h1, void* xch, void* logits, int ld,
+                       int n_out, int64_t G, long long* debug, int late_trigger, bool pdl, void* stream);

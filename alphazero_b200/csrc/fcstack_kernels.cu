@@ -418,6 +418,10 @@ static bool fc_plan(int K1, int N1, int N2, int n_out, int RT, int NS, FcPlan* p
     if ((N1 % NS) || (N2 % NS)) return false;
     static const bool v1_only = getenv("AZ_B200_FCSTACK_V1") != nullptr;
     if (RT == 1 && NS == 4 && !v1_only && fc_plan2(K1, N1, N2, n_out, pl)) return true;
+    // RT = 2: the same shapes on CTA pairs, if the partial sums of a row tile fit its share of the h2 scratch
+    if (RT == 2 && NS == 4 && !v1_only && fc_plan2(K1, N1, N2, n_out, pl)) {
+        if (12 * (pl->Nc[2] / 16) * 2048 + 256 <= 128 * N2 * 2) { pl->variant = 3; return true; }
+    }
     pl->variant = 1;
     pl->hpc = (((n_out + NS - 1) / NS) + 1) & ~1;      // even: the heads' epilogue stores bf16 pairs
     pl->n3c = ((pl->hpc + 15) / 16) * 16;
@@ -488,10 +492,13 @@ extern "C" int az_net_fcstack(const void* x, const void* wblob, void* h1, void* 
         (G > 0 && (!x || !wblob || !h1 || !logits)))
         return AZ_ERR_ARG;
     if (pl.variant == 1 && G > 0 && !h2) return AZ_ERR_ARG;
-    if (pl.variant == 2 && (ld & 1)) return AZ_ERR_ARG;      // the logits rows are stored as 4-byte words
+    if (pl.variant >= 2 && (ld & 1)) return AZ_ERR_ARG;      // the logits rows are stored as 4-byte words
+    if (pl.variant == 3 && G > 0 && !h2) return AZ_ERR_ARG;
     if (G == 0) return AZ_OK;
     static const int late_trigger = getenv("AZ_B200_FCSTACK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_FCSTACK_LATE_TRIGGER")) : 0;
     static const bool no_pdl = getenv("AZ_B200_NO_PDL") != nullptr;
+    if (pl.variant == 3)
+        return az_fcstack3_launch(pl, x, wblob, h1, h2, logits, ld, n_out, G, g_fcstack_debug, late_trigger, !no_pdl, stream);
     if (pl.variant == 2)
         return az_fcstack2_launch(pl, x, wblob, h1, logits, ld, n_out, G, g_fcstack_debug, late_trigger, !no_pdl, stream);
     static bool attr_set = false;

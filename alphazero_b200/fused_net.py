@@ -92,7 +92,8 @@ def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int, RT: int = 1):
     column, K % 8 = the tcgen05 K-major no-swizzle B operand, one contiguous block per (slice, chunk) -- then the float32
     biases; the heads are spread over the slices hpc outputs each, zero padded to a multiple of 16 columns.
     Variant 2 (include/az_b200.h): fc1 in 2 NS pass-slices, fc2 in NS slices, the heads in NS K slices of all (padded)
-    outputs; biases in natural order."""
+    outputs; biases in natural order.  Variant 3: the same with every column group split once more into the two halves
+    the CTAs of a pair stage."""
     n_out, N2 = wh.shape
     plan = fcstack_plan(w1.shape[1], w1.shape[0], w2.shape[0], n_out, NS, RT)
     blob = np.zeros(plan["bytes"], dtype=np.uint8)
@@ -101,16 +102,17 @@ def pack_fcstack(w1, b1, w2, b2, wh, bh, NS: int, RT: int = 1):
         raw = np.ascontiguousarray(arr).reshape(-1).view(np.uint8)
         blob[off:off + raw.size] = raw
 
-    if plan["variant"] == 2:
+    if plan["variant"] in (2, 3):
+        halves = 2 if plan["variant"] == 3 else 1      # variant 3: every column group once more in two halves (CTA pair)
         n3, nc2 = plan["Nc"][2], plan["Nc"][1]
         wh_p = torch.zeros(n3, N2, dtype=torch.float64)
         bh_p = torch.zeros(n3, dtype=torch.float64)
         wh_p[:n_out] = wh.double().cpu()
         bh_p[:n_out] = bh.double().cpu()
-        put(plan["w_off"][0], _kmajor(w1, 2 * NS))
-        put(plan["w_off"][1], _kmajor(w2, NS))
-        # heads: K slice c of every output: [NS][Nc2/8][n3][8]
-        put(plan["w_off"][2], _bf16_bits(wh_p).reshape(n3, NS, nc2 // 8, 8).transpose(1, 2, 0, 3))
+        put(plan["w_off"][0], _kmajor(w1, 2 * NS * halves))
+        put(plan["w_off"][1], _kmajor(w2, NS * halves))
+        # heads: K slice c (and column half r) of every output: [NS][halves][Nc2/8][n3/halves][8]
+        put(plan["w_off"][2], _bf16_bits(wh_p).reshape(halves, n3 // halves, NS, nc2 // 8, 8).transpose(2, 0, 3, 1, 4))
         for L, b in enumerate((b1, b2, bh_p)):
             put(plan["b_off"][L], b.float().cpu().numpy().astype(np.float32))
         return torch.from_numpy(blob), plan

@@ -109,7 +109,8 @@ def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int
     """The same walk-through for k_net_fcstack2 (variant 2 of the plan): fc1 in two passes, h1 through global blocks
     fetched stage by stage in the order f2_kc names, h2 in shared memory, the heads split over K and their four partial
     sums added by the CTA that owns the row quarter."""
-    assert plan["variant"] == 2
+    assert plan["variant"] in (2, 3)
+    pair = plan["variant"] == 3       # k_net_fcstack3: every B block comes in two column halves, one per CTA of a pair
     K1, N1, N2 = plan["K"]
     PW, Nc2, n3 = plan["Nc"]
     n_out = plan["n_out"]
@@ -120,6 +121,19 @@ def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int
     a1, b1 = cps * 16384, cps * 64 * PW * 2
     a2, b2, hb_bytes = cps2 * 16384, 64 * Nc2 * 2, Nc2 * n3 * 2
     tiles = (G + 127) // 128
+
+    def b_operand(base, group, blocks_per_group, block, nbytes, cols, ksteps):
+        """B of a stage: `nbytes` at block `block` of column group `group`; for a pair the two CTAs stage the halves
+        2 group + r, r = 0, 1 (cols / 2 columns, nbytes / 2 bytes each) and the tensor cores read [half 0; half 1]."""
+        if not pair:
+            src = base + (group * blocks_per_group + block) * nbytes
+            return _read_operand(blob[src:src + nbytes], cols, ksteps, 16 * cols)
+        halves = []
+        for r in range(2):
+            src = base + ((group * 2 + r) * blocks_per_group + block) * (nbytes // 2)
+            halves.append(_read_operand(blob[src:src + nbytes // 2], cols // 2, ksteps, 16 * (cols // 2)))
+        return np.vstack(halves)
+
     h1 = np.zeros(tiles * 128 * N1 * 2, np.uint8)
     logits = np.full((G, ld), np.nan, dtype=np.float32)
     bias1 = blob[plan["b_off"][0]:plan["b_off"][0] + N1 * 4].view(np.float32)
@@ -131,9 +145,8 @@ def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int
             for h in range(2):
                 acc = np.zeros((128, PW), np.float32)
                 for q in range(n1p):
-                    src = plan["w_off"][0] + ((c * 2 + h) * n1p + q) * b1
                     A = _read_operand(X[q * a1:(q + 1) * a1], 128, cps * 4, 2048)
-                    B = _read_operand(blob[src:src + b1], PW, cps * 4, 16 * PW)
+                    B = b_operand(plan["w_off"][0], c * 2 + h, n1p, q, b1, PW, cps * 4)
                     acc += A @ B.T
                 bits = _f32_to_bf16_bits(np.maximum(acc + bias1[c * 2 * PW + h * PW:c * 2 * PW + (h + 1) * PW][None, :], 0.0))
                 dst16 = h1.view(np.uint16)
@@ -152,9 +165,9 @@ def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int
                 kc = _kc2(s * cps2, c, bpp)
                 seen += list(range(kc, kc + cps2))
                 a0 = (m * nch2 + kc) * 16384
-                srcb = plan["w_off"][1] + (c * nch2 + kc) * b2
                 A = _read_operand(h1[a0:a0 + a2], 128, cps2 * 4, 2048)
-                B = _read_operand(blob[srcb:srcb + cps2 * b2], Nc2, cps2 * 4, 16 * Nc2)
+                # blocks of b2 bytes per chunk; a stage takes cps2 consecutive ones
+                B = b_operand(plan["w_off"][1], c, nch2 // cps2, kc // cps2, cps2 * b2, Nc2, cps2 * 4)
                 acc += A @ B.T
             assert sorted(seen) == list(range(nch2))             # every K chunk exactly once
             bits = _f32_to_bf16_bits(np.maximum(acc + bias2[c * Nc2:(c + 1) * Nc2][None, :], 0.0))
@@ -165,9 +178,8 @@ def emulate2(x_packed: np.ndarray, blob: np.ndarray, plan: dict, G: int, ld: int
                     for row in range(128):
                         off = ((g * 4 + pl) * 2048 + row * 16) // 2
                         d16[off:off + 8] = bits[row, g * 32 + pl * 8:g * 32 + pl * 8 + 8]
-            srch = plan["w_off"][2] + c * hb_bytes
             A = _read_operand(h2s, 128, Nc2 // 16, 2048)
-            B = _read_operand(blob[srch:srch + hb_bytes], n3, Nc2 // 16, 16 * n3)
+            B = b_operand(plan["w_off"][2], c, 1, 0, hb_bytes, n3, Nc2 // 16)
             partial[c] = A @ B.T
         for owner in range(4):                                   # rows 32 owner .. : own registers + bias, then the peers in sender order
             rows = slice(owner * 32, owner * 32 + 32)

@@ -21,7 +21,9 @@ def _bf(x):
 
 
 @pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
-    (512, 1024, 512, 66, 2, 4, 300),     # OthelloNet 8x8: three row tiles -> two clusters, the last one half empty
+    (512, 1024, 512, 66, 2, 4, 300),     # OthelloNet 8x8 on CTA pairs (variant 3): three row tiles -> two groups
+    (128, 1024, 512, 38, 2, 4, 200),     # OthelloNet 6x6 on CTA pairs
+    (512, 1024, 512, 96, 2, 4, 300),     # the first kernel on clusters of 8, the last one half empty
     (512, 1024, 512, 66, 1, 4, 300),     # the evaluator's shape: k_net_fcstack2 (variant 2 of the plan)
     (128, 1024, 512, 38, 1, 4, 128),     # OthelloNet 6x6 (variant 2)
     (192, 512, 256, 80, 1, 4, 130),      # variant 2 with one block per pass, an odd number of input chunks, 64-column fc2 slices
@@ -35,14 +37,14 @@ def test_packing_matches_the_kernels_addressing(K1, N1, N2, n_out, RT, NS, G):
     w1, b1, w2, b2, wh, bh = _stack(K1, N1, N2, n_out, seed=K1 + NS)
     blob, plan = pack_fcstack(w1, b1, w2, b2, wh, bh, NS, RT)
     assert blob.numel() == plan["bytes"]
-    assert plan["variant"] == (2 if (RT, NS) == (1, 4) and n_out <= 80 else 1)
+    assert plan["variant"] == ({1: 2, 2: 3}[RT] if NS == 4 and n_out <= 80 else 1)
     x = _bf(torch.randn(G, K1, generator=torch.Generator().manual_seed(1)))
     tiles = -(-((G + 127) // 128) // RT) * RT
     xp = torch.zeros(tiles * 128, K1)
     xp[:G] = x
     packed = pack_rows(xp.to(torch.bfloat16), plan["kch"][0]).reshape(-1).view(torch.uint8).numpy()
     ld = ((n_out + 7) // 8) * 8
-    if plan["variant"] == 2:
+    if plan["variant"] >= 2:
         got = emulate2(packed, blob.numpy(), plan, G, ld)
     else:
         got = emulate(packed, blob.numpy(), plan, G, ld, RT, NS)
@@ -62,8 +64,11 @@ def test_plan_refuses_shapes_without_a_mapping():
     with pytest.raises(ValueError):
         fcstack_plan(500, 1024, 512, 66, 4)          # K1 not a whole number of chunks
     p = fcstack_plan(512, 1024, 512, 66, 4, RT=2)
+    assert p["variant"] == 3 and p["Nc"] == [128, 128, 80]
+    assert fcstack_plan(192, 512, 256, 80, 4, RT=2)["variant"] == 1      # partial sums would not fit the h2 scratch
+    p = fcstack_plan(512, 1024, 512, 96, 4, RT=2)
     assert p["variant"] == 1
-    assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 18      # even: bf16 pairs
+    assert p["kch"] == [64, 64, 64] and p["Nc"] == [256, 128, 32] and p["hpc"] == 24      # even: bf16 pairs
     assert p["bytes"] == (1024 * 512 + 512 * 1024 + 128 * 512) * 2 + (1024 + 512 + 128) * 4
     p = fcstack_plan(512, 1024, 512, 66, 4)
     assert p["variant"] == 2 and p["Nc"] == [128, 128, 80]       # two passes of 128 columns, all heads padded to 80

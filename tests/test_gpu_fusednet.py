@@ -156,7 +156,8 @@ def test_fused_heads_kernel_matches_library_heads(n, G):
     (128, 1024, 512, 38, 1, 4, 700),     # OthelloNet 6x6 on k_net_fcstack2, ragged last tile
     (192, 512, 256, 80, 1, 4, 333),      # k_net_fcstack2: odd number of input chunks, one block per pass, 64-column fc2 slices
     (512, 1024, 512, 96, 1, 4, 200),     # more outputs than k_net_fcstack2's exchange buffer holds: the first kernel
-    (512, 1024, 512, 66, 2, 4, 4096),    # the first kernel, 16 clusters of 8
+    (512, 1024, 512, 66, 2, 4, 4096),    # k_net_fcstack3: 16 groups of 4 CTA pairs (cta_group::2)
+    (512, 1024, 512, 96, 2, 4, 300),     # the first kernel on clusters of 8, ragged
     (512, 1024, 512, 66, 2, 4, 300),     # ragged: three row tiles, the second cluster half empty
     (512, 1024, 512, 66, 1, 4, 129),
     (512, 1024, 512, 66, 1, 8, 1000),

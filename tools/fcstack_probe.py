@@ -94,7 +94,7 @@ def run(K1, N1, N2, n_out, shapes, G):
                      31: "L3 epilogue: accumulator in registers",
                      20: "producer: total wait empty", 21: "producer: total wait ready", 22: "mma: total wait full",
                      23: "mma: total issue"}
-            if plan["variant"] == 2:      # stamp slots of k_net_fcstack2 (csrc/fcstack2_kernels.cu)
+            if plan["variant"] >= 2:      # stamp slots of k_net_fcstack2 / 3 (csrc/fcstack2_kernels.cu, fcstack3_kernels.cu)
                 names = {1: "setup done (cluster sync, pdl wait)", 2: "fc1 first stage full", 3: "fc1 pass 0 issued",
                          4: "fc1 pass 1 issued", 5: "pass 0 accumulator seen by the epilogue", 6: "pass 0 blocks published",
                          7: "pass 1 accumulator seen", 8: "pass 1 blocks published", 9: "fc2 first stage full",
@@ -102,8 +102,15 @@ def run(K1, N1, N2, n_out, shapes, G):
                          13: "h2 in shared memory", 14: "heads: operands ready", 15: "heads issued",
                          16: "heads accumulator seen", 17: "partial sums sent", 18: "after the cluster barrier",
                          24: "exit (logits stored)"}
+                if plan["variant"] == 3:
+                    names.update({18: "owner: peers' partial sums seen", 20: "leader: total wait own full",
+                                  21: "leader: total wait peer full", 22: "leader: total issue + commit",
+                                  26: "owner: logits stored", 23: "before the pair barrier"})
             for i, nm in names.items():
-                print(f"    {nm:44s} median {d[:, i].median().item():8.0f}  min {d[:, i].min().item():8.0f}  max {d[:, i].max().item():8.0f} cycles")
+                col = d[:, i]
+                if plan["variant"] == 3 and i in (2, 3, 4, 9, 10, 11, 14, 15, 20, 21, 22):
+                    col = d[0::2, i]      # stamps of the control warp of rank 0
+                print(f"    {nm:44s} median {col.median().item():8.0f}  min {col.min().item():8.0f}  max {col.max().item():8.0f} cycles")
         us = time_graph(call)
         flops = 2.0 * G * (K1 * N1 + N1 * N2 + N2 * n_out)
         print(f"RT={RT} NS={NS} variant {plan['variant']}: max |err| {err:.4f} (logit scale {scale:.2f}, bf16 ulp {scale * 2 ** -8:.4f}) pad untouched {pad_ok}"
@@ -129,6 +136,10 @@ if __name__ == "__main__":
         run(512, 1024, 512, 66, [(2, 4), (1, 4), (1, 8)], G)
     if which == "othello8_14":
         run(512, 1024, 512, 66, [(1, 4)], G)
+    if which == "v3":
+        run(512, 1024, 512, 66, [(2, 4), (1, 4)], G)
+        run(512, 1024, 512, 66, [(2, 4)], 300)
+        run(128, 1024, 512, 38, [(2, 4)], 1000)
     if which == "v2":
         run(512, 1024, 512, 66, [(1, 4)], G)
         run(512, 1024, 512, 66, [(1, 4)], 300)
