@@ -577,6 +577,14 @@ extern "C" int az_net_fcstack_static(const void* x, const void* wblob, void* log
     uint8_t* scratch = nullptr;
     const int rc = fcstack_static_scratch(&scratch);
     if (rc != AZ_OK) return rc;
-    // nothing in the scratch has to start at zero: every block of h1 / h2 is written in this launch before it is read
+    // h1 / h2 blocks are written in this launch before they are read; the only words that must start at zero are the
+    // counters of the pair kernel (variant 3: the last 256 bytes of every row tile's h2 region), and an earlier call of
+    // another shape may have left activations there: clear them in stream order (a memset node, no allocation)
+    FcPlan pl;
+    if (fc_plan(K1, N1, N2, n_out, RT, NS, &pl) && pl.variant == 3) {
+        const size_t tile_bytes = (size_t)128 * N2 * 2;
+        AZ_CUDA_TRY(cudaMemset2DAsync(scratch + h1_bytes + tile_bytes - 256, tile_bytes, 0, 256, (size_t)tiles,
+                                      (cudaStream_t)stream));
+    }
     return az_net_fcstack(x, wblob, scratch, scratch + h1_bytes, logits, ld, n_out, G, K1, N1, N2, RT, NS, stream);
 }

@@ -341,7 +341,15 @@ int az_net_headgemm(const void* h2, int K, const void* wblob, int NH, int action
  * MMAs of pass 1; the heads split over K with the fp32 partial sums reduced through distributed shared memory, so
  * that h2 never leaves the SM (`h2` unused).  Its blob: fc1 [8][K1/64][8][PW][8] (pass-slice 2c + h = columns
  * (2c + h) PW ..), fc2 [4][N1/64][8][N2/4][8], heads [4][N2/32][n3][8] (K slice c, n3 = n_out rounded up to 16, zero
- * padded), then the biases in natural column order; `ld` must be even. */
+ * padded), then the biases in natural column order; `ld` must be even.
+ * Variant 3 (k_net_fcstack3; RT = 2, NS = 4, the shapes of variant 2 with 1536 n3 + 256 <= 256 N2): the same schedule
+ * on CTA pairs (tcgen05.mma.cta_group::2, M = 256: two row tiles share a column slice's weights, each CTA stages half
+ * of its columns); the four pairs of a row-tile pair exchange h1 and the heads' partial sums through `h1` / `h2` and
+ * gpu-scope counters in the last 256 bytes of every row tile's 128 x N2 x 2 bytes of `h2`.  THOSE COUNTERS MUST BE ZERO
+ * before the first launch (allocate `h2` zeroed and let nothing else write it; the kernel leaves them zero); a launch
+ * that finds them dirty traps after ~2 s instead of hanging.  Its blob: every column group of variant 2 once more in
+ * two halves (fc1 [16][K1/64][8][PW/2][8], fc2 [8][N1/64][8][N2/8][8], heads [4][2][N2/32][n3/2][8]).  Measured slower
+ * than variant 2 (profiles/r2_fcstack_experiments.txt); the evaluator uses RT = 1. */
 int az_net_fcstack_plan(int K1, int N1, int N2, int n_out, int RT, int NS, int64_t* out);
 /* Measurement hook: while buf != NULL every az_net_fcstack launch writes per-CTA SM-clock stamps of its pipeline phases
  * to buf ([grid][32] int64, device memory; layout in csrc/fcstack_kernels.cu / tools/fcstack_probe.py). */
@@ -354,7 +362,8 @@ int az_net_fcstack(const void* x, const void* wblob, void* h1, void* h2, void* l
  * (6 MB = 2048 positions at N1 + N2 = 1536, held by every GPU that loads the library until the process exits); the
  * call allocates and frees nothing.  Shapes whose h1 + h2 (ceil(G/128) rounded up to RT, x 128 x (N1 + N2) x 2 bytes)
  * exceed the array return AZ_ERR_CAPACITY with the sizes in az_last_cuda_error().  All calls on a device share the
- * array (it keeps the last call's contents; nothing in it has to start at zero): calls that overlap on the GPU --
+ * array (it keeps the last call's contents; the only words that have to start at zero, the counters of plan variant
+ * 3, are cleared by a memset node in front of the launch): calls that overlap on the GPU --
  * different streams, or graphs replayed concurrently -- race; serialise them or use az_net_fcstack. */
 int az_net_fcstack_static(const void* x, const void* wblob, void* logits, int ld, int n_out, int64_t G, int K1, int N1,
                           int N2, int RT, int NS, void* stream);

@@ -31,7 +31,8 @@ def _operands(K1, N1, N2, n_out, RT, NS, G, seed):
 
 @pytest.mark.parametrize("K1,N1,N2,n_out,RT,NS,G", [
     (512, 1024, 512, 66, 1, 4, 2048),    # OthelloNet 8x8 (k_net_fcstack2) at the static array's limit
-    (512, 1024, 512, 66, 2, 4, 300),     # the first kernel, clusters of 8, ragged
+    (192, 512, 256, 60, 1, 2, 1100),     # the first kernel: leaves h1 / h2 activations where the next case's counters lie
+    (512, 1024, 512, 66, 2, 4, 300),     # CTA pairs (k_net_fcstack3): its counters in the h2 region must be cleared first
     (192, 64, 32, 8, 1, 1, 1000),        # Connect4Net
 ])
 def test_static_scratch_matches_the_allocating_entry_point(K1, N1, N2, n_out, RT, NS, G):
