@@ -229,6 +229,9 @@ def run_ours(args):
             batch = gather_samples(batch, episode_offset=rank * G)
         return batch
 
+    from alphazero_b200.selfplay import HostStaging
+    staging = HostStaging()     # pinned buffers of the device -> host read, reused by every e2e step
+
     def step_e2e():
         own = h_own.to(dev, non_blocking=True); opp = h_opp.to(dev, non_blocking=True)
         player = h_player.to(dev, non_blocking=True)
@@ -236,7 +239,7 @@ def run_ours(args):
         if world > 1:
             from alphazero_b200.distributed import gather_samples
             batch = gather_samples(batch, episode_offset=rank * G)
-        host = batch.cpu() if rank == 0 or world == 1 else None
+        host = batch.cpu(staging) if rank == 0 or world == 1 else None
         return batch, host
 
     for _ in range(args.warmup):

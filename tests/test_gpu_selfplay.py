@@ -203,3 +203,22 @@ def test_samples_pack_kernel_matches_torch_indexing(game):
     # ordered by episode, then move; every game contributes a prefix of plies
     ep, mv = got.episode_idx.cpu().numpy(), got.move_idx.cpu().numpy()
     assert (np.diff(ep) >= 0).all() and ((np.diff(mv) == 1) | (np.diff(ep) == 1)).all()
+
+
+def test_host_staging_reuses_its_pinned_buffers():
+    """SampleBatch.cpu(staging): the same values as cpu(), in pinned buffers that are reused while batches fit."""
+    from alphazero_b200.evaluators import HashEvaluator
+    from alphazero_b200.selfplay import HostStaging, SelfPlayEngine
+    eng = SelfPlayEngine(None, 16, n=6, n_sim=8, seed=4, evaluator_factory=lambda t: HashEvaluator(5, t))
+    a = eng.play()
+    st = HostStaging()
+    h = a.cpu(st)
+    ref = a.cpu()
+    for f in ("own", "opp", "pi", "z", "episode_idx", "move_idx"):
+        assert getattr(h, f).is_pinned() and torch.equal(getattr(h, f), getattr(ref, f))
+    ptrs = {k: v.data_ptr() for k, v in st._buf.items()}
+    b = eng.play()
+    assert len(b) <= len(a) * 3 // 2         # inside the 50 % headroom: no new allocation
+    hb = b.cpu(st)
+    assert {k: v.data_ptr() for k, v in st._buf.items()} == ptrs
+    assert torch.equal(hb.pi, b.pi.cpu()) and torch.equal(hb.own, b.own.cpu())
