@@ -559,14 +559,16 @@ __device__ __forceinline__ void az_select(const az_tree& t, const az_dims& d, az
 // MODE (AZ_MODE_NEURAL / AZ_MODE_ROLLOUT) is a template parameter so that each instantiation only carries its own mode's
 // code: the kernel is bound by instruction fetch and dependent-issue latency, not by memory (ncu: `no_instructions` is the
 // top warp stall), so everything that is not on the per-simulation path is compiled out or kept out of line.
+// The block size is the launcher's choice (az_tree_step: any number of warps up to AZ_TREE_MIN_CTAS * AZ_WARPS_PER_CTA
+// -- one warp per game, no block-level cooperation); the bound below gives the same 72-register budget as (128, 7).
 template <int GAME, int MODE>
-__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32, AZ_TREE_MIN_CTAS) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
+__global__ void __launch_bounds__(AZ_WARPS_PER_CTA * 32 * AZ_TREE_MIN_CTAS, 1) k_tree_step(az_tree t, int n_sim, int do_finish, int do_select) {
     // launched with az_launch_pdl: every warp waits for the evaluator's outputs (probs / value) before anything else --
     // also the warps of finished games, so that this grid never completes before its predecessor has -- and then lets
     // the next kernel (the network trunk of the following step) start its prologue beside the tail of this one
     az_pdl_wait();
     az_pdl_trigger();
-    const int g = blockIdx.x * AZ_WARPS_PER_CTA + (threadIdx.x >> 5);
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (g >= t.G) return;
     const az_dims d = az_rules<GAME>::dims(t.n, t.height);
@@ -1171,7 +1173,33 @@ extern "C" int az_tree_step(const az_tree* t, int n_sim, int do_finish, int do_s
     int rc = az_check_tree(t);
     if (rc) return rc;
     if (n_sim < 0) return AZ_ERR_ARG;
-    const dim3 grid(az_warp_grid(t->G)), block(AZ_WARPS_PER_CTA * 32);
+    // Warps (= games) per CTA of the parity step kernel.  All games of a batch must be resident at once (one warp each, a
+    // long dependent chain per warp), and 28 warps fill an SM's register file either way; what the block size decides is
+    // how many CTAs have to be launched behind the network kernel that held every SM: at 4096 games one CTA of 28 warps
+    // per SM (147 CTAs) against 1024 CTAs of 4 warps is 0.5 us per simulation step (52.6 against 53.1 us; 8 warps per CTA
+    // would leave room for 3 CTAs = 24 warps per SM and split the batch in two waves: 57.8 us).  Small batches keep small
+    // CTAs so that they spread over the SMs.  AZ_B200_TREE_WARPS overrides.
+    static const int forced_warps = []() {
+        const char* v = getenv("AZ_B200_TREE_WARPS");
+        const int w = v ? atoi(v) : 0;
+        return w >= 1 && w <= AZ_WARPS_PER_CTA * AZ_TREE_MIN_CTAS ? w : 0;
+    }();
+    int step_warps = forced_warps;
+    if (!step_warps) {
+        static int n_sm = 0;
+        if (!n_sm) {
+            int dev = 0;
+            if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm < 1)
+                n_sm = 148;
+        }
+        const int64_t per_sm = (t->G + n_sm - 1) / n_sm;
+        step_warps = per_sm <= AZ_WARPS_PER_CTA ? AZ_WARPS_PER_CTA
+                   : (per_sm <= 2 * AZ_WARPS_PER_CTA * AZ_TREE_MIN_CTAS / 4 ? 2 * AZ_WARPS_PER_CTA * AZ_TREE_MIN_CTAS / 4
+                                                                          : AZ_WARPS_PER_CTA * AZ_TREE_MIN_CTAS);
+    }
+    const bool multi = t->n_leaves >= 1 && t->mode == AZ_MODE_NEURAL;
+    const int wpc = multi ? AZ_WARPS_PER_CTA : step_warps;
+    const dim3 grid((unsigned)((t->G + wpc - 1) / wpc)), block(wpc * 32);
     cudaError_t e;
 #define AZ_STEP(GAME, MODE) az_launch_pdl(k_tree_step<GAME, MODE>, grid, block, 0, (cudaStream_t)stream, *t, n_sim, do_finish, do_select)
     const bool neural = t->mode == AZ_MODE_NEURAL;
