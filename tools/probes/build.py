@@ -31,6 +31,6 @@ def lib() -> ctypes.CDLL:
         L.az_peak_mma.restype = c_int
         L.az_peak_mma.argtypes = [c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]
         L.az_probe_mma2.restype = c_int
-        L.az_probe_mma2.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]
+        L.az_probe_mma2.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]
         _lib = L
     return _lib

@@ -12,22 +12,27 @@
 #define P2_K 64
 
 __global__ void __launch_bounds__(128, 1) k_mma2_probe(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ B,
-                                                        float* __restrict__ D, int N, int swap_b) {
+                                                        float* __restrict__ D, int N, int swap_b, int shift) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     uint32_t rank;
     asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     const int nh = N / 2;
-    uint8_t* a_s = smem;                              // [8 planes][128 rows][8] bf16 = 16 KB
-    uint8_t* b_s = smem + 16384;                      // [8 planes][nh rows][8]
-    const uint32_t bar = smem_u32(smem + 16384 + 8 * 16 * 128);
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + 16384 + 8 * 16 * 128 + 16);
+    // A: [8 planes][8 zero rows | 128 rows | 8 zero rows][8] bf16; the descriptor may start `shift` rows (16 bytes each)
+    // off the first data row: does a K-major no-swizzle operand need more than 16-byte alignment of its start?
+    constexpr int A_PLANE = (128 + 16) * 16;
+    uint8_t* a_s = smem;
+    uint8_t* b_s = smem + 8 * A_PLANE;                // [8 planes][nh rows][8]
+    const uint32_t bar = smem_u32(smem + 8 * A_PLANE + 8 * 16 * 128);
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + 8 * A_PLANE + 8 * 16 * 128 + 16);
+    for (int i = tid; i < 8 * A_PLANE / 16; i += 128) reinterpret_cast<uint4*>(a_s)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();
 
     // operands: thread = row
     {
         const __nv_bfloat16* src = A + (size_t)(rank * 128 + tid) * P2_K;
         for (int pl = 0; pl < 8; ++pl)
-            *reinterpret_cast<uint4*>(a_s + pl * 2048 + tid * 16) = *reinterpret_cast<const uint4*>(src + pl * 8);
+            *reinterpret_cast<uint4*>(a_s + pl * A_PLANE + (8 + tid) * 16) = *reinterpret_cast<const uint4*>(src + pl * 8);
         const int half = swap_b ? 1 - (int)rank : (int)rank;
         if (tid < nh) {
             const __nv_bfloat16* bs = B + (size_t)(half * nh + tid) * P2_K;
@@ -54,7 +59,7 @@ __global__ void __launch_bounds__(128, 1) k_mma2_probe(const __nv_bfloat16* __re
         if (elect_one()) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (((uint32_t)N >> 3) << 17) | ((256u >> 4) << 24);
             for (int k = 0; k < P2_K / 16; ++k) {
-                const uint64_t ad = umma_desc(smem_u32(a_s) + (uint32_t)k * 4096u, 2048u, 128u);
+                const uint64_t ad = umma_desc(smem_u32(a_s) + (uint32_t)(k * 2 * A_PLANE + (8 + shift) * 16), (uint32_t)A_PLANE, 128u);
                 const uint64_t bd = umma_desc(smem_u32(b_s) + (uint32_t)(k * 32 * nh), (uint32_t)(16 * nh), 128u);
                 asm volatile(
                     "{\n\t"
@@ -92,9 +97,9 @@ __global__ void __launch_bounds__(128, 1) k_mma2_probe(const __nv_bfloat16* __re
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256));
 }
 
-extern "C" int az_probe_mma2(const void* A, const void* B, void* D, int N, int swap_b, void* stream) {
-    if (N < 32 || N > 256 || (N % 32)) return -1;
-    const int smem_bytes = 16384 + 8 * 16 * 128 + 64;
+extern "C" int az_probe_mma2(const void* A, const void* B, void* D, int N, int swap_b, int shift, void* stream) {
+    if (N < 32 || N > 256 || (N % 32) || shift < -8 || shift > 8) return -1;
+    const int smem_bytes = 8 * (128 + 16) * 16 + 8 * 16 * 128 + 64;
     cudaFuncSetAttribute(k_mma2_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem_bytes; cfg.stream = (cudaStream_t)stream;
@@ -102,7 +107,7 @@ extern "C" int az_probe_mma2(const void* A, const void* B, void* D, int N, int s
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, k_mma2_probe, (const __nv_bfloat16*)A, (const __nv_bfloat16*)B, (float*)D, N, swap_b);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_mma2_probe, (const __nv_bfloat16*)A, (const __nv_bfloat16*)B, (float*)D, N, swap_b, shift);
     if (e != cudaSuccess) return -2;
     return cudaGetLastError() == cudaSuccess ? 0 : -3;
 }
