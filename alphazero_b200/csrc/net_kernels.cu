@@ -34,6 +34,7 @@
 #include "common.cuh"
 #include "net_heads.cuh"
 #include "umma.cuh"
+#include "trunk2.cuh"
 
 #define NET_CH 32                 // channels of every conv layer
 #define NET_TILE_M 128            // rows per MMA tile
@@ -692,6 +693,7 @@ extern "C" int az_net_trunk_boards_per_group(int rows, int64_t G) {
     if (cudaGetDevice(&dev) != cudaSuccess ||
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
         return AZ_ERR_CUDA;
+    if (rows == 8 && G >= AZ_TRUNK2_MIN_G && az_trunk2_enabled()) return AZ_TRUNK2_BOARDS_PER_GROUP;    // k_net_trunk2 (opt-in)
     net_group_shape(rows, G, n_sms, &nb, &tiles);
     return nb;
 }
@@ -711,14 +713,19 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
         AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk<7, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, SM_TOTAL));
         attr_set = true;
     }
+    static const int late_trigger = getenv("AZ_B200_TRUNK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_TRUNK_LATE_TRIGGER")) : 0;
+    // 8 x 8 boards in large batches: the shuffle-free kernel (trunk2_kernels.cu); the cycle-accounting mode
+    // (debug_layer 100) belongs to this file's kernel
+    if (rows == 8 && cols == 8 && G >= AZ_TRUNK2_MIN_G && ((features_packed & 2) || az_trunk2_enabled()) &&
+        !(debug && debug_layer == 100))
+        return az_trunk2_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
     NetTrunkParams p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;
     p.G = (int)G; p.rows = rows; p.cols = cols;
     net_group_shape(rows, G, n_sms, &p.boards_per_group, &p.n_tiles);
     p.debug_layer = debug ? debug_layer : 0;
-    p.features_packed = features_packed ? 1 : 0;
-    static const int late_trigger = getenv("AZ_B200_TRUNK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_TRUNK_LATE_TRIGGER")) : 0;
+    p.features_packed = features_packed & 1;
     p.late_trigger = late_trigger;
     const int n_groups = (int)((G + p.boards_per_group - 1) / p.boards_per_group);
     const int grid = n_groups < n_sms ? n_groups : n_sms;   // persistent: one CTA per SM

@@ -74,6 +74,64 @@ def test_trunk_layers_match_fp32(n):
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
+def test_trunk2_layers_match_fp32():
+    """k_net_trunk2 (opt-in; 8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, no shuffles): every
+    conv layer through its debug dump, the zero pad lanes, the features, and the policy / value against fp32."""
+    from alphazero_b200 import _lib
+    from alphazero_b200.fused_net import FusedOthelloEvaluator
+    n = 8
+    net = _net(n, seed=11)
+    tree, x, G0 = _setup(n, 400, seed=13)
+    # 1030 boards: 73 full groups of 14 and one of 8; the positions repeat, which also checks that a board's result
+    # does not depend on where it sits in a group
+    from alphazero_b200.engine import TreeBatch
+    G = 1030
+    idx = torch.arange(G) % G0
+    big = TreeBatch(G, n=n, mode="neural", capacity=64)
+    big.leaf_own.copy_(tree.leaf_own[idx.cuda()]); big.leaf_opp.copy_(tree.leaf_opp[idx.cuda()])
+    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=2)
+    with torch.no_grad():
+        a1 = F.relu(net.bn1(net.conv1(x.view(-1, 1, n, n))))
+        a2 = F.relu(net.bn2(net.conv2(a1)))
+        a3 = F.relu(net.bn3(net.conv3(a2)))
+        a4 = F.relu(net.bn4(net.conv4(a3)))
+    NB, n_groups = 14, (G + 13) // 14
+    lanes = (torch.arange(14)[:, None] * 9 + torch.arange(8)[None, :]).reshape(-1)          # lane of (board, column)
+    for layer, ref, off in ((1, a1, 0), (2, a2, 0), (3, a3, 1)):
+        dbg = torch.zeros(n_groups, 1024, 32, dtype=torch.bfloat16, device="cuda")
+        ev.trunk(debug=dbg, debug_layer=layer)
+        torch.cuda.synchronize()
+        d = dbg.float().cpu().reshape(n_groups, 8, 128, 32)
+        cells = d[:, :, lanes].reshape(n_groups, 8, 14, 8, 32).permute(0, 2, 4, 1, 3).reshape(n_groups * 14, 32, 8, 8)[:G]
+        m = ref.shape[-1]
+        got = cells[:, :, off:off + m, off:off + m]
+        scale = ref.abs().max().item()
+        err = (got - ref[idx]).abs().max().item()
+        assert err < 0.02 * scale + 0.02, (layer, err, scale)
+        if layer == 1:    # conv2's zero padding: the pad column, the two unused lanes and the boards a partial group lacks
+            pad = torch.ones(128, dtype=torch.bool)
+            pad[lanes] = False
+            assert d[:, :, pad].abs().max() == 0
+            assert d[-1, :, (G - (n_groups - 1) * 14) * 9:].abs().max() == 0
+    ev.trunk()
+    torch.cuda.synchronize()
+    feat = ev.features_rowmajor().float().cpu().reshape(G, 16, 32).permute(0, 2, 1).reshape(G, 32, 4, 4)
+    assert (feat - a4[idx]).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
+    assert (feat[G0:2 * G0] == feat[:G0]).all()
+    # the first kernel on the same batch accumulates the same products in another order: both within the layer tolerance,
+    # and the whole forward within the north star's 1e-2 of fp32
+    ev1 = FusedOthelloEvaluator(net, big, use_cuda_graph=False)
+    ev1.trunk()
+    torch.cuda.synchronize()
+    feat1 = ev1.features_rowmajor().float().cpu().reshape(G, 16, 32).permute(0, 2, 1).reshape(G, 32, 4, 4)
+    assert (feat - feat1).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
+    ev(big)
+    torch.cuda.synchronize()
+    ref_p, ref_v = net.predict(x)
+    assert (big.probs.cpu() - ref_p[idx]).abs().max().item() < 1e-2
+    assert (big.value.cpu() - ref_v.reshape(-1)[idx]).abs().max().item() < 1e-2
+
+
 @pytest.mark.parametrize("n,graph", [(8, True), (8, False), (6, True)])
 def test_fused_forward_within_1e2_of_fp32(n, graph):
     from alphazero_b200.fused_net import FusedOthelloEvaluator
