@@ -1,5 +1,7 @@
-"""Where a self-play move's device time goes besides the search: the loop of SelfPlayEngine.play with CUDA events
-around each phase (history copies, search, bookkeeping, choose, advance, terminal test + masks, the host sync)."""
+"""Where a self-play move's device time went besides the search in ROUND 1: the ply loop SelfPlayEngine.play had then
+(history copies, search, bookkeeping, choose, advance, terminal test + masks, the host sync as separate launches), with
+CUDA events around each phase -- profiles/r1_move_phases_*.txt.  The shipped loop is one az_tree_move launch per ply
+(DESIGN 5.2); its share is bench.py's `search_share_of_batch`."""
 import sys, os, time, collections
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
