@@ -65,7 +65,6 @@ static_assert(F3_SM_TOTAL <= 232448, "shared memory per CTA on sm_100");
 // 64 counters in the last 256 bytes: [0, 16) h1 block kc stored (8 warps), [16, 20) partials for owner quarter q stored
 // (3 senders x 4 warps), [20] CTAs of the group that have finished (first tile of the group only)
 #define F3_FLAG_BYTES 256
-#define F3_PART_BYTES(ngrp) (12 * (ngrp) * 2048)
 
 struct Fc3Params {
     const uint8_t* x;          // layer-1 input, packed A: [tiles][K1/64][8][128][8] bf16, tiles even

@@ -118,7 +118,6 @@ __device__ __forceinline__ int t2_mlo(int L) { return L == 3 ? 1 : 0; }
 __device__ __forceinline__ int t2_mcnt(int L) { return L == 3 ? 6 : 8; }
 __device__ __forceinline__ int t2_joff(int L) { return L * 8; }
 __device__ __forceinline__ int t2_ilo(int L) { return L == 0 ? 0 : (L == 3 ? 0 : -1); }
-__device__ __forceinline__ int t2_icnt(int L) { return (L == 0 || L == 3) ? 8 : 10; }
 __device__ __forceinline__ int t2_ioff(int L) { return L == 0 ? 0 : (L == 1 ? 8 : (L == 2 ? 18 : 28)); }
 __device__ __forceinline__ int t2_olo(int L) { return L < 2 ? 0 : L - 1; }          // conv3: 1, conv4: 2
 __device__ __forceinline__ int t2_ohi(int L) { return L < 2 ? 7 : 8 - L; }          // conv3: 6, conv4: 5
