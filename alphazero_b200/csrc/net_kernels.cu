@@ -172,9 +172,10 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
 
     // ---- one-time setup: barriers, async bulk copy of the weights, zeroed activation buffers, TMEM
     if (tid == 0) {
-        for (int st = 0; st < NET_STAGES; ++st) { mbar_init(bar_full0 + 8 * st, 1); mbar_init(bar_empty0 + 8 * st, 128); }
-        for (int t = 0; t < NET_SLOTS * NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 128);
-        for (int sl = 0; sl < NET_SLOTS; ++sl) { mbar_init(bar_im2col0 + 8 * sl, NET_PRODUCERS); mbar_init(bar_i2free0 + 8 * sl, 1); }
+        // (arrivals are per warp -- lane 0 after __syncwarp: 32 lanes arriving on one barrier word serialise)
+        for (int st = 0; st < NET_STAGES; ++st) { mbar_init(bar_full0 + 8 * st, 1); mbar_init(bar_empty0 + 8 * st, 4); }
+        for (int t = 0; t < NET_SLOTS * NET_TILES; ++t) mbar_init(bar_ready0 + 8 * t, 4);
+        for (int sl = 0; sl < NET_SLOTS; ++sl) { mbar_init(bar_im2col0 + 8 * sl, NET_PRODUCERS / 32); mbar_init(bar_i2free0 + 8 * sl, 1); }
         mbar_init(bar_weights, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
@@ -233,7 +234,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            mbar_arrive(bar_im2col0 + 8 * slot);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_im2col0 + 8 * slot);
         }
     } else if (warp >= MMA_WARP) {
         // ================================================================== MMA issue of slot `slot`
@@ -329,7 +331,7 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 asm volatile("bar.sync %0, 128;" ::"r"(1 + (int)slot) : "memory");     // the team's named barrier
-                if (tt < NET_PRODUCERS) mbar_arrive(bar_im2col0 + 8 * slot);
+                if (tt < NET_PRODUCERS / 32) mbar_arrive(bar_im2col0 + 8 * slot);
             }
         }
         mbar_wait(bar_weights, 0u);
@@ -363,7 +365,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         uint32_t acc[32];
                         tmem_ld32(t_lane, acc);
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                        mbar_arrive(bar_empty0 + 8 * stage);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_empty0 + 8 * stage);
 #pragma unroll
                         for (int co = 0; co < 32; co += 2) {
                             float x0, x1;
@@ -403,7 +406,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                         }
                         tmem_ld48_wait(lo1, mid1, hi1);
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                        mbar_arrive(bar_empty0 + 8 * stage);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_empty0 + 8 * stage);
 #pragma unroll
                         for (int co = 0; co < 16; co += 2) {
                             const float up0 = __shfl_up_sync(0xffffffffu, __uint_as_float(lo1[co]), 1);
@@ -426,7 +430,8 @@ __global__ void __launch_bounds__(NET_THREADS, 1) k_net_trunk(NetTrunkParams p) 
                             *reinterpret_cast<uint4*>(d + ch * NET_CHUNK_BYTES) =
                                 make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        mbar_arrive(bar_ready + 8 * t);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar_ready + 8 * t);
                         if (p.debug && p.debug_layer == layer + 1)
                             for (int ch = 0; ch < 4; ++ch)
                                 *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * NET_DEBUG_ROWS + row) * 32 + ch * 8) =
