@@ -33,7 +33,7 @@ WORKLOAD = "othello8x8_alphazero_selfplay_neural_mcts"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--steps", type=int, default=4)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--games", type=int, default=4096, help="concurrent games per GPU")
@@ -291,9 +291,11 @@ def run_ours(args):
     dev_run = e2e_run = None
     sampler = ClockSampler(local_rank)      # one clock record over the whole timed region (both kinds of step)
     sampler.start()
+    per_step_ms = {"device": [], "e2e": []}      # every timed step on its own (an outlier shows up here)
     for _ in range(args.steps):
         a = timed(step_device, 1, sample=False)
         b = timed(step_e2e, 1, sample=False)
+        per_step_ms["device"].append(round(a["ms"], 2)); per_step_ms["e2e"].append(round(max(b["ms"], b["wall_ms"]), 2))
         if dev_run is None:
             dev_run, e2e_run = a, b
         else:
@@ -393,6 +395,7 @@ def run_ours(args):
         "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
         "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
         "search_share_of_batch": search_ms / (dev_run["ms"] / args.steps),
+        "per_step_ms": per_step_ms,
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
