@@ -295,7 +295,7 @@ class FusedNetEvaluator:
             own, opp = self.img_own, self.img_opp
         _lib.check(_lib.lib().az_net_trunk(_ptr(own), _ptr(opp), self.rows, self.cols, t.G, _ptr(self.wblob),
                                            _ptr(self.features),
-                                           (1 if self.heads == "stack" else 0) | (2 if self.trunk_variant == 2 else 0), _ptr(debug),
+                                           (1 if self.heads == "stack" else 0) | (2 if self.trunk_variant == 2 else 0) | (4 if self.trunk_variant == 3 else 0), _ptr(debug),
                                            int(debug_layer), _stream()), "az_net_trunk")
 
     def _forward(self, output_transform: bool = True) -> None:

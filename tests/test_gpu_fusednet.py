@@ -74,9 +74,11 @@ def test_trunk_layers_match_fp32(n):
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
-def test_trunk2_layers_match_fp32():
-    """k_net_trunk2 (opt-in; 8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, no shuffles): every
-    conv layer through its debug dump, the zero pad lanes, the features, and the policy / value against fp32."""
+@pytest.mark.parametrize("variant", [2, 3])
+def test_trunk2_layers_match_fp32(variant):
+    """k_net_trunk2 / k_net_trunk3 (8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, no shuffles;
+    the third kernel with one accumulator per output tile): every conv layer through its debug dump, the zero pad lanes,
+    the features, and the policy / value against fp32."""
     from alphazero_b200 import _lib
     from alphazero_b200.fused_net import FusedOthelloEvaluator
     n = 8
@@ -89,7 +91,7 @@ def test_trunk2_layers_match_fp32():
     idx = torch.arange(G) % G0
     big = TreeBatch(G, n=n, mode="neural", capacity=64)
     big.leaf_own.copy_(tree.leaf_own[idx.cuda()]); big.leaf_opp.copy_(tree.leaf_opp[idx.cuda()])
-    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=2)
+    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=variant)
     with torch.no_grad():
         a1 = F.relu(net.bn1(net.conv1(x.view(-1, 1, n, n))))
         a2 = F.relu(net.bn2(net.conv2(a1)))

@@ -1,4 +1,5 @@
-"""Cycle stamps of k_net_trunk2 (debug_layer 200) and its time in a CUDA graph.   python tools/trunk2_probe.py [G]"""
+"""Cycle stamps of k_net_trunk2 / k_net_trunk3 (debug_layer 200) and their time in a CUDA graph.
+   python tools/trunk2_probe.py [G] [variant 2|3]"""
 import os
 import sys
 
@@ -10,11 +11,12 @@ from alphazero_b200.fused_net import FusedOthelloEvaluator
 from alphazero_b200.games.othello import OthelloNet
 
 G = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+VARIANT = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 torch.manual_seed(0)
 net = OthelloNet(n=8)
 tree = TreeBatch(G, n=8, mode="neural", capacity=64)
 tree.leaf_own.random_(0, 2**62); tree.leaf_opp.copy_(~tree.leaf_own & torch.randint(0, 2**62, (G,), device="cuda"))
-ev = FusedOthelloEvaluator(net, tree, use_cuda_graph=False, trunk_variant=2)
+ev = FusedOthelloEvaluator(net, tree, use_cuda_graph=False, trunk_variant=VARIANT)
 n_ctas = min(148, (G + 13) // 14)
 dbg = torch.zeros(n_ctas * 16, dtype=torch.int64, device="cuda")
 for _ in range(3):
@@ -23,7 +25,7 @@ torch.cuda.synchronize()
 d = dbg.reshape(n_ctas, 16).double()
 names = {0: "setup done (after pdl wait)", 1: "im2col of group 0 built", 8: "group 0: conv1 issued",
          9: "group 0: conv2 issued", 10: "group 0: conv3 issued", 3: "group 0 issued (conv4)", 11: "exit",
-         12: "mma: total wait im2col", 5: "mma: total wait ready", 6: "mma: total wait empty", 7: "mma: total issue + commit",
+         12: "mma: total wait im2col", 5: "mma: total wait ready", 6: "mma: total wait empty (v2) / conv4 read (v3)", 7: "mma: total issue + commit",
          13: "epilogue team 0: total wait full", 14: "epilogue team 0: total work"}
 for i, nm in names.items():
     print(f"    {nm:40s} median {d[:, i].median().item():8.0f}  min {d[:, i].min().item():8.0f}  max {d[:, i].max().item():8.0f} cycles")
@@ -45,4 +47,4 @@ for _ in range(10):
     g.replay()
 e1.record()
 torch.cuda.synchronize()
-print(f"trunk, {G} positions: {1000 * e0.elapsed_time(e1) / 200:.2f} us per launch in a graph")
+print(f"trunk variant {VARIANT}, {G} positions: {1000 * e0.elapsed_time(e1) / 200:.2f} us per launch in a graph")
