@@ -64,7 +64,9 @@
 #define TC_O4DONE 54                                   // conv4's accumulators of the group have been read (16 warps)
 #define TC_COUNT 55
 #define T3_SM_ITEMS (T3_SM_BARS + 8 * 56)              // uint32 [26]: layer, tile, last job, TMEM column of each epilogue item
-#define T3_SM_TMEM_PTR (T3_SM_ITEMS + 4 * 28)
+#define T3_CJOBS 14                                    // jobs of conv2..conv4 per group and issuing warp
+#define T3_SM_JOBS (T3_SM_ITEMS + 4 * 28)              // uint4 [2][14]: what the issuing thread needs to know about a job
+#define T3_SM_TMEM_PTR (T3_SM_JOBS + 16 * 2 * T3_CJOBS)
 #define T3_SM_TOTAL (T3_SM_TMEM_PTR + 16)
 static_assert(T3_SM_TOTAL <= 232448, "shared memory per CTA on sm_100");
 #define T3_WAIT_LIMIT (4000000000LL)
@@ -98,6 +100,25 @@ __device__ __forceinline__ void t3_wait(uint32_t bar, uint32_t parity) {
 // arrivals that do not wait for the barrier's state word to come back
 __device__ __forceinline__ void t3_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// tcgen05.mma with K-major no-swizzle descriptors given by their low words (start address >> 4 | LBO >> 4 << 16; the
+// high word -- SBO = 128 bytes, descriptor version 1 -- is the same for every operand of this kernel): moving an
+// operand by d bytes adds d >> 4 to the low word (shared memory addresses stay below 2^18), which is all the issuing
+// thread computes per instruction
+__device__ __forceinline__ void t3_mma(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %5};\n\t"
+        "mov.b64 db, {%2, %5};\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t"
+        "}" ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "r"(0x4008u) : "memory");
+}
+__device__ __forceinline__ uint32_t t3_desc_lo(uint32_t smem_addr, uint32_t lbo) {
+    return ((smem_addr >> 4) & 0x3FFFu) | ((lbo >> 4) << 16);
 }
 
 // Per layer L = 0..3 (conv1..conv4): first MMA tile, number of MMA tiles, job offset inside a group; first / last
@@ -149,7 +170,10 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_net_trunk3(Trunk3Params p) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int n_groups = (p.G + T3_NB - 1) / T3_NB;
     // debug_layer 200: cycle stamps instead of activations, int64 [n_ctas][16] (tools/trunk2_probe.py)
-    long long* stamps = (p.debug && p.debug_layer == 200) ? reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 16 : nullptr;
+    // (201: the same without the MMA warps' waits for the epilogue, 202: also with N = 32 MMAs only -- wrong results, the
+    // cost of the MMA stream alone)
+    const int hack = p.debug_layer >= 200 ? p.debug_layer - 200 : 0;
+    long long* stamps = (p.debug && p.debug_layer >= 200) ? reinterpret_cast<long long*>(p.debug) + (size_t)blockIdx.x * 16 : nullptr;
     const long long t_entry = stamps ? clock64() : 0;
     const uint32_t sbase = smem_u32(smem);
     const uint32_t bars = smem_u32(smem + T3_SM_BARS);
@@ -173,13 +197,48 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_net_trunk3(Trunk3Params p) {
         // are read by the other warp too, whose job on that tile is the item's second barrier.
         const int idx = tid - 64;
         const int L = idx < 8 ? 0 : (idx < 16 ? 1 : (idx < 22 ? 2 : 3));
-        const int r = idx - (L == 0 ? 0 : (L == 1 ? 8 : (L == 2 ? 16 - 1 : 22 - 2)));
+        // (both the jobs of a warp and the items of a layer go from the border outwards -- tiles 3, 4, 2, 5, 1, 6, 0, 7 --
+        // so that what the next layer needs first is complete first)
+        const int pos = idx - (L == 0 ? 0 : (L == 1 ? 8 : (L == 2 ? 16 : 22)));
+        const int r = (pos & 1) ? 4 + (pos >> 1) : 3 - (pos >> 1);
         const int h = r >> 2;
-        const int job = h * T3_HJOBS + (L == 0 ? r - 4 * h : t3_jloc(L) + min(r + 1, t3_thi(h, L)) - t3_tlo(h, L));
+        int j;                                                     // the step of warp h that completes the accumulator
+        if (L == 0) j = h ? r - 4 : 3 - r;
+        else j = h ? min(r + 1, t3_thi(1, L)) - t3_tlo(1, L) : t3_thi(0, L) - max(r - 1, t3_tlo(0, L));
+        const int job = h * T3_HJOBS + t3_jloc(L) + j;
         int job2 = job;
-        if (L > 0 && (r == 3 || r == 4)) job2 = (1 - h) * T3_HJOBS + t3_jloc(L) + r - t3_tlo(1 - h, L);
+        if (L > 0 && (r == 3 || r == 4)) job2 = (1 - h) * T3_HJOBS + t3_jloc(L);      // tile 3 / 4 is the other warp's first job
         reinterpret_cast<uint32_t*>(smem + T3_SM_ITEMS)[idx] =
             (uint32_t)L | ((uint32_t)r << 4) | ((uint32_t)job << 8) | ((uint32_t)job2 << 14) | (t3_ocol(L, r) << 20);
+    }
+    if (tid >= 96 && tid < 96 + 2 * T3_CJOBS) {
+        // job jj of issuing warp h in conv2..conv4 (its step j of layer L): everything about it that does not depend on the
+        // group.  Warp 0 goes down from the border (tiles 4, 3, ..), warp 1 up (3, 4, ..).
+        const int h = (tid - 96) / T3_CJOBS, jj = (tid - 96) % T3_CJOBS;
+        const int L = jj < 5 ? 1 : (jj < 10 ? 2 : 3), j = jj - (5 * L - 5);
+        const int tlo = t3_tlo(h, L), thi = t3_thi(h, L), olo = t3_holo(h, L), ohi = t3_hohi(h, L);
+        const int r = h ? tlo + j : thi - j;
+        // kernel rows whose output tile r - kh + 1 this warp produces: kh = klo .. khi, 32 accumulator columns each, output
+        // tiles descending = columns ascending from that of tile r - klo + 1
+        const int klo = max(0, r + 1 - ohi), khi = min(2, r + 1 - olo), nblk = khi - klo + 1;
+        const uint32_t d_col = (uint32_t)((L & 1) * 256 + 32 * (6 - r + klo));
+        // the first contribution to an output tile must not accumulate: all of the warp's first job of the layer; of every
+        // other, the block of the output tile it reaches first -- tile r - 1 (kh = 2, the last block) going down, tile
+        // r + 1 (kh = 0, the first block) going up -- by an N = 32 MMA of its own before the rest
+        const bool first = j == 0, init = !first && (h ? klo == 0 : khi == 2);
+        uint32_t z = d_col | ((uint32_t)nblk << 9);
+        if (!init) z |= (0u << 11) | ((uint32_t)nblk << 13) | ((first ? 0u : 1u) << 15);
+        else {
+            const uint32_t ipos = h ? 0u : (uint32_t)(nblk - 1), rpos = h ? 1u : 0u;
+            z |= (ipos << 11) | (1u << 13) | (0u << 15);
+            if (nblk > 1) z |= (1u << 16) | (rpos << 17) | ((uint32_t)(nblk - 1) << 19);
+        }
+        if (L == 1 && j == 0) z |= 1u << 21;
+        const uint32_t wl = sbase + T3_SM_W + (uint32_t)((L - 1) * 3) * T3_W_DC_BYTES + (uint32_t)(klo * 32 * 16);
+        reinterpret_cast<uint4*>(smem + T3_SM_JOBS)[tid - 96] =
+            make_uint4((uint32_t)(T3_MARGIN + r * 128 - 1),            // A: the tile's rows shifted by -1 column, in 16-byte rows
+                       t3_desc_lo(wl, 96u * 16u), z,
+                       (uint32_t)r | (((r >= 1 && r <= 6) ? 3u : 2u) << 3) | ((uint32_t)(L - 1) << 5));
     }
     // the rows nothing ever writes: the margins of the activation buffers (the row before tile 0 is lane 0's left
     // neighbour = zero padding) and the two unused lanes of every tile (lane 127 is the left neighbour of the next
@@ -264,11 +323,16 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_net_trunk3(Trunk3Params p) {
         }
     } else if (warp >= T3_MMA_WARP) {
         // ================================================================== MMA issue: warp h issues the tile jobs that
-        // accumulate into the output tiles 4 h .. 4 h + 3, in program order, by one thread (one thread issues an MMA
-        // every ~65 cycles at best: two of them keep the tensor pipe busy, and their accumulators are disjoint)
+        // accumulate into the output tiles 4 h .. 4 h + 3, in program order, by one elected thread of a converged warp
+        // (a single lane in divergent code costs an election and seven register broadcasts per MMA: measured slower).
+        // The issuing thread is the serial resource of this kernel (a tcgen05.mma costs it ~65 cycles; two of them
+        // keep the tensor pipe busy), so what a job needs beyond the group's buffer is in the table built at set-up.
         const int h = warp - T3_MMA_WARP;
         const uint32_t jobs = bars + 8 * (TC_JOB + h * T3_HJOBS);
-        const uint32_t idesc32 = umma_idesc_bf16_m128(32u), idesc64 = umma_idesc_bf16_m128(64u), idesc96 = umma_idesc_bf16_m128(96u);
+        const uint32_t idesc32 = umma_idesc_bf16_m128(32u);
+        constexpr uint32_t IDESC_BLK = (32u >> 3) << 17;          // one more kernel row = 32 more columns
+        const uint4* table = reinterpret_cast<const uint4*>(smem + T3_SM_JOBS) + h * T3_CJOBS;
+        const uint32_t w1_lo = t3_desc_lo(sbase + T3_SM_W1, 512u);
         uint32_t k = 0;                               // group counter of this CTA
         long long w_ready = 0, w_o4 = 0, t_issue = 0, w_im2col = 0;
         for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++k) {
@@ -283,9 +347,9 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_net_trunk3(Trunk3Params p) {
             if (elect_one()) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const int r = 4 * h + i;
-                    umma_bf16(tmem_base + t3_ocol(0, r), umma_desc(sbase + T3_SM_IM2COL + (uint32_t)(T3_MARGIN + r * 128) * 16u, T3_PLANE, 128u),
-                              umma_desc(sbase + T3_SM_W1, 512u, 128u), idesc32, 0u);
+                    const int r = h ? 4 + i : 3 - i;
+                    t3_mma(tmem_base + t3_ocol(0, r), t3_desc_lo(sbase + T3_SM_IM2COL + (uint32_t)(T3_MARGIN + r * 128) * 16u, T3_PLANE), w1_lo,
+                           idesc32, 0u);
                     umma_commit(jobs + 8 * i);
                 }
                 umma_commit(bars + 8 * TC_I2FREE);    // conv1 has read the im2col buffer: the producers may build the next group's
@@ -293,57 +357,44 @@ __global__ void __launch_bounds__(T3_THREADS, 1) k_net_trunk3(Trunk3Params p) {
             __syncwarp();
             if (stamps) t_issue += clock64() - c_j;
             if (stamps && lane == 0 && k == 0 && h == 0) stamps[8] = clock64() - t_entry;
+            const uint32_t abuf_lo = t3_desc_lo(sbase + T3_SM_BUF(buf), T3_PLANE);
+            const uint32_t ready = bars + 8 * (TC_READY + buf * 8);
 #pragma unroll 1
-            for (int L = 1; L < 4; ++L) {
-                const int mlo = t3_tlo(h, L), mhi = t3_thi(h, L), olo = t3_holo(h, L), ohi = t3_hohi(h, L);
-                const uint32_t wl = sbase + T3_SM_W + (uint32_t)((L - 1) * 3) * T3_W_DC_BYTES;
-                const uint32_t region = tmem_base + (uint32_t)((L & 1) * 256);
-#pragma unroll 1
-                for (int r = mlo; r <= mhi; ++r) {
-                    const long long c0 = stamps ? clock64() : 0;
-                    {   // layer L - 1's output tile r: phase (use * P + L - 1) of ready[buf][r], P = layers that write tile r
-                        const uint32_t P = (r >= 1 && r <= 6) ? 3u : 2u;
-                        t3_wait(bars + 8 * (TC_READY + buf * 8 + r), (use * P + (uint32_t)(L - 1)) & 1u);
-                    }
-                    const long long c1 = stamps ? clock64() : 0;
-                    // region 1 still holds conv4's accumulators of the previous group until its four epilogue items have read them
-                    if (L == 1 && r == mlo && k > 0) t3_wait(bars + 8 * TC_O4DONE, (k - 1u) & 1u);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const long long c2 = stamps ? clock64() : 0;
-                    if (elect_one()) {
-                        // kernel rows whose output tile r - kh + 1 the layer produces: kh = klo .. khi, 32 accumulator columns each
-                        const int klo = max(0, r + 1 - ohi), khi = min(2, r + 1 - olo), nblk = khi - klo + 1;
-                        const uint32_t d_tmem = region + (uint32_t)(32 * (6 - r + klo));
-                        const uint32_t idesc = nblk == 3 ? idesc96 : (nblk == 2 ? idesc64 : idesc32);
-                        const uint32_t a0 = sbase + T3_SM_BUF(buf) + (uint32_t)(T3_MARGIN + r * 128) * 16u;
-                        const uint32_t b0 = wl + (uint32_t)(klo * 32 * 16);
-                        // the first contribution to an output tile must not accumulate: all of the layer's first job, the
-                        // kh = 0 block (output tile r + 1) of every other
-                        const bool first = r == mlo;
-#pragma unroll
-                        for (int kw = 0; kw < 3; ++kw) {
-#pragma unroll
-                            for (int kk = 0; kk < 2; ++kk) {
-                                // A: the tile's rows shifted by kw - 1 columns (= rows of 16 bytes), channels 16 kk ..
-                                const uint32_t aa = a0 + (uint32_t)((kw - 1) * 16 + kk * 2 * T3_PLANE);
-                                const uint32_t bb = b0 + (uint32_t)(kw * T3_W_DC_BYTES + kk * 2 * 96 * 16);
-                                if (kw == 0 && kk == 0 && !first && klo == 0) {
-                                    umma_bf16(d_tmem, umma_desc(aa, T3_PLANE, 128u), umma_desc(bb, 96u * 16u, 128u), idesc32, 0u);
-                                    if (nblk > 1)
-                                        umma_bf16(d_tmem + 32u, umma_desc(aa, T3_PLANE, 128u), umma_desc(bb + 512u, 96u * 16u, 128u),
-                                                  nblk == 3 ? idesc64 : idesc32, 1u);
-                                } else {
-                                    umma_bf16(d_tmem, umma_desc(aa, T3_PLANE, 128u), umma_desc(bb, 96u * 16u, 128u), idesc,
-                                              (kw == 0 && kk == 0 && first) ? 0u : 1u);
-                                }
-                            }
-                        }
-                        umma_commit(jobs + 8 * (t3_jloc(L) + r - mlo));
-                    }
-                    __syncwarp();
-                    if (stamps) { const long long c3 = clock64(); w_ready += c1 - c0; w_o4 += c2 - c1; t_issue += c3 - c2; }
+            for (int jj = 0; jj < T3_CJOBS; ++jj) {
+                const uint4 e = table[jj];
+                const long long c0 = stamps ? clock64() : 0;
+                {   // the input: layer L - 1's output tile r = phase (use * P + L - 1) of ready[buf][r], P = layers that write tile r
+                    const uint32_t r = e.w & 7u, P = (e.w >> 3) & 3u, Lm1 = (e.w >> 5) & 3u;
+                    if (hack == 0) t3_wait(ready + 8 * r, (use * P + Lm1) & 1u);
                 }
-                if (stamps && lane == 0 && k == 0 && h == 0) stamps[8 + L] = clock64() - t_entry;      // group 0: layer L issued
+                const long long c1 = stamps ? clock64() : 0;
+                // region 1 still holds conv4's accumulators of the previous group until its four epilogue items have read them
+                if (((e.z >> 21) & 1u) && k > 0 && hack == 0) t3_wait(bars + 8 * TC_O4DONE, (k - 1u) & 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const long long c2 = stamps ? clock64() : 0;
+                const uint32_t d_tmem = tmem_base + (e.z & 511u);
+                const uint32_t idesc = idesc32 + (hack == 2 ? 0u : (((e.z >> 9) & 3u) - 1u) * IDESC_BLK);
+                const uint32_t a_lo = abuf_lo + e.x, b_lo = e.y;
+                if (elect_one()) {
+                {   // kernel column 0, channels 0..15: whole, or the block that must not accumulate and then the rest
+                    const uint32_t pos = (e.z >> 11) & 3u;
+                    t3_mma(d_tmem + 32u * pos, a_lo, b_lo + 32u * pos, idesc32 + (((e.z >> 13) & 3u) - 1u) * IDESC_BLK, (e.z >> 15) & 1u);
+                    if ((e.z >> 16) & 1u) {
+                        const uint32_t pos2 = (e.z >> 17) & 3u;
+                        t3_mma(d_tmem + 32u * pos2, a_lo, b_lo + 32u * pos2, idesc32 + (((e.z >> 19) & 3u) - 1u) * IDESC_BLK, 1u);
+                    }
+                }
+#pragma unroll
+                for (int i = 1; i < 6; ++i) {
+                    const int kw = i >> 1, kk = i & 1;
+                    t3_mma(d_tmem, a_lo + (uint32_t)(kw + kk * (2 * T3_PLANE >> 4)),
+                           b_lo + (uint32_t)(kw * (T3_W_DC_BYTES >> 4) + kk * (2 * 96 * 16 >> 4)), idesc, 1u);
+                }
+                umma_commit(jobs + 8 * (4 + jj));
+                }
+                __syncwarp();
+                if (stamps) { const long long c3 = clock64(); w_ready += c1 - c0; w_o4 += c2 - c1; t_issue += c3 - c2; }
+                if (stamps && lane == 0 && k == 0 && h == 0 && (jj == 4 || jj == 9)) stamps[jj == 4 ? 9 : 10] = clock64() - t_entry;   // group 0: conv2 / conv3 issued
             }
             if (stamps && lane == 0 && k == 0 && h == 0) stamps[3] = clock64() - t_entry;
         }

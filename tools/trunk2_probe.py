@@ -19,16 +19,20 @@ tree.leaf_own.random_(0, 2**62); tree.leaf_opp.copy_(~tree.leaf_own & torch.rand
 ev = FusedOthelloEvaluator(net, tree, use_cuda_graph=False, trunk_variant=VARIANT)
 n_ctas = min(148, (G + 13) // 14)
 dbg = torch.zeros(n_ctas * 16, dtype=torch.int64, device="cuda")
+MODE = int(sys.argv[3]) if len(sys.argv) > 3 else 200       # variant 3: 201 = no waits for the epilogue, 202 = and N = 32 only
 for _ in range(3):
-    ev.trunk(debug=dbg.view(torch.bfloat16), debug_layer=200)
+    ev.trunk(debug=dbg.view(torch.bfloat16), debug_layer=MODE)
 torch.cuda.synchronize()
 d = dbg.reshape(n_ctas, 16).double()
+print(f"stamps, mode {MODE}")
 names = {0: "setup done (after pdl wait)", 1: "im2col of group 0 built", 8: "group 0: conv1 issued",
          9: "group 0: conv2 issued", 10: "group 0: conv3 issued", 3: "group 0 issued (conv4)", 11: "exit",
          12: "mma: total wait im2col", 5: "mma: total wait ready", 6: "mma: total wait empty (v2) / conv4 read (v3)", 7: "mma: total issue + commit",
          13: "epilogue team 0: total wait full", 14: "epilogue team 0: total work"}
 for i, nm in names.items():
     print(f"    {nm:40s} median {d[:, i].median().item():8.0f}  min {d[:, i].min().item():8.0f}  max {d[:, i].max().item():8.0f} cycles")
+if MODE != 200:
+    sys.exit(0)
 g = torch.cuda.CUDAGraph()
 s = torch.cuda.Stream()
 s.wait_stream(torch.cuda.current_stream())
