@@ -217,7 +217,7 @@ int az_set_cuda_error(cudaError_t e, const char* where) {
     return AZ_ERR_CUDA;
 }
 
-extern "C" int az_abi_version(void) { return 9; }
+extern "C" int az_abi_version(void) { return 10; }
 // a non-CUDA failure with a message for az_last_cuda_error (argument / capacity errors that deserve an explanation)
 int az_set_error_message(int code, const char* msg) {
     snprintf(g_last_error, sizeof(g_last_error), "%s", msg);

@@ -34,8 +34,7 @@
 #include "common.cuh"
 #include "net_heads.cuh"
 #include "umma.cuh"
-#include "trunk2.cuh"
-#include "trunk3.cuh"
+#include "trunk_rows.cuh"
 
 #define NET_CH 32                 // channels of every conv layer
 #define NET_TILE_M 128            // rows per MMA tile
@@ -699,7 +698,7 @@ extern "C" int az_net_trunk_boards_per_group(int rows, int64_t G) {
     if (cudaGetDevice(&dev) != cudaSuccess ||
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
         return AZ_ERR_CUDA;
-    if (rows == 8 && G >= AZ_TRUNK2_MIN_G && (az_trunk2_enabled() || az_trunk3_enabled())) return AZ_TRUNK2_BOARDS_PER_GROUP;    // k_net_trunk2 / 3 (opt-in)
+    if (rows == 8 && G >= AZ_TRUNK_ROWS_MIN_G && az_trunk_rows_enabled()) return AZ_TRUNK_ROWS_BOARDS_PER_GROUP;    // k_net_trunk_rows
     net_group_shape(rows, G, n_sms, &nb, &tiles);
     return nb;
 }
@@ -720,14 +719,11 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
         attr_set = true;
     }
     static const int late_trigger = getenv("AZ_B200_TRUNK_LATE_TRIGGER") ? atoi(getenv("AZ_B200_TRUNK_LATE_TRIGGER")) : 0;
-    // 8 x 8 boards in large batches: the shuffle-free kernel (trunk2_kernels.cu); the cycle-accounting mode
-    // (debug_layer 100) belongs to this file's kernel
-    if (rows == 8 && cols == 8 && G >= AZ_TRUNK3_MIN_G && ((features_packed & 4) || az_trunk3_enabled()) &&
+    // 8 x 8 boards in large batches: k_net_trunk_rows (trunk_rows_kernels.cu) unless the caller (bit 1) or the
+    // environment asks for this file's kernel; the cycle-accounting mode (debug_layer 100) belongs to this file's kernel
+    if (rows == 8 && cols == 8 && G >= AZ_TRUNK_ROWS_MIN_G && !(features_packed & 2) && az_trunk_rows_enabled() &&
         !(debug && debug_layer == 100))
-        return az_trunk3_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
-    if (rows == 8 && cols == 8 && G >= AZ_TRUNK2_MIN_G && ((features_packed & 2) || az_trunk2_enabled()) &&
-        !(debug && debug_layer == 100))
-        return az_trunk2_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
+        return az_trunk_rows_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
     NetTrunkParams p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;

@@ -1,0 +1,11 @@
+// k_net_trunk_rows (trunk_rows_kernels.cu): the convolution trunk for 8 x 8 boards in batches of 1024 positions and
+// more (tile = one board row of 14 boards, one TMEM accumulator per output tile); launched by az_net_trunk.
+#pragma once
+#include <stdint.h>
+
+#define AZ_TRUNK_ROWS_BOARDS_PER_GROUP 14
+#define AZ_TRUNK_ROWS_MIN_G 1024        // smaller batches keep the first kernel (smaller groups spread over more SMs)
+
+bool az_trunk_rows_enabled();
+int az_trunk_rows_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
+                     int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream);

@@ -292,11 +292,11 @@ int az_net_wblob_bytes(void);
  * tcgen05 implicit GEMM, activations resident in shared memory.
  * debug (optional): bf16 [ceil(G / boards_per_group)][768][32] dump of the activations after conv<debug_layer>
  * (az_net_trunk_boards_per_group gives boards_per_group).
- * Bit 1 of features_packed (or AZ_B200_TRUNK_V2=1 in the environment) selects k_net_trunk2 for 8 x 8 images in batches
- * of 1024 and more: the same results from a formulation without cross-lane traffic in the epilogue (tile = one board
- * row of 14 boards, kernel column = a 16-byte shift of the A operand, kernel row = the N dimension; csrc/
- * trunk2_kernels.cu).  Its debug dump is bf16 [ceil(G/14)][1024][32], row = board_row * 128 + (g % 14) * 9 + column.
- * Measured slower than the first kernel so far (profiles/r2_trunk_experiments.txt), hence opt-in. */
+ * 8 x 8 images in batches of 1024 positions and more are computed by k_net_trunk_rows (csrc/trunk_rows_kernels.cu: tile =
+ * one board row of 14 boards, kernel column = a 16-byte shift of the A operand, kernel row = the N dimension, one TMEM
+ * accumulator per output tile; the same results within bf16 rounding, 19.6 against 22.9 us per 4096 positions).  Its
+ * debug dump is bf16 [ceil(G/14)][1024][32], row = board_row * 128 + (g % 14) * 9 + column.  Bit 1 of features_packed
+ * (or AZ_B200_TRUNK_V1=1 in the environment) keeps the first kernel for such a batch too. */
 int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob,
                  void* features, int features_packed, void* debug, int debug_layer, void* stream);
 

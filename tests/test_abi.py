@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(L, name), f"{name} declared in az_b200.h but not exported"
         assert name in _lib.SIGNATURES, f"{name} has no ctypes signature in alphazero_b200/_lib.py"
     assert set(_lib.SIGNATURES) == set(names)
-    assert _lib.lib().az_abi_version() == 9
+    assert _lib.lib().az_abi_version() == 10
 
 
 def test_struct_layout_matches_c(tmp_path):

@@ -74,11 +74,10 @@ def test_trunk_layers_match_fp32(n):
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
-@pytest.mark.parametrize("variant", [2, 3])
-def test_trunk2_layers_match_fp32(variant):
-    """k_net_trunk2 / k_net_trunk3 (8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, no shuffles;
-    the third kernel with one accumulator per output tile): every conv layer through its debug dump, the zero pad lanes,
-    the features, and the policy / value against fp32."""
+def test_trunk_rows_layers_match_fp32():
+    """k_net_trunk_rows (8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, one accumulator per
+    output tile): every conv layer through its debug dump, the zero pad lanes, the features, and the policy / value
+    against fp32; and against k_net_trunk on the same batch."""
     from alphazero_b200 import _lib
     from alphazero_b200.fused_net import FusedOthelloEvaluator
     n = 8
@@ -91,7 +90,8 @@ def test_trunk2_layers_match_fp32(variant):
     idx = torch.arange(G) % G0
     big = TreeBatch(G, n=n, mode="neural", capacity=64)
     big.leaf_own.copy_(tree.leaf_own[idx.cuda()]); big.leaf_opp.copy_(tree.leaf_opp[idx.cuda()])
-    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=variant)
+    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False)
+    assert _lib.lib().az_net_trunk_boards_per_group(8, G) == 14
     with torch.no_grad():
         a1 = F.relu(net.bn1(net.conv1(x.view(-1, 1, n, n))))
         a2 = F.relu(net.bn2(net.conv2(a1)))
@@ -122,7 +122,7 @@ def test_trunk2_layers_match_fp32(variant):
     assert (feat[G0:2 * G0] == feat[:G0]).all()
     # the first kernel on the same batch accumulates the same products in another order: both within the layer tolerance,
     # and the whole forward within the north star's 1e-2 of fp32
-    ev1 = FusedOthelloEvaluator(net, big, use_cuda_graph=False)
+    ev1 = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=1)
     ev1.trunk()
     torch.cuda.synchronize()
     feat1 = ev1.features_rowmajor().float().cpu().reshape(G, 16, 32).permute(0, 2, 1).reshape(G, 32, 4, 4)
