@@ -339,6 +339,9 @@ def run_ours(args):
     step_ms = full_ms / max(1, search_steps)
     eval_ms, tree_ms, timing = eager_eval_ms, eager_tree_ms, "eager calls between CUDA events"
     kernel_ms = None
+    # the trunk kernel az_net_trunk takes for this batch (include/az_b200.h)
+    trunk_kernel = ("k_net_trunk_rows" if args.game == "othello" and n == 8 and G >= 1024
+                    and not os.environ.get("AZ_B200_TRUNK_V1") else "k_net_trunk")
     if hasattr(engine.evaluator, "enqueue") and tree.graph_search:
         K = 64
         net_graph = torch.cuda.CUDAGraph()
@@ -371,7 +374,7 @@ def run_ours(args):
                 return a0.elapsed_time(a1) / (8 * reps)
             L = _lib.lib()
             stream = lambda: torch.cuda.current_stream().cuda_stream
-            kernel_ms = {"k_net_trunk": in_graph(ev.trunk),
+            kernel_ms = {trunk_kernel: in_graph(ev.trunk),
                          "k_net_fcstack": in_graph(lambda: _lib.check(L.az_net_fcstack(
                              ev.features.data_ptr(), ev.stack_blob.data_ptr(), ev.h1.data_ptr(), ev.h2.data_ptr(),
                              ev.logits.data_ptr(), ev.ld, ev.A + 1, ev.tree.G, ev.K1, ev.N1, ev.N2, ev.RT, ev.NS, stream()),
@@ -382,15 +385,15 @@ def run_ours(args):
     tflops = G * flop_per_eval / (eval_ms * 1e-3) / 1e12
     roofline = {
         "bound": "tensor",
-        "kernel": "policy-value network forward over the leaf batch = k_net_trunk (conv1-4, tcgen05) + k_net_fcstack "
+        "kernel": f"policy-value network forward over the leaf batch = {trunk_kernel} (conv1-4, tcgen05) + k_net_fcstack "
                   "(fc1, fc2, heads, tcgen05 cluster kernel), both hand-written, bf16, inside the whole-search CUDA graph"
                   if args.net == "fused" else "the torch module's own bf16 forward (library kernels)",
         "library_share": 0.0 if args.net == "fused" else 1.0,
         "kernel_ms_alone_in_graph": kernel_ms,
         "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": tflops / peaks["bf16_tflops_sustained"], "peak_source": peaks["source"] + " (sustained: timed inside a long step)",
-        "traffic": ncu_traffic("k_net_trunk", ("r2_ncu_full_summary.json", "r1_ncu_full_summary.json")) if args.net == "fused" else None,
-        "traffic_note": "DRAM bytes per k_net_trunk launch (ncu --set full summary under profiles/); activations never "
+        "traffic": ncu_traffic(trunk_kernel, ("r2_ncu_full_summary.json", "r1_ncu_full_summary.json")) if args.net == "fused" else None,
+        "traffic_note": f"DRAM bytes per {trunk_kernel} launch (ncu --set full summary under profiles/); activations never "
                         "leave shared memory, features / h1 / h2 stay in the L2 for the fc stack",
         "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
         "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
