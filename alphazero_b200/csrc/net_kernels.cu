@@ -668,7 +668,10 @@ __global__ void __launch_bounds__(HG_THREADS, 1) k_net_headgemm(HeadGemmParams p
 
 // ------------------------------------------------------------------------------------------------ C ABI
 
-extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES; }
+// k_net_trunk's blob, then conv2..conv4 once more in the order k_net_trunk_rows stages them by one bulk copy
+// ([layer][kernel column][ci chunk][(kernel row, co)][8]: trunk_rows.cuh)
+static_assert(NET_WBLOB_BYTES == AZ_TRUNK_ROWS_BLOB_OFFSET, "trunk_rows.cuh knows where its section of the blob starts");
+extern "C" int az_net_wblob_bytes(void) { return NET_WBLOB_BYTES + AZ_TRUNK_ROWS_BLOB_BYTES; }
 
 // Boards per group / tiles per group for a launch over G positions on n_sms persistent CTAs: a group is 2, 4 or 6
 // tiles of 128 rows (rows per board = (n + 1) * 8, plus one closing ring row); the shape that needs the fewest

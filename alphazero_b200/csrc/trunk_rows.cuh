@@ -4,6 +4,8 @@
 #include <stdint.h>
 
 #define AZ_TRUNK_ROWS_BOARDS_PER_GROUP 14
+#define AZ_TRUNK_ROWS_BLOB_OFFSET 56832   // bytes of k_net_trunk's weight blob, which the kernel's own section follows
+#define AZ_TRUNK_ROWS_BLOB_BYTES 55296    // conv2..conv4 as [layer 3][kernel column 3][ci chunk 4][(kernel row, co) 96][8] bf16
 #define AZ_TRUNK_ROWS_MIN_G 1024        // smaller batches keep the first kernel (smaller groups spread over more SMs)
 
 bool az_trunk_rows_enabled();

@@ -72,8 +72,10 @@
 #define TRB_IM2COL 52                                   // conv1's A operand of the next group is in place
 #define TRB_I2FREE 53                                   // conv1's MMAs of the current group have read it
 #define TRB_O4DONE 54                                   // conv4's accumulators of the group have been read (16 warps)
-#define TRB_COUNT 55
-#define TR_SM_ITEMS (TR_SM_BARS + 8 * 56)              // uint32 [26]: layer, tile, last job, TMEM column of each epilogue item
+#define TRB_W1 55                                      // conv1's weights and the biases have landed (bulk copy)
+#define TRB_W 56                                       // conv2..conv4's weights have landed
+#define TRB_COUNT 57
+#define TR_SM_ITEMS (TR_SM_BARS + 8 * 58)              // uint32 [26]: layer, tile, last job, TMEM column of each epilogue item
 #define TR_CJOBS 14                                    // jobs of conv2..conv4 per group and issuing warp
 #define TR_SM_JOBS (TR_SM_ITEMS + 4 * 28)              // uint4 [2][14]: what the issuing thread needs to know about a job
 #define TR_SM_TMEM_PTR (TR_SM_JOBS + 16 * 2 * TR_CJOBS)
@@ -150,7 +152,8 @@ __device__ __forceinline__ int tr_hohi(int h, int L) { return min(tr_ohi(L), 4 *
 __device__ __forceinline__ int tr_tlo(int h, int L) { return L == 0 ? 4 * h : max(tr_mlo(L), tr_holo(h, L) - 1); }
 __device__ __forceinline__ int tr_thi(int h, int L) { return L == 0 ? 4 * h + 3 : min(tr_mlo(L) + tr_mcnt(L) - 1, tr_hohi(h, L) + 1); }
 __device__ __forceinline__ int tr_jloc(int L) { return L == 0 ? 0 : 5 * L - 1; }       // 0, 4, 9, 14
-// TMEM column of the accumulator of output tile r of layer L
+// TMEM column of the accumulator of output tile r of layer L.  (conv4's four accumulators at the two ends of its region,
+// where conv2 of the next group writes last, so that its wait for conv4's items comes two jobs later: measured, no gain.)
 __device__ __forceinline__ uint32_t tr_ocol(int L, int r) { return (uint32_t)((L & 1) * 256 + 32 * (7 - r)); }
 
 // conv1's A operand for one row (tile r, lane): the 9 taps of player * grid around cell (r, c) as bf16 (+1 own, -1 opp,
@@ -205,6 +208,18 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
         else if (tid == TRB_O4DONE) count = 4u * 4u;                // conv4's four output tiles, 4 warps each
         mbar_init(bars + 8 * tid, count);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // the weights by two asynchronous bulk copies (they do not depend on the launch before this one): conv1's tile +
+        // the four bias rows, which the first MMAs and items need, and conv2..conv4 in the kernel's own order
+        // (AZ_TRUNK_ROWS_BLOB_OFFSET of the blob), which nothing needs before conv1 is through
+        if (tid == TRB_W1 || tid == TRB_W) {
+            const uint32_t bytes = tid == TRB_W1 ? 1024u + 512u : (uint32_t)AZ_TRUNK_ROWS_BLOB_BYTES;
+            const uint8_t* src = p.wblob + (tid == TRB_W1 ? AZ_TRUNK_ROWS_BLOB_OFFSET - 1536 : AZ_TRUNK_ROWS_BLOB_OFFSET);
+            const uint32_t dst = sbase + (tid == TRB_W1 ? TR_SM_W1 : TR_SM_W);
+            asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}"
+                         ::"r"(bars + 8 * tid), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst), "l"(src), "r"(bytes), "r"(bars + 8 * tid) : "memory");
+        }
     }
     if (tid >= 64 && tid < 64 + TR_ITEMS) {
         // item idx of a group: layer L, output tile r, the job whose completion completes the tile's accumulator (of the
@@ -237,7 +252,7 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
         // kernel rows whose output tile r - kh + 1 this warp produces: kh = klo .. khi, 32 accumulator columns each, output
         // tiles descending = columns ascending from that of tile r - klo + 1
         const int klo = max(0, r + 1 - ohi), khi = min(2, r + 1 - olo), nblk = khi - klo + 1;
-        const uint32_t d_col = (uint32_t)((L & 1) * 256 + 32 * (6 - r + klo));
+        const uint32_t d_col = tr_ocol(L, r - klo + 1);
         // the first contribution to an output tile must not accumulate: all of the warp's first job of the layer; of every
         // other, the block of the output tile it reaches first -- tile r - 1 (kh = 2, the last block) going down, tile
         // r + 1 (kh = 0, the first block) going up -- by an N = 32 MMA of its own before the rest
@@ -269,27 +284,6 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
         *reinterpret_cast<uint4*>(smem + TR_SM_BUF(bufi) + pl * TR_PLANE + (TR_MARGIN + tile * 128 + ln) * 16) =
             make_uint4(0u, 0u, 0u, 0u);
     }
-    {   // blob: [layer][kh][ci chunk][(kw, co)][8] -> shared memory [layer][kw][ci chunk][(kh, co)][8], 16-byte units
-        const uint4* src = reinterpret_cast<const uint4*>(p.wblob);
-        uint4* dst = reinterpret_cast<uint4*>(smem + TR_SM_W);
-        constexpr int UNITS = 3 * 3 * 4 * 96, PER = (UNITS + TR_THREADS - 1) / TR_THREADS;
-        uint4 v[PER];                                              // all loads in flight before the first store
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int u = tid + i * TR_THREADS;
-            v[i] = u < UNITS ? src[u] : make_uint4(0u, 0u, 0u, 0u);
-        }
-#pragma unroll
-        for (int i = 0; i < PER; ++i) {
-            const int u = tid + i * TR_THREADS;
-            if (u < UNITS) {
-                const int co = u & 31, kw = (u >> 5) % 3, cc = (u / 96) & 3, kh = (u / 384) % 3, li = u / 1152;
-                dst[(((li * 3 + kw) * 4 + cc) * 3 + kh) * 32 + co] = v[i];
-            }
-        }
-        const uint4* tail = src + 3 * 3 * 4 * 96;                  // conv1 tile (1024 B), then the four bias rows (512 B)
-        for (int u = tid; u < (1024 + 512) / 16; u += TR_THREADS) reinterpret_cast<uint4*>(smem + TR_SM_W1)[u] = tail[u];
-    }
     if (warp == TR_MMA_WARP) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -305,12 +299,35 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
     if (!p.late_trigger) az_pdl_trigger();
     if (stamps && tid == 0) stamps[0] = clock64() - t_entry;
 
+    {   // conv1's A operand of the CTA's first group, by all threads: two rows each, both boards loaded before either row
+        // is built (the loads are the first thing after the wait and come from the L2: their latency is most of this)
+        static_assert(TR_ROWS == 2 * TR_THREADS, "two rows per thread");
+        const int board0 = blockIdx.x * TR_NB, n_boards = min(TR_NB, p.G - board0);
+        uint64_t o[2], q[2];
+        int cc[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int l = (tid + j * TR_THREADS) & 127, bb = l / TR_PITCH;
+            cc[j] = l - bb * TR_PITCH;
+            const bool ok = bb < n_boards && l < TR_NB * TR_PITCH && cc[j] < 8;
+            o[j] = ok ? p.own[board0 + bb] : 0ULL;
+            q[j] = ok ? p.opp[board0 + bb] : 0ULL;
+            if (!ok) cc[j] = -1;
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) tr_im2col_row(smem + TR_SM_IM2COL, tid + j * TR_THREADS, (tid + j * TR_THREADS) >> 7, cc[j], o[j], q[j]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid < TR_PRODUCERS / 32) mbar_arrive(bars + 8 * TRB_IM2COL);
+        if (stamps && tid == 0) stamps[1] = clock64() - t_entry;
+    }
+
     if (warp >= TR_MMA_WARP + TR_MMA_WARPS) {
         // ================================================================== producers: conv1's A operand (9-tap im2col
         // of player * grid, K = 16) of every group of this CTA.  Thread = lanes ptid and ptid + 64 of all 8 tiles.
         const int ptid = tid - (TR_EPI_THREADS + 32 * TR_MMA_WARPS);
         uint8_t* im2col = smem + TR_SM_IM2COL;
-        // (the first group's is built by the epilogue teams, which have nothing else to do yet)
+        // (the first group's is built by all threads above)
         uint32_t k = 1;
         for (int grp = blockIdx.x + gridDim.x; grp < n_groups; grp += gridDim.x, ++k) {
             const int board0 = grp * TR_NB, n_boards = min(TR_NB, p.G - board0);
@@ -355,6 +372,7 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
             const uint32_t buf = k & 1u, use = k >> 1;
             const long long c_i = stamps ? clock64() : 0;
             tr_wait(bars + 8 * TRB_IM2COL, k & 1u);
+            if (k == 0) tr_wait(bars + 8 * TRB_W1, 0u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const long long c_j = stamps ? clock64() : 0;
             if (stamps) w_im2col += c_j - c_i;
@@ -373,6 +391,7 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
             __syncwarp();
             if (stamps) t_issue += clock64() - c_j;
             if (stamps && lane == 0 && k == 0 && h == 0) stamps[8] = clock64() - t_entry;
+            if (k == 0) tr_wait(bars + 8 * TRB_W, 0u);
             const uint32_t abuf_lo = tr_desc_lo(sbase + TR_SM_BUF(buf), TR_PLANE);
             const uint32_t ready = bars + 8 * (TRB_READY + buf * 8);
 #pragma unroll 1
@@ -426,19 +445,7 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
         const int b = tl / TR_PITCH, c = tl - b * TR_PITCH;     // board of the group, column (8 = pad)
         const float* bias_all = reinterpret_cast<const float*>(smem + TR_SM_BIAS);
         const uint32_t t_quarter = tmem_base + ((uint32_t)(quarter * 32) << 16);
-        {   // conv1's A operand of the CTA's first group, by all epilogue threads (three rows each)
-            const int board0 = blockIdx.x * TR_NB, n_boards = min(TR_NB, p.G - board0);
-            uint8_t* im2col = smem + TR_SM_IM2COL;
-            for (int row = tid; row < TR_ROWS; row += TR_EPI_THREADS) {
-                const int r = row >> 7, l = row & 127, bb = l / TR_PITCH, cc = l - bb * TR_PITCH;
-                const bool ok = bb < n_boards && l < TR_NB * TR_PITCH && cc < 8;
-                tr_im2col_row(im2col, row, r, ok ? cc : -1, ok ? p.own[board0 + bb] : 0ULL, ok ? p.opp[board0 + bb] : 0ULL);
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("bar.sync 1, %0;" ::"r"(TR_EPI_THREADS) : "memory");
-            if (tid < TR_PRODUCERS / 32) mbar_arrive(bars + 8 * TRB_IM2COL);
-            if (stamps && tid == 0) stamps[1] = clock64() - t_entry;
-        }
+        tr_wait(bars + 8 * TRB_W1, 0u);                          // the biases
         uint32_t k = 0;
         long long e_wait = 0, e_work = 0;
         for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++k) {

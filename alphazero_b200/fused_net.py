@@ -43,7 +43,8 @@ def _bf16_bits(t: torch.Tensor) -> np.ndarray:
 def pack_trunk_weights(net) -> torch.Tensor:
     """uint8 blob for az_net_trunk:
     [conv2|conv3|conv4: 3 kernel rows x [ci chunk 4][(dc, co) 96][ci%8] bf16][conv1: [k chunk 2][co 32][8] bf16, taps 0..8 then 0]
-    [b1..b4 float32 [4][32]]  -- all with eval-mode BatchNorm folded in."""
+    [b1..b4 float32 [4][32]]  -- all with eval-mode BatchNorm folded in -- and, for k_net_trunk_rows, conv2..conv4 once
+    more with the roles of kernel row and kernel column exchanged: 3 kernel columns x [ci chunk 4][(dr, co) 96][ci%8]."""
     assert net.n_channels == 32
     n_bytes = int(_lib.lib().az_net_wblob_bytes())
     mma = np.zeros((3, 3, 4, 96, 8), dtype=np.uint16)
@@ -60,8 +61,9 @@ def pack_trunk_weights(net) -> torch.Tensor:
         for kh in range(3):
             for kw in range(3):
                 mma[li, kh, :, kw * 32:(kw + 1) * 32] = wb[:, :, kh, kw].reshape(32, 4, 8).transpose(1, 0, 2)   # [ci chunk][co][ci % 8]
+    rows = np.ascontiguousarray(mma.reshape(3, 3, 4, 3, 32, 8).transpose(0, 3, 2, 1, 4, 5))     # [layer][kw][ci chunk][kh][co][8]
     packed = np.concatenate([mma.reshape(-1).view(np.uint8), np.ascontiguousarray(c1).reshape(-1).view(np.uint8),
-                             biases.reshape(-1).view(np.uint8)])
+                             biases.reshape(-1).view(np.uint8), rows.reshape(-1).view(np.uint8)])
     assert packed.nbytes == n_bytes, (packed.nbytes, n_bytes)
     return torch.from_numpy(packed.copy())
 
