@@ -62,7 +62,7 @@
 // shared memory map
 #define TR_SM_BUF(i) ((i) * TR_BUF)
 #define TR_SM_IM2COL (2 * TR_BUF)
-#define TR_SM_W (TR_SM_IM2COL + TR_IM2COL)             // conv2..4 reordered: [layer 3][kw 3][ci chunk 4][(kh, co) 96][8] bf16
+#define TR_SM_W (TR_SM_IM2COL + TR_IM2COL)             // conv2..4 (the blob's own section): [layer 3][kw 3][ci chunk 4][(kh, co) 96][8] bf16
 #define TR_W_DC_BYTES (4 * 96 * 16)                    // one (layer, kernel column): 6 144 B
 #define TR_SM_W1 (TR_SM_W + 9 * TR_W_DC_BYTES)         // conv1: [k chunk 2][co 32][8] bf16
 #define TR_SM_BIAS (TR_SM_W1 + 1024)                   // float [4][32]
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(TR_THREADS, 1) k_net_trunk_rows(TrunkRowsParam
     const uint32_t bars = smem_u32(smem + TR_SM_BARS);
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + TR_SM_TMEM_PTR);
 
-    // ---- one-time setup: barriers, zeroed buffers (margins, unused lanes), weights (reordered from the blob), TMEM
+    // ---- one-time setup: barriers, weights (bulk copies), the item / job tables, zeroed margins and unused lanes, TMEM
     if (tid < TRB_COUNT) {
         // arrivals are per WARP (lane 0 after __syncwarp): 32 lanes arriving on one barrier word serialise
         uint32_t count = 1u;                                       // job[][]: one tcgen05.commit
