@@ -277,7 +277,14 @@ int az_greedy_move(int game, const uint64_t* own, const uint64_t* opp, const uin
 
 /* ---------------------------------------------------------------- fused network kernels ---------------- */
 
-/* Bytes of the packed trunk weights expected by az_net_trunk (built by alphazero_b200/fused_net.py). */
+/* Bytes of the packed trunk weights expected by az_net_trunk (built by alphazero_b200/fused_net.py:
+ * pack_trunk_weights), BatchNorm folded, bf16 in the tcgen05 K-major operand layout:
+ *   [conv2 | conv3 | conv4: 3 kernel rows x [ci chunk 4][(kernel column, co) 96][ci % 8]]   3 x 18 432 bytes
+ *   [conv1: [k chunk 2][co 32][8], taps 0..8 then zeros]                                       1 024 bytes
+ *   [biases of conv1..conv4: float32 [4][32]]                                                    512 bytes
+ *   [conv2 | conv3 | conv4 once more with kernel row and column exchanged:
+ *    3 kernel columns x [ci chunk 4][(kernel row, co) 96][ci % 8]]                          3 x 18 432 bytes
+ * (the last section is what k_net_trunk_rows stages by one bulk copy). */
 int az_net_wblob_bytes(void);
 
 /* Fused conv1..conv4 (+ folded BatchNorm + ReLU) of OthelloNet.forward / Connect4Net.forward
