@@ -104,7 +104,7 @@ class ClockSampler:
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "power_w_max": max(power),
+        return {"sm_mhz": sm[len(sm) // 2], "sm_min_mhz": sm[0], "sm_max_mhz": max(mx), "power_w_max": max(power),
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
@@ -288,22 +288,40 @@ def run_ours(args):
 
     step_e2e()          # warm-up of the end-to-end path (pinned staging buffers of the device->host read)
     # device-resident and end-to-end steps alternate, so that the two numbers see the same clocks and the same box
-    dev_run = e2e_run = None
-    sampler = ClockSampler(local_rank)      # one clock record over the whole timed region (both kinds of step)
-    sampler.start()
-    per_step_ms = {"device": [], "e2e": []}      # every timed step on its own (an outlier shows up here)
-    for _ in range(args.steps):
-        a = timed(step_device, 1, sample=False)
-        b = timed(step_e2e, 1, sample=False)
-        per_step_ms["device"].append(round(a["ms"], 2)); per_step_ms["e2e"].append(round(max(b["ms"], b["wall_ms"]), 2))
-        if dev_run is None:
-            dev_run, e2e_run = a, b
-        else:
-            for acc, x in ((dev_run, a), (e2e_run, b)):
-                for key in ("ms", "wall_ms", "sims", "moves", "games", "launches"):
-                    acc[key] += x[key]
-                acc["last"] = x["last"]
-    dev_run["clocks"] = e2e_run["clocks"] = sampler.stop()
+    def measure():
+        """args.steps device-resident and args.steps end-to-end steps, alternating; one clock record over all of them."""
+        dev_run = e2e_run = None
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        per_step_ms = {"device": [], "e2e": []}      # every timed step on its own (an outlier shows up here)
+        for _ in range(args.steps):
+            a = timed(step_device, 1, sample=False)
+            b = timed(step_e2e, 1, sample=False)
+            per_step_ms["device"].append(round(a["ms"], 2)); per_step_ms["e2e"].append(round(max(b["ms"], b["wall_ms"]), 2))
+            if dev_run is None:
+                dev_run, e2e_run = a, b
+            else:
+                for acc, x in ((dev_run, a), (e2e_run, b)):
+                    for key in ("ms", "wall_ms", "sims", "moves", "games", "launches"):
+                        acc[key] += x[key]
+                    acc["last"] = x["last"]
+        dev_run["clocks"] = e2e_run["clocks"] = sampler.stop()
+        return dev_run, e2e_run, per_step_ms
+
+    dev_run, e2e_run, per_step_ms = measure()
+    # The engine's batches take the same time to +-1.5 % (profiles/r2_step_jitter.txt: 180 consecutive batches), but a
+    # timed step has been seen to take a third longer once in ~40 (a stall outside the engine: not reproducible in
+    # isolation).  Such a set of steps is measured ONCE more -- all of it, args.steps consecutive steps again -- and
+    # the rejected set is reported beside the one that counts (`remeasured`), like a run that saw a thermal slowdown.
+    remeasured = None
+    worst = max(per_step_ms["device"] + per_step_ms["e2e"])
+    typical = sorted(per_step_ms["device"] + per_step_ms["e2e"])[args.steps - 1]      # lower median of the 2 K steps
+    outlier = float(os.environ.get("AZ_B200_BENCH_OUTLIER", "1.15"))      # (a value below 1 exercises the path)
+    if args.steps >= 2 and worst > outlier * typical:   # (times are maxima over the ranks: every rank decides alike)
+        remeasured = {"reason": f"a step of {worst:.0f} ms among steps of {typical:.0f} ms", "rejected_per_step_ms": per_step_ms,
+                      "rejected_clocks": dev_run["clocks"]}
+        dev_run["last"] = e2e_run["last"] = None
+        dev_run, e2e_run, per_step_ms = measure()
     # the e2e region includes host-side packing, so its clock is the wall clock between the two barriers
     e2e_ms = max(e2e_run["ms"], e2e_run["wall_ms"])
     batch, host = e2e_run["last"]
@@ -398,7 +416,7 @@ def run_ours(args):
         "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
         "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
         "search_share_of_batch": search_ms / (dev_run["ms"] / args.steps),
-        "per_step_ms": per_step_ms,
+        "per_step_ms": per_step_ms, "remeasured": remeasured,
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
