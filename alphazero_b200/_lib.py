@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_HERE, "libaz_b200.so")
 CSRC = os.path.join(_HERE, "csrc")
-SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "trunk_rows_kernels.cu", "fcstack_kernels.cu", "fcstack2_kernels.cu", "fcstack3_kernels.cu", "sample_kernels.cu", "player_kernels.cu"]
+SOURCES = ["board_kernels.cu", "connect4_kernels.cu", "tictactoe_kernels.cu", "tree_kernels.cu", "net_kernels.cu", "trunk_rows_kernels.cu", "trunk_rows2_kernels.cu", "fcstack_kernels.cu", "fcstack2_kernels.cu", "fcstack3_kernels.cu", "sample_kernels.cu", "player_kernels.cu"]
 
 AZ_OK, AZ_ERR_ARG, AZ_ERR_CUDA, AZ_ERR_CAPACITY = 0, -1, -2, -3
 AZ_PASS = 64

@@ -726,7 +726,10 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
     // environment asks for this file's kernel; the cycle-accounting mode (debug_layer 100) belongs to this file's kernel
     if (rows == 8 && cols == 8 && G >= AZ_TRUNK_ROWS_MIN_G && !(features_packed & 2) && az_trunk_rows_enabled() &&
         !(debug && debug_layer == 100))
-        return az_trunk_rows_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
+        return (az_trunk_rows2_enabled() && !(features_packed & 4) && (G + AZ_TRUNK_ROWS_BOARDS_PER_GROUP - 1) / AZ_TRUNK_ROWS_BOARDS_PER_GROUP > n_sms &&
+                !(debug && debug_layer >= 200))
+                   ? az_trunk_rows2_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream)
+                   : az_trunk_rows_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
     NetTrunkParams p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;

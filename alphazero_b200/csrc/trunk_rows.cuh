@@ -11,3 +11,8 @@
 bool az_trunk_rows_enabled();
 int az_trunk_rows_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
                      int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream);
+
+// k_net_trunk_rows2 (trunk_rows2_kernels.cu): the same formulation with two CTAs per SM
+bool az_trunk_rows2_enabled();
+int az_trunk_rows2_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
+                          int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream);

@@ -182,7 +182,8 @@ class FusedNetEvaluator:
         three cuBLASLt GEMMs of the first version (kept as a cross-check); "fused" = library fc1 / fc2 + az_net_headgemm.
         stack_shape: (RT, NS) cluster shape of az_net_fcstack, default by batch size (env AZ_B200_FCSTACK="RT,NS").
         trunk_variant: 0 = the library's choice (k_net_trunk_rows for 8 x 8 images in batches of 1024 and more, else
-        k_net_trunk); 1 = k_net_trunk whatever the batch (include/az_b200.h).
+        k_net_trunk -- and among the former k_net_trunk_rows2, two CTAs per SM, when there are more groups of 14 boards
+        than SMs); 1 = k_net_trunk whatever the batch; 2 = k_net_trunk_rows rather than k_net_trunk_rows2 (include/az_b200.h).
         heads_in_tree: inside a whole-search graph (TreeBatch.search -> enqueue()) the softmax / tanh of the heads is
         left to the tree step, which reads the bf16 logits row itself (az_tree.logits, same arithmetic and bits as
         az_net_heads); a plain call still runs az_net_heads so that tree.probs / tree.value are always valid."""
@@ -298,7 +299,7 @@ class FusedNetEvaluator:
             own, opp = self.img_own, self.img_opp
         _lib.check(_lib.lib().az_net_trunk(_ptr(own), _ptr(opp), self.rows, self.cols, t.G, _ptr(self.wblob),
                                            _ptr(self.features),
-                                           (1 if self.heads == "stack" else 0) | (2 if self.trunk_variant == 1 else 0), _ptr(debug),
+                                           (1 if self.heads == "stack" else 0) | (2 if self.trunk_variant == 1 else 0) | (4 if self.trunk_variant == 2 else 0), _ptr(debug),
                                            int(debug_layer), _stream()), "az_net_trunk")
 
     def _forward(self, output_transform: bool = True) -> None:

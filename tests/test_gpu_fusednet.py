@@ -74,23 +74,24 @@ def test_trunk_layers_match_fp32(n):
     assert (feat - a4).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
-def test_trunk_rows_layers_match_fp32():
-    """k_net_trunk_rows (8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, one accumulator per
-    output tile): every conv layer through its debug dump, the zero pad lanes, the features, and the policy / value
-    against fp32; and against k_net_trunk on the same batch."""
+@pytest.mark.parametrize("variant,G", [(0, 1030), (2, 2200), (0, 2200), (0, 4300)])
+def test_trunk_rows_layers_match_fp32(variant, G):
+    """k_net_trunk_rows / k_net_trunk_rows2 (8 x 8 boards, batches of 1024 and more: tile = one board row of 14 boards, one
+    accumulator per output tile): every conv layer through its debug dump, the zero pad lanes, the features, and the
+    policy / value against fp32; and against k_net_trunk on the same batch."""
     from alphazero_b200 import _lib
     from alphazero_b200.fused_net import FusedOthelloEvaluator
     n = 8
     net = _net(n, seed=11)
     tree, x, G0 = _setup(n, 400, seed=13)
-    # 1030 boards: 73 full groups of 14 and one of 8; the positions repeat, which also checks that a board's result
-    # does not depend on where it sits in a group
+    # 1030 boards: 73 full groups of 14 and one of 8 (k_net_trunk_rows); 2200: more groups than SMs = k_net_trunk_rows2
+    # (two CTAs per SM; variant 2 keeps k_net_trunk_rows), the last group of 2; 4300: CTAs with more than one group.
+    # The positions repeat, which also checks that a board's result does not depend on where it sits in a group.
     from alphazero_b200.engine import TreeBatch
-    G = 1030
     idx = torch.arange(G) % G0
     big = TreeBatch(G, n=n, mode="neural", capacity=64)
     big.leaf_own.copy_(tree.leaf_own[idx.cuda()]); big.leaf_opp.copy_(tree.leaf_opp[idx.cuda()])
-    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False)
+    ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=variant)
     assert _lib.lib().az_net_trunk_boards_per_group(8, G) == 14
     with torch.no_grad():
         a1 = F.relu(net.bn1(net.conv1(x.view(-1, 1, n, n))))
@@ -127,6 +128,12 @@ def test_trunk_rows_layers_match_fp32():
     torch.cuda.synchronize()
     feat1 = ev1.features_rowmajor().float().cpu().reshape(G, 16, 32).permute(0, 2, 1).reshape(G, 32, 4, 4)
     assert (feat - feat1).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
+    if variant == 0 and G > 148 * 14:
+        # k_net_trunk_rows2 feeds every accumulator the same MMAs in the same order as k_net_trunk_rows: the same bits
+        ev2 = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=2)
+        ev2.trunk()
+        torch.cuda.synchronize()
+        assert torch.equal(ev2.features_rowmajor(), ev.features_rowmajor())
     ev(big)
     torch.cuda.synchronize()
     ref_p, ref_v = net.predict(x)

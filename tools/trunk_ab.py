@@ -1,4 +1,4 @@
-"""The two trunk kernels on the same batch in one process (same GPU, same clocks: the boxes differ by +-5 %): us per
+"""The trunk kernels on the same batch in one process (same GPU, same clocks: the boxes differ by +-5 %): us per
 launch in a CUDA graph.      python tools/trunk_ab.py [G]"""
 import os
 import sys
@@ -39,6 +39,6 @@ def timed(ev):
     return 1000 * e0.elapsed_time(e1) / 200
 
 
-evs = {v: FusedOthelloEvaluator(net, tree, use_cuda_graph=False, trunk_variant=v) for v in (1, 0)}
+evs = {v: FusedOthelloEvaluator(net, tree, use_cuda_graph=False, trunk_variant=v) for v in (1, 2, 0)}
 for rep in range(2):
-    print(f"{G} positions, us per launch: k_net_trunk {timed(evs[1]):.2f} | k_net_trunk_rows {timed(evs[0]):.2f}")
+    print(f"{G} positions, us per launch: k_net_trunk {timed(evs[1]):.2f} | k_net_trunk_rows {timed(evs[2]):.2f} | az_net_trunk's choice (k_net_trunk_rows2 above 2072 positions) {timed(evs[0]):.2f}")
