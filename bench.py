@@ -442,7 +442,7 @@ def run_ours(args):
         engine = None
         torch.cuda.empty_cache()
 
-        def side_run(label, game="othello", games=G, sims=n_sim, leaves=None, warm=1):
+        def side_run(label, game="othello", games=G, sims=n_sim, leaves=None, warm=2):
             """One more configuration, one timed batch: value = simulations of all ranks / max-over-ranks device time."""
             try:
                 torch.manual_seed(0)
