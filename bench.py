@@ -88,9 +88,18 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
+        return self.summary(0)
+
+    def mark(self) -> int:
+        """Number of samples taken so far: summary(mark) covers what comes after."""
+        return len(self.lines)
+
+    def summary(self, since: int = 0):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in list(self.lines)[since:]:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -242,6 +251,11 @@ def run_ours(args):
         host = batch.cpu(staging) if rank == 0 or world == 1 else None
         return batch, host
 
+    # The poller runs from before the warm-up to the end of the timed region, and a clock record is the samples of its
+    # window: the first seconds of an nvidia-smi process (NVML start-up on every GPU of the box) have stalled a timed
+    # step by 150 - 250 ms more than once when it was started right before the timed region.
+    poller = ClockSampler(local_rank)
+    poller.start()
     for _ in range(args.warmup):
         step_device()
 
@@ -288,11 +302,22 @@ def run_ours(args):
 
     step_e2e()          # warm-up of the end-to-end path (pinned staging buffers of the device->host read)
     # device-resident and end-to-end steps alternate, so that the two numbers see the same clocks and the same box
+    gc_pauses = []                  # (generation, ms) of every garbage collection of 1 ms and more inside the timed steps
+    gc_t0 = [0.0]
+
+    def gc_watch(phase, info):
+        if phase == "start":
+            gc_t0[0] = time.perf_counter()
+        elif 1000.0 * (time.perf_counter() - gc_t0[0]) >= 1.0:
+            gc_pauses.append((info["generation"], round(1000.0 * (time.perf_counter() - gc_t0[0]), 1)))
+
+    import gc
+    gc.callbacks.append(gc_watch)
+
     def measure():
         """args.steps device-resident and args.steps end-to-end steps, alternating; one clock record over all of them."""
         dev_run = e2e_run = None
-        sampler = ClockSampler(local_rank)
-        sampler.start()
+        since = poller.mark()
         per_step_ms = {"device": [], "e2e": []}      # every timed step on its own (an outlier shows up here)
         for _ in range(args.steps):
             a = timed(step_device, 1, sample=False)
@@ -305,7 +330,7 @@ def run_ours(args):
                     for key in ("ms", "wall_ms", "sims", "moves", "games", "launches"):
                         acc[key] += x[key]
                     acc["last"] = x["last"]
-        dev_run["clocks"] = e2e_run["clocks"] = sampler.stop()
+        dev_run["clocks"] = e2e_run["clocks"] = poller.summary(since)
         return dev_run, e2e_run, per_step_ms
 
     dev_run, e2e_run, per_step_ms = measure()
@@ -322,6 +347,7 @@ def run_ours(args):
                       "rejected_clocks": dev_run["clocks"]}
         dev_run["last"] = e2e_run["last"] = None
         dev_run, e2e_run, per_step_ms = measure()
+    poller.stop()
     # the e2e region includes host-side packing, so its clock is the wall clock between the two barriers
     e2e_ms = max(e2e_run["ms"], e2e_run["wall_ms"])
     batch, host = e2e_run["last"]
@@ -416,7 +442,7 @@ def run_ours(args):
         "ms_per_launch": eval_ms, "share_of_step": eval_ms / (eval_ms + tree_ms), "timing": timing,
         "ms_per_launch_eager": eager_eval_ms, "ms_per_search_step": step_ms,
         "search_share_of_batch": search_ms / (dev_run["ms"] / args.steps),
-        "per_step_ms": per_step_ms, "remeasured": remeasured,
+        "per_step_ms": per_step_ms, "remeasured": remeasured, "gc_pauses_ms": gc_pauses,
     }
     # tree kernel: algorithmic bytes per simulation at the measured mean depth d, branching b ~ 10 (SURVEY.md 8d,
     # 32-byte records): select d*32*b + backup d*32 + expand 32*b+32 + encode 128 + probs 260 + value 4 + leaf 40
