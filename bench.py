@@ -303,12 +303,12 @@ def run_ours(args):
     step_e2e()          # warm-up of the end-to-end path (pinned staging buffers of the device->host read)
     # device-resident and end-to-end steps alternate, so that the two numbers see the same clocks and the same box
     gc_pauses = []                  # (generation, ms) of every garbage collection of 1 ms and more inside the timed steps
-    gc_t0 = [0.0]
+    gc_t0, gc_timed = [0.0], [False]
 
     def gc_watch(phase, info):
         if phase == "start":
             gc_t0[0] = time.perf_counter()
-        elif 1000.0 * (time.perf_counter() - gc_t0[0]) >= 1.0:
+        elif gc_timed[0] and 1000.0 * (time.perf_counter() - gc_t0[0]) >= 1.0:
             gc_pauses.append((info["generation"], round(1000.0 * (time.perf_counter() - gc_t0[0]), 1)))
 
     import gc
@@ -317,6 +317,9 @@ def run_ours(args):
     def measure():
         """args.steps device-resident and args.steps end-to-end steps, alternating; one clock record over all of them."""
         dev_run = e2e_run = None
+        gc.collect()                # no collection inside the timed steps (a generation-2 pass of this process is ~40 ms)
+        gc.disable()
+        gc_timed[0] = True
         since = poller.mark()
         per_step_ms = {"device": [], "e2e": []}      # every timed step on its own (an outlier shows up here)
         for _ in range(args.steps):
@@ -331,6 +334,8 @@ def run_ours(args):
                         acc[key] += x[key]
                     acc["last"] = x["last"]
         dev_run["clocks"] = e2e_run["clocks"] = poller.summary(since)
+        gc.enable()
+        gc_timed[0] = False
         return dev_run, e2e_run, per_step_ms
 
     dev_run, e2e_run, per_step_ms = measure()
@@ -384,8 +389,10 @@ def run_ours(args):
     eval_ms, tree_ms, timing = eager_eval_ms, eager_tree_ms, "eager calls between CUDA events"
     kernel_ms = None
     # the trunk kernel az_net_trunk takes for this batch (include/az_b200.h)
-    trunk_kernel = ("k_net_trunk_rows" if args.game == "othello" and n == 8 and G >= 1024
-                    and not os.environ.get("AZ_B200_TRUNK_V1") else "k_net_trunk")
+    trunk_kernel = "k_net_trunk"
+    if args.game == "othello" and n == 8 and G >= 1024 and not os.environ.get("AZ_B200_TRUNK_V1"):
+        two_per_sm = (G + 13) // 14 > torch.cuda.get_device_properties(dev).multi_processor_count
+        trunk_kernel = "k_net_trunk_rows2" if two_per_sm and not os.environ.get("AZ_B200_TRUNK_ROWS1") else "k_net_trunk_rows"
     if hasattr(engine.evaluator, "enqueue") and tree.graph_search:
         K = 64
         net_graph = torch.cuda.CUDAGraph()
