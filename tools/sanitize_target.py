@@ -26,6 +26,16 @@ ev = FusedNetEvaluator(net, tree, use_cuda_graph=False)
 ev(tree)
 torch.cuda.synchronize()
 print("fc stack ok", float(tree.probs.sum()))
+# the 8 x 8 trunk kernels of large batches: k_net_trunk_rows (1030 positions: a partial last group) and k_net_trunk_rows2
+# (4200 positions: two CTAs per SM, a few CTAs with two groups), each followed by the fc stack
+net8 = OthelloNet(n=8)
+for G8 in (1030, 4200):
+    t8 = TreeBatch(G8, n=8, mode="neural", capacity=64)
+    t8.leaf_own.copy_(t8.root_own); t8.leaf_opp.copy_(t8.root_opp)
+    ev8 = FusedNetEvaluator(net8, t8, use_cuda_graph=False)
+    ev8(t8)
+    torch.cuda.synchronize()
+    print("8 x 8 trunk ok", G8, float(t8.probs.sum()))
 # throughput mode: 4 leaves in flight, hash evaluator, tree reuse over two moves
 t4 = TreeBatch(16, n=6, mode="neural", tie_random=False, capacity=2048, leaves=4, graph_search=False)
 h = HashEvaluator(3, t4.leaf_view)
