@@ -141,6 +141,34 @@ def test_trunk_rows_layers_match_fp32(variant, G):
     assert (big.value.cpu() - ref_v.reshape(-1)[idx]).abs().max().item() < 1e-2
 
 
+@pytest.mark.parametrize("G", [2073, 2087, 3001, 4097, 8200])
+def test_trunk_rows2_bit_identical_to_trunk_rows(G):
+    """Batches with more groups of 14 boards than SMs go to k_net_trunk_rows2 (two CTAs per SM; from 297 groups on a CTA
+    runs several groups back to back): the same features, bit for bit, as k_net_trunk_rows on every size -- a last
+    group of 1, 5, 9 boards, one CTA more than SMs, CTAs with two groups."""
+    from alphazero_b200.engine import TreeBatch
+    from alphazero_b200.fused_net import FusedOthelloEvaluator
+    net = _net(8, seed=21)
+    tree, x, G0 = _setup(8, 500, seed=23)
+    idx = (torch.arange(G) * 7) % G0
+    big = TreeBatch(G, n=8, mode="neural", capacity=64)
+    big.leaf_own.copy_(tree.leaf_own[idx.cuda()]); big.leaf_opp.copy_(tree.leaf_opp[idx.cuda()])
+    feats = []
+    for variant in (0, 2, 0):               # twice through the default: the second launch finds used shared memory / TMEM
+        ev = FusedOthelloEvaluator(net, big, use_cuda_graph=False, trunk_variant=variant)
+        ev.features.fill_(-3.0)
+        ev.trunk()
+        torch.cuda.synchronize()
+        feats.append(ev.features_rowmajor().clone())
+    assert torch.equal(feats[0], feats[1]) and torch.equal(feats[0], feats[2])
+    with torch.no_grad():
+        a = x.view(-1, 1, 8, 8)
+        for conv, bn in ((net.conv1, net.bn1), (net.conv2, net.bn2), (net.conv3, net.bn3), (net.conv4, net.bn4)):
+            a = F.relu(bn(conv(a)))
+    got = feats[0].float().cpu().reshape(G, 16, 32).permute(0, 2, 1).reshape(G, 32, 4, 4)
+    assert (got - a[idx]).abs().max().item() < 0.02 * a.abs().max().item() + 0.02
+
+
 @pytest.mark.parametrize("n,graph", [(8, True), (8, False), (6, True)])
 def test_fused_forward_within_1e2_of_fp32(n, graph):
     from alphazero_b200.fused_net import FusedOthelloEvaluator
