@@ -347,7 +347,7 @@ def run_ours(args):
     worst = max(per_step_ms["device"] + per_step_ms["e2e"])
     typical = sorted(per_step_ms["device"] + per_step_ms["e2e"])[args.steps - 1]      # lower median of the 2 K steps
     outlier = float(os.environ.get("AZ_B200_BENCH_OUTLIER", "1.15"))      # (a value below 1 exercises the path)
-    if args.steps >= 2 and worst > outlier * typical:   # (times are maxima over the ranks: every rank decides alike)
+    if worst > outlier * typical:                       # (times are maxima over the ranks: every rank decides alike)
         remeasured = {"reason": f"a step of {worst:.0f} ms among steps of {typical:.0f} ms", "rejected_per_step_ms": per_step_ms,
                       "rejected_clocks": dev_run["clocks"]}
         dev_run["last"] = e2e_run["last"] = None
