@@ -701,7 +701,8 @@ extern "C" int az_net_trunk_boards_per_group(int rows, int64_t G) {
     if (cudaGetDevice(&dev) != cudaSuccess ||
         cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
         return AZ_ERR_CUDA;
-    if (rows == 8 && G >= AZ_TRUNK_ROWS_MIN_G && az_trunk_rows_enabled()) return AZ_TRUNK_ROWS_BOARDS_PER_GROUP;    // k_net_trunk_rows
+    if (rows == 8 && G >= AZ_TRUNK_ROWS_MIN_G && az_trunk_rows_enabled()) return AZ_TRUNK_ROWS_BOARDS_PER_GROUP;    // k_net_trunk_rows / rows2
+    if (rows == 7 && az_trunk_rows_enabled() && az_trunk_rows2_enabled() && (G + 17) / 18 > n_sms) return 18;       // k_net_trunk_rows2<7, 6>
     net_group_shape(rows, G, n_sms, &nb, &tiles);
     return nb;
 }
@@ -728,8 +729,12 @@ extern "C" int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, 
         !(debug && debug_layer == 100))
         return (az_trunk_rows2_enabled() && !(features_packed & 4) && (G + AZ_TRUNK_ROWS_BOARDS_PER_GROUP - 1) / AZ_TRUNK_ROWS_BOARDS_PER_GROUP > n_sms &&
                 !(debug && debug_layer >= 200))
-                   ? az_trunk_rows2_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream)
+                   ? az_trunk_rows2_launch(own, opp, 8, 8, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream)
                    : az_trunk_rows_launch(own, opp, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
+    // Connect4Net's 7 x 6 image: the same two-CTAs-per-SM kernel once there are more groups of 18 boards than SMs
+    if (rows == 7 && cols == 6 && !(features_packed & 6) && az_trunk_rows_enabled() && az_trunk_rows2_enabled() &&
+        (G + az_trunk_rows2_boards_per_group(7) - 1) / az_trunk_rows2_boards_per_group(7) > n_sms && !(debug && debug_layer >= 100))
+        return az_trunk_rows2_launch(own, opp, 7, 6, G, wblob, features, features_packed & 1, debug, debug_layer, n_sms, late_trigger, stream);
     NetTrunkParams p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob;
     p.features = (__nv_bfloat16*)features; p.debug = (__nv_bfloat16*)debug;

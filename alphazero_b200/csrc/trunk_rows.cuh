@@ -12,7 +12,9 @@ bool az_trunk_rows_enabled();
 int az_trunk_rows_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
                      int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream);
 
-// k_net_trunk_rows2 (trunk_rows2_kernels.cu): the same formulation with two CTAs per SM
+// k_net_trunk_rows2<rows, cols> (trunk_rows2_kernels.cu): the same formulation with two CTAs per SM, for the 8 x 8 image
+// (14 boards per group) and Connect4Net's 7 x 6 image (18 boards per group)
 bool az_trunk_rows2_enabled();
-int az_trunk_rows2_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
+int az_trunk_rows2_boards_per_group(int rows);
+int az_trunk_rows2_launch(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob, void* features,
                           int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream);

@@ -23,6 +23,9 @@
 //     154 instead of 200 MMAs per group -- was measured too: 17.3 against 16.7 us, the single thread's chain is longer.)
 // A CTA with more than one group runs them back to back with a block barrier in between (the other CTA of the SM fills
 // the bubble).  az_net_trunk takes this kernel when there are more groups than SMs, k_net_trunk_rows below that.
+// Templated on the image: T rows x C columns, a tile = image row r of floor(128 / (C + 1)) boards -- 8 x 8 (Othello, 14
+// boards per group) and 7 x 6 (Connect4Net's (width, height) view of the board, connect4.py:397-403: 18 boards per
+// group).  The shared-memory and TMEM layouts are those of 8 tiles for both; the 7 x 6 image leaves the last tile unused.
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -33,9 +36,7 @@
 #include "umma.cuh"
 #include "trunk_rows.cuh"
 
-#define R2_NB 14                  // boards per group
-#define R2_PITCH 9                // lanes per board in a tile
-#define R2_TILES 8                // tiles per layer = board rows
+#define R2_TILES 8                // tiles per layer in the layout = the largest number of image rows
 #define R2_ROWS (R2_TILES * 128)
 #define R2_MARGIN 8               // zero rows before / after the buffer (the +-1 row shifts of the first / last tile)
 #define R2_PLANE ((R2_ROWS + 2 * R2_MARGIN) * 16)      // one 8-channel chunk plane: 16 640 B (= LBO of the A operand)
@@ -44,9 +45,9 @@
 #define R2_EPI_THREADS (128 * R2_TEAMS)
 #define R2_MMA_WARP (R2_EPI_THREADS / 32)
 #define R2_THREADS (R2_EPI_THREADS + 64)
-#define R2_HJOBS 18               // MMA tile jobs per group and issuing warp: 4 + 5 + 5 + 4
+#define R2_HJOBS 18               // MMA tile jobs per group and issuing warp, at most: 4 + 5 + 5 + 4
 #define R2_CJOBS 14               // of which conv2..conv4
-#define R2_ITEMS 26               // epilogue items per group = output tiles that are used: 8 + 8 + 6 + 4
+#define R2_ITEMS 26               // epilogue items per group = output tiles that are used, at most: 8 + 8 + 6 + 4
 #define R2_LAYER_BYTES 18432      // one layer's weights: [kw 3][ci chunk 4][(kh, co) 96][8] bf16
 #define R2_W_DC_BYTES (4 * 96 * 16)                    // one kernel column of them: 6 144 B
 // shared memory map
@@ -60,9 +61,7 @@
 #define R2B_W1 44                                      // conv1's weights and the biases have landed
 #define R2B_WB 45                                      // [2] a layer's weights have landed in buffer i
 #define R2B_COUNT 47
-#define R2_SM_ITEMS (R2_SM_BARS + 8 * 48)              // uint32 [26]: layer, tile, job barriers, TMEM column of each epilogue item
-#define R2_SM_JOBS (R2_SM_ITEMS + 4 * 28)              // uint4 [2][14]: what the issuing thread needs to know about a job
-#define R2_SM_TMEM_PTR (R2_SM_JOBS + 16 * 2 * R2_CJOBS)
+#define R2_SM_TMEM_PTR (R2_SM_BARS + 8 * 48)
 #define R2_SM_TOTAL (R2_SM_TMEM_PTR + 16)
 static_assert(2 * (R2_SM_TOTAL + 1024) <= 233472, "two CTAs per SM");
 #define R2_WAIT_LIMIT (4000000000LL)
@@ -118,19 +117,97 @@ __device__ __forceinline__ uint32_t r2_desc_lo(uint32_t smem_addr, uint32_t lbo)
     return ((smem_addr >> 4) & 0x3FFFu) | ((lbo >> 4) << 16);
 }
 
-// Per layer L = 0..3 (conv1..conv4): first MMA tile, number of MMA tiles; first / last output tile that is used; per
-// issuing warp h: the output tiles it produces, the input tiles that contribute to them, its first job of the layer.
-__device__ __forceinline__ int r2_mlo(int L) { return L == 3 ? 1 : 0; }
-__device__ __forceinline__ int r2_mcnt(int L) { return L == 3 ? 6 : 8; }
-__device__ __forceinline__ int r2_olo(int L) { return L < 2 ? 0 : L - 1; }          // conv3: 1, conv4: 2
-__device__ __forceinline__ int r2_ohi(int L) { return L < 2 ? 7 : 8 - L; }          // conv3: 6, conv4: 5
-__device__ __forceinline__ int r2_holo(int h, int L) { return max(r2_olo(L), 4 * h); }
-__device__ __forceinline__ int r2_hohi(int h, int L) { return min(r2_ohi(L), 4 * h + 3); }
-__device__ __forceinline__ int r2_tlo(int h, int L) { return L == 0 ? 4 * h : max(r2_mlo(L), r2_holo(h, L) - 1); }
-__device__ __forceinline__ int r2_thi(int h, int L) { return L == 0 ? 4 * h + 3 : min(r2_mlo(L) + r2_mcnt(L) - 1, r2_hohi(h, L) + 1); }
-__device__ __forceinline__ int r2_jloc(int L) { return L == 0 ? 0 : 5 * L - 1; }       // 0, 4, 9, 14
-// layers that write tile r into the buffer per group (conv1, conv2 all of them, conv3 tiles 1..6): its "ready" phases
-__device__ __forceinline__ uint32_t r2_writes(int r) { return (r >= 1 && r <= 6) ? 3u : 2u; }
+// Per layer L = 0..3 (conv1..conv4) of a T-row image: first MMA tile, number of MMA tiles; first / last output tile that
+// is used; per issuing warp h (output tiles 0..3 / 4..T-1): the output tiles it produces, the input tiles that contribute
+// to them = its jobs of the layer, their number, its first job of the layer among its jobs of a group.
+__host__ __device__ constexpr int r2_min(int a, int b) { return a < b ? a : b; }
+__host__ __device__ constexpr int r2_max(int a, int b) { return a > b ? a : b; }
+__host__ __device__ constexpr int r2_mlo(int L) { return L == 3 ? 1 : 0; }
+__host__ __device__ constexpr int r2_mcnt(int L, int T) { return L == 3 ? T - 2 : T; }
+__host__ __device__ constexpr int r2_olo(int L) { return L < 2 ? 0 : L - 1; }                  // conv3: 1, conv4: 2
+__host__ __device__ constexpr int r2_ohi(int L, int T) { return L < 2 ? T - 1 : T - L; }       // conv3: T - 2, conv4: T - 3
+__host__ __device__ constexpr int r2_holo(int h, int L) { return r2_max(r2_olo(L), 4 * h); }
+__host__ __device__ constexpr int r2_hohi(int h, int L, int T) { return r2_min(r2_ohi(L, T), 4 * h + 3); }
+__host__ __device__ constexpr int r2_tlo(int h, int L) { return L == 0 ? 4 * h : r2_max(r2_mlo(L), r2_holo(h, L) - 1); }
+__host__ __device__ constexpr int r2_thi(int h, int L, int T) {
+    return L == 0 ? r2_min(4 * h + 3, T - 1) : r2_min(r2_mlo(L) + r2_mcnt(L, T) - 1, r2_hohi(h, L, T) + 1);
+}
+__host__ __device__ constexpr int r2_cnt(int h, int L, int T) { return r2_thi(h, L, T) - r2_tlo(h, L) + 1; }
+__host__ __device__ constexpr int r2_jloc(int h, int L, int T) {
+    int j = 0;
+    for (int l = 0; l < L; ++l) j += r2_cnt(h, l, T);
+    return j;
+}
+// layers that write tile r into the buffer per group (conv1, conv2 all of them, conv3 tiles 1..T-2): its "ready" phases
+__host__ __device__ constexpr uint32_t r2_writes(int r, int T) { return (r >= 1 && r <= T - 2) ? 3u : 2u; }
+
+// What does not depend on the launch, computed by the compiler and read from constant memory (every access is uniform
+// across its warp): the items of the epilogue teams and the jobs of the issuing warps.
+struct R2Tables {
+    uint32_t items[R2_ITEMS + 2];            // layer | tile << 4 | job barrier << 8 | second job barrier << 14 | TMEM column << 20; 0xFFFFFFFF ends the list
+    uint32_t jobs[2][R2_CJOBS][4];           // per issuing warp and job of conv2..conv4, see r2_make_tables
+    int cnt[2][4];                           // jobs of issuing warp h in layer L
+};
+constexpr R2Tables r2_make_tables(int T) {
+    R2Tables t{};
+    for (int h = 0; h < 2; ++h)
+        for (int L = 0; L < 4; ++L) t.cnt[h][L] = r2_cnt(h, L, T);
+    // Items: layer L, output tile r, the job whose completion completes the tile's accumulator (of the warp that owns it,
+    // its last input tile that contributes), the accumulator's TMEM column.  The item overwrites INPUT tile r in place:
+    // the tiles next to the border (3, 4) are read by the other warp too, whose job on that tile is the item's second
+    // barrier.  Jobs and items go from the border outwards -- tiles 3, 4, 2, 5, 1, 6, 0, 7 as far as the layer produces
+    // them --, so that what the next layer needs first is complete first; tiles 0..3 are team 0's, the others team 1's.
+    int n = 0;
+    for (int L = 0; L < 4; ++L)
+        for (int pos = 0; pos < 8; ++pos) {
+            const int r = (pos & 1) ? 4 + (pos >> 1) : 3 - (pos >> 1);
+            if (r < r2_olo(L) || r > r2_ohi(L, T)) continue;
+            const int h = r >> 2;
+            int j = 0;                                                  // the step of warp h that completes the accumulator
+            if (L == 0) j = h ? r - 4 : 3 - r;
+            else j = h ? r2_min(r + 1, r2_thi(1, L, T)) - r2_tlo(1, L) : r2_thi(0, L, T) - r2_max(r - 1, r2_tlo(0, L));
+            const int job = h * R2_HJOBS + r2_jloc(h, L, T) + j;
+            int job2 = job;
+            if (L > 0 && (r == 3 || r == 4)) job2 = (1 - h) * R2_HJOBS + r2_jloc(1 - h, L, T);    // tile 3 / 4 is the other warp's first job
+            t.items[n++] = (uint32_t)L | ((uint32_t)r << 4) | ((uint32_t)job << 8) | ((uint32_t)job2 << 14) | ((uint32_t)(32 * (7 - r)) << 20);
+        }
+    for (; n < R2_ITEMS + 2; ++n) t.items[n] = 0xFFFFFFFFu;
+    // Jobs: job jj of issuing warp h in conv2..conv4 (its step j of layer L).  Warp 0 goes down from the border (tiles 4, 3,
+    // ..), warp 1 up (3, 4, ..).
+    for (int h = 0; h < 2; ++h) {
+        const int c1 = t.cnt[h][1], c2 = t.cnt[h][2], c3 = t.cnt[h][3];
+        for (int jj = 0; jj < c1 + c2 + c3; ++jj) {
+            const int L = jj < c1 ? 1 : (jj < c1 + c2 ? 2 : 3), j = jj - (L == 1 ? 0 : (L == 2 ? c1 : c1 + c2));
+            const int tlo = r2_tlo(h, L), thi = r2_thi(h, L, T), olo = r2_holo(h, L), ohi = r2_hohi(h, L, T);
+            const int r = h ? tlo + j : thi - j;
+            // kernel rows whose output tile r - kh + 1 this warp produces: kh = klo .. khi, 32 accumulator columns each,
+            // output tiles descending = columns ascending from that of tile r - klo + 1
+            const int klo = r2_max(0, r + 1 - ohi), khi = r2_min(2, r + 1 - olo), nblk = khi - klo + 1;
+            const uint32_t d_col = (uint32_t)(32 * (6 - r + klo));
+            // the first contribution to an output tile must not accumulate: all of the warp's first job of the layer; of
+            // every other, the block of the output tile it reaches first -- tile r - 1 (kh = 2, the last block) going
+            // down, tile r + 1 (kh = 0, the first block) going up -- by an N = 32 MMA of its own before the rest.  That
+            // tile's accumulator is the previous layer's until its item has read it: the job waits for tile x to be
+            // "ready" too.
+            const bool first = j == 0, fresh = h ? klo == 0 : khi == 2, init = !first && fresh;
+            uint32_t z = d_col | ((uint32_t)nblk << 9);
+            if (!init) z |= (0u << 11) | ((uint32_t)nblk << 13) | ((first ? 0u : 1u) << 15);
+            else {
+                const uint32_t ipos = h ? 0u : (uint32_t)(nblk - 1), rpos = h ? 1u : 0u;
+                z |= (ipos << 11) | (1u << 13) | (0u << 15);
+                if (nblk > 1) z |= (1u << 16) | (rpos << 17) | ((uint32_t)(nblk - 1) << 19);
+            }
+            const int x = fresh ? (h ? r + 1 : r - 1) : 15;
+            t.jobs[h][jj][0] = (uint32_t)(R2_MARGIN + r * 128 - 1);    // A: the tile's rows shifted by -1 column, in 16-byte rows
+            t.jobs[h][jj][1] = (uint32_t)((R2_SM_WB(L == 2 ? 1 : 0) + klo * 32 * 16) >> 4);      // B: the layer's buffer, kernel rows from klo
+            t.jobs[h][jj][2] = z;
+            t.jobs[h][jj][3] = (uint32_t)r | ((uint32_t)(L - 1) << 5) | ((uint32_t)x << 7);
+        }
+    }
+    return t;
+}
+__constant__ R2Tables c_r2_tables_8 = r2_make_tables(8);
+__constant__ R2Tables c_r2_tables_7 = r2_make_tables(7);
 
 // conv1's A operand for one row (tile r, lane): the 9 taps of player * grid around cell (r, c) as bf16 (+1 own, -1 opp,
 // 0 empty / off-board), then zeros up to K = 16; c < 0 (pad column, unused lane, missing board) = a zero row.
@@ -159,10 +236,14 @@ __device__ __forceinline__ void r2_im2col_row(uint8_t* im2col, int row, int r, i
     *reinterpret_cast<uint4*>(dst + R2_PLANE) = make_uint4(w[4], 0u, 0u, 0u);
 }
 
+template <int T, int C>
 __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Params p) {
+    constexpr int PITCH = C + 1, NB = 128 / PITCH, NPOS = (T - 4) * (C - 4);     // lanes per board, boards per group, outputs per board
+    static_assert(T >= 7 && T <= R2_TILES && C <= 8 && NPOS % 2 == 0, "image shapes this kernel is laid out for");
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int n_groups = (p.G + R2_NB - 1) / R2_NB;
+    const R2Tables& tb = T == 8 ? c_r2_tables_8 : c_r2_tables_7;
+    const int n_groups = (p.G + NB - 1) / NB;
     const uint32_t sbase = smem_u32(smem);
     const uint32_t bars = smem_u32(smem + R2_SM_BARS);
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + R2_SM_TMEM_PTR);
@@ -178,62 +259,14 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
         if (tid == R2B_WB) r2_bulk_load(sbase + R2_SM_WB(0), w_rows, R2_LAYER_BYTES, bars + 8 * tid);
         if (tid == R2B_WB + 1) r2_bulk_load(sbase + R2_SM_WB(1), w_rows + R2_LAYER_BYTES, R2_LAYER_BYTES, bars + 8 * tid);
     }
-    if (tid >= 64 && tid < 64 + R2_ITEMS) {
-        // item idx of a group: layer L, output tile r, the job whose completion completes the tile's accumulator (of the
-        // warp that owns it, its last input tile that contributes), the accumulator's TMEM column.  The item overwrites
-        // INPUT tile r in place: the tiles next to the border (3, 4) are read by the other warp too, whose job on that
-        // tile is the item's second barrier.  Jobs and items go from the border outwards: tiles 3, 4, 2, 5, 1, 6, 0, 7;
-        // even positions (tiles 3..0) are team 0's, odd ones (tiles 4..7) team 1's.
-        const int idx = tid - 64;
-        const int L = idx < 8 ? 0 : (idx < 16 ? 1 : (idx < 22 ? 2 : 3));
-        const int pos = idx - (L == 0 ? 0 : (L == 1 ? 8 : (L == 2 ? 16 : 22)));
-        const int r = (pos & 1) ? 4 + (pos >> 1) : 3 - (pos >> 1);
-        const int h = r >> 2;
-        int j;                                                     // the step of warp h that completes the accumulator
-        if (L == 0) j = h ? r - 4 : 3 - r;
-        else j = h ? min(r + 1, r2_thi(1, L)) - r2_tlo(1, L) : r2_thi(0, L) - max(r - 1, r2_tlo(0, L));
-        const int job = h * R2_HJOBS + r2_jloc(L) + j;
-        int job2 = job;
-        if (L > 0 && (r == 3 || r == 4)) job2 = (1 - h) * R2_HJOBS + r2_jloc(L);      // tile 3 / 4 is the other warp's first job
-        reinterpret_cast<uint32_t*>(smem + R2_SM_ITEMS)[idx] =
-            (uint32_t)L | ((uint32_t)r << 4) | ((uint32_t)job << 8) | ((uint32_t)job2 << 14) | ((uint32_t)(32 * (7 - r)) << 20);
-    }
-    if (tid >= 96 && tid < 96 + 2 * R2_CJOBS) {
-        // job jj of issuing warp h in conv2..conv4 (its step j of layer L): everything about it that does not depend on the
-        // group.  Warp 0 goes down from the border (tiles 4, 3, ..), warp 1 up (3, 4, ..).
-        const int h = (tid - 96) / R2_CJOBS, jj = (tid - 96) % R2_CJOBS;
-        const int L = jj < 5 ? 1 : (jj < 10 ? 2 : 3), j = jj - (5 * L - 5);
-        const int tlo = r2_tlo(h, L), thi = r2_thi(h, L), olo = r2_holo(h, L), ohi = r2_hohi(h, L);
-        const int r = h ? tlo + j : thi - j;
-        // kernel rows whose output tile r - kh + 1 this warp produces: kh = klo .. khi, 32 accumulator columns each, output
-        // tiles descending = columns ascending from that of tile r - klo + 1
-        const int klo = max(0, r + 1 - ohi), khi = min(2, r + 1 - olo), nblk = khi - klo + 1;
-        const uint32_t d_col = (uint32_t)(32 * (6 - r + klo));
-        // the first contribution to an output tile must not accumulate: all of the warp's first job of the layer; of every
-        // other, the block of the output tile it reaches first -- tile r - 1 (kh = 2, the last block) going down, tile
-        // r + 1 (kh = 0, the first block) going up -- by an N = 32 MMA of its own before the rest.  That tile's
-        // accumulator is the previous layer's until its item has read it: the job waits for tile x to be "ready" too.
-        const bool first = j == 0, fresh = h ? klo == 0 : khi == 2, init = !first && fresh;
-        uint32_t z = d_col | ((uint32_t)nblk << 9);
-        if (!init) z |= (0u << 11) | ((uint32_t)nblk << 13) | ((first ? 0u : 1u) << 15);
-        else {
-            const uint32_t ipos = h ? 0u : (uint32_t)(nblk - 1), rpos = h ? 1u : 0u;
-            z |= (ipos << 11) | (1u << 13) | (0u << 15);
-            if (nblk > 1) z |= (1u << 16) | (rpos << 17) | ((uint32_t)(nblk - 1) << 19);
-        }
-        const int x = fresh ? (h ? r + 1 : r - 1) : 15;
-        const uint32_t wl = sbase + R2_SM_WB(L == 2 ? 1 : 0) + (uint32_t)(klo * 32 * 16);
-        reinterpret_cast<uint4*>(smem + R2_SM_JOBS)[tid - 96] =
-            make_uint4((uint32_t)(R2_MARGIN + r * 128 - 1),            // A: the tile's rows shifted by -1 column, in 16-byte rows
-                       r2_desc_lo(wl, 96u * 16u), z, (uint32_t)r | ((uint32_t)(L - 1) << 5) | ((uint32_t)x << 7));
-    }
     // the rows nothing ever writes: the margins of the buffer (the row before tile 0 is lane 0's left neighbour = zero
     // padding) and the two unused lanes of every tile (lane 127 is the left neighbour of the next tile's lane 0)
     if (tid >= 128 && tid < 192) {
         const int u = tid - 128, pl = (u >> 4) & 3, side = (u >> 3) & 1, row = u & 7;
         *reinterpret_cast<uint4*>(smem + R2_SM_BUF + pl * R2_PLANE + (side ? R2_MARGIN + R2_ROWS + row : row) * 16) = make_uint4(0u, 0u, 0u, 0u);
     } else if (tid >= 192 && tid < 256) {
-        const int u = tid - 192, pl = (u >> 4) & 3, tile = (u >> 1) & 7, ln = R2_NB * R2_PITCH + (u & 1);
+        const int u = tid - 192, pl = (u >> 4) & 3, tile = (u >> 1) & 7, ln = NB * PITCH + (u & 1);
+        static_assert(NB * PITCH == 126, "two spare lanes per tile");
         *reinterpret_cast<uint4*>(smem + R2_SM_BUF + pl * R2_PLANE + (R2_MARGIN + tile * 128 + ln) * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
     if (warp == R2_MMA_WARP) {
@@ -254,7 +287,7 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
     constexpr uint32_t IDESC_BLK = (32u >> 3) << 17;              // one more kernel row = 32 more columns
     uint32_t k = 0;                                               // group counter of this CTA
     for (int grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++k) {
-        const int board0 = grp * R2_NB, n_boards = min(R2_NB, p.G - board0);
+        const int board0 = grp * NB, n_boards = min(NB, p.G - board0);
         // (conv4 of the previous group has completed -- block barrier at the end of the loop: its weights make room for conv2's)
         if (k > 0 && tid == 0) r2_bulk_load(sbase + R2_SM_WB(0), w_rows, R2_LAYER_BYTES, bars + 8 * R2B_WB);
         {   // conv1's A operand (9-tap im2col of player * grid, K = 16) in planes 2 - 3 of the buffer, by all threads: up to
@@ -264,9 +297,9 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
             int cc[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const int row = tid + j * R2_THREADS, l = row & 127, bb = l / R2_PITCH;
-                cc[j] = l - bb * R2_PITCH;
-                const bool ok = row < R2_ROWS && bb < n_boards && l < R2_NB * R2_PITCH && cc[j] < 8;
+                const int row = tid + j * R2_THREADS, l = row & 127, bb = l / PITCH;
+                cc[j] = l - bb * PITCH;
+                const bool ok = row < T * 128 && bb < n_boards && l < NB * PITCH && cc[j] < C;
                 o[j] = ok ? p.own[board0 + bb] : 0ULL;
                 q[j] = ok ? p.opp[board0 + bb] : 0ULL;
                 if (!ok) cc[j] = -1;
@@ -274,7 +307,7 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int row = tid + j * R2_THREADS;
-                if (row < R2_ROWS) r2_im2col_row(im2col, row, row >> 7, cc[j], o[j], q[j]);
+                if (row < T * 128) r2_im2col_row(im2col, row, row >> 7, cc[j], o[j], q[j]);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
@@ -285,7 +318,8 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
             // accumulate into the output tiles 4 h .. 4 h + 3, in program order, by one elected thread of a converged warp
             const int h = warp - R2_MMA_WARP;
             const uint32_t jobs = bars + 8 * (R2B_JOB + h * R2_HJOBS);
-            const uint4* table = reinterpret_cast<const uint4*>(smem + R2_SM_JOBS) + h * R2_CJOBS;
+            const int c0 = tb.cnt[h][0], c1 = tb.cnt[h][1], c2 = tb.cnt[h][2], n_jobs = c1 + c2 + tb.cnt[h][3];
+            const uint32_t wbase_lo = r2_desc_lo(sbase, 96u * 16u);
             if (k == 0) r2_wait(bars + 8 * R2B_W1, 0u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // conv1: one K = 16 MMA per tile into the tile's accumulator
@@ -294,6 +328,7 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const int r = h ? 4 + i : 3 - i;
+                    if (r >= T) break;
                     r2_mma(tmem_base + (uint32_t)(32 * (7 - r)),
                            r2_desc_lo(sbase + R2_SM_BUF + 2 * R2_PLANE + (uint32_t)(R2_MARGIN + r * 128) * 16u, R2_PLANE), w1_lo, idesc32, 0u);
                     umma_commit(jobs + 8 * i);
@@ -303,29 +338,31 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
             const uint32_t abuf_lo = r2_desc_lo(sbase + R2_SM_BUF, R2_PLANE);
             const uint32_t ready = bars + 8 * R2B_READY;
 #pragma unroll 1
-            for (int jj = 0; jj < R2_CJOBS; ++jj) {
-                const uint4 e = table[jj];
+            for (int jj = 0; jj < n_jobs; ++jj) {
+                const uint4 e = make_uint4(tb.jobs[h][jj][0], wbase_lo + tb.jobs[h][jj][1], tb.jobs[h][jj][2], tb.jobs[h][jj][3]);
                 // the layer's weights: conv2 = load 2 k of buffer 0, conv4 = load 2 k + 1 of it; conv3 stays in buffer 1
                 if (jj == 0) r2_wait(bars + 8 * R2B_WB, 0u);
-                else if (jj == 5) r2_wait(bars + 8 * (R2B_WB + 1), 0u);
-                else if (jj == 10) r2_wait(bars + 8 * R2B_WB, 1u);
+                else if (jj == c1) r2_wait(bars + 8 * (R2B_WB + 1), 0u);
+                else if (jj == c1 + c2) r2_wait(bars + 8 * R2B_WB, 1u);
                 {   // the input: layer L - 1's output tile r = write (k * P + L - 1) of tile r into the buffer (P = layers that
                     // write tile r); and tile x, whose accumulator this job initialises for layer L
                     const uint32_t r = e.w & 7u, Lm1 = (e.w >> 5) & 3u, x = (e.w >> 7) & 15u;
-                    r2_wait(ready + 8 * r, (k * r2_writes((int)r) + Lm1) & 1u);
-                    if (x != 15u) r2_wait(ready + 8 * x, (k * r2_writes((int)x) + Lm1) & 1u);
+                    r2_wait(ready + 8 * r, (k * r2_writes((int)r, T) + Lm1) & 1u);
+                    if (x != 15u) r2_wait(ready + 8 * x, (k * r2_writes((int)x, T) + Lm1) & 1u);
                 }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d_tmem = tmem_base + (e.z & 511u);
                 const uint32_t idesc = idesc32 + (((e.z >> 9) & 3u) - 1u) * IDESC_BLK;
                 const uint32_t a_lo = abuf_lo + e.x, b_lo = e.y;
-                if (h == 0 && jj == 7) {
+                const bool reload = h == 0 && jj == c1 + 2;       // warp 0's third job of conv3
+                if (reload) {
                     // conv2's MMAs of both warps have long completed: conv4's weights may replace conv2's
-                    r2_wait(bars + 8 * (R2B_JOB + 8), k & 1u);
-                    r2_wait(bars + 8 * (R2B_JOB + R2_HJOBS + 8), k & 1u);
+                    constexpr int last_a = r2_jloc(0, 2, T) - 1, last_b = r2_jloc(1, 2, T) - 1;      // the warps' last jobs of conv2
+                    r2_wait(bars + 8 * (R2B_JOB + last_a), k & 1u);
+                    r2_wait(bars + 8 * (R2B_JOB + R2_HJOBS + last_b), k & 1u);
                 }
                 if (elect_one()) {
-                    if (h == 0 && jj == 7) r2_bulk_load(sbase + R2_SM_WB(0), w_rows + 2 * R2_LAYER_BYTES, R2_LAYER_BYTES, bars + 8 * R2B_WB);
+                    if (reload) r2_bulk_load(sbase + R2_SM_WB(0), w_rows + 2 * R2_LAYER_BYTES, R2_LAYER_BYTES, bars + 8 * R2B_WB);
                     {   // kernel column 0, channels 0..15: whole, or the block that must not accumulate and then the rest
                         const uint32_t pos = (e.z >> 11) & 3u;
                         r2_mma(d_tmem + 32u * pos, a_lo, b_lo + 32u * pos, idesc32 + (((e.z >> 13) & 3u) - 1u) * IDESC_BLK, (e.z >> 15) & 1u);
@@ -340,7 +377,7 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
                         r2_mma(d_tmem, a_lo + (uint32_t)(kw + kk * (2 * R2_PLANE >> 4)),
                                b_lo + (uint32_t)(kw * (R2_W_DC_BYTES >> 4) + kk * (2 * 96 * 16 >> 4)), idesc, 1u);
                     }
-                    umma_commit(jobs + 8 * (4 + jj));
+                    umma_commit(jobs + 8 * (c0 + jj));
                 }
                 __syncwarp();
             }
@@ -349,16 +386,18 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
             // warp's half of the tiles
             const int team = warp >> 2, quarter = warp & 3;
             const int tl = quarter * 32 + lane;                     // TMEM lane = lane of the tile
-            const int b = tl / R2_PITCH, c = tl - b * R2_PITCH;     // board of the group, column (8 = pad)
+            const int b = tl / PITCH, c = tl - b * PITCH;           // board of the group, column (C = pad)
             const float* bias_all = reinterpret_cast<const float*>(smem + R2_SM_BIAS);
             const uint32_t t_quarter = tmem_base + ((uint32_t)(quarter * 32) << 16);
-            const bool used = tl < R2_NB * R2_PITCH;                // not one of the tile's two spare lanes
-            const bool cell = b < n_boards && used && c < 8;        // a real cell of a real board
+            const bool used = tl < NB * PITCH;                      // not one of the tile's two spare lanes
+            const bool cell = b < n_boards && used && c < C;        // a real cell of a real board
             if (k == 0) r2_wait(bars + 8 * R2B_W1, 0u);             // the biases
 #pragma unroll 1
-            for (int idx = team; idx < R2_ITEMS; idx += R2_TEAMS) {
-                const uint32_t it = reinterpret_cast<const uint32_t*>(smem + R2_SM_ITEMS)[idx];
+            for (int idx = 0; idx < R2_ITEMS; ++idx) {
+                const uint32_t it = tb.items[idx];
+                if (it == 0xFFFFFFFFu) break;
                 const int L = (int)(it & 3u), r = (int)((it >> 4) & 15u);
+                if ((r >> 2) != team) continue;                     // the other team's half of the tiles
                 // (one polling warp per team, the other three behind a named barrier: measured, no difference)
                 r2_wait(bars + 8 * (R2B_JOB + ((it >> 8) & 63u)), k & 1u);
                 if (((it >> 14) & 63u) != ((it >> 8) & 63u)) r2_wait(bars + 8 * (R2B_JOB + ((it >> 14) & 63u)), k & 1u);
@@ -398,18 +437,18 @@ __global__ void __launch_bounds__(R2_THREADS, 2) k_net_trunk_rows2(TrunkRows2Par
                             *reinterpret_cast<uint4*>(p.debug + ((size_t)grp * R2_ROWS + r * 128 + tl) * 32 + ch * 8) =
                                 used ? make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]) : make_uint4(0u, 0u, 0u, 0u);
                     }
-                } else if (cell && c >= 2 && c < 6) {
-                    // conv4: the outputs are the cells at an inset of 2; features[board][pos * 32 + co], pos = (r-2)*4 + (c-2)
-                    const int pos = (r - 2) * 4 + (c - 2), g = board0 + b;
+                } else if (cell && c >= 2 && c < C - 2) {
+                    // conv4: the outputs are the cells at an inset of 2; features[board][pos * 32 + co], pos = (r-2)*(C-4) + (c-2)
+                    const int pos = (r - 2) * (C - 4) + (c - 2), g = board0 + b;
                     if (p.features_packed) {
                         // K = pos*32 + 8*ch: chunk pos / 2 (64 wide, 16 KB per row tile of 128 positions), plane (pos % 2)*4 + ch
-                        uint8_t* f = reinterpret_cast<uint8_t*>(p.features) + ((size_t)(g >> 7) * 8 + (size_t)(pos >> 1)) * 16384 +
+                        uint8_t* f = reinterpret_cast<uint8_t*>(p.features) + ((size_t)(g >> 7) * (NPOS / 2) + (size_t)(pos >> 1)) * 16384 +
                                      (size_t)((pos & 1) * 4) * 2048 + (size_t)(g & 127) * 16;
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
                             *reinterpret_cast<uint4*>(f + ch * 2048) = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
                     } else {
-                        uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)g * 16 + pos) * 32);
+                        uint4* f = reinterpret_cast<uint4*>(p.features + ((size_t)g * NPOS + pos) * 32);
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch)
                             f[ch] = make_uint4(out[ch * 4], out[ch * 4 + 1], out[ch * 4 + 2], out[ch * 4 + 3]);
@@ -437,21 +476,28 @@ bool az_trunk_rows2_enabled() {
     return on;
 }
 
-int az_trunk_rows2_launch(const uint64_t* own, const uint64_t* opp, int64_t G, const void* wblob, void* features,
+int az_trunk_rows2_boards_per_group(int rows) { return rows == 8 ? 14 : 18; }
+
+int az_trunk_rows2_launch(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob, void* features,
                           int features_packed, void* debug, int debug_layer, int n_sms, int late_trigger, void* stream) {
+    if (!((rows == 8 && cols == 8) || (rows == 7 && cols == 6))) return AZ_ERR_ARG;
     static bool attr_set = false;
     if (!attr_set) {
-        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2, cudaFuncAttributeMaxDynamicSharedMemorySize, R2_SM_TOTAL));
-        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, R2_SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2<8, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2<7, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, R2_SM_TOTAL));
+        AZ_CUDA_TRY(cudaFuncSetAttribute(k_net_trunk_rows2<7, 6>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         attr_set = true;
     }
     TrunkRows2Params p;
     p.own = own; p.opp = opp; p.wblob = (const uint8_t*)wblob; p.features = (__nv_bfloat16*)features;
     p.debug = (__nv_bfloat16*)debug; p.G = (int)G; p.debug_layer = debug ? debug_layer : 0;
     p.features_packed = features_packed ? 1 : 0; p.late_trigger = late_trigger;
-    const int n_groups = (int)((G + R2_NB - 1) / R2_NB);
+    const int nb = az_trunk_rows2_boards_per_group(rows);
+    const int n_groups = (int)((G + nb - 1) / nb);
     const int grid = n_groups < 2 * n_sms ? n_groups : 2 * n_sms;      // persistent: two CTAs per SM
-    cudaError_t e = az_launch_pdl(k_net_trunk_rows2, dim3(grid), dim3(R2_THREADS), R2_SM_TOTAL, (cudaStream_t)stream, p);
+    cudaError_t e = rows == 8 ? az_launch_pdl(k_net_trunk_rows2<8, 8>, dim3(grid), dim3(R2_THREADS), R2_SM_TOTAL, (cudaStream_t)stream, p)
+                              : az_launch_pdl(k_net_trunk_rows2<7, 6>, dim3(grid), dim3(R2_THREADS), R2_SM_TOTAL, (cudaStream_t)stream, p);
     if (e != cudaSuccess) return az_set_cuda_error(e, "k_net_trunk_rows2");
     AZ_CHECK_LAUNCH("k_net_trunk_rows2");
     return AZ_OK;

@@ -546,6 +546,17 @@ def test_fused_connect4_net_matches_reference_outputs(golden_dir):
     torch.cuda.synchronize()
     p = big.probs.cpu().numpy()
     assert np.abs(p[:G] - d["probs"]).max() < 1e-2 and (p[G:2 * G] == p[:G]).all()
+    # that batch has more groups of 18 boards than the GPU has SMs: its trunk is k_net_trunk_rows2<7, 6> (two CTAs per SM);
+    # its features against the fp32 module and against the first kernel (trunk_variant = 1) on the same batch
+    from alphazero_b200 import _lib
+    assert _lib.lib().az_net_trunk_boards_per_group(7, G2) == 18
+    f2 = ev2.features_rowmajor().float().cpu().reshape(G2, 6, 32).permute(0, 2, 1).reshape(G2, 32, 3, 2)
+    assert (f2 - a4[idx]).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
+    ev1 = FusedNetEvaluator(net, big, use_cuda_graph=False, trunk_variant=1)
+    ev1.trunk()
+    torch.cuda.synchronize()
+    f1 = ev1.features_rowmajor().float().cpu().reshape(G2, 6, 32).permute(0, 2, 1).reshape(G2, 32, 3, 2)
+    assert (f2 - f1).abs().max().item() < 0.02 * a4.abs().max().item() + 0.02
 
 
 def test_self_play_connect4_fused_path_is_used():
