@@ -302,9 +302,10 @@ int az_net_wblob_bytes(void);
  * 8 x 8 images in batches of 1024 positions and more are computed by k_net_trunk_rows (csrc/trunk_rows_kernels.cu: tile =
  * one board row of 14 boards, kernel column = a 16-byte shift of the A operand, kernel row = the N dimension, one TMEM
  * accumulator per output tile; the same results within bf16 rounding, 18.5 against 22.6 us per 4096 positions) or, when
- * there are more groups of 14 boards than SMs, by k_net_trunk_rows2 (csrc/trunk_rows2_kernels.cu: the same formulation
- * with two CTAs per SM, bit-identical to k_net_trunk_rows, 16.7 us; bit 2 of features_packed or AZ_B200_TRUNK_ROWS1=1
- * keeps k_net_trunk_rows).  Its
+ * there are more groups of 14 boards than SMs, by k_net_trunk_rows2<8, 8> (csrc/trunk_rows2_kernels.cu: the same formulation
+ * with two CTAs per SM, bit-identical to k_net_trunk_rows, 16.5 us; bit 2 of features_packed or AZ_B200_TRUNK_ROWS1=1
+ * keeps k_net_trunk_rows).  k_net_trunk_rows2<7, 6> (groups of 18 boards) takes Connect4's 7 x 6 image above 2664
+ * positions (debug dump as for 8 x 8 with 7 lanes per board; bit 1 or 2 keeps the first kernel).  Its
  * debug dump is bf16 [ceil(G/14)][1024][32], row = board_row * 128 + (g % 14) * 9 + column.  Bit 1 of features_packed
  * (or AZ_B200_TRUNK_V1=1 in the environment) keeps the first kernel for such a batch too. */
 int az_net_trunk(const uint64_t* own, const uint64_t* opp, int rows, int cols, int64_t G, const void* wblob,
