@@ -206,6 +206,76 @@ constexpr R2Tables r2_make_tables(int T) {
     }
     return t;
 }
+// The schedule the tables encode, checked by the compiler: per layer and output tile, the owning warp's jobs in order --
+// (1) every (input tile, kernel row) that contributes appears exactly once, on the right accumulator columns, (2) the
+// first MMA that touches the accumulator does not accumulate and every later one does, (3) a job that initialises an
+// accumulator waits for the tile whose previous-layer accumulator it replaces (its own input tile or tile x), (4) the
+// tile's item waits for the last of those jobs, and -- tiles 3 / 4 -- for the other warp's job that reads the tile.
+constexpr bool r2_check_tables(int T) {
+    const R2Tables t = r2_make_tables(T);
+    int n_items = 0;
+    for (int L = 1; L < 4; ++L) {
+        const int mlo = r2_mlo(L), mhi = mlo + r2_mcnt(L, T) - 1;
+        for (int o = r2_olo(L); o <= r2_ohi(L, T); ++o) {
+            const int h = o >> 2, off = (L > 1 ? t.cnt[h][1] : 0) + (L > 2 ? t.cnt[h][2] : 0);
+            int seen = 0, last = -1;
+            bool inited = false;
+            for (int j = 0; j < t.cnt[h][L]; ++j) {
+                const uint32_t* e = t.jobs[h][off + j];
+                const int r = (int)(e[3] & 7u), x = (int)((e[3] >> 7) & 15u);
+                if ((int)((e[3] >> 5) & 3u) != L - 1 || r < mlo || r > mhi) return false;
+                const int klo = ((int)(e[1] << 4) - R2_SM_WB(L == 2 ? 1 : 0)) / 512, nblk = (int)((e[2] >> 9) & 3u);
+                const int p1 = (int)((e[2] >> 11) & 3u), n1 = (int)((e[2] >> 13) & 3u), acc1 = (int)((e[2] >> 15) & 1u);
+                const bool has2 = (e[2] >> 16) & 1u;
+                const int p2 = (int)((e[2] >> 17) & 3u), n2 = (int)((e[2] >> 19) & 3u);
+                if (has2 ? !((p1 == 0 && p2 == n1 && n1 + n2 == nblk) || (p2 == 0 && p1 == n2 && n1 + n2 == nblk)) : !(p1 == 0 && n1 == nblk))
+                    return false;                                       // the first MMA (or its two parts) covers the job's blocks once
+                for (int blk = 0; blk < nblk; ++blk) {
+                    const int kh = klo + blk, tile = 7 - ((int)(e[2] & 511u) + 32 * blk) / 32;
+                    if (kh > 2 || tile != r - kh + 1 || (tile >> 2) != h) return false;     // right columns, the warp's own half
+                    if (tile != o) continue;
+                    const bool in1 = blk >= p1 && blk < p1 + n1;
+                    const int acc = in1 ? acc1 : 1;
+                    if (inited ? acc != 1 : acc != 0) return false;
+                    if (!inited && tile != r && tile != x) return false;                   // waits for what it replaces
+                    inited = true;
+                    if (seen & (1 << kh)) return false;
+                    seen |= 1 << kh;
+                    last = j;
+                }
+            }
+            int want = 0;
+            for (int kh = 0; kh < 3; ++kh)
+                if (o + kh - 1 >= mlo && o + kh - 1 <= mhi) want |= 1 << kh;
+            if (seen != want) return false;
+            // the tile's item
+            bool found = false;
+            for (int i = 0; i < R2_ITEMS; ++i) {
+                const uint32_t it = t.items[i];
+                if (it == 0xFFFFFFFFu || (int)(it & 3u) != L || (int)((it >> 4) & 15u) != o) continue;
+                if (found) return false;
+                found = true;
+                if ((int)((it >> 8) & 63u) != h * R2_HJOBS + r2_jloc(h, L, T) + last) return false;
+                if ((int)(it >> 20) != 32 * (7 - o)) return false;
+                const int job2 = (int)((it >> 14) & 63u);
+                if (o == 3 || o == 4) {
+                    const int g = 1 - h, off2 = (L > 1 ? t.cnt[g][1] : 0) + (L > 2 ? t.cnt[g][2] : 0);
+                    if (job2 != g * R2_HJOBS + r2_jloc(g, L, T) || (int)(t.jobs[g][off2][3] & 7u) != o) return false;
+                } else if (job2 != (int)((it >> 8) & 63u)) return false;
+            }
+            if (!found) return false;
+            ++n_items;
+        }
+    }
+    for (int i = 0; i < R2_ITEMS + 2; ++i)
+        if (t.items[i] != 0xFFFFFFFFu && (t.items[i] & 3u) == 0u) ++n_items;    // conv1: one item per tile
+    int listed = 0;
+    for (int i = 0; i < R2_ITEMS + 2; ++i) listed += t.items[i] != 0xFFFFFFFFu;
+    return n_items == listed && listed == T + T + (T - 2) + (T - 4) && t.cnt[0][0] + t.cnt[1][0] == T &&
+           t.cnt[0][0] + t.cnt[0][1] + t.cnt[0][2] + t.cnt[0][3] <= R2_HJOBS && t.cnt[1][0] + t.cnt[1][1] + t.cnt[1][2] + t.cnt[1][3] <= R2_HJOBS;
+}
+static_assert(r2_check_tables(8), "schedule of the 8 x 8 image");
+static_assert(r2_check_tables(7), "schedule of the 7 x 6 image");
 __constant__ R2Tables c_r2_tables_8 = r2_make_tables(8);
 __constant__ R2Tables c_r2_tables_7 = r2_make_tables(7);
 
